@@ -1,0 +1,131 @@
+"""fc_caption forward + greedy decode, restated on torch CPU float32.
+
+TEST INFRASTRUCTURE (see oracle/__init__.py).  PINNED: bit-identical to the
+imported reference on seeded inputs (oracle/refcheck.py, tests/golden/).
+
+Follows, without copying, the reference's
+  * LSTMCore.forward            src/captioning/nets.py:98-134  (5-chunk maxout LSTM)
+  * FCModel._sample(greedy)     src/captioning/nets.py:183-245 (18-iteration loop)
+  * PolicyNet.set_from_vector   src/algorithm/nets.py:163-165  (flat theta -> tensors)
+torch's CPU kernels are used for the float32 linear algebra precisely because
+they are what the reference itself calls, so results agree to the bit.
+"""
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from .noise import flat_layout
+
+
+class Dims:
+    def __init__(self, vocab_size, input_encoding_size, rnn_size, fc_feat_size,
+                 seq_length=16, layer_n=False, layer_n_affine=False):
+        self.vocab_size = vocab_size
+        self.input_encoding_size = input_encoding_size
+        self.rnn_size = rnn_size
+        self.fc_feat_size = fc_feat_size
+        self.seq_length = seq_length
+        self.layer_n = bool(layer_n)
+        self.layer_n_affine = bool(layer_n_affine)
+
+    def layout(self):
+        return flat_layout(self.vocab_size, self.input_encoding_size, self.rnn_size,
+                           self.fc_feat_size, self.layer_n, self.layer_n_affine)
+
+    def num_params(self):
+        lay = self.layout()
+        return lay[-1][2] + lay[-1][3]
+
+
+def unflatten(dims, theta):
+    """flat float32 theta -> {name: tensor view}; asserts the length like
+    src/algorithm/nets.py:164."""
+    theta = torch.as_tensor(np.asarray(theta))
+    assert theta.numel() == dims.num_params()
+    return {name: theta[start:start + cnt].view(*shape) for name, shape, start, cnt in dims.layout()}
+
+
+def xavier_theta(dims, seed):
+    """Reference-style init (src/algorithm/nets.py:62-69): Xavier-normal weights,
+    zero biases, LayerNorm left at 1/0.  The normals come from this build's own
+    Philox table generator (oracle/noise.py) so that fixtures can rebuild theta
+    from a seed on any box without storing D floats."""
+    from .noise import table_slice
+    theta = np.zeros(dims.num_params(), dtype=np.float32)
+    for name, shape, start, cnt in dims.layout():
+        if 'ln' in name:
+            if name.endswith('weight'):
+                theta[start:start + cnt] = 1.0
+        elif name.endswith('weight'):
+            fan_out, fan_in = shape
+            std = np.float32((2.0 / (fan_in + fan_out)) ** 0.5)
+            theta[start:start + cnt] = table_slice(seed, start, cnt).astype(np.float32) * std
+    return theta
+
+
+def _ln(x, n, w, b):
+    return F.layer_norm(x, (n,), w, b, 1e-5)
+
+
+def lstm_core(dims, p, xt, h, c):
+    """src/captioning/nets.py:98-134."""
+    R = dims.rnn_size
+    a_i = F.linear(xt, p['core.i2h.weight'], p['core.i2h.bias'])
+    a_h = F.linear(h, p['core.h2h.weight'], p['core.h2h.bias'])
+    if dims.layer_n:
+        a_i = _ln(a_i, 5 * R, p.get('core.i2h_ln.weight'), p.get('core.i2h_ln.bias'))
+        a_h = _ln(a_h, 5 * R, p.get('core.h2h_ln.weight'), p.get('core.h2h_ln.bias'))
+    sums = a_i + a_h
+    sig = torch.sigmoid(sums[:, :3 * R])
+    in_gate, forget_gate, out_gate = sig[:, :R], sig[:, R:2 * R], sig[:, 2 * R:3 * R]
+    in_transform = torch.max(sums[:, 3 * R:4 * R], sums[:, 4 * R:5 * R])
+    next_c = forget_gate * c + in_gate * in_transform
+    act_c = _ln(next_c, R, p.get('core.c_ln.weight'), p.get('core.c_ln.bias')) if dims.layer_n else next_c
+    next_h = out_gate * torch.tanh(act_c)
+    return next_h, next_c
+
+
+def decode_greedy(dims, theta, fc_feats, trace=False):
+    """FCModel._sample(fc, greedy=True) -- src/captioning/nets.py:183-245.
+
+    Returns seq int64 [B, T], seq_logprobs float32 [B, T] (and, with trace, the
+    per-step hidden states / logits the necessary schedule produces: 1 image
+    step, T+1 core steps, T vocabulary projections).
+    """
+    with torch.no_grad():
+        p = unflatten(dims, theta)
+        fc = torch.as_tensor(np.asarray(fc_feats, dtype=np.float32))
+        B, T, R = fc.shape[0], dims.seq_length, dims.rnn_size
+        h = torch.zeros(B, R)
+        c = torch.zeros(B, R)
+        seq = torch.zeros(B, T, dtype=torch.long)
+        lps = torch.zeros(B, T)
+        tr = {'h': [], 'c': [], 'logits': [], 'x': []}
+        unfinished = None
+        it = None
+        for t in range(T + 1):
+            if t == 0:
+                xt = F.linear(fc, p['img_embed.weight'], p['img_embed.bias'])
+            else:
+                if t == 1:
+                    it = torch.zeros(B, dtype=torch.long)   # <bos>
+                xt = F.embedding(it, p['embed.weight'])
+            h, c = lstm_core(dims, p, xt, h, c)
+            if trace:
+                tr['x'].append(xt.numpy().copy()); tr['h'].append(h.numpy().copy()); tr['c'].append(c.numpy().copy())
+            if t == 0:
+                continue          # the reference computes and discards these logits (:202-206)
+            logits = F.linear(h, p['logit.weight'], p['logit.bias'])
+            logprobs = F.log_softmax(logits, dim=1)
+            if trace:
+                tr['logits'].append(logits.numpy().copy())
+            lp, it = torch.max(logprobs, 1)
+            unfinished = (it > 0) if t == 1 else unfinished * (it > 0)
+            it = it * unfinished.type_as(it)
+            seq[:, t - 1] = it
+            lps[:, t - 1] = lp
+            if unfinished.sum() == 0:
+                break
+        if trace:
+            return seq.numpy(), lps.numpy(), tr
+        return seq.numpy(), lps.numpy()

@@ -1,0 +1,98 @@
+"""Pin the oracle against the REAL reference, imported from /root/reference.
+
+Run in the build container:  python -m oracle.refcheck
+Every comparison is bit-exact (np.array_equal) -- the oracle calls the same
+torch/numpy CPU kernels the reference does.  TEST INFRASTRUCTURE.
+"""
+import sys
+import numpy as np
+import torch
+
+from . import _refimport, fc_caption, nes_math, noise
+
+
+def check_decode(ref, V, E, R, Fd, B, ln=False, affine=False, seed=0):
+    opt = ref.ModelOptions(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd,
+                           layer_n=ln, layer_n_affine=affine)
+    torch.manual_seed(seed)
+    model = ref.FCModel(options=opt)
+    dims = fc_caption.Dims(V, E, R, Fd, layer_n=ln, layer_n_affine=affine)
+    # layout: names, shapes and order must match named_parameters()
+    got = [(n, tuple(p.shape)) for n, p in model.named_parameters()]
+    want = [(n, tuple(s)) for n, s, _, _ in dims.layout()]
+    assert got == want, (got, want)
+    assert model.nb_learnable_params == dims.num_params()
+    theta = model.parameter_vector().numpy().copy()
+    fc = torch.randn(B, Fd)
+    seq_r, lp_r = model(fc, greedy=True)
+    seq_o, lp_o = fc_caption.decode_greedy(dims, theta, fc.numpy())
+    assert np.array_equal(seq_r.numpy(), seq_o), 'seq differs'
+    assert np.array_equal(lp_r.numpy(), lp_o), 'logprobs differ'
+    # perturbed member through the reference's own set_from_vector
+    G = noise.granularity(E, R, Fd)
+    play, D, D_pad = noise.padded_layout(dims.layout(), G)
+    eps = noise.noise_row(77, 3 * G, play, D)
+    for sign in (+1, -1):
+        th, nz = noise.member_theta(theta, eps, 0.01, sign)
+        model.set_from_vector(torch.from_numpy(th.copy()))
+        seq_r, lp_r = model(fc, greedy=True)
+        seq_o, lp_o = fc_caption.decode_greedy(dims, th, fc.numpy())
+        assert np.array_equal(seq_r.numpy(), seq_o) and np.array_equal(lp_r.numpy(), lp_o)
+    return True
+
+
+def check_master_math(ref, F=37, D=1000, seed=0):
+    rs = np.random.RandomState(seed)
+    m = object.__new__(ref.NESMaster)      # the math methods use no instance state
+    fit = rs.randn(F, 2) * 10
+    nz = rs.randn(F, D).astype(np.float32) * 0.01
+    assert np.array_equal(m.compute_centered_ranks(fit), nes_math.compute_centered_ranks(fit))
+    assert np.array_equal(m.compute_ranks(fit.ravel()), nes_math.compute_ranks(fit.ravel()))
+    g_r = m.gradient_estimate(fit, nz)
+    g_o = nes_math.gradient_estimate(fit, nz)
+    assert g_r.dtype == g_o.dtype and np.array_equal(g_r, g_o)
+    # > 500 rows exercises the chunking of batched_weighted_sum
+    F2 = 1203
+    fit2 = rs.randn(F2, 2); nz2 = rs.randn(F2, 64).astype(np.float32)
+    assert np.array_equal(m.gradient_estimate(fit2, nz2), nes_math.gradient_estimate(fit2, nz2))
+    kat = m.compute_centered_ranks(np.array([[101, 200], [2, 100]]))
+    assert np.allclose(kat, [[0.16666667, 0.5], [-0.5, -0.16666667]])
+    return True
+
+
+def check_optimizers(ref, D=513, steps=5, seed=0):
+    rs = np.random.RandomState(seed)
+    theta0 = rs.randn(D).astype(np.float32)
+    for name, kw in (('Adam', dict(stepsize=0.001)), ('SGD', dict(stepsize=0.02, momentum=0.9))):
+        o_r = getattr(ref.optimizers, name)(theta0.copy(), **kw)
+        o_o = getattr(nes_math, name)(theta0.copy(), **kw)
+        th_r = theta0.copy(); th_o = theta0.copy()
+        for _ in range(steps):
+            g = rs.randn(D).astype(np.float32) * 0.1
+            r1, th_r = o_r.update(-g + 1e-7 * th_r)
+            r2, th_o = nes_math.master_update(o_o, th_o, g, 1e-7)
+            assert r1 == r2 and np.array_equal(th_r, th_o) and th_r.dtype == th_o.dtype
+    return True
+
+
+def main():
+    if not _refimport.available():
+        print('reference not present; nothing checked'); return 1
+    ref = _refimport.load()
+    torch.set_grad_enabled(False)
+    n = 0
+    for cfg in [dict(V=199, E=64, R=64, Fd=128, B=8), dict(V=999, E=64, R=128, Fd=256, B=5),
+                dict(V=300, E=128, R=128, Fd=512, B=12, ln=True),
+                dict(V=300, E=128, R=128, Fd=512, B=12, ln=True, affine=True),
+                dict(V=9487, E=128, R=128, Fd=2048, B=4)]:
+        check_decode(ref, **cfg); n += 1
+    # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)
+    assert fc_caption.Dims(9487, 128, 128, 2048).num_params() == 2865808
+    assert fc_caption.Dims(9487, 512, 512, 2048).num_params() == 13400848
+    check_master_math(ref); check_optimizers(ref)
+    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers OK' % n)
+    return 0
+
+
+if __name__ == '__main__':
+    sys.exit(main())

@@ -1,0 +1,76 @@
+"""Oracle vs the golden vectors the REAL reference produced (CPU, no GPU)."""
+import numpy as np
+import pytest
+
+from oracle import fc_caption, nes_math, noise
+
+
+@pytest.mark.parametrize('name', ['g1', 'g2', 'g3', 'g5', 'g6'])
+def test_decode_matches_reference_golden(name, golden, golden_mod):
+    c = golden_mod.CASES[name]
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    assert np.float64(theta.astype(np.float64).sum()) == golden[name + '_theta_sum']
+    s0, lp0 = fc_caption.decode_greedy(dims, theta, fc)
+    assert np.array_equal(s0, golden[name + '_seq_theta'])
+    assert np.array_equal(lp0, golden[name + '_logprobs_theta'])
+    for i in range(c['F']):
+        eps = noise.noise_row(golden_mod.TABLE_SEED, offs[i], play, D)
+        for j, sign in enumerate((+1, -1)):
+            th, _ = noise.member_theta(theta, eps, c['sigma'], sign)
+            s, lp = fc_caption.decode_greedy(dims, th, fc)
+            assert np.array_equal(s, golden[name + '_seq'][i, j])
+            assert np.array_equal(lp, golden[name + '_logprobs'][i, j])
+
+
+def test_centered_ranks_known_answer(golden):
+    # the reference's only published known answer: nic_nes_master.py:189
+    got = nes_math.compute_centered_ranks(np.array([[101, 200], [2, 100]]))
+    assert np.allclose(got, [[0.16666667, 0.5], [-0.5, -0.16666667]], atol=1e-8)
+    assert np.array_equal(got, golden['mm_kat_out'])
+
+
+def test_gradient_and_ranks_match_reference_golden(golden, golden_mod):
+    c = golden_mod.CASES['g1']
+    dims, G, play, D, D_pad, L, theta, fc, _ = golden_mod.case_inputs(c)
+    fit, offs = golden['mm_fitness'], golden['mm_offsets']
+    assert np.array_equal(nes_math.compute_centered_ranks(fit), golden['mm_centered_ranks'])
+    nz = np.stack([noise.member_theta(theta, noise.noise_row(golden_mod.TABLE_SEED, o, play, D), 0.01, +1)[1]
+                   for o in offs])
+    assert np.array_equal(nes_math.gradient_estimate(fit, nz), golden['mm_grad'])
+
+
+@pytest.mark.parametrize('oname', ['adam', 'sgd'])
+def test_optimizer_trajectory_matches_reference_golden(oname, golden, golden_mod):
+    c = golden_mod.CASES['g1']
+    dims, G, play, D, D_pad, L, theta, fc, _ = golden_mod.case_inputs(c)
+    g = golden['mm_grad']
+    opt = {'adam': lambda: nes_math.Adam(theta.copy(), stepsize=0.001),
+           'sgd': lambda: nes_math.SGD(theta.copy(), stepsize=0.02, momentum=0.9)}[oname]()
+    th = theta.copy()
+    ratios = []
+    for step in range(3):
+        gi = (g * np.float32(1.0 + 0.5 * step)).astype(np.float32)
+        r, th = nes_math.master_update(opt, th, gi, 1e-7)
+        ratios.append(r)
+        if step == 0:
+            assert np.array_equal(th[::16], golden['opt_%s_theta1_s16' % oname])
+    assert np.array_equal(np.array(ratios), golden['opt_%s_ratios' % oname])
+    assert np.array_equal(th[::16], golden['opt_%s_theta3_s16' % oname])
+    assert th.sum() == golden['opt_%s_theta3_sum' % oname]
+
+
+def test_rank_ties_use_index_order():
+    # D7: the reference's default argsort leaves tie order unspecified; this build's rule is stable
+    x = np.array([3., 1., 3., 1., 2.])
+    assert list(nes_math.compute_ranks(x)) == [3, 0, 4, 1, 2]
+
+
+def test_early_break_leaves_zeros():
+    # a model whose argmax is token 0 at the first step stops immediately (nets.py:242-243)
+    dims = fc_caption.Dims(9, 8, 8, 8)
+    theta = np.zeros(dims.num_params(), dtype=np.float32)
+    lay = {n: (s, c) for n, _, s, c in dims.layout()}
+    s, c = lay['logit.bias']
+    theta[s] = 5.0
+    seq, lp = fc_caption.decode_greedy(dims, theta, np.ones((3, 8), dtype=np.float32))
+    assert (seq == 0).all() and (lp[:, 1:] == 0).all() and (lp[:, 0] < 0).all()
