@@ -1,0 +1,146 @@
+/* nes_b200.h -- C ABI of the B200-native NIC-ES / NIC-NES population-evaluation path.
+ *
+ * The reference (rubencart/NES-img-captioning, pure Python) has no FFI; its
+ * boundary for this path is the Python Policy / PolicyNet / NESMaster /
+ * Optimizer objects.  Each entry point below names the reference method it
+ * replaces (paths relative to /root/reference/src).  The Python mirror of those
+ * classes lives in nes-img-captioning_b200/{nets,policies,master}.py and calls
+ * nothing but these symbols (ctypes).
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; the message is
+ *     available from nes_last_error() (thread-local).
+ *   - every pointer argument may be a HOST or a DEVICE pointer (UVA); data is
+ *     staged through context-owned device buffers with cudaMemcpyAsync on the
+ *     context stream.  The caller owns every buffer it passes; the context keeps
+ *     no alias to caller memory after return (contrast: PolicyNet.set_from_vector,
+ *     algorithm/nets.py:163-165, aliases the caller's vector).
+ *   - one context per device, not thread-safe, all work on one CUDA stream.
+ *   - calls are asynchronous w.r.t. the host unless an output pointer is a host
+ *     pointer (then the call synchronises the stream before returning).
+ */
+#ifndef NES_B200_H
+#define NES_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nes_ctx nes_ctx;
+
+/* fc_caption dimensions: ModelOptions of algorithm/policies.py:36-41 as used by
+ * captioning/nets.py:138-176 (FCModel) and :73-96 (LSTMCore). */
+typedef struct nes_fc_dims {
+    int32_t vocab_size;            /* V; logits have V+1 columns */
+    int32_t input_encoding_size;   /* E */
+    int32_t rnn_size;              /* R */
+    int32_t fc_feat_size;          /* Fd */
+    int32_t seq_length;            /* T = 16 (captioning/nets.py:147) */
+    int32_t layer_n;               /* LayerNorm on i2h / h2h / c (captioning/nets.py:93-96) */
+    int32_t layer_n_affine;
+} nes_fc_dims;
+
+/* precision of the population GEMMs */
+#define NES_PREC_FAST  0   /* fp16 operands (theta_hi, x_hi, eps exact), fp32 accumulate          */
+#define NES_PREC_EXACT 1   /* split-fp16 (hi+lo) theta and activations: ~fp32 products, 5 MMAs    */
+
+/* optimizer kinds (algorithm/nic_nes/optimizers.py) */
+#define NES_OPT_SGD  0
+#define NES_OPT_ADAM 1
+
+const char* nes_last_error(void);
+int  nes_version(void);
+
+/* ---- context ------------------------------------------------------------------------------- */
+/* fc_caption context: flat-theta layout = FCModel.named_parameters() order (captioning/nets.py:150-153).
+ * table_len: number of fp16 elements of the shared noise table (multiple of 4).
+ * n_parents: how many theta vectors the context holds (1 for NIC-NES; mu for NIC-ES).
+ * wave_members / rows: capacity of the decode workspace (members evaluated per wave, rows per rollout). */
+int nes_ctx_create_fc(nes_ctx** out, int device, const nes_fc_dims* dims, uint64_t seed,
+                      int64_t table_len, int n_parents, int wave_members, int rows);
+/* generic flat context (master-side math only: ranks, gradient, optimizer; no decode), e.g. MnistNet
+ * (classification/nets.py) or the config-5 sweep.  counts[n_tensors] in flat order; granule = slot alignment. */
+int nes_ctx_create_flat(nes_ctx** out, int device, const int64_t* counts, int n_tensors, int64_t granule,
+                        uint64_t seed, int64_t table_len, int n_parents);
+int nes_ctx_destroy(nes_ctx* ctx);
+int nes_set_stream(nes_ctx* ctx, void* cuda_stream);
+int nes_sync(nes_ctx* ctx);
+int64_t nes_num_params(const nes_ctx* ctx);   /* D      = PolicyNet.nb_learnable_params (algorithm/nets.py:46-50) */
+int64_t nes_padded_params(const nes_ctx* ctx);/* D_pad  (noise-row length in table elements) */
+int64_t nes_granule(const nes_ctx* ctx);      /* G */
+int64_t nes_table_len(const nes_ctx* ctx);
+int64_t nes_gpu_launches(const nes_ctx* ctx); /* kernels launched by this context so far */
+
+/* ---- noise table (replaces the per-worker torch normal_ of algorithm/nets.py:92-102) -------- */
+int nes_fill_table(nes_ctx* ctx);                                     /* K1: Philox4x32-10 -> Box-Muller -> fp16 */
+int nes_table_slice(nes_ctx* ctx, int64_t start, int64_t count, void* out_f16);
+int nes_sample_offsets(nes_ctx* ctx, uint64_t iteration, int64_t F, int64_t* out);
+int nes_sample_parents(nes_ctx* ctx, uint64_t iteration, int64_t F, int32_t n_parents, int32_t* out);
+
+/* ---- theta (Policy.set_from_parameter_vector / parameter_vector, algorithm/policies.py:102-111) */
+int nes_set_theta(nes_ctx* ctx, int parent, const void* theta, int is_f64);
+int nes_get_theta(nes_ctx* ctx, int parent, void* out, int as_f64);
+/* PolicyNet.evolve (algorithm/nets.py:83-119) against table row `offset`: noise = f32(sigma)*eps,
+ * member = theta + sign*noise.  Either output may be NULL.  If dst_parent >= 0 the member also becomes
+ * parent `dst_parent` (NIC-ES survivor materialisation, nic_es_worker.py:188 without the .pth file). */
+int nes_evolve(nes_ctx* ctx, int parent, int64_t offset, float sign, float sigma,
+               float* member_out, float* noise_out, int dst_parent);
+
+/* ---- population rollout (NESWorker.fitness nic_nes_worker.py:131-154 / ESWorker.fitness
+ *      nic_es_worker.py:142-175 -> CaptPolicy.rollout captioning/policies.py:86-116 ->
+ *      FCModel._sample(greedy) captioning/nets.py:183-245), CIDEr scoring excluded --------------- */
+/* member m = theta[parents[m]] + signs[m]*sigma*eps(offsets[m]); parents may be NULL (all 0).
+ * fc: float32 [rows, Fd] if shared_batch else [n_members, rows, Fd].
+ * seq: int64 [n_members, rows, T]; logprobs: float32 [n_members, rows, T]. */
+int nes_rollout(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs,
+                const int32_t* parents, const float* fc, int rows, int shared_batch, float sigma,
+                int precision, int64_t* seq, float* logprobs);
+/* test hook: teacher-forced decode of ONE wave with per-step dumps.  forced_tokens int64 [n_members, rows, T]
+ * (NULL = greedy feedback); h_trace float32 [T+1, n_members, rows, R]; logit_trace float32 [T, n_members, rows, V+1]
+ * (either may be NULL). */
+int nes_rollout_trace(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs,
+                      const int32_t* parents, const float* fc, int rows, int shared_batch, float sigma,
+                      int precision, const int64_t* forced_tokens, int64_t* seq, float* logprobs,
+                      float* h_trace, float* logit_trace);
+/* sum over time of seq_logprobs per member -> float64 [n_members] (device-side stand-in fitness for benches) */
+int nes_logprob_fitness(nes_ctx* ctx, int64_t n_members, int rows, double* out);
+
+/* ---- master math ------------------------------------------------------------------------------ */
+/* K6: NESMaster.compute_centered_ranks + weights (nic_nes_master.py:178-179,184-205); stable tie rule.
+ * fitness float64 [F,2]; centered float64 [F,2] (nullable); weights float32 [F] (nullable; kept in ctx). */
+int nes_rank_weights(nes_ctx* ctx, const double* fitness, int64_t F, double* centered, float* weights);
+/* ranks of a flat float64 vector (compute_ranks, nic_nes_master.py:196-205) -> int64 [n] */
+int nes_compute_ranks(nes_ctx* ctx, const double* x, int64_t n, int64_t* ranks);
+/* K7: NESMaster.gradient_estimate / batched_weighted_sum (nic_nes_master.py:170-182,207-221):
+ * g = f32(sigma) * sum_i w_i eps_i / (2F) over table rows; weights NULL = the ctx weights of the last
+ * nes_rank_weights.  g_out float32 [D] nullable (the gradient stays resident in the ctx). */
+int nes_gradient(nes_ctx* ctx, const int64_t* offsets, const float* weights, int64_t F, float sigma, float* g_out);
+/* K8: G = -g + l2*theta; Optimizer.update (optimizers.py:15-22) with SGD (:44-47) or Adam (:78-83);
+ * float64 state, float64 master theta, float32 + split-fp16 evaluation copies refreshed in the same pass.
+ * grad NULL = the resident gradient.  ratio_out float64 (nullable) = |step| / |theta|. */
+int nes_opt_init(nes_ctx* ctx, int kind, double stepsize, double momentum_or_beta1, double beta2, double epsilon);
+int nes_opt_set_stepsize(nes_ctx* ctx, double stepsize);
+int nes_opt_update(nes_ctx* ctx, const float* grad, double l2coeff, double* ratio_out);
+/* Optimizer.update(globalg) verbatim (optimizers.py:15-22): globalg float32 or float64 [D]; numpy keeps
+ * (1-beta)*globalg in float32 when globalg is float32, and so does this. */
+int nes_opt_update_direct(nes_ctx* ctx, const void* globalg, int is_f64, double* ratio_out);
+int nes_opt_get_state(nes_ctx* ctx, double* m, double* v, int64_t* t);   /* Optimizer.save_to_file payload */
+int nes_opt_set_state(nes_ctx* ctx, const double* m, const double* v, int64_t t);
+/* one whole master step: ranks -> weights -> gradient -> update (run_master nic_nes_master.py:123-136) */
+int nes_master_step(nes_ctx* ctx, const double* fitness, const int64_t* offsets, int64_t F, float sigma,
+                    double l2coeff, double* ratio_out);
+
+/* timing of the last K7 launch on the context stream, CUDA events (ms); bench.py roofline */
+int nes_last_gradient_ms(nes_ctx* ctx, float* ms);
+int nes_last_rollout_ms(nes_ctx* ctx, float* ms);
+
+/* standalone tensor-core self test through the same tcgen05/TMA kernel the decode uses:
+ * C[M,N] = A[M,K] W[N,K]^T + sigma * A[M,K] f16(E[N,K])^T, float32 in/out (host or device pointers). */
+int nes_gemm_selftest(int device, int M, int N, int K, const float* A, const float* W, const float* E,
+                      float sigma, int precision, float* C);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,263 @@
+"""NesContext: one per GPU.  Owns (through the C library) theta, the shared noise table and the decode
+workspace; every method forwards to one extern "C" entry point of include/nes_b200.h."""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from .layout import build_layout, fc_tensors, granule
+
+PREC_FAST, PREC_EXACT = 0, 1
+OPT_SGD, OPT_ADAM = 0, 1
+
+
+class NesContext:
+    def __init__(self, model_options=None, *, counts=None, flat_granule=64, seed=1234, table_len=1 << 28,
+                 n_parents=1, wave_members=256, rows=128, device=0, fill=True):
+        """model_options: dict / namedtuple with the fc_caption ModelOptions fields (vocab_size,
+        input_encoding_size, rnn_size, fc_feat_size, layer_n, layer_n_affine[, seq_length]); or
+        counts=[...] for a generic flat parameter vector (master math only)."""
+        self.lib = _lib.load()
+        self.device = int(device)
+        self._h = ctypes.c_void_p()
+        self.seed, self.table_len, self.n_parents = int(seed), int(table_len), int(n_parents)
+        if model_options is not None:
+            mo = model_options._asdict() if hasattr(model_options, '_asdict') else dict(model_options)
+            self.dims = dict(vocab_size=int(mo['vocab_size']), input_encoding_size=int(mo['input_encoding_size']),
+                             rnn_size=int(mo['rnn_size']), fc_feat_size=int(mo['fc_feat_size']),
+                             seq_length=int(mo.get('seq_length') or 16), layer_n=int(bool(mo.get('layer_n'))),
+                             layer_n_affine=int(bool(mo.get('layer_n_affine'))))
+            d = _lib.FcDims(**self.dims)
+            self.G = granule(self.dims['input_encoding_size'], self.dims['rnn_size'], self.dims['fc_feat_size'])
+            self.tensors, self.D, self.D_pad = build_layout(
+                fc_tensors(self.dims['vocab_size'], self.dims['input_encoding_size'], self.dims['rnn_size'],
+                           self.dims['fc_feat_size'], self.dims['layer_n'], self.dims['layer_n_affine']), self.G)
+            _lib.check(self.lib.nes_ctx_create_fc(ctypes.byref(self._h), self.device, ctypes.byref(d), self.seed,
+                                                  self.table_len, self.n_parents, int(wave_members), int(rows)))
+            self.wave_members, self.rows_cap = int(wave_members), int(rows)
+        else:
+            assert counts is not None, 'give model_options or counts'
+            self.dims = None
+            self.G = int(flat_granule)
+            self.tensors, self.D, self.D_pad = build_layout([('t%d' % i, (int(c),)) for i, c in enumerate(counts)], self.G)
+            arr = (ctypes.c_int64 * len(counts))(*[int(c) for c in counts])
+            _lib.check(self.lib.nes_ctx_create_flat(ctypes.byref(self._h), self.device, arr, len(counts), self.G,
+                                                    self.seed, self.table_len, self.n_parents))
+        assert self.lib.nes_num_params(self._h) == self.D and self.lib.nes_padded_params(self._h) == self.D_pad \
+            and self.lib.nes_granule(self._h) == self.G, 'host / library layout mismatch'
+        self.dev = torch.device('cuda', self.device)
+        self.use_stream(torch.cuda.current_stream(self.dev))
+        if fill:
+            self.fill_table()
+
+    # ---- plumbing
+    def use_stream(self, stream):
+        self._stream = stream
+        _lib.check(self.lib.nes_set_stream(self._h, ctypes.c_void_p(stream.cuda_stream)))
+
+    def sync(self):
+        _lib.check(self.lib.nes_sync(self._h))
+
+    def close(self):
+        if self._h:
+            self.lib.nes_ctx_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def gpu_launches(self):
+        return int(self.lib.nes_gpu_launches(self._h))
+
+    @property
+    def n_slots(self):
+        return (self.table_len - self.D_pad) // self.G + 1
+
+    # ---- noise table
+    def fill_table(self):
+        _lib.check(self.lib.nes_fill_table(self._h))
+
+    def table_slice(self, start, count):
+        out = np.empty(int(count), dtype=np.float16)
+        _lib.check(self.lib.nes_table_slice(self._h, int(start), int(count), _lib.ptr(out)))
+        return out
+
+    def sample_offsets(self, iteration, F, device=False):
+        out = torch.empty(int(F), dtype=torch.int64, device=self.dev if device else 'cpu')
+        _lib.check(self.lib.nes_sample_offsets(self._h, int(iteration), int(F), _lib.ptr(out)))
+        return out
+
+    def sample_parents(self, iteration, F, n_parents):
+        out = torch.empty(int(F), dtype=torch.int32)
+        _lib.check(self.lib.nes_sample_parents(self._h, int(iteration), int(F), int(n_parents), _lib.ptr(out)))
+        return out
+
+    # ---- theta
+    def set_theta(self, vector, parent=0):
+        """vector: numpy / torch, float32 or float64, host or device, length D (asserted like
+        src/algorithm/nets.py:164)."""
+        if isinstance(vector, np.ndarray):
+            vector = torch.from_numpy(np.ascontiguousarray(vector))
+        assert vector.numel() == self.D, 'len(vector) == nb_learnable_params'
+        assert vector.dtype in (torch.float32, torch.float64)
+        vector = vector.contiguous()
+        _lib.check(self.lib.nes_set_theta(self._h, int(parent), _lib.ptr(vector), int(vector.dtype == torch.float64)))
+
+    def get_theta(self, parent=0, dtype=torch.float32, device='cpu'):
+        out = torch.empty(self.D, dtype=dtype, device=device)
+        _lib.check(self.lib.nes_get_theta(self._h, int(parent), _lib.ptr(out), int(dtype == torch.float64)))
+        return out
+
+    def evolve(self, offset, sigma, sign=1.0, parent=0, want_member=True, want_noise=True, dst_parent=-1, device='cpu'):
+        member = torch.empty(self.D, dtype=torch.float32, device=device) if want_member else None
+        noise = torch.empty(self.D, dtype=torch.float32, device=device) if want_noise else None
+        _lib.check(self.lib.nes_evolve(self._h, int(parent), int(offset), float(sign), float(sigma),
+                                       _lib.ptr(member), _lib.ptr(noise), int(dst_parent)))
+        return member, noise
+
+    # ---- population rollout
+    def rollout(self, offsets, signs, fc, sigma, parents=None, precision=PREC_EXACT, shared_batch=None,
+                out_device='cpu', forced_tokens=None, trace=False):
+        """offsets int64 [P], signs float32 [P], fc float32 [rows, Fd] (shared) or [P, rows, Fd].
+        Returns seq int64 [P, rows, T], logprobs float32 [P, rows, T] (+ h_trace, logit_trace when trace)."""
+        offsets = torch.as_tensor(offsets, dtype=torch.int64).contiguous()
+        signs = torch.as_tensor(signs, dtype=torch.float32).contiguous()
+        if isinstance(fc, np.ndarray):
+            fc = torch.from_numpy(np.ascontiguousarray(fc, dtype=np.float32))
+        fc = fc.to(torch.float32).contiguous()
+        P = offsets.numel()
+        assert signs.numel() == P
+        if shared_batch is None:
+            shared_batch = fc.dim() == 2
+        rows = fc.shape[-2]
+        assert fc.shape[-1] == self.dims['fc_feat_size']
+        assert shared_batch or fc.shape[0] == P
+        if parents is not None:
+            parents = torch.as_tensor(parents, dtype=torch.int32).contiguous()
+            assert parents.numel() == P
+        T, R, V1 = self.dims['seq_length'], self.dims['rnn_size'], self.dims['vocab_size'] + 1
+        seq = torch.empty((P, rows, T), dtype=torch.int64, device=out_device)
+        lp = torch.empty((P, rows, T), dtype=torch.float32, device=out_device)
+        if not trace and forced_tokens is None:
+            _lib.check(self.lib.nes_rollout(self._h, P, _lib.ptr(offsets), _lib.ptr(signs), _lib.ptr(parents), _lib.ptr(fc),
+                                            int(rows), int(bool(shared_batch)), float(sigma), int(precision),
+                                            _lib.ptr(seq), _lib.ptr(lp)))
+            return seq, lp
+        h_tr = torch.zeros((T + 1, P, rows, R), dtype=torch.float32, device=self.dev) if trace else None
+        l_tr = torch.zeros((T, P, rows, V1), dtype=torch.float32, device=self.dev) if trace else None
+        if forced_tokens is not None:
+            forced_tokens = torch.as_tensor(forced_tokens, dtype=torch.int64).contiguous()
+            assert tuple(forced_tokens.shape) == (P, rows, T)
+        _lib.check(self.lib.nes_rollout_trace(self._h, P, _lib.ptr(offsets), _lib.ptr(signs), _lib.ptr(parents), _lib.ptr(fc),
+                                              int(rows), int(bool(shared_batch)), float(sigma), int(precision),
+                                              _lib.ptr(forced_tokens), _lib.ptr(seq), _lib.ptr(lp), _lib.ptr(h_tr), _lib.ptr(l_tr)))
+        self.sync()
+        return seq, lp, h_tr, l_tr
+
+    def logprob_fitness(self, n_members, rows, device='cpu'):
+        out = torch.empty(int(n_members), dtype=torch.float64, device=device)
+        _lib.check(self.lib.nes_logprob_fitness(self._h, int(n_members), int(rows), _lib.ptr(out)))
+        return out
+
+    # ---- master math
+    def compute_ranks(self, x):
+        x = torch.as_tensor(np.asarray(x, dtype=np.float64)).contiguous() if not torch.is_tensor(x) else x.to(torch.float64).contiguous()
+        out = torch.empty(x.numel(), dtype=torch.int64)
+        _lib.check(self.lib.nes_compute_ranks(self._h, _lib.ptr(x), x.numel(), _lib.ptr(out)))
+        return out
+
+    def rank_weights(self, fitness, want_centered=True):
+        fit = fitness if torch.is_tensor(fitness) else torch.from_numpy(np.ascontiguousarray(fitness, dtype=np.float64))
+        fit = fit.to(torch.float64).contiguous()
+        F = fit.shape[0]
+        assert fit.numel() == 2 * F
+        cen = torch.empty((F, 2), dtype=torch.float64) if want_centered else None
+        w = torch.empty(F, dtype=torch.float32)
+        _lib.check(self.lib.nes_rank_weights(self._h, _lib.ptr(fit), F, _lib.ptr(cen), _lib.ptr(w)))
+        return cen, w
+
+    def gradient(self, offsets, weights, sigma, out_device='cpu', want=True):
+        offsets = torch.as_tensor(offsets, dtype=torch.int64).contiguous()
+        F = offsets.numel()
+        if weights is not None:
+            weights = torch.as_tensor(weights, dtype=torch.float32).contiguous()
+            assert weights.numel() == F
+        g = torch.empty(self.D, dtype=torch.float32, device=out_device) if want else None
+        _lib.check(self.lib.nes_gradient(self._h, _lib.ptr(offsets), _lib.ptr(weights), F, float(sigma), _lib.ptr(g)))
+        return g
+
+    def opt_init(self, kind, stepsize, momentum_or_beta1=0.9, beta2=0.999, epsilon=1e-8):
+        _lib.check(self.lib.nes_opt_init(self._h, int(kind), float(stepsize), float(momentum_or_beta1), float(beta2), float(epsilon)))
+
+    def opt_set_stepsize(self, stepsize):
+        _lib.check(self.lib.nes_opt_set_stepsize(self._h, float(stepsize)))
+
+    def opt_update(self, grad=None, l2coeff=0.0, want_ratio=True):
+        if grad is not None:
+            grad = torch.as_tensor(grad, dtype=torch.float32).contiguous()
+            assert grad.numel() == self.D
+        ratio = ctypes.c_double(0.0)
+        _lib.check(self.lib.nes_opt_update(self._h, _lib.ptr(grad), float(l2coeff), ctypes.byref(ratio) if want_ratio else None))
+        return ratio.value if want_ratio else None
+
+    def opt_update_direct(self, globalg, want_ratio=True):
+        """Optimizer.update(globalg): globalg float32 or float64 numpy / torch, length D"""
+        if isinstance(globalg, np.ndarray):
+            globalg = torch.from_numpy(np.ascontiguousarray(globalg))
+        assert globalg.numel() == self.D and globalg.dtype in (torch.float32, torch.float64)
+        globalg = globalg.contiguous()
+        ratio = ctypes.c_double(0.0)
+        _lib.check(self.lib.nes_opt_update_direct(self._h, _lib.ptr(globalg), int(globalg.dtype == torch.float64),
+                                                  ctypes.byref(ratio) if want_ratio else None))
+        return ratio.value if want_ratio else None
+
+    def opt_get_state(self):
+        m = torch.empty(self.D, dtype=torch.float64)
+        v = torch.empty(self.D, dtype=torch.float64)
+        t = ctypes.c_int64(0)
+        _lib.check(self.lib.nes_opt_get_state(self._h, _lib.ptr(m), _lib.ptr(v), ctypes.byref(t)))
+        return m, v, t.value
+
+    def opt_set_state(self, m, v, t):
+        m = None if m is None else torch.as_tensor(m, dtype=torch.float64).contiguous()
+        v = None if v is None else torch.as_tensor(v, dtype=torch.float64).contiguous()
+        _lib.check(self.lib.nes_opt_set_state(self._h, _lib.ptr(m), _lib.ptr(v), int(t)))
+
+    def master_step(self, fitness, offsets, sigma, l2coeff=0.0, want_ratio=True):
+        fit = fitness if torch.is_tensor(fitness) else torch.from_numpy(np.ascontiguousarray(fitness, dtype=np.float64))
+        fit = fit.to(torch.float64).contiguous()
+        offsets = torch.as_tensor(offsets, dtype=torch.int64).contiguous()
+        F = offsets.numel()
+        assert fit.numel() == 2 * F
+        ratio = ctypes.c_double(0.0)
+        _lib.check(self.lib.nes_master_step(self._h, _lib.ptr(fit), _lib.ptr(offsets), F, float(sigma), float(l2coeff),
+                                            ctypes.byref(ratio) if want_ratio else None))
+        return ratio.value if want_ratio else None
+
+    def last_gradient_ms(self):
+        ms = ctypes.c_float(0)
+        _lib.check(self.lib.nes_last_gradient_ms(self._h, ctypes.byref(ms)))
+        return ms.value
+
+    def last_rollout_ms(self):
+        ms = ctypes.c_float(0)
+        _lib.check(self.lib.nes_last_rollout_ms(self._h, ctypes.byref(ms)))
+        return ms.value
+
+
+def gemm_selftest(A, W, E=None, sigma=0.0, precision=PREC_EXACT, device=0):
+    lib = _lib.load()
+    A = torch.as_tensor(A, dtype=torch.float32).contiguous()
+    W = torch.as_tensor(W, dtype=torch.float32).contiguous()
+    if E is not None:
+        E = torch.as_tensor(E, dtype=torch.float32).contiguous()
+    M, K = A.shape
+    N = W.shape[0]
+    C = torch.empty((M, N), dtype=torch.float32)
+    _lib.check(lib.nes_gemm_selftest(int(device), M, N, K, _lib.ptr(A), _lib.ptr(W), _lib.ptr(E), float(sigma), int(precision), _lib.ptr(C)))
+    return C

@@ -1,0 +1,135 @@
+// Shared declarations for the B200-native NIC-ES/NIC-NES hot path.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/nes_b200.h"
+
+namespace nes {
+
+// ---------------------------------------------------------------------------------------------
+// errors
+void set_error(const std::string& msg);
+#define NES_CHECK(cond, msg)                                                        \
+    do { if (!(cond)) { ::nes::set_error(std::string(msg) + " [" #cond "] at " __FILE__ ":" + std::to_string(__LINE__)); return 1; } } while (0)
+#define NES_CUDA(call)                                                              \
+    do { cudaError_t e__ = (call); if (e__ != cudaSuccess) {                        \
+        ::nes::set_error(std::string("CUDA error: ") + cudaGetErrorString(e__) + " in " #call " at " __FILE__ ":" + std::to_string(__LINE__)); \
+        return 1; } } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// flat / padded layout of theta and of one noise row (spec: oracle/noise.py header)
+constexpr int kMaxTensors = 16;
+struct TensorDesc {
+    int64_t start;   // flat start (elements)
+    int64_t count;   // elements
+    int64_t pstart;  // start inside a padded noise row / padded theta shadow (multiple of G)
+    int32_t rows;    // [rows, cols] for matrices, rows = count, cols = 1 for vectors
+    int32_t cols;
+};
+struct Layout {
+    int n;
+    TensorDesc t[kMaxTensors];
+    int64_t D, D_pad, G;
+};
+// fc_caption tensor indices (FCModel.named_parameters() order)
+enum { T_IMG_W = 0, T_IMG_B, T_EMB_W, T_LOGIT_W, T_LOGIT_B, T_I2H_W, T_I2H_B, T_H2H_W, T_H2H_B,
+       T_I2H_LN_W, T_I2H_LN_B, T_H2H_LN_W, T_H2H_LN_B, T_C_LN_W, T_C_LN_B };
+
+// theta / activation scaling of the split-fp16 operands (exact powers of two)
+constexpr float kThetaScale = 256.0f;     // theta_hi + theta_lo = theta * 2^8
+constexpr float kActScale   = 32.0f;      // x_hi + x_lo = x * 2^5
+
+// ---------------------------------------------------------------------------------------------
+struct DecodeWorkspace;   // decode.cu
+
+struct Ctx {
+    int device = 0;
+    cudaStream_t stream = 0;
+    bool is_fc = false;
+    nes_fc_dims dims{};
+    Layout lay{};
+    uint64_t seed = 0;
+    int64_t table_len = 0;
+    int n_parents = 1;
+    int64_t launches = 0;
+
+    __half* table = nullptr;          // [table_len]
+    double* theta64 = nullptr;        // [n_parents, D]  master copy
+    float*  theta32 = nullptr;        // [n_parents, D]  evaluation copy (what the reference's workers load)
+    __half* theta_hi = nullptr;       // [n_parents, D_pad] padded layout, theta*2^8 split hi/lo
+    __half* theta_lo = nullptr;
+    uint8_t* theta_is_f32 = nullptr;  // host flags [n_parents]: master theta still has float32 provenance
+    Layout* d_lay = nullptr;          // device copy of lay
+
+    // master math
+    float*  grad = nullptr;           // [D]
+    double* opt_m = nullptr;          // [D]
+    double* opt_v = nullptr;          // [D]
+    int64_t opt_t = 0;
+    int opt_kind = -1;
+    double opt_stepsize = 0, opt_b1 = 0, opt_b2 = 0, opt_eps = 0;
+    double* d_norm_partials = nullptr; int norm_blocks = 0;
+    double* d_norms = nullptr;        // [2]
+    double* d_G64 = nullptr;          // [D] staging for a float64 globalg (lazy)
+
+    // scratch for per-iteration small arrays
+    int64_t* d_offsets = nullptr; float* d_weights = nullptr; double* d_fitness = nullptr;
+    double* d_centered = nullptr; int64_t* d_ranks = nullptr; int64_t small_cap = 0;
+
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr;
+    bool grad_timed = false, rollout_timed = false;
+
+    DecodeWorkspace* ws = nullptr;
+};
+
+int ensure_small(Ctx* c, int64_t n);   // (re)allocate the small per-iteration scratch arrays for n members
+
+// noise.cu
+int launch_fill_table(Ctx* c);
+int launch_sample_offsets(Ctx* c, uint64_t iteration, int64_t F, int64_t* d_out);
+int launch_sample_parents(Ctx* c, uint64_t iteration, int64_t F, int32_t n_parents, int32_t* d_out);
+int launch_theta_shadow(Ctx* c, int parent);      // theta32 -> theta_hi/lo (padded)
+int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64);
+int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, float* d_member, float* d_noise, int dst_parent);
+
+// master.cu
+int launch_ranks(Ctx* c, const double* d_x, int64_t n, int64_t* d_ranks);
+int launch_rank_weights(Ctx* c, const double* d_fit, int64_t F, double* d_centered, float* d_w);
+int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g);
+int launch_opt_update(Ctx* c, const float* d_g, const double* d_G64, int direct, double l2, double* ratio_host_or_null);
+
+// decode.cu
+int decode_create(Ctx* c, int wave_members, int rows);
+void decode_destroy(Ctx* c);
+int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,
+                   const float* fc, int rows, int shared_batch, float sigma, int precision,
+                   const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace);
+int decode_logprob_fitness(Ctx* c, int64_t n_members, int rows, double* out);
+
+}  // namespace nes
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., SC'11) -- identical to oracle/noise.py
+namespace nes {
+__host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                              uint32_t k0, uint32_t k1, uint32_t out[4]) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint64_t p0 = (uint64_t)M0 * c0;
+        uint64_t p1 = (uint64_t)M1 * c2;
+        uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0;
+        uint32_t hi1 = (uint32_t)(p1 >> 32), lo1 = (uint32_t)p1;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += W0; k1 += W1;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+constexpr uint32_t kOffsetDomain = 0x4F464653u;  // "OFFS"
+constexpr uint32_t kParentDomain = 0x50415245u;  // "PARE"
+}  // namespace nes

@@ -1,0 +1,558 @@
+// Greedy decode of a wave of perturbed members: FCModel._sample(fc, greedy=True)
+// (captioning/nets.py:183-245) for every member of the population at once.
+//   t = 0      x0 = img_embed(fc)                      PLAIN member GEMM (K = Fd)
+//              (h, c) = core(x0, 0)                    LSTM member GEMM  (K = E + R)
+//   t = 1..T   x_t = embed(it_{t-1}) (it_0 = <bos> = 0)  k_finalize gather
+//              (h, c) = core(x_t, (h, c))              LSTM member GEMM
+//              logits = logit(h) -> argmax, log-prob    LOGIT member GEMM + k_finalize
+// Finished-mask, early break and the seq / seq_logprobs writes follow :233-243.
+#include "member_gemm.cuh"
+#include <map>
+#include <tuple>
+
+namespace nes {
+
+// ---------------------------------------------------------------------------------------------
+// TMA descriptor creation through the driver entry point (no link-time libcuda dependency, so the
+// library also loads on a CPU-only box)
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled get_encode() {
+    static PFN_encodeTiled fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (PFN_encodeTiled)p;
+    }
+    return fn;
+}
+// fp16 matrix viewed as [rows, K] row-major, box = 64 columns x box_rows rows, 128-byte swizzle
+static int make_map(CUtensorMap* m, const void* base, int64_t rows, int64_t K, int box_rows) {
+    PFN_encodeTiled enc = get_encode();
+    NES_CHECK(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+    NES_CHECK(K % 64 == 0, "inner dimension must be a multiple of 64");
+    NES_CHECK(rows >= 1, "empty tensor map");
+    cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    NES_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed");
+    return 0;
+}
+
+struct DecodeWorkspace {
+    int W = 0, rows_cap = 0, rows_pad = 0;
+    int E = 0, R = 0, Fd = 0, V1 = 0, T = 0, nt_logit = 0;
+    // activations (fp16 split operands, scaled by kActScale)
+    float* fc32 = nullptr; __half *fc_hi = nullptr, *fc_lo = nullptr; int64_t fc_members = 0;   // capacity in members (1 = shared only)
+    __half *x_hi = nullptr, *x_lo = nullptr;
+    __half *h_hi[2] = {nullptr, nullptr}, *h_lo[2] = {nullptr, nullptr};
+    float* c_state = nullptr;
+    float *pre_i = nullptr, *pre_h = nullptr;               // LayerNorm path
+    LogitPartial* partials = nullptr;
+    uint8_t* unfinished = nullptr; int32_t* unf_count = nullptr;
+    // per call
+    int64_t cap_members = 0;
+    int64_t* d_off = nullptr; float* d_sign = nullptr; int32_t* d_parent = nullptr;
+    int64_t* d_seq = nullptr; float* d_lp = nullptr; int64_t out_cap = 0;
+    int64_t* d_forced = nullptr; int64_t forced_cap = 0;
+    std::map<std::tuple<const void*, int64_t, int64_t, int>, CUtensorMap> maps;
+    bool attrs_set = false;
+};
+
+static int get_map(DecodeWorkspace* ws, CUtensorMap* out, const void* base, int64_t rows, int64_t K, int box_rows) {
+    auto key = std::make_tuple(base, rows, K, box_rows);
+    auto it = ws->maps.find(key);
+    if (it == ws->maps.end()) {
+        CUtensorMap m;
+        if (make_map(&m, base, rows, K, box_rows)) return 1;
+        it = ws->maps.emplace(key, m).first;
+    }
+    *out = it->second;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// helper kernels
+__global__ void __launch_bounds__(256) k_split_rows(const float* __restrict__ src, __half* __restrict__ hi, __half* __restrict__ lo,
+                                                    int64_t n_blocks, int rows, int rows_pad, int K) {
+    // src [n_blocks, rows, K] -> hi/lo [n_blocks, rows_pad, K] (padding rows zero)
+    const int64_t total = n_blocks * rows_pad * (int64_t)K;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int k = (int)(i % K);
+        const int64_t rr = i / K;
+        const int r = (int)(rr % rows_pad);
+        const int64_t b = rr / rows_pad;
+        __half a = __float2half_rn(0.f), l = a;
+        if (r < rows) split_half_dev(src[(b * rows + r) * K + k], kActScale, a, l);
+        hi[i] = a; lo[i] = l;
+    }
+}
+
+struct FinalizeParams {
+    const LogitPartial* partials; int n_tiles;
+    int rows, rows_pad, T, E, t;                 // t in 1..T (0: <bos> gather only)
+    int64_t n_members;
+    const int64_t* off; const float* sign; const int32_t* parent;
+    const float* theta32; const __half* table; int64_t D;
+    int64_t emb_start, emb_pstart;
+    float sigma;
+    uint8_t* unfinished; int32_t* unf_count;     // [T+1, W]
+    int W;
+    int64_t* seq; float* lp;                     // wave-local [n_members, rows, T]
+    const int64_t* forced;                       // nullable
+    __half *x_hi, *x_lo;
+    int gather;                                  // write x for the next step
+};
+// one warp per (member, row): merge the per-tile (max, argmax, sum-exp) partials, apply the
+// finished-mask bookkeeping of captioning/nets.py:233-243, gather the next input embedding.
+__global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (wid >= p.n_members * p.rows) return;
+    const int64_t member = wid / p.rows;
+    const int r = (int)(wid % p.rows);
+    const int64_t grow = member * p.rows_pad + r;
+    const float sgn = p.sign[member];
+    int64_t tok = 0;
+    if (p.t >= 1) {
+        float mx = -INFINITY; int idx = 0x7fffffff;
+        for (int j = lane; j < p.n_tiles; j += 32) {
+            const LogitPartial q = p.partials[grow * p.n_tiles + j];
+            if (q.mx > mx || (q.mx == mx && q.idx < idx)) { mx = q.mx; idx = q.idx; }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+            if (om > mx || (om == mx && oi < idx)) { mx = om; idx = oi; }
+        }
+        float s = 0.f;
+        for (int j = lane; j < p.n_tiles; j += 32) {
+            const LogitPartial q = p.partials[grow * p.n_tiles + j];
+            s += q.sum * expf(q.mx - mx);
+        }
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float logp = -logf(s);                              // logit_max - logsumexp
+        const bool done = p.t > 1 && p.unf_count[(p.t - 1) * p.W + member] == 0;   // the reference broke out of the loop
+        int64_t it = 0;
+        if (!done) {
+            const bool prev = p.t == 1 ? true : (p.unfinished[grow] != 0);
+            const bool unf = prev && idx > 0;
+            it = unf ? idx : 0;
+            if (lane == 0) {
+                const int64_t o = (member * p.rows + r) * p.T + (p.t - 1);
+                p.seq[o] = it; p.lp[o] = logp;
+                p.unfinished[grow] = unf ? 1 : 0;
+                if (unf) atomicAdd(&p.unf_count[p.t * p.W + member], 1);
+            }
+        }
+        tok = it;
+        if (p.forced) tok = p.forced[(member * p.rows + r) * p.T + (p.t - 1)];
+    }
+    if (!p.gather) return;
+    const int par = p.parent ? p.parent[member] : 0;
+    const float* te = p.theta32 + (int64_t)par * p.D + p.emb_start + tok * p.E;
+    const __half* ee = p.table + p.off[member] + p.emb_pstart + tok * p.E;
+    for (int e = lane * 8; e < p.E; e += 256) {
+        const uint4 ev = *reinterpret_cast<const uint4*>(ee + e);
+        const __half* eh = reinterpret_cast<const __half*>(&ev);
+        __half hh[8], hl[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const float nz = __fmul_rn(p.sigma, __half2float(eh[u]));
+            const float x = sgn > 0.f ? __fadd_rn(te[e + u], nz) : __fsub_rn(te[e + u], nz);
+            split_half_dev(x, kActScale, hh[u], hl[u]);
+        }
+        *reinterpret_cast<uint4*>(p.x_hi + grow * p.E + e) = *reinterpret_cast<uint4*>(hh);
+        *reinterpret_cast<uint4*>(p.x_lo + grow * p.E + e) = *reinterpret_cast<uint4*>(hl);
+    }
+}
+
+struct LnParams {
+    const float *pre_i, *pre_h; float* c_state; __half *h_hi, *h_lo; float* h_trace;
+    int rows, rows_pad, R; int64_t n_members;
+    const int64_t* off; const float* sign; const int32_t* parent; const float* theta32; const __half* table; int64_t D;
+    int affine; int64_t ln_start[6], ln_pstart[6];     // i2h_ln.w, i2h_ln.b, h2h_ln.w, h2h_ln.b, c_ln.w, c_ln.b
+    float sigma;
+};
+__device__ __forceinline__ float block_sum_128(float v, float* sh) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    return sh[0] + sh[1] + sh[2] + sh[3];
+}
+__device__ __forceinline__ float member_param(const LnParams& p, int which, int par, int64_t off, float sgn, int j, float dflt) {
+    if (!p.affine) return dflt;
+    const float t = p.theta32[(int64_t)par * p.D + p.ln_start[which] + j];
+    const float nz = __fmul_rn(p.sigma, __half2float(p.table[off + p.ln_pstart[which] + j]));
+    return sgn > 0.f ? __fadd_rn(t, nz) : __fsub_rn(t, nz);
+}
+// LayerNorm variant of the cell (captioning/nets.py:102-104,126-127): LN over 5R of each addend, LN over R of c'.
+__global__ void __launch_bounds__(128) k_ln_gates(const LnParams p) {
+    __shared__ float sh[4];
+    extern __shared__ float s_sum[];                     // [5R] normalised sums, then [R] c'
+    const int64_t wid = blockIdx.x;
+    const int64_t member = wid / p.rows;
+    const int r = (int)(wid % p.rows);
+    const int64_t grow = member * p.rows_pad + r;
+    const int R = p.R, N = 5 * p.R;
+    const float sgn = p.sign[member];
+    const int64_t off = p.off[member];
+    const int par = p.parent ? p.parent[member] : 0;
+    const float* src[2] = {p.pre_i + grow * N, p.pre_h + grow * N};
+    for (int j = threadIdx.x; j < N; j += 128) s_sum[j] = 0.f;
+    for (int a = 0; a < 2; ++a) {
+        float s = 0.f;
+        for (int j = threadIdx.x; j < N; j += 128) s += src[a][j];
+        const float mean = block_sum_128(s, sh) / (float)N;
+        float v = 0.f;
+        for (int j = threadIdx.x; j < N; j += 128) { const float d = src[a][j] - mean; v += d * d; }
+        const float rstd = 1.0f / sqrtf(block_sum_128(v, sh) / (float)N + 1e-5f);
+        for (int j = threadIdx.x; j < N; j += 128) {
+            const float w = member_param(p, 2 * a, par, off, sgn, j, 1.f), b = member_param(p, 2 * a + 1, par, off, sgn, j, 0.f);
+            s_sum[j] += (src[a][j] - mean) * rstd * w + b;
+        }
+    }
+    __syncthreads();
+    float* cs = p.c_state + grow * R;
+    float* s_c = s_sum + N;
+    float cs_sum = 0.f;
+    for (int j = threadIdx.x; j < R; j += 128) {
+        const float ig = sigmoid_f(s_sum[j]), fg = sigmoid_f(s_sum[R + j]);
+        const float cand = fmaxf(s_sum[3 * R + j], s_sum[4 * R + j]);
+        const float cn = __fadd_rn(__fmul_rn(fg, cs[j]), __fmul_rn(ig, cand));
+        s_c[j] = cn; cs[j] = cn; cs_sum += cn;
+    }
+    const float mean = block_sum_128(cs_sum, sh) / (float)R;
+    float v = 0.f;
+    for (int j = threadIdx.x; j < R; j += 128) { const float d = s_c[j] - mean; v += d * d; }
+    const float rstd = 1.0f / sqrtf(block_sum_128(v, sh) / (float)R + 1e-5f);
+    for (int j = threadIdx.x; j < R; j += 128) {
+        const float w = member_param(p, 4, par, off, sgn, j, 1.f), b = member_param(p, 5, par, off, sgn, j, 0.f);
+        const float og = sigmoid_f(s_sum[2 * R + j]);
+        const float hn = og * tanhf((s_c[j] - mean) * rstd * w + b);
+        __half a, l; split_half_dev(hn, kActScale, a, l);
+        p.h_hi[grow * R + j] = a; p.h_lo[grow * R + j] = l;
+        if (p.h_trace) p.h_trace[(member * p.rows + r) * (int64_t)R + j] = hn;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_logprob_fitness(const float* __restrict__ lp, int64_t per_member, double* __restrict__ out) {
+    __shared__ double sh[8];
+    const float* src = lp + blockIdx.x * per_member;
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < per_member; i += 256) s += (double)src[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) { double a = 0; for (int q = 0; q < 8; ++q) a += sh[q]; out[blockIdx.x] = a; }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+template <typename T> static int dmalloc(T** p, int64_t n) {
+    NES_CUDA(cudaMalloc((void**)p, sizeof(T) * (size_t)(n > 0 ? n : 1)));
+    return 0;
+}
+
+int decode_create(Ctx* c, int wave_members, int rows) {
+    NES_CHECK(c->is_fc, "decode needs an fc_caption context");
+    NES_CHECK(wave_members >= 1 && rows >= 1, "wave_members and rows must be positive");
+    const nes_fc_dims& d = c->dims;
+    NES_CHECK(d.input_encoding_size % 64 == 0 && d.rnn_size % 64 == 0 && d.fc_feat_size % 64 == 0,
+              "input_encoding_size, rnn_size and fc_feat_size must be multiples of 64 (UMMA K block)");
+    DecodeWorkspace* ws = new DecodeWorkspace();
+    c->ws = ws;
+    ws->W = wave_members; ws->rows_cap = rows; ws->rows_pad = (rows + 127) / 128 * 128;
+    ws->E = d.input_encoding_size; ws->R = d.rnn_size; ws->Fd = d.fc_feat_size; ws->V1 = d.vocab_size + 1; ws->T = d.seq_length;
+    ws->nt_logit = (ws->V1 + 127) / 128;
+    const int64_t WR = (int64_t)ws->W * ws->rows_pad;
+    if (dmalloc(&ws->x_hi, WR * ws->E) || dmalloc(&ws->x_lo, WR * ws->E)) return 1;
+    for (int b = 0; b < 2; ++b) if (dmalloc(&ws->h_hi[b], WR * ws->R) || dmalloc(&ws->h_lo[b], WR * ws->R)) return 1;
+    if (dmalloc(&ws->c_state, WR * ws->R)) return 1;
+    if (dmalloc(&ws->partials, WR * ws->nt_logit)) return 1;
+    if (dmalloc(&ws->unfinished, WR) || dmalloc(&ws->unf_count, (int64_t)(ws->T + 2) * ws->W)) return 1;
+    if (d.layer_n) { if (dmalloc(&ws->pre_i, WR * 5 * ws->R) || dmalloc(&ws->pre_h, WR * 5 * ws->R)) return 1; }
+    // zero everything once: padding rows of the operand buffers must stay finite forever
+    NES_CUDA(cudaMemsetAsync(ws->x_hi, 0, sizeof(__half) * WR * ws->E, c->stream));
+    NES_CUDA(cudaMemsetAsync(ws->x_lo, 0, sizeof(__half) * WR * ws->E, c->stream));
+    for (int b = 0; b < 2; ++b) {
+        NES_CUDA(cudaMemsetAsync(ws->h_hi[b], 0, sizeof(__half) * WR * ws->R, c->stream));
+        NES_CUDA(cudaMemsetAsync(ws->h_lo[b], 0, sizeof(__half) * WR * ws->R, c->stream));
+    }
+    NES_CUDA(cudaMemsetAsync(ws->c_state, 0, sizeof(float) * WR * ws->R, c->stream));
+    return 0;
+}
+
+void decode_destroy(Ctx* c) {
+    DecodeWorkspace* ws = c->ws;
+    if (!ws) return;
+    void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
+                    ws->pre_i, ws->pre_h, ws->partials, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
+                    ws->d_lp, ws->d_forced};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    delete ws;
+    c->ws = nullptr;
+}
+
+template <int EPI, int PREC>
+static int launch_gemm(Ctx* c, const GemmParams& p, int64_t n_members) {
+    using C = GemmCfg<EPI, PREC>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        NES_CUDA(cudaFuncSetAttribute(k_member_gemm<EPI, PREC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        attr_done = true;
+    }
+    NES_CHECK(n_members % p.group == 0, "member count must be a multiple of the scheduling group");
+    const int64_t grid = n_members * p.m_tiles * p.n_tiles;
+    NES_CHECK(grid < (1ll << 31), "grid too large");
+    k_member_gemm<EPI, PREC><<<(unsigned)grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+template <int EPI>
+static int launch_gemm_prec(Ctx* c, const GemmParams& p, int64_t n_members, int prec) {
+    return prec == NES_PREC_EXACT ? launch_gemm<EPI, NES_PREC_EXACT>(c, p, n_members) : launch_gemm<EPI, NES_PREC_FAST>(c, p, n_members);
+}
+
+// fill one GEMM segment: activations A (hi/lo buffers with `a_rows` rows), weight tensor wt, bias tensor bt (-1 none)
+static int fill_seg(Ctx* c, GemmParams& p, int s, const __half* a_hi, const __half* a_lo, int64_t a_rows, int K, int a_shared,
+                    int wt, int bt, int box_rows) {
+    DecodeWorkspace* ws = c->ws;
+    const Layout& L = c->lay;
+    if (get_map(ws, &p.maps[s].a_hi, a_hi, a_rows, K, 128) || get_map(ws, &p.maps[s].a_lo, a_lo, a_rows, K, 128)) return 1;
+    const int64_t th_rows = (int64_t)c->n_parents * L.D_pad / K;
+    if (get_map(ws, &p.maps[s].w_hi, c->theta_hi, th_rows, K, box_rows) || get_map(ws, &p.maps[s].w_lo, c->theta_lo, th_rows, K, box_rows)) return 1;
+    if (get_map(ws, &p.maps[s].eps, c->table, c->table_len / K, K, box_rows)) return 1;
+    p.seg[s].K = K; p.seg[s].a_shared = a_shared; p.seg[s].w_pstart = L.t[wt].pstart;
+    p.seg[s].b_start = bt >= 0 ? L.t[bt].start : -1;
+    p.seg[s].b_pstart = bt >= 0 ? L.t[bt].pstart : -1;
+    return 0;
+}
+
+static int ensure_call_buffers(Ctx* c, int64_t n_members, int rows, bool forced) {
+    DecodeWorkspace* ws = c->ws;
+    if (n_members > ws->cap_members) {
+        if (ws->d_off) { cudaFree(ws->d_off); cudaFree(ws->d_sign); cudaFree(ws->d_parent); }
+        if (dmalloc(&ws->d_off, n_members) || dmalloc(&ws->d_sign, n_members) || dmalloc(&ws->d_parent, n_members)) return 1;
+        ws->cap_members = n_members;
+    }
+    const int64_t out_n = n_members * rows * ws->T;
+    if (out_n > ws->out_cap) {
+        if (ws->d_seq) { cudaFree(ws->d_seq); cudaFree(ws->d_lp); }
+        if (dmalloc(&ws->d_seq, out_n) || dmalloc(&ws->d_lp, out_n)) return 1;
+        ws->out_cap = out_n;
+    }
+    if (forced && out_n > ws->forced_cap) {
+        if (ws->d_forced) cudaFree(ws->d_forced);
+        if (dmalloc(&ws->d_forced, out_n)) return 1;
+        ws->forced_cap = out_n;
+    }
+    return 0;
+}
+
+int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,
+                   const float* fc, int rows, int shared_batch, float sigma, int precision,
+                   const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace) {
+    DecodeWorkspace* ws = c->ws;
+    NES_CHECK(ws != nullptr, "context has no decode workspace");
+    NES_CHECK(rows >= 1 && rows <= ws->rows_cap, "rows exceeds the workspace capacity given to nes_ctx_create_fc");
+    NES_CHECK(precision == NES_PREC_FAST || precision == NES_PREC_EXACT, "unknown precision");
+    NES_CHECK(n_members >= 0, "negative member count");
+    const bool tracing = h_trace || logit_trace || forced;
+    NES_CHECK(!tracing || n_members <= ws->W, "trace mode handles a single wave");
+    if (n_members == 0) return 0;
+    const Layout& L = c->lay;
+    const int E = ws->E, R = ws->R, Fd = ws->Fd, V1 = ws->V1, T = ws->T;
+    const int rows_pad = (rows + 127) / 128 * 128, m_tiles = rows_pad / 128;
+    if (ensure_call_buffers(c, n_members, rows, forced != nullptr)) return 1;
+    NES_CUDA(cudaMemcpyAsync(ws->d_off, offsets, sizeof(int64_t) * n_members, cudaMemcpyDefault, c->stream));
+    NES_CUDA(cudaMemcpyAsync(ws->d_sign, signs, sizeof(float) * n_members, cudaMemcpyDefault, c->stream));
+    if (parents) NES_CUDA(cudaMemcpyAsync(ws->d_parent, parents, sizeof(int32_t) * n_members, cudaMemcpyDefault, c->stream));
+    else NES_CUDA(cudaMemsetAsync(ws->d_parent, 0, sizeof(int32_t) * n_members, c->stream));
+    if (forced) NES_CUDA(cudaMemcpyAsync(ws->d_forced, forced, sizeof(int64_t) * n_members * rows * T, cudaMemcpyDefault, c->stream));
+    NES_CUDA(cudaMemsetAsync(ws->d_seq, 0, sizeof(int64_t) * n_members * rows * T, c->stream));
+    NES_CUDA(cudaMemsetAsync(ws->d_lp, 0, sizeof(float) * n_members * rows * T, c->stream));
+
+    // fc features -> split fp16 operand
+    const int64_t fc_blocks = shared_batch ? 1 : n_members;
+    const int64_t fc_need = shared_batch ? 1 : ws->W;
+    if (fc_need > ws->fc_members || rows_pad > 0) {
+        if (fc_need > ws->fc_members) {
+            if (ws->fc32) { cudaFree(ws->fc32); cudaFree(ws->fc_hi); cudaFree(ws->fc_lo); }
+            if (dmalloc(&ws->fc32, fc_need * ws->rows_cap * Fd) || dmalloc(&ws->fc_hi, fc_need * ws->rows_pad * Fd) ||
+                dmalloc(&ws->fc_lo, fc_need * ws->rows_pad * Fd)) return 1;
+            ws->fc_members = fc_need;
+        }
+    }
+    if (c->rollout_timed) NES_CUDA(cudaEventRecord(c->ev_c, c->stream));
+
+    for (int64_t m0 = 0; m0 < n_members; m0 += ws->W) {
+        const int64_t nm = (n_members - m0) < ws->W ? (n_members - m0) : ws->W;
+        const int64_t WR = nm * rows_pad;
+        // ---- stage inputs / reset state
+        const int64_t nb = shared_batch ? 1 : nm;
+        if (!shared_batch || m0 == 0) {
+            const float* src = fc + (shared_batch ? 0 : m0 * rows * (int64_t)Fd);
+            NES_CUDA(cudaMemcpyAsync(ws->fc32, src, sizeof(float) * nb * rows * Fd, cudaMemcpyDefault, c->stream));
+            k_split_rows<<<148 * 4, 256, 0, c->stream>>>(ws->fc32, ws->fc_hi, ws->fc_lo, nb, rows, rows_pad, Fd);
+            c->launches++;
+            NES_CUDA(cudaGetLastError());
+        }
+        (void)fc_blocks;
+        NES_CUDA(cudaMemsetAsync(ws->c_state, 0, sizeof(float) * WR * R, c->stream));
+        NES_CUDA(cudaMemsetAsync(ws->h_hi[0], 0, sizeof(__half) * WR * R, c->stream));
+        NES_CUDA(cudaMemsetAsync(ws->h_lo[0], 0, sizeof(__half) * WR * R, c->stream));
+        NES_CUDA(cudaMemsetAsync(ws->unf_count, 0, sizeof(int32_t) * (T + 2) * ws->W, c->stream));
+
+        GemmParams base{};
+        base.rows = rows; base.rows_pad = rows_pad; base.m_tiles = m_tiles;
+        base.group = 1;
+        base.D = L.D; base.D_pad = L.D_pad;
+        base.off = ws->d_off + m0; base.sign = ws->d_sign + m0; base.parent = ws->d_parent + m0;
+        base.theta32 = c->theta32; base.table = c->table; base.sigma = sigma;
+        // antithetic pairs (+eps, -eps adjacent) share their eps tiles through L2 when scheduled together
+        if (nm % 2 == 0) base.group = 2;
+
+        const int64_t a_rows_w = (int64_t)ws->W * ws->rows_pad;
+        // ---- t = 0 : x0 = img_embed(fc)
+        {
+            GemmParams p = base;
+            p.nseg = 1; p.N = E; p.chunk_stride = 0; p.n_tiles = (E + 127) / 128;
+            if (fill_seg(c, p, 0, ws->fc_hi, ws->fc_lo, ws->fc_members * ws->rows_pad, Fd, shared_batch ? 1 : 0, T_IMG_W, T_IMG_B, 128)) return 1;
+            p.out_hi = ws->x_hi; p.out_lo = ws->x_lo;
+            if (launch_gemm_prec<EPI_PLAIN>(c, p, nm, precision)) return 1;
+        }
+        int hb = 0;   // h buffer holding the current state
+        for (int t = 0; t <= T; ++t) {
+            // ---- (h, c) = core(x_t, (h, c))
+            float* ht = h_trace ? h_trace + (int64_t)t * n_members * rows * R : nullptr;
+            if (!c->dims.layer_n) {
+                GemmParams p = base;
+                p.nseg = 2; p.N = R; p.chunk_stride = R; p.n_tiles = R / 16;
+                if (fill_seg(c, p, 0, ws->x_hi, ws->x_lo, a_rows_w, E, 0, T_I2H_W, T_I2H_B, 16)) return 1;
+                if (fill_seg(c, p, 1, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_H2H_W, T_H2H_B, 16)) return 1;
+                p.c_state = ws->c_state; p.out_hi = ws->h_hi[hb ^ 1]; p.out_lo = ws->h_lo[hb ^ 1]; p.h_trace = ht;
+                if (launch_gemm_prec<EPI_LSTM>(c, p, nm, precision)) return 1;
+            } else {
+                for (int s = 0; s < 2; ++s) {
+                    GemmParams p = base;
+                    p.nseg = 1; p.N = 5 * R; p.chunk_stride = 0; p.n_tiles = (5 * R + 127) / 128;
+                    if (s == 0) { if (fill_seg(c, p, 0, ws->x_hi, ws->x_lo, a_rows_w, E, 0, T_I2H_W, T_I2H_B, 128)) return 1; }
+                    else        { if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_H2H_W, T_H2H_B, 128)) return 1; }
+                    p.out_f32 = s == 0 ? ws->pre_i : ws->pre_h; p.ld_out = 5 * R;
+                    if (launch_gemm_prec<EPI_PLAIN>(c, p, nm, precision)) return 1;
+                }
+                LnParams q{};
+                q.pre_i = ws->pre_i; q.pre_h = ws->pre_h; q.c_state = ws->c_state; q.h_hi = ws->h_hi[hb ^ 1]; q.h_lo = ws->h_lo[hb ^ 1];
+                q.h_trace = ht; q.rows = rows; q.rows_pad = rows_pad; q.R = R; q.n_members = nm;
+                q.off = base.off; q.sign = base.sign; q.parent = base.parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D;
+                q.affine = c->dims.layer_n_affine; q.sigma = sigma;
+                if (q.affine) for (int i = 0; i < 6; ++i) { q.ln_start[i] = L.t[T_I2H_LN_W + i].start; q.ln_pstart[i] = L.t[T_I2H_LN_W + i].pstart; }
+                k_ln_gates<<<(unsigned)(nm * rows), 128, sizeof(float) * 6 * R, c->stream>>>(q);
+                c->launches++;
+                NES_CUDA(cudaGetLastError());
+            }
+            hb ^= 1;
+            // ---- logits of step t (t >= 1), argmax / log-prob, next input
+            if (t >= 1) {
+                GemmParams p = base;
+                p.nseg = 1; p.N = V1; p.chunk_stride = 0; p.n_tiles = ws->nt_logit;
+                if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128)) return 1;
+                p.partials = ws->partials;
+                p.logit_trace = logit_trace ? logit_trace + (int64_t)(t - 1) * n_members * rows * V1 : nullptr; p.ld_trace = V1;
+                if (launch_gemm_prec<EPI_LOGIT>(c, p, nm, precision)) return 1;
+            }
+            if (t < T || t >= 1) {
+                FinalizeParams f{};
+                f.partials = ws->partials; f.n_tiles = ws->nt_logit; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
+                f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table;
+                f.D = L.D; f.emb_start = L.t[T_EMB_W].start; f.emb_pstart = L.t[T_EMB_W].pstart; f.sigma = sigma;
+                f.unfinished = ws->unfinished; f.unf_count = ws->unf_count; f.W = ws->W;
+                f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;
+                f.forced = forced ? ws->d_forced + m0 * rows * T : nullptr;
+                f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0;
+                k_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(f);
+                c->launches++;
+                NES_CUDA(cudaGetLastError());
+            }
+        }
+    }
+    if (c->rollout_timed) NES_CUDA(cudaEventRecord(c->ev_d, c->stream));
+    if (seq)  NES_CUDA(cudaMemcpyAsync(seq, ws->d_seq, sizeof(int64_t) * n_members * rows * T, cudaMemcpyDefault, c->stream));
+    if (logp) NES_CUDA(cudaMemcpyAsync(logp, ws->d_lp, sizeof(float) * n_members * rows * T, cudaMemcpyDefault, c->stream));
+    return 0;
+}
+
+int decode_logprob_fitness(Ctx* c, int64_t n_members, int rows, double* out) {
+    DecodeWorkspace* ws = c->ws;
+    NES_CHECK(ws && ws->d_lp && n_members * rows * ws->T <= ws->out_cap, "no rollout results resident for that many members");
+    if (n_members == 0) return 0;
+    if (ensure_small(c, n_members)) return 1;
+    k_logprob_fitness<<<(unsigned)n_members, 256, 0, c->stream>>>(ws->d_lp, (int64_t)rows * ws->T, c->d_fitness);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    NES_CUDA(cudaMemcpyAsync(out, c->d_fitness, sizeof(double) * n_members, cudaMemcpyDefault, c->stream));
+    return 0;
+}
+
+}  // namespace nes
+
+// ---------------------------------------------------------------------------------------------
+// standalone self test of the tcgen05/TMA pipeline (PLAIN epilogue, one pseudo member)
+namespace nes {
+__global__ void k_split_scaled(const float* __restrict__ src, __half* __restrict__ hi, __half* __restrict__ lo, int64_t n, int64_t n_pad, float scale) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pad; i += (int64_t)gridDim.x * blockDim.x) {
+        __half a = __float2half_rn(0.f), l = a;
+        if (i < n && src) {
+            if (lo) split_half_dev(src[i], scale, a, l); else a = __float2half_rn(src[i] * scale);
+        }
+        hi[i] = a; if (lo) lo[i] = l;
+    }
+}
+}  // namespace nes
+
+extern "C" int nes_gemm_selftest(int device, int M, int N, int K, const float* A, const float* W, const float* E, float sigma,
+                                 int precision, float* Cout) {
+    using namespace nes;
+    NES_CHECK(M >= 1 && N >= 1 && K >= 64 && K % 64 == 0, "selftest: need M,N >= 1 and K a multiple of 64");
+    NES_CHECK(A && W && Cout, "selftest: null argument");
+    NES_CUDA(cudaSetDevice(device));
+    const int64_t Mp = (M + 127) / 128 * 128, Np = (N + 127) / 128 * 128;
+    float *dA = nullptr, *dW = nullptr, *dE = nullptr, *dC = nullptr;
+    __half *a_hi, *a_lo, *w_hi, *w_lo, *e16;
+    int64_t* d_off; float* d_sign;
+    NES_CUDA(cudaMalloc((void**)&dA, sizeof(float) * M * K)); NES_CUDA(cudaMalloc((void**)&dW, sizeof(float) * N * K));
+    NES_CUDA(cudaMalloc((void**)&dC, sizeof(float) * M * N));
+    NES_CUDA(cudaMemcpy(dA, A, sizeof(float) * M * K, cudaMemcpyDefault)); NES_CUDA(cudaMemcpy(dW, W, sizeof(float) * N * K, cudaMemcpyDefault));
+    if (E) { NES_CUDA(cudaMalloc((void**)&dE, sizeof(float) * N * K)); NES_CUDA(cudaMemcpy(dE, E, sizeof(float) * N * K, cudaMemcpyDefault)); }
+    NES_CUDA(cudaMalloc((void**)&a_hi, 2 * Mp * K)); NES_CUDA(cudaMalloc((void**)&a_lo, 2 * Mp * K));
+    NES_CUDA(cudaMalloc((void**)&w_hi, 2 * Np * K)); NES_CUDA(cudaMalloc((void**)&w_lo, 2 * Np * K)); NES_CUDA(cudaMalloc((void**)&e16, 2 * Np * K));
+    NES_CUDA(cudaMalloc((void**)&d_off, 8)); NES_CUDA(cudaMalloc((void**)&d_sign, 4));
+    const int64_t zero = 0; const float one = 1.f;
+    NES_CUDA(cudaMemcpy(d_off, &zero, 8, cudaMemcpyHostToDevice)); NES_CUDA(cudaMemcpy(d_sign, &one, 4, cudaMemcpyHostToDevice));
+    k_split_scaled<<<256, 256>>>(dA, a_hi, a_lo, (int64_t)M * K, Mp * K, kActScale);
+    k_split_scaled<<<256, 256>>>(dW, w_hi, w_lo, (int64_t)N * K, Np * K, kThetaScale);
+    k_split_scaled<<<256, 256>>>(dE, e16, nullptr, (int64_t)N * K, Np * K, 1.0f);
+    NES_CUDA(cudaGetLastError());
+    GemmParams p{};
+    if (make_map(&p.maps[0].a_hi, a_hi, Mp, K, 128) || make_map(&p.maps[0].a_lo, a_lo, Mp, K, 128) || make_map(&p.maps[0].w_hi, w_hi, Np, K, 128) ||
+        make_map(&p.maps[0].w_lo, w_lo, Np, K, 128) || make_map(&p.maps[0].eps, e16, Np, K, 128)) return 1;
+    p.maps[1] = p.maps[0];
+    p.nseg = 1; p.seg[0].K = K; p.seg[0].a_shared = 0; p.seg[0].w_pstart = 0; p.seg[0].b_start = -1; p.seg[0].b_pstart = -1;
+    p.rows = M; p.rows_pad = (int)Mp; p.m_tiles = (int)(Mp / 128); p.n_tiles = (int)(Np / 128); p.group = 1; p.N = N; p.chunk_stride = 0;
+    p.D = 0; p.D_pad = 0; p.off = d_off; p.sign = d_sign; p.parent = nullptr; p.theta32 = nullptr; p.table = nullptr; p.sigma = sigma;
+    p.out_f32 = dC; p.ld_out = N;
+    Ctx tmp; tmp.stream = 0;
+    int rc = launch_gemm_prec<EPI_PLAIN>(&tmp, p, 1, precision);
+    if (!rc) { NES_CUDA(cudaDeviceSynchronize()); NES_CUDA(cudaMemcpy(Cout, dC, sizeof(float) * M * N, cudaMemcpyDefault)); }
+    void* ptrs[] = {dA, dW, dE, dC, a_hi, a_lo, w_hi, w_lo, e16, d_off, d_sign};
+    for (void* q : ptrs) if (q) cudaFree(q);
+    return rc;
+}

@@ -1,0 +1,246 @@
+// K6 (ranks / centred-rank weights), K7 (fitness-weighted reduction over noise-table rows),
+// K8 (fused L2 + SGD/Adam update).  Reference: algorithm/nic_nes/nic_nes_master.py:123-136,170-221
+// and algorithm/nic_nes/optimizers.py:15-22,44-47,78-83.
+#include "common.cuh"
+
+namespace nes {
+
+// ---- K6 -----------------------------------------------------------------------------------------
+// rank[i] = #{j : x[j] < x[i]} + #{j < i : x[j] == x[i]}   (== stable argsort ranks; the reference's
+// default argsort leaves tie order unspecified).  O(n^2) compares, n = 2F <= ~40k.
+__global__ void __launch_bounds__(256) k_ranks(const double* __restrict__ x, int64_t n, int64_t* __restrict__ ranks) {
+    __shared__ double tile[1024];
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const double xi = i < n ? x[i] : 0.0;
+    int64_t cnt = 0;
+    for (int64_t base = 0; base < n; base += 1024) {
+        const int m = (int)((n - base) < 1024 ? (n - base) : 1024);
+        __syncthreads();
+        for (int t = threadIdx.x; t < m; t += blockDim.x) tile[t] = x[base + t];
+        __syncthreads();
+        if (i < n) {
+#pragma unroll 8
+            for (int t = 0; t < m; ++t) {
+                const double xj = tile[t];
+                cnt += (xj < xi) || (xj == xi && (base + t) < i);
+            }
+        }
+    }
+    if (i < n) ranks[i] = cnt;
+}
+// centred = rank/(2F-1) - 0.5 (float64, same operation order as nic_nes_master.py:191-193);
+// w_i = centred[i,0] - centred[i,1] (:179), cast to float32 where the reference does (:219)
+__global__ void k_rank_weights(const int64_t* __restrict__ ranks, int64_t F, double* __restrict__ centered, float* __restrict__ w) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= F) return;
+    const double denom = (double)(2 * F - 1);
+    const double a = __dsub_rn(__ddiv_rn((double)ranks[2 * i], denom), 0.5);
+    const double b = __dsub_rn(__ddiv_rn((double)ranks[2 * i + 1], denom), 0.5);
+    if (centered) { centered[2 * i] = a; centered[2 * i + 1] = b; }
+    if (w) w[i] = (float)__dsub_rn(a, b);
+}
+
+int launch_ranks(Ctx* c, const double* d_x, int64_t n, int64_t* d_ranks) {
+    if (n == 0) return 0;
+    k_ranks<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(d_x, n, d_ranks);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+int launch_rank_weights(Ctx* c, const double* d_fit, int64_t F, double* d_centered, float* d_w) {
+    if (F == 0) return 0;
+    if (launch_ranks(c, d_fit, 2 * F, c->d_ranks)) return 1;
+    k_rank_weights<<<(unsigned)((F + 255) / 256), 256, 0, c->stream>>>(c->d_ranks, F, d_centered, d_w);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- K7 -----------------------------------------------------------------------------------------
+// g[p] = f32(sigma) * (sum_i w_i * eps_i[p]) / (2F), eps_i = table[off_i + pstart_k + (p - start_k)].
+// HBM-bound: reads F * D * 2 bytes (fp16 table) once, writes 4*D.  One thread owns 8 consecutive
+// elements (one 128-bit load per row); the row loop is unrolled so 8 independent loads are in flight.
+struct GradPlan { int n; int64_t vec_prefix[kMaxTensors + 1]; };
+
+__device__ __forceinline__ uint4 ld_stream_128(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void fma8(float (&acc)[8], const uint4& v, float w) {
+    const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        float2 f = __half22float2(h[e]);
+        acc[2 * e]     = fmaf(w, f.x, acc[2 * e]);
+        acc[2 * e + 1] = fmaf(w, f.y, acc[2 * e + 1]);
+    }
+}
+
+constexpr int kGradChunk = 512;
+template <int UNROLL>
+__global__ void __launch_bounds__(256) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
+                                                  const float* __restrict__ w, int64_t F, GradPlan plan,
+                                                  const Layout* __restrict__ lay, float sigma, float* __restrict__ g) {
+    __shared__ int64_t s_off[kGradChunk];
+    __shared__ float s_w[kGradChunk];
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = v < plan.vec_prefix[plan.n];
+    int k = 0;
+    if (active) { while (v >= plan.vec_prefix[k + 1]) ++k; }
+    const TensorDesc t = lay->t[k];
+    const int64_t j0 = active ? (v - plan.vec_prefix[k]) * 8 : 0;
+    const __half* base = table + t.pstart + j0;
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+
+    for (int64_t c0 = 0; c0 < F; c0 += kGradChunk) {
+        const int m = (int)((F - c0) < kGradChunk ? (F - c0) : kGradChunk);
+        __syncthreads();
+        for (int i = threadIdx.x; i < m; i += blockDim.x) { s_off[i] = off[c0 + i]; s_w[i] = w[c0 + i]; }
+        __syncthreads();
+        if (active) {
+            int i = 0;
+            for (; i + UNROLL <= m; i += UNROLL) {
+                uint4 buf[UNROLL];
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u) buf[u] = ld_stream_128(base + s_off[i + u]);
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u) fma8(acc, buf[u], s_w[i + u]);
+            }
+            for (; i < m; ++i) { uint4 b = ld_stream_128(base + s_off[i]); fma8(acc, b, s_w[i]); }
+        }
+    }
+    if (active) {
+        const float denom = (float)(2 * F);
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+            if (j0 + e < t.count) g[t.start + j0 + e] = __fdiv_rn(__fmul_rn(sigma, acc[e]), denom);
+    }
+}
+
+int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g) {
+    GradPlan plan; plan.n = c->lay.n; plan.vec_prefix[0] = 0;
+    for (int k = 0; k < c->lay.n; ++k) plan.vec_prefix[k + 1] = plan.vec_prefix[k] + (c->lay.t[k].count + 7) / 8;
+    const int64_t total = plan.vec_prefix[plan.n];
+    if (F == 0) { NES_CUDA(cudaMemsetAsync(d_g, 0, sizeof(float) * c->lay.D, c->stream)); return 0; }
+    unsigned grid = (unsigned)((total + 255) / 256);
+    if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_a, c->stream));
+    k_gradient<8><<<grid, 256, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g);
+    if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_b, c->stream));
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- K8 -----------------------------------------------------------------------------------------
+// One pass: G = -g + l2*theta ; Adam / SGD-momentum step in float64 with the reference's operation
+// order (no FMA contraction) ; theta64' = theta64 + step ; theta32' = f32(theta64') ; partial sums of
+// |step|^2 and |theta|^2 for Optimizer.update's ratio (optimizers.py:19).
+// GMODE says where G comes from and which dtype it has IN THE REFERENCE, because numpy keeps
+// (1-beta)*G and G*G in float32 when G is a float32 array (python-scalar * float32 array):
+//   0 fused, theta has float64 provenance: G = -(double)g + l2*theta               (float64; iterations >= 2)
+//   1 fused, theta has float32 provenance: G = f32(-g + f32(l2)*f32(theta))        (float32; first iteration)
+//   2 direct float32 G (Optimizer.update(globalg) with a float32 array)
+//   3 direct float64 G
+template <int KIND, int GMODE>
+__global__ void __launch_bounds__(256) k_opt_update(const float* __restrict__ g, const double* __restrict__ G64,
+                                                    double* __restrict__ t64, float* __restrict__ t32,
+                                                    double* __restrict__ m, double* __restrict__ v, int64_t D, double l2,
+                                                    double a_or_lr, double b1, double b2, double eps,
+                                                    double* __restrict__ partials) {
+    double s_step = 0.0, s_theta = 0.0;
+    const float l2f = (float)l2;
+    const double omb1 = 1.0 - b1, omb2 = 1.0 - b2;
+    const float omb1f = (float)omb1, omb2f = (float)omb2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += (int64_t)gridDim.x * blockDim.x) {
+        const double th = t64[i];
+        double G, gm, gv;       // G, (1-b1)*G, (1-b2)*G*G  with the reference's dtypes
+        if (GMODE == 1 || GMODE == 2) {
+            const float Gf = (GMODE == 1) ? __fadd_rn(-g[i], __fmul_rn(l2f, (float)th)) : g[i];
+            G = (double)Gf;
+            gm = (double)__fmul_rn(omb1f, Gf);
+            gv = (double)__fmul_rn(omb2f, __fmul_rn(Gf, Gf));
+        } else {
+            G = (GMODE == 0) ? __dadd_rn(-(double)g[i], __dmul_rn(l2, th)) : G64[i];
+            gm = __dmul_rn(omb1, G);
+            gv = __dmul_rn(omb2, __dmul_rn(G, G));
+        }
+        double step;
+        if (KIND == NES_OPT_ADAM) {
+            const double mi = __dadd_rn(__dmul_rn(b1, m[i]), gm);
+            const double vi = __dadd_rn(__dmul_rn(b2, v[i]), gv);
+            m[i] = mi; v[i] = vi;
+            step = __ddiv_rn(__dmul_rn(-a_or_lr, mi), __dadd_rn(__dsqrt_rn(vi), eps));
+        } else {
+            const double vi = __dadd_rn(__dmul_rn(b1, v[i]), gm);
+            v[i] = vi;
+            step = __dmul_rn(-a_or_lr, vi);
+        }
+        const double nt = __dadd_rn(th, step);
+        t64[i] = nt;
+        t32[i] = (float)nt;
+        s_step = fma(step, step, s_step);
+        s_theta = fma(th, th, s_theta);
+    }
+    __shared__ double sh[2][8];
+    for (int o = 16; o > 0; o >>= 1) {
+        s_step += __shfl_xor_sync(0xffffffffu, s_step, o);
+        s_theta += __shfl_xor_sync(0xffffffffu, s_theta, o);
+    }
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sh[0][wid] = s_step; sh[1][wid] = s_theta; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0, b = 0;
+        for (int q = 0; q < 8; ++q) { a += sh[0][q]; b += sh[1][q]; }
+        partials[2 * blockIdx.x] = a; partials[2 * blockIdx.x + 1] = b;
+    }
+}
+__global__ void k_norm_finalize(const double* __restrict__ partials, int nblocks, double* __restrict__ norms) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        double a = 0, b = 0;
+        for (int q = 0; q < nblocks; ++q) { a += partials[2 * q]; b += partials[2 * q + 1]; }
+        norms[0] = sqrt(a); norms[1] = sqrt(b);
+    }
+}
+
+template <int KIND>
+static void opt_dispatch(Ctx* c, int gmode, const float* d_g, const double* d_G64, double l2, double a_or_lr) {
+    const int grid = c->norm_blocks;
+#define NES_OPT_LAUNCH(GM) k_opt_update<KIND, GM><<<grid, 256, 0, c->stream>>>(d_g, d_G64, c->theta64, c->theta32, c->opt_m, c->opt_v, \
+        c->lay.D, l2, a_or_lr, c->opt_b1, c->opt_b2, c->opt_eps, c->d_norm_partials)
+    switch (gmode) { case 0: NES_OPT_LAUNCH(0); break; case 1: NES_OPT_LAUNCH(1); break; case 2: NES_OPT_LAUNCH(2); break; default: NES_OPT_LAUNCH(3); }
+#undef NES_OPT_LAUNCH
+}
+
+// direct: 0 = fused from the gradient estimate g (nic_nes_master.py:123-133), 1 = d_g IS globalg (float32), 2 = d_G64 is globalg (float64)
+int launch_opt_update(Ctx* c, const float* d_g, const double* d_G64, int direct, double l2, double* ratio_out) {
+    NES_CHECK(c->opt_kind == NES_OPT_ADAM || c->opt_kind == NES_OPT_SGD, "nes_opt_init has not been called");
+    c->opt_t += 1;
+    const int gmode = direct == 0 ? (c->theta_is_f32[0] ? 1 : 0) : (direct == 1 ? 2 : 3);
+    if (c->opt_kind == NES_OPT_ADAM) {
+        const double t = (double)c->opt_t;
+        const double a = c->opt_stepsize * sqrt(1.0 - pow(c->opt_b2, t)) / (1.0 - pow(c->opt_b1, t));
+        opt_dispatch<NES_OPT_ADAM>(c, gmode, d_g, d_G64, l2, a);
+    } else {
+        opt_dispatch<NES_OPT_SGD>(c, gmode, d_g, d_G64, l2, c->opt_stepsize);
+    }
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    k_norm_finalize<<<1, 32, 0, c->stream>>>(c->d_norm_partials, c->norm_blocks, c->d_norms);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    c->theta_is_f32[0] = 0;
+    if (launch_theta_shadow(c, 0)) return 1;
+    if (ratio_out) {
+        double h[2];
+        NES_CUDA(cudaMemcpyAsync(h, c->d_norms, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+        NES_CUDA(cudaStreamSynchronize(c->stream));
+        *ratio_out = h[0] / h[1];
+    }
+    return 0;
+}
+
+}  // namespace nes

@@ -1,0 +1,168 @@
+// K1: shared noise table, offset / parent sampling, theta copies, member materialisation.
+//
+// The reference has no noise table: every worker draws torch.empty_like(theta).normal_(0, sigma)
+// (algorithm/nets.py:92-102) and ships the float32 vector through Redis
+// (nic_nes_worker.py:156-161).  Here eps lives once in HBM as an fp16 table addressed by an int64
+// offset; the specification is the header of oracle/noise.py and this file is its CUDA statement.
+#include "common.cuh"
+
+namespace nes {
+
+// ---- K1: table fill ---------------------------------------------------------------------------
+// one thread = one Philox block = 4 table elements (one 8-byte store).  Box-Muller in float64 so
+// the fp16 results equal the numpy restatement bit for bit.
+__global__ void __launch_bounds__(256) k_fill_table(__half* __restrict__ table, int64_t n_blocks, uint32_t k0, uint32_t k1) {
+    const double two_m32 = 2.3283064365386963e-10;           // 2^-32
+    const double two_pi  = 6.283185307179586;                // float64(2*pi), as (2.0*math.pi) in the spec
+    for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < n_blocks; b += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t r[4];
+        philox4x32_10((uint32_t)b, (uint32_t)((uint64_t)b >> 32), 0u, 0u, k0, k1, r);
+        __half h[4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            double u1 = __dmul_rn(__dadd_rn((double)r[2 * j], 0.5), two_m32);
+            double u2 = __dmul_rn(__dadd_rn((double)r[2 * j + 1], 0.5), two_m32);
+            double rad = sqrt(__dmul_rn(-2.0, log(u1)));
+            double ang = __dmul_rn(two_pi, u2);
+            double s, c;
+            sincos(ang, &s, &c);
+            h[2 * j]     = __float2half_rn(__double2float_rn(__dmul_rn(rad, c)));
+            h[2 * j + 1] = __float2half_rn(__double2float_rn(__dmul_rn(rad, s)));
+        }
+        uint2 packed;
+        packed.x = (uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16);
+        packed.y = (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16);
+        *reinterpret_cast<uint2*>(table + 4 * b) = packed;
+    }
+}
+
+int launch_fill_table(Ctx* c) {
+    int64_t n_blocks = c->table_len / 4;
+    int grid = 148 * 16;
+    k_fill_table<<<grid, 256, 0, c->stream>>>(c->table, n_blocks, (uint32_t)c->seed, (uint32_t)(c->seed >> 32));
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- offsets / parents ------------------------------------------------------------------------
+__global__ void k_sample_offsets(int64_t* __restrict__ out, int64_t F, uint32_t it_lo, uint32_t it_hi,
+                                 uint32_t k0, uint32_t k1, uint64_t n_slots, int64_t G) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= F) return;
+    uint32_t r[4];
+    philox4x32_10((uint32_t)i, it_lo, it_hi, kOffsetDomain, k0, k1, r);
+    uint64_t slot = ((uint64_t)r[0] * n_slots) >> 32;
+    out[i] = (int64_t)slot * G;
+}
+__global__ void k_sample_parents(int32_t* __restrict__ out, int64_t F, uint32_t it_lo, uint32_t it_hi,
+                                 uint32_t k0, uint32_t k1, uint32_t n_parents) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= F) return;
+    uint32_t r[4];
+    philox4x32_10((uint32_t)i, it_lo, it_hi, kParentDomain, k0, k1, r);
+    out[i] = (int32_t)(((uint64_t)r[0] * n_parents) >> 32);
+}
+
+int launch_sample_offsets(Ctx* c, uint64_t iteration, int64_t F, int64_t* d_out) {
+    if (F == 0) return 0;
+    int64_t n_slots = (c->table_len - c->lay.D_pad) / c->lay.G + 1;
+    NES_CHECK(n_slots >= 1 && n_slots < (1ll << 32), "noise table too small (or too large) for this layout");
+    k_sample_offsets<<<(unsigned)((F + 255) / 256), 256, 0, c->stream>>>(d_out, F, (uint32_t)iteration, (uint32_t)(iteration >> 32),
+                                                                       (uint32_t)c->seed, (uint32_t)(c->seed >> 32), (uint64_t)n_slots, c->lay.G);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+int launch_sample_parents(Ctx* c, uint64_t iteration, int64_t F, int32_t n_parents, int32_t* d_out) {
+    if (F == 0) return 0;
+    NES_CHECK(n_parents >= 1, "n_parents must be >= 1");
+    k_sample_parents<<<(unsigned)((F + 255) / 256), 256, 0, c->stream>>>(d_out, F, (uint32_t)iteration, (uint32_t)(iteration >> 32),
+                                                                       (uint32_t)c->seed, (uint32_t)(c->seed >> 32), (uint32_t)n_parents);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- theta copies -----------------------------------------------------------------------------
+// split x*scale into fp16 hi + lo (hi = rn(x*scale), lo = rn(x*scale - hi))
+__device__ __forceinline__ void split_half(float x, float scale, __half& hi, __half& lo) {
+    float xs = x * scale;
+    hi = __float2half_rn(xs);
+    lo = __float2half_rn(xs - __half2float(hi));
+}
+
+// theta32 [D] (flat) -> theta_hi / theta_lo [D_pad] (padded layout, zero in the padding)
+__global__ void __launch_bounds__(256) k_theta_shadow(const float* __restrict__ th, __half* __restrict__ hi, __half* __restrict__ lo,
+                                                      const Layout* __restrict__ lay) {
+    const int k = blockIdx.y;
+    const TensorDesc t = lay->t[k];
+    const int64_t pend = (k + 1 < lay->n) ? lay->t[k + 1].pstart : lay->D_pad;
+    const int64_t span = pend - t.pstart;
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < span; j += (int64_t)gridDim.x * blockDim.x) {
+        __half a = __float2half_rn(0.f), b = a;
+        if (j < t.count) split_half(th[t.start + j], kThetaScale, a, b);
+        hi[t.pstart + j] = a;
+        lo[t.pstart + j] = b;
+    }
+}
+int launch_theta_shadow(Ctx* c, int parent) {
+    dim3 grid(148 * 2, c->lay.n);
+    k_theta_shadow<<<grid, 256, 0, c->stream>>>(c->theta32 + (int64_t)parent * c->lay.D,
+                                                c->theta_hi + (int64_t)parent * c->lay.D_pad,
+                                                c->theta_lo + (int64_t)parent * c->lay.D_pad, c->d_lay);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_set_theta(const T* __restrict__ src, double* __restrict__ t64, float* __restrict__ t32, int64_t D) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += (int64_t)gridDim.x * blockDim.x) {
+        T v = src[i];
+        t64[i] = (double)v;
+        t32[i] = (float)v;
+    }
+}
+int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64) {
+    const int64_t D = c->lay.D;
+    int grid = (int)((D + 255) / 256 < 148 * 8 ? (D + 255) / 256 : 148 * 8);
+    if (grid < 1) grid = 1;
+    if (is_f64) k_set_theta<double><<<grid, 256, 0, c->stream>>>((const double*)d_src, c->theta64 + parent * D, c->theta32 + parent * D, D);
+    else        k_set_theta<float><<<grid, 256, 0, c->stream>>>((const float*)d_src, c->theta64 + parent * D, c->theta32 + parent * D, D);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    c->theta_is_f32[parent] = is_f64 ? 0 : 1;
+    return launch_theta_shadow(c, parent);
+}
+
+// ---- member materialisation: PolicyNet.evolve (algorithm/nets.py:101-119) ----------------------
+// noise = f32(sigma) * f32(eps) ; member = theta + noise  (sign<0: theta - noise, nic_nes_worker.py:151)
+__global__ void __launch_bounds__(256) k_evolve(const float* __restrict__ th, const __half* __restrict__ row, const Layout* __restrict__ lay,
+                                                float sign, float sigma, float* __restrict__ member, float* __restrict__ noise,
+                                                double* __restrict__ dst64, float* __restrict__ dst32) {
+    const TensorDesc t = lay->t[blockIdx.y];
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < t.count; j += (int64_t)gridDim.x * blockDim.x) {
+        float nz = __fmul_rn(sigma, __half2float(row[t.pstart + j]));
+        float th0 = th[t.start + j];
+        float m = sign > 0.f ? __fadd_rn(th0, nz) : __fsub_rn(th0, nz);
+        if (noise)  noise[t.start + j] = nz;
+        if (member) member[t.start + j] = m;
+        if (dst32) { dst32[t.start + j] = m; dst64[t.start + j] = (double)m; }
+    }
+}
+int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, float* d_member, float* d_noise, int dst_parent) {
+    const int64_t D = c->lay.D;
+    NES_CHECK(offset >= 0 && offset + c->lay.D_pad <= c->table_len && offset % c->lay.G == 0, "offset outside the noise table or not slot aligned");
+    NES_CHECK(dst_parent != parent, "dst_parent must differ from the source parent");
+    dim3 grid(148 * 2, c->lay.n);
+    k_evolve<<<grid, 256, 0, c->stream>>>(c->theta32 + parent * D, c->table + offset, c->d_lay, sign, sigma, d_member, d_noise,
+                                          dst_parent >= 0 ? c->theta64 + dst_parent * D : nullptr,
+                                          dst_parent >= 0 ? c->theta32 + dst_parent * D : nullptr);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    if (dst_parent >= 0) { c->theta_is_f32[dst_parent] = 1; return launch_theta_shadow(c, dst_parent); }
+    return 0;
+}
+
+}  // namespace nes

@@ -1,0 +1,42 @@
+"""Flat-theta layout of the fc_caption model and the padded noise-row layout (product-side statement of
+the spec in DESIGN.md; the C library computes the same thing internally and tests compare the two).
+
+Parameter order = FCModel.named_parameters() of the reference (src/captioning/nets.py:150-153, LSTMCore
+:81-96): img_embed, embed, logit, core.i2h, core.h2h [, core.i2h_ln, core.h2h_ln, core.c_ln]."""
+import math
+from collections import namedtuple
+
+import numpy as np
+
+TensorSpec = namedtuple('TensorSpec', ['name', 'shape', 'start', 'count', 'pstart'])
+
+
+def fc_tensors(vocab_size, input_encoding_size, rnn_size, fc_feat_size, layer_n=False, layer_n_affine=False):
+    V1, E, R, Fd = vocab_size + 1, input_encoding_size, rnn_size, fc_feat_size
+    t = [('img_embed.weight', (E, Fd)), ('img_embed.bias', (E,)), ('embed.weight', (V1, E)),
+         ('logit.weight', (V1, R)), ('logit.bias', (V1,)),
+         ('core.i2h.weight', (5 * R, E)), ('core.i2h.bias', (5 * R,)),
+         ('core.h2h.weight', (5 * R, R)), ('core.h2h.bias', (5 * R,))]
+    if layer_n and layer_n_affine:
+        t += [('core.i2h_ln.weight', (5 * R,)), ('core.i2h_ln.bias', (5 * R,)),
+              ('core.h2h_ln.weight', (5 * R,)), ('core.h2h_ln.bias', (5 * R,)),
+              ('core.c_ln.weight', (R,)), ('core.c_ln.bias', (R,))]
+    return t
+
+
+def granule(input_encoding_size, rnn_size, fc_feat_size):
+    g = 1
+    for x in (fc_feat_size, input_encoding_size, rnn_size):
+        g = g * x // math.gcd(g, x)
+    return g
+
+
+def build_layout(tensors, G):
+    """tensors: [(name, shape)] -> ([TensorSpec], D, D_pad)"""
+    out, pos, p = [], 0, 0
+    for name, shape in tensors:
+        cnt = int(np.prod(shape))
+        out.append(TensorSpec(name, tuple(shape), pos, cnt, p))
+        pos += cnt
+        p = -(-(p + cnt) // G) * G
+    return out, pos, p

@@ -1,0 +1,154 @@
+"""Master-side math with the reference's interface: NESMaster.gradient_estimate /
+compute_centered_ranks / compute_ranks (src/algorithm/nic_nes/nic_nes_master.py:170-205), the
+SGD / Adam optimizers (src/algorithm/nic_nes/optimizers.py) and one whole NIC-NES iteration
+(run_master :120-137 + NESWorker.fitness nic_nes_worker.py:131-154) as an in-process, population-
+sharded step: every rank evaluates its slice of antithetic pairs, fitness scalars are all-gathered
+(NCCL on GPUs; gloo in the CPU tests of the sharding logic), and every rank applies the identical update.
+"""
+import numpy as np
+import torch
+
+from .context import NesContext, OPT_ADAM, OPT_SGD, PREC_EXACT
+
+
+class NESMaster:
+    """Only the math of the reference's NESMaster; the Redis loop around it is out of scope."""
+
+    def __init__(self, ctx: NesContext):
+        self.ctx = ctx
+
+    def compute_ranks(self, x):
+        x = np.asarray(x)
+        assert x.ndim == 1
+        return self.ctx.compute_ranks(x.astype(np.float64)).numpy()
+
+    def compute_centered_ranks(self, x):
+        x = np.asarray(x, dtype=np.float64)
+        assert x.ndim == 2 and x.shape[1] == 2
+        cen, _ = self.ctx.rank_weights(x)
+        return cen.numpy()
+
+    def gradient_estimate(self, fitnesses, offsets, sigma):
+        """fitnesses float64 [F, 2]; offsets int64 [F] name the noise-table rows that the reference
+        would have shipped as noise_vecs [F, D] (nic_nes/iteration.py:69-70)."""
+        _, w = self.ctx.rank_weights(np.asarray(fitnesses, dtype=np.float64), want_centered=False)
+        return self.ctx.gradient(offsets, w, sigma).numpy()
+
+
+class Optimizer:
+    """theta lives in the context (float64 master copy + float32 / split-fp16 evaluation copies)."""
+    KIND = None
+
+    def __init__(self, ctx: NesContext, theta=None):
+        self.ctx = ctx
+        if theta is not None:
+            ctx.set_theta(theta)
+        self.dim = ctx.D
+        self.t = 0
+
+    def update(self, globalg):
+        """-> (ratio, new_theta float64 numpy) like optimizers.py:15-22"""
+        self.t += 1
+        ratio = self.ctx.opt_update_direct(globalg)
+        return ratio, self.ctx.get_theta(dtype=torch.float64).numpy()
+
+    def step(self, grad_estimate=None, l2coeff=0.0, fetch=False):
+        """G = -grad_estimate + l2coeff*theta fused with the update (nic_nes_master.py:123-133);
+        grad_estimate None = the gradient resident from the last gradient() call."""
+        self.t += 1
+        ratio = self.ctx.opt_update(grad_estimate, l2coeff)
+        return (ratio, self.ctx.get_theta(dtype=torch.float64).numpy()) if fetch else ratio
+
+    @property
+    def stepsize(self):
+        return self._stepsize
+
+    @stepsize.setter
+    def stepsize(self, v):
+        self._stepsize = float(v)
+        self.ctx.opt_set_stepsize(self._stepsize)
+
+
+class SGD(Optimizer):
+    KIND = OPT_SGD
+
+    def __init__(self, ctx, theta=None, stepsize=0.01, momentum=0.9):
+        super().__init__(ctx, theta)
+        self.momentum = momentum
+        ctx.opt_init(OPT_SGD, stepsize, momentum)
+        self._stepsize = float(stepsize)
+
+    def save_to_file(self, path):
+        _, v, t = self.ctx.opt_get_state()
+        torch.save({'dim': self.dim, 't': t, 'momentum': self.momentum, 'stepsize': self.stepsize, 'v': v.numpy()}, path)
+
+    def load_from_file(self, path):
+        s = torch.load(path, map_location='cpu', weights_only=False)
+        self.dim, self.t, self.momentum = s['dim'], s['t'], s['momentum']
+        self.ctx.opt_init(OPT_SGD, s['stepsize'], self.momentum)
+        self._stepsize = float(s['stepsize'])
+        self.ctx.opt_set_state(None, np.asarray(s['v'], dtype=np.float64), self.t)
+
+
+class Adam(Optimizer):
+    KIND = OPT_ADAM
+
+    def __init__(self, ctx, theta=None, stepsize=0.001, beta1=0.9, beta2=0.999, epsilon=1e-08):
+        super().__init__(ctx, theta)
+        self.beta1, self.beta2, self.epsilon = beta1, beta2, epsilon
+        ctx.opt_init(OPT_ADAM, stepsize, beta1, beta2, epsilon)
+        self._stepsize = float(stepsize)
+
+    def save_to_file(self, path):
+        m, v, t = self.ctx.opt_get_state()
+        torch.save({'dim': self.dim, 't': t, 'stepsize': self.stepsize, 'beta1': self.beta1, 'beta2': self.beta2,
+                    'epsilon': self.epsilon, 'm': m.numpy(), 'v': v.numpy()}, path)
+
+    def load_from_file(self, path):
+        s = torch.load(path, map_location='cpu', weights_only=False)
+        self.dim, self.t = s['dim'], s['t']
+        self.beta1, self.beta2, self.epsilon = s['beta1'], s['beta2'], s['epsilon']
+        self.ctx.opt_init(OPT_ADAM, s['stepsize'], self.beta1, self.beta2, self.epsilon)
+        self._stepsize = float(s['stepsize'])
+        self.ctx.opt_set_state(np.asarray(s['m'], dtype=np.float64), np.asarray(s['v'], dtype=np.float64), self.t)
+
+
+# ---------------------------------------------------------------------------------------------
+# population sharding: rank r evaluates noise rows [lo, hi); both signs of a pair stay together
+def shard_bounds(F, world_size, rank):
+    base, rem = divmod(int(F), int(world_size))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def all_gather_fitness(local_fit, F, world_size, rank, group=None):
+    """local_fit float64 [hi-lo, 2] (torch, on the device the process group communicates on) -> [F, 2].
+    The only per-iteration message of the design (80 KB at F = 5000)."""
+    import torch.distributed as dist
+    if world_size == 1:
+        return local_fit
+    sizes = [shard_bounds(F, world_size, r) for r in range(world_size)]
+    maxn = max(hi - lo for lo, hi in sizes)
+    pad = torch.zeros((maxn, 2), dtype=torch.float64, device=local_fit.device)
+    pad[:local_fit.shape[0]] = local_fit
+    out = [torch.empty_like(pad) for _ in range(world_size)]
+    dist.all_gather(out, pad, group=group)
+    return torch.cat([o[:hi - lo] for o, (lo, hi) in zip(out, sizes)], 0)
+
+
+def nes_iteration(ctx: NesContext, optimizer: Optimizer, iteration, F, fc, sigma, l2coeff, fitness_fn,
+                  world_size=1, rank=0, precision=PREC_EXACT, group=None):
+    """One NIC-NES iteration.  fitness_fn(seq [P,rows,T], logprobs [P,rows,T]) -> float64 [P] scores the
+    decoded captions (CIDEr-D in the reference, captioning/policies.py:117-125; host-side, off the CUDA path).
+    Returns (update_ratio, fitness [F,2])."""
+    offsets = ctx.sample_offsets(iteration, F)                       # identical on every rank (same seed)
+    lo, hi = shard_bounds(F, world_size, rank)
+    n = hi - lo
+    offs2 = offsets[lo:hi].repeat_interleave(2)
+    signs = torch.tensor([1.0, -1.0], dtype=torch.float32).repeat(n)
+    seq, lp = ctx.rollout(offs2, signs, fc, sigma, precision=precision, out_device=ctx.dev)
+    fit = torch.as_tensor(fitness_fn(seq, lp), dtype=torch.float64).reshape(n, 2)
+    fit = all_gather_fitness(fit.to(ctx.dev), F, world_size, rank, group)
+    ratio = ctx.master_step(fit, offsets, sigma, l2coeff)
+    optimizer.t += 1
+    return ratio, fit

@@ -1,0 +1,142 @@
+"""PolicyNet / FCModel with the reference's interface (src/algorithm/nets.py:24-168,
+src/captioning/nets.py:138-245), backed by a NesContext instead of nn.Module parameters.
+
+Differences that follow from the design (documented in DESIGN.md):
+  * evolve() draws its noise from the shared noise table (a fresh offset per call) instead of an
+    unseeded torch.normal_ -- the returned vector is still float32 sigma*eps of length D;
+  * set_from_vector() copies (the reference aliases the caller's memory, nets.py:163-165);
+  * only Mutation.DEFAULT runs on the CUDA path; safe mutations raise.
+"""
+from collections import OrderedDict, namedtuple
+from enum import Enum
+
+import numpy as np
+import torch
+
+from .context import NesContext, PREC_EXACT
+
+_model_opt_fields = ['vocab_size', 'input_encoding_size', 'rnn_type', 'rnn_size', 'num_layers',
+                     'drop_prob_lm', 'seq_length', 'fc_feat_size', 'vbn', 'vbn_e', 'vbn_affine', 'layer_n',
+                     'layer_n_affine', 'safe_mutation_underflow', 'safe_mutations', 'safe_mutation_vector',
+                     'safe_mutation_batch_size']
+ModelOptions = namedtuple('ModelOptions', field_names=_model_opt_fields, defaults=(0,) * len(_model_opt_fields))
+
+
+class Mutation(Enum):
+    SAFE_GRAD_SUM = 'SM-G-SUM'
+    SAFE_GRAD_ABS = 'SM-G-ABS'
+    SAFE_VECTOR = 'SM-VECTOR'
+    SAFE_PROPORTIONAL = 'SM-PROPORTIONAL'
+    DEFAULT = ''
+
+
+class PolicyNet:
+    """Flat-theta get/set and Gaussian mutation for one individual (parent slot `parent` of `ctx`)."""
+
+    def __init__(self, ctx: NesContext, parent=0, options=None, vbn=False):
+        self.ctx, self.parent = ctx, int(parent)
+        self.mutations = Mutation((options and options.safe_mutations) or '')
+        if self.mutations != Mutation.DEFAULT:
+            raise NotImplementedError('safe mutations are not on the B200 path (SURVEY 8f-3)')
+        if vbn:
+            raise NotImplementedError('virtual batch norm is not on the B200 path (SURVEY 8f-3)')
+        self.nb_learnable_params = ctx.D
+        self.nb_params = ctx.D
+        self._theta_dtype = torch.float32
+        self._evolve_counter = 0
+
+    # -- src/algorithm/nets.py:163-168
+    def set_from_vector(self, vector):
+        assert len(vector) == self.nb_learnable_params
+        if isinstance(vector, np.ndarray):
+            vector = torch.from_numpy(np.ascontiguousarray(vector))
+        self._theta_dtype = vector.dtype if vector.dtype == torch.float64 else torch.float32
+        self.ctx.set_theta(vector.to(self._theta_dtype), self.parent)
+
+    def parameter_vector(self):
+        return self.ctx.get_theta(self.parent, dtype=self._theta_dtype)
+
+    def get_nb_learnable_params(self):
+        return self.nb_learnable_params
+
+    def count_parameters(self):
+        return self.nb_params
+
+    # -- src/algorithm/nets.py:83-119
+    def evolve(self, sigma, rng_state=None, offset=None):
+        """theta <- theta + sigma*eps(offset); returns the float32 noise vector (numpy, owned)."""
+        if offset is None:
+            it = self._evolve_counter if rng_state is None else int(rng_state)
+            offset = int(self.ctx.sample_offsets((1 << 40) + it, 1)[0])
+            self._evolve_counter += 1
+        member, noise = self.ctx.evolve(offset, sigma, +1.0, self.parent, device=self.ctx.dev)
+        self.ctx.set_theta(member, self.parent)
+        self._theta_dtype = torch.float32
+        self.last_offset = offset
+        return noise.cpu().numpy().astype(np.float32)
+
+    # -- state_dict compatibility with the reference's .pth files (named tensors in registration order)
+    def state_dict(self):
+        flat = self.ctx.get_theta(self.parent, dtype=torch.float32)
+        return OrderedDict((t.name, flat[t.start:t.start + t.count].view(*t.shape).clone()) for t in self.ctx.tensors)
+
+    def load_state_dict(self, sd):
+        flat = torch.empty(self.ctx.D, dtype=torch.float32)
+        for t in self.ctx.tensors:
+            v = sd[t.name]
+            assert tuple(v.shape) == tuple(t.shape), (t.name, tuple(v.shape), t.shape)
+            flat[t.start:t.start + t.count] = v.reshape(-1).to(torch.float32)
+        self.set_from_vector(flat)
+
+    def serialize(self, path=''):
+        torch.save(self.state_dict(), path)
+        return path
+
+    def from_serialized(self, serialized):
+        self.load_state_dict(torch.load(serialized, map_location='cpu'))
+
+    def calc_sensitivity(self, *a, **k):
+        return None     # no-op for Mutation.DEFAULT, like the reference (nets.py:121-123)
+
+
+class FCModel(PolicyNet):
+    """fc_caption: img_embed -> maxout-LSTM core -> logit, greedy decode (src/captioning/nets.py:138-245)."""
+
+    def __init__(self, ctx: NesContext = None, parent=0, options=None, rng_state=None, from_param_file=None,
+                 vbn=False, **ctx_kwargs):
+        if ctx is None:
+            ctx = NesContext(options, **ctx_kwargs)
+        super().__init__(ctx, parent, options, vbn)
+        self.seq_length = ctx.dims['seq_length']
+        self.precision = PREC_EXACT
+        if from_param_file:
+            self.from_serialized(from_param_file)
+        else:
+            self.initialize_params(rng_state)
+
+    def initialize_params(self, rng_state=None):
+        """Xavier-normal weights, zero biases, LayerNorm at 1/0 (src/algorithm/nets.py:62-69)."""
+        gen = torch.Generator()
+        gen.manual_seed(int(rng_state) if rng_state is not None else torch.seed() % (1 << 31))
+        flat = torch.zeros(self.ctx.D, dtype=torch.float32)
+        for t in self.ctx.tensors:
+            if 'ln' in t.name:
+                if t.name.endswith('weight'):
+                    flat[t.start:t.start + t.count] = 1.0
+            elif t.name.endswith('weight'):
+                fan_out, fan_in = t.shape
+                std = (2.0 / (fan_in + fan_out)) ** 0.5
+                flat[t.start:t.start + t.count] = torch.randn(t.count, generator=gen) * std
+        self.set_from_vector(flat)
+
+    def forward(self, fc_feats, greedy=True):
+        """-> seq int64 [B, T], seq_logprobs float32 [B, T]  (FCModel._sample, nets.py:183-245)"""
+        if not greedy:
+            raise NotImplementedError('sampled decode is not on the B200 path (SURVEY 8f-2)')
+        off = torch.zeros(1, dtype=torch.int64)
+        sg = torch.ones(1, dtype=torch.float32)
+        par = torch.tensor([self.parent], dtype=torch.int32)
+        seq, lp = self.ctx.rollout(off, sg, fc_feats, 0.0, parents=par, precision=self.precision, shared_batch=True)
+        return seq[0], lp[0]
+
+    __call__ = forward

@@ -1,0 +1,150 @@
+"""Policy / CaptPolicy / PolicyFactory with the reference's interface (src/algorithm/policies.py:44-186,
+src/captioning/policies.py:64-128).  `rollout` keeps its signature; the CIDEr-D scorer is off the CUDA
+path (BASELINE.json north_star) and is injected as a callable.  `rollout_population` is the batched form
+that the per-member evolve_model + rollout pair of NESWorker.fitness (nic_nes_worker.py:131-154)
+degenerates to at F = 1."""
+from collections import namedtuple
+from enum import Enum
+
+import numpy as np
+import torch
+
+from .context import NesContext, PREC_EXACT
+from .nets import FCModel, ModelOptions, PolicyNet
+
+
+class SuppDataset(Enum):
+    MNIST = 'mnist'
+    MSCOCO = 'mscoco'
+
+
+class Net(Enum):
+    MNIST = 'mnist'
+    FC_CAPTION = 'fc_caption'
+
+
+_opt_fields = ['net', 'safe_mutations', 'model_options', 'safe_mutation_underflow', 'fitness',
+               'vbn', 'safe_mutation_batch_size', 'safe_mutation_vector']
+PolicyOptions = namedtuple('PolicyOptions', field_names=_opt_fields, defaults=[None, '', {}, 0.01, None, False, 32, None])
+
+
+class Policy:
+    def __init__(self, dataset, options: PolicyOptions, ctx: NesContext = None, **ctx_kwargs):
+        assert isinstance(dataset, SuppDataset)
+        self.dataset, self.options = dataset, options
+        self.net = Net(options.net)
+        if self.net != Net.FC_CAPTION:
+            raise NotImplementedError('only the fc_caption net is on the B200 path (config 1, MNIST, stays on the CPU reference)')
+        self.vbn = bool(options.vbn)
+        self.ref_batch = None
+        mo = dict(options.model_options)
+        mo['vbn'] = self.vbn
+        self.model_options = ModelOptions(**mo)
+        self.policy_net: PolicyNet = None
+        self._ctx, self._ctx_kwargs = ctx, ctx_kwargs
+        self.init_model(self.generate_model())
+
+    # ---- src/algorithm/policies.py:102-111
+    def parameter_vector(self):
+        assert self.policy_net is not None, 'set model first!'
+        return self.policy_net.parameter_vector()
+
+    def set_from_parameter_vector(self, vector):
+        assert self.policy_net is not None, 'set model first!'
+        assert isinstance(vector, np.ndarray) or isinstance(vector, torch.Tensor)
+        if isinstance(vector, np.ndarray):
+            vector = torch.from_numpy(vector)
+        self.policy_net.set_from_vector(vector)
+
+    def nb_learnable_params(self):
+        assert self.policy_net is not None, 'set model first!'
+        return self.policy_net.get_nb_learnable_params()
+
+    def serialized(self, path=''):
+        return self.policy_net.serialize(path=path)
+
+    def init_model(self, model=None):
+        assert self.policy_net is None
+        assert isinstance(model, PolicyNet), '{}'.format(type(model))
+        self.policy_net = model
+
+    def set_model(self, model):
+        assert self.policy_net is not None
+        assert isinstance(model, PolicyNet) or isinstance(model, dict) or isinstance(model, str), '{}'.format(type(model))
+        if isinstance(model, PolicyNet):
+            self.policy_net.load_state_dict(model.state_dict())
+        elif isinstance(model, dict):
+            self.policy_net.load_state_dict(model)
+        else:
+            self.policy_net.from_serialized(model)
+
+    def generate_model(self, from_param_file=None, start_rng=None):
+        model = FCModel(self._ctx, 0, self.model_options, rng_state=start_rng, from_param_file=from_param_file,
+                        vbn=self.vbn, **self._ctx_kwargs)
+        self._ctx = model.ctx
+        return model
+
+    def evolve_model(self, sigma):
+        assert self.policy_net is not None, 'set model first!'
+        return self.policy_net.evolve(sigma)
+
+    def get_model(self):
+        return self.policy_net
+
+    def calc_sensitivity(self, task_id, parent_id, experiences, batch_size, directory):
+        assert self.policy_net is not None, 'set model first!'
+        self.policy_net.calc_sensitivity(task_id, parent_id, experiences, batch_size, directory)
+
+    def set_ref_batch(self, ref_batch):
+        self.ref_batch = ref_batch
+
+    def rollout(self, placeholder, data, config):
+        raise NotImplementedError
+
+    def accuracy_on(self, dataloader, config, directory) -> float:
+        raise NotImplementedError('validation needs the COCO/Java scorers, which are outside the hot path (SURVEY 2.1)')
+
+
+class CaptPolicy(Policy):
+    """scorer(seq int64 [rows, T] numpy, data dict) -> float fitness (the reference's CIDEr-D * 100,
+    src/captioning/policies.py:117-125,145-193).  The reference forwards batch_size*seq_per_img rows that
+    are 5x replicated images (dataloader.py:175); greedy decode of a replica is identical, so unique rows
+    are decoded once and token rows repeated (`seq_per_img`)."""
+
+    def __init__(self, dataset, options, ctx=None, scorer=None, seq_per_img=1, **ctx_kwargs):
+        super().__init__(dataset, options, ctx, **ctx_kwargs)
+        self.scorer, self.seq_per_img = scorer, int(seq_per_img)
+        self.precision = PREC_EXACT
+
+    @property
+    def ctx(self):
+        return self.policy_net.ctx
+
+    def _unique_rows(self, fc):
+        fc = np.asarray(fc, dtype=np.float32)
+        return fc[::self.seq_per_img] if self.seq_per_img > 1 else fc
+
+    def rollout_tokens(self, data):
+        seq, lp = self.policy_net(torch.from_numpy(np.ascontiguousarray(self._unique_rows(data['fc_feats']))), greedy=True)
+        if self.seq_per_img > 1:
+            seq, lp = seq.repeat_interleave(self.seq_per_img, 0), lp.repeat_interleave(self.seq_per_img, 0)
+        return seq, lp
+
+    def rollout(self, placeholder, data, config):
+        assert self.scorer is not None, 'CaptPolicy.rollout needs a scorer callable (CIDEr-D is off the CUDA path)'
+        seq, _ = self.rollout_tokens(data)
+        return float(self.scorer(seq.numpy(), data))
+
+    def rollout_population(self, offsets, signs, data, sigma, parents=None, out_device='cpu'):
+        """all members at once -> seq int64 [P, rows, T], logprobs float32 [P, rows, T] (unique rows)."""
+        fc = torch.from_numpy(np.ascontiguousarray(self._unique_rows(data['fc_feats'])))
+        return self.ctx.rollout(offsets, signs, fc, sigma, parents=parents, precision=self.precision, out_device=out_device)
+
+
+class PolicyFactory:
+    @staticmethod
+    def create(dataset, exp, **kw):
+        options = PolicyOptions(**exp['policy_options'])
+        if dataset == SuppDataset.MSCOCO:
+            return CaptPolicy(dataset, options, **kw)
+        raise NotImplementedError('only MSCOCO / fc_caption is on the B200 path')

@@ -170,3 +170,13 @@ def member_theta(theta, eps, sigma, sign):
     src/algorithm/nic_nes/nic_nes_worker.py:151)."""
     noise = np.float32(sigma) * eps.astype(np.float32)
     return (theta + noise) if sign > 0 else (theta - noise), noise
+
+
+def sample_parents(seed, iteration, F, n_parents):
+    """NIC-ES parent pick for offspring i (uniform, nic_es_worker.py:161 uses an unseeded random.choice;
+    this build's rule): parent_i = (philox(i, it, PARENT_DOMAIN)[0] * n_parents) >> 32."""
+    k0, k1 = _key(seed)
+    i = np.arange(F, dtype=np.uint64)
+    it = int(iteration) & 0xFFFFFFFFFFFFFFFF
+    r0, _, _, _ = philox4x32_10(i, it & 0xFFFFFFFF, it >> 32, PARENT_DOMAIN, k0, k1)
+    return ((r0.astype(np.uint64) * np.uint64(n_parents)) >> np.uint64(32)).astype(np.int32)

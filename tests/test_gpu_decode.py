@@ -1,0 +1,165 @@
+"""GPU parity of the population decode against the reference's golden outputs and the pinned oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import fc_caption, noise
+
+pytestmark = pytest.mark.gpu
+
+
+def _ctx_for(c, golden_mod, L, wave=8, n_parents=1):
+    import nes_b200
+    mo = dict(vocab_size=c['V'], input_encoding_size=c['E'], rnn_size=c['R'], fc_feat_size=c['Fd'],
+              layer_n=c.get('ln', False), layer_n_affine=c.get('affine', False))
+    return nes_b200.NesContext(mo, seed=golden_mod.TABLE_SEED, table_len=L, n_parents=n_parents, wave_members=wave, rows=c['B'])
+
+
+def _members(offs):
+    offs2 = np.repeat(np.asarray(offs, dtype=np.int64), 2)
+    signs = np.tile(np.array([1.0, -1.0], dtype=np.float32), len(offs))
+    return offs2, signs
+
+
+@pytest.mark.parametrize('name', ['g1', 'g2', 'g3', 'g4', 'g5', 'g6'])
+def test_tokens_and_logprobs_match_reference_golden_exact_mode(name, golden, golden_mod):
+    """token ids bit-exact, log-probs to float32 round-off, against what the REAL reference produced"""
+    import nes_b200
+    c = golden_mod.CASES[name]
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    ctx = _ctx_for(c, golden_mod, L)
+    ctx.set_theta(theta)
+    offs2, signs = _members(offs)
+    seq, lp = ctx.rollout(offs2, signs, fc, c['sigma'], precision=nes_b200.PREC_EXACT)
+    want_seq = golden[name + '_seq'].reshape(-1, c['B'], 16).astype(np.int64)
+    want_lp = golden[name + '_logprobs'].reshape(-1, c['B'], 16)
+    assert seq.dtype == torch.int64 and tuple(seq.shape) == want_seq.shape
+    assert np.array_equal(seq.numpy(), want_seq)
+    assert np.allclose(lp.numpy(), want_lp, rtol=1e-4, atol=1e-5)
+    # the unperturbed theta through the single-individual API (FCModel.__call__)
+    model = nes_b200.FCModel(ctx, from_param_file=None, options=None, rng_state=1)
+    model.set_from_vector(theta)
+    s0, lp0 = model(torch.from_numpy(fc), greedy=True)
+    assert np.array_equal(s0.numpy(), golden[name + '_seq_theta'].astype(np.int64))
+    assert np.allclose(lp0.numpy(), golden[name + '_logprobs_theta'], rtol=1e-4, atol=1e-5)
+    ctx.close()
+
+
+@pytest.mark.parametrize('name,prec,tol', [('g1', 1, 2e-5), ('g3', 1, 2e-5), ('g1', 0, 1e-3), ('g3', 0, 1e-3), ('g5', 0, 1e-3), ('g5', 1, 2e-5)])
+def test_hidden_states_and_logits_teacher_forced(name, prec, tol, golden_mod):
+    """per-step h and logits against the oracle trace when both follow the oracle's token path:
+    within 1e-3 relative (north_star) for the fp16-operand mode, ~fp32 for the split mode"""
+    c = golden_mod.CASES[name]
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    ctx = _ctx_for(c, golden_mod, L)
+    ctx.set_theta(theta)
+    offs2, signs = _members(offs[:1])
+    eps = noise.noise_row(golden_mod.TABLE_SEED, offs[0], play, D)
+    forced, traces = [], []
+    for sgn in (+1, -1):
+        th, _ = noise.member_theta(theta, eps, c['sigma'], sgn)
+        s, lp, tr = fc_caption.decode_greedy(dims, th, fc, trace=True)
+        assert len(tr['logits']) == 16, 'golden case must not break early for this test'
+        forced.append(s); traces.append(tr)
+    forced = np.stack(forced).astype(np.int64)
+    # feed token = the oracle's (masked) token, exactly what its embedding lookup saw
+    seq, lp, h_tr, l_tr = ctx.rollout(offs2, signs, fc, c['sigma'], precision=prec, forced_tokens=forced, trace=True)
+    h_tr, l_tr = h_tr.cpu().numpy(), l_tr.cpu().numpy()
+    for m in range(2):
+        for t in range(17):
+            ref_h = traces[m]['h'][t]
+            assert np.max(np.abs(h_tr[t, m] - ref_h)) <= tol * max(np.max(np.abs(ref_h)), 1e-6), ('h', m, t)
+        for t in range(16):
+            ref_l = traces[m]['logits'][t]
+            assert np.max(np.abs(l_tr[t, m] - ref_l)) <= tol * np.max(np.abs(ref_l)), ('logits', m, t)
+    ctx.close()
+
+
+def test_fused_argmax_equals_argmax_of_its_own_logits(golden_mod):
+    """the online (max, argmax, log-sum-exp) epilogue against torch on the SAME logits (first index on ties)"""
+    import nes_b200
+    c = golden_mod.CASES['g3']
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    ctx = _ctx_for(c, golden_mod, L)
+    ctx.set_theta(theta)
+    offs2, signs = _members(offs)
+    for prec in (nes_b200.PREC_FAST, nes_b200.PREC_EXACT):
+        seq, lp, h_tr, l_tr = ctx.rollout(offs2, signs, fc, c['sigma'], precision=prec, trace=True)
+        logits = l_tr.cpu()                                        # [T, P, B, V1]
+        lsm = torch.log_softmax(logits, dim=-1)
+        best_lp, best = lsm.max(-1)
+        raw = best.permute(1, 2, 0)                                # [P, B, T]
+        unfinished = torch.cumprod((raw > 0).long(), dim=-1)
+        assert torch.equal(seq, raw * unfinished)
+        assert torch.allclose(lp, best_lp.permute(1, 2, 0), rtol=1e-5, atol=1e-6)
+    ctx.close()
+
+
+def test_fast_mode_token_agreement_is_reported(golden, golden_mod, capsys):
+    """fp16-operand mode: not bit-exact by construction; measure and bound the agreement"""
+    import nes_b200
+    c = golden_mod.CASES['g3']
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    ctx = _ctx_for(c, golden_mod, L)
+    ctx.set_theta(theta)
+    offs2, signs = _members(offs)
+    seq, lp = ctx.rollout(offs2, signs, fc, c['sigma'], precision=nes_b200.PREC_FAST)
+    want = golden['g3_seq'].reshape(-1, c['B'], 16).astype(np.int64)
+    agree = float((seq.numpy() == want).mean())
+    print('FAST-mode token agreement with the fp32 reference on g3: %.4f' % agree)
+    assert agree > 0.9
+    ctx.close()
+
+
+def test_early_break_zeroes_later_logprobs():
+    """all rows emit token 0 at the first step -> the reference breaks (nets.py:242-243): later columns stay 0"""
+    import nes_b200
+    mo = dict(vocab_size=63, input_encoding_size=64, rnn_size=64, fc_feat_size=64)
+    ctx = nes_b200.NesContext(mo, seed=1, table_len=1 << 20, wave_members=4, rows=3)
+    dims = fc_caption.Dims(63, 64, 64, 64)
+    theta = np.zeros(ctx.D, dtype=np.float32)
+    lay = {t.name: t for t in ctx.tensors}
+    theta[lay['logit.bias'].start] = 5.0
+    ctx.set_theta(theta)
+    fc = np.ones((3, 64), dtype=np.float32)
+    seq, lp = ctx.rollout(np.zeros(2, dtype=np.int64), np.array([1., -1.], dtype=np.float32), fc, 0.0)
+    s_ref, lp_ref = fc_caption.decode_greedy(dims, theta, fc)
+    for m in range(2):
+        assert np.array_equal(seq[m].numpy(), s_ref) and (seq[m] == 0).all()
+        assert (lp[m][:, 1:] == 0).all() and np.allclose(lp[m].numpy(), lp_ref, rtol=1e-5, atol=1e-6)
+    ctx.close()
+
+
+def test_es_parents_per_member_batches_and_waves(golden_mod):
+    """NIC-ES shape: several parents, single-sign members, per-member batches, more members than one wave"""
+    import nes_b200
+    c = golden_mod.CASES['g1']
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    ctx = _ctx_for(c, golden_mod, L, wave=3, n_parents=2)
+    theta_b = fc_caption.xavier_theta(dims, 99)
+    ctx.set_theta(theta, 0); ctx.set_theta(theta_b, 1)
+    P = 7
+    offs_all = ctx.sample_offsets(3, P).numpy()
+    parents = ctx.sample_parents(3, P, 2).numpy()
+    fcs = np.stack([noise.table_slice(50 + i, 0, c['B'] * c['Fd']).astype(np.float32).reshape(c['B'], c['Fd']) for i in range(P)])
+    seq, lp = ctx.rollout(offs_all, np.ones(P, dtype=np.float32), fcs, 0.02, parents=parents, shared_batch=False)
+    for i in range(P):
+        base = theta if parents[i] == 0 else theta_b
+        th, _ = noise.member_theta(base, noise.noise_row(golden_mod.TABLE_SEED, offs_all[i], play, D), 0.02, +1)
+        s, l = fc_caption.decode_greedy(dims, th, fcs[i])
+        assert np.array_equal(seq[i].numpy(), s), i
+        assert np.allclose(lp[i].numpy(), l, rtol=1e-4, atol=1e-5)
+    ctx.close()
+
+
+def test_rollout_rejects_bad_arguments():
+    import nes_b200
+    mo = dict(vocab_size=63, input_encoding_size=64, rnn_size=64, fc_feat_size=64)
+    ctx = nes_b200.NesContext(mo, seed=1, table_len=1 << 20, wave_members=2, rows=4)
+    with pytest.raises(nes_b200.NesError):
+        ctx.rollout(np.zeros(1, dtype=np.int64), np.ones(1, dtype=np.float32), np.zeros((5, 64), dtype=np.float32), 0.0)   # rows > capacity
+    with pytest.raises(nes_b200.NesError):
+        nes_b200.NesContext(dict(vocab_size=63, input_encoding_size=48, rnn_size=64, fc_feat_size=64), table_len=1 << 20)
+    seq, lp = ctx.rollout(np.zeros(0, dtype=np.int64), np.zeros(0, dtype=np.float32), np.zeros((4, 64), dtype=np.float32), 0.0)
+    assert tuple(seq.shape) == (0, 4, 16)
+    ctx.close()
