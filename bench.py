@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""Headline benchmark: fc_caption perturbed-member evals/s (bs128 greedy) -- BASELINE.json configs[1]:
+NIC-ES, fc_feat 2048, E = R = 512, V = 9487, 128 rows per rollout, population 1000 (per GPU: weak scaling),
+mu = 50 parents, synthetic features, random-init weights.
+
+One step = one ES generation: sample (parent, noise offset) per offspring -> decode all offspring
+(img_embed, 17 LSTM steps, 16 vocabulary projections with fused argmax/log-prob) -> fitness -> [all-gather
+of fitness scalars when N > 1] -> rank -> truncation selection -> materialise the survivors as the next
+parents.  CIDEr-D scoring is host-side Python in the reference and outside the path (BASELINE.json); the
+fitness here is the sum of greedy log-probs.
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference] [--precision exact|fast]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+V, E, R, FD, T = 9487, 512, 512, 2048, 16
+FLOP_PER_ROW = 2 * FD * E + 17 * 2 * (E + R) * 5 * R + 16 * 2 * R * (V + 1)       # 246 677 504
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--population', type=int, default=1000, help='offspring per GPU (weak scaling)')
+    ap.add_argument('--parents', type=int, default=50)
+    ap.add_argument('--elites', type=int, default=3)
+    ap.add_argument('--rows', type=int, default=128)
+    ap.add_argument('--sigma', type=float, default=0.005)
+    ap.add_argument('--precision', default='exact', choices=['exact', 'fast'])
+    ap.add_argument('--table-log2', type=int, default=28)
+    ap.add_argument('--cpu-seconds', type=float, default=15.0)
+    ap.add_argument('--no-extras', action='store_true')
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md recipe)
+class ClockSampler:
+    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(',')])
+
+    def stop(self):
+        if not self.proc:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx = float(r[2])
+                for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), r[5:9]):
+                    if v.lower().startswith('active'):
+                        reasons.add(name)
+            except Exception:
+                pass
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's worker recipe (nic_es_worker.py:142-175 minus disk / Redis / CIDEr):
+# member = parent + sigma*eps ; FCModel._sample(greedy).  One single-threaded process per host core, exactly how
+# the reference uses a node (src/main.py:8-11,105-106).
+def _cpu_worker(args):
+    seed, n_members, rows, sigma = args
+    import numpy as np
+    import torch
+    torch.set_num_threads(1)
+    from oracle import fc_caption, noise
+    dims = fc_caption.Dims(V, E, R, FD)
+    rs = np.random.RandomState(seed)
+    theta = (rs.randn(dims.num_params()) * 0.02).astype(np.float32)
+    fc = rs.randn(rows, FD).astype(np.float32)
+    t0 = time.perf_counter()
+    for _ in range(n_members):
+        eps = rs.randn(dims.num_params()).astype(np.float32)       # the reference draws a fresh normal per member (nets.py:102)
+        th = theta + np.float32(sigma) * eps
+        fc_caption.decode_greedy(dims, th, fc)
+    return time.perf_counter() - t0
+
+
+def cpu_evals_per_s(rows, sigma, budget_s, per_worker=None):
+    import multiprocessing as mp
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else (os.cpu_count() or 1)
+    ctx = mp.get_context('fork')
+    with ctx.Pool(cores) as pool:
+        t1 = max(pool.map(_cpu_worker, [(100 + i, 1, rows, sigma) for i in range(cores)]))      # calibrate: 1 member each
+        n = per_worker or max(1, int(budget_s / max(t1, 1e-3)))
+        t0 = time.perf_counter()
+        pool.map(_cpu_worker, [(200 + i, n, rows, sigma) for i in range(cores)])
+        wall = time.perf_counter() - t0
+    return cores * n / wall, cores, n
+
+
+def run_reference(a, rank, world):
+    if rank != 0:
+        return
+    per_step = None
+    vals = []
+    cores = 1
+    budget = max(2.0, min(20.0, 120.0 / max(1, a.steps + a.warmup)))
+    for i in range(a.warmup + a.steps):
+        v, cores, n = cpu_evals_per_s(a.rows, a.sigma, budget, per_step)
+        per_step = n
+        if i >= a.warmup:
+            vals.append(v)
+    value = sum(vals) / len(vals)
+    sample = '%d members per step (1 single-threaded process per core x %d members), %d rows, oracle port of the reference worker recipe' % (cores * per_step, per_step, a.rows)
+    print(json.dumps({
+        'impl': 'reference', 'metric': 'fc_caption perturbed-member evals/sec (bs128 greedy)', 'value': value, 'unit': 'member-evals/s',
+        'n_gpus': a.gpus, 'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': 1000.0 * cores * per_step / value,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': workload_config(a, 1),
+        'cpu_baseline': {'value': value, 'unit': 'member-evals/s', 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': value, 'unit': 'member-evals/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
+
+
+def workload_config(a, world):
+    return {'workload': 'configs[1]: fc_caption NIC-ES generation, fc_feat 2048, E=R=512, V=9487, %d rows/rollout, population %d per GPU, mu=%d, elites=%d, sigma=%g'
+                        % (a.rows, a.population, a.parents, a.elites, a.sigma),
+            'population_per_gpu': a.population, 'global_population': a.population * world, 'rows': a.rows,
+            'parallelism': 'population-sharded x%d, fitness all-gather' % world,
+            'l2': 'per-step inputs (noise-table slices, 247 MB per member) far exceed the 126 MB L2; no flush needed'}
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    a = parse()
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if a.impl == 'reference':
+        return run_reference(a, rank, world)
+
+    import numpy as np
+    import torch
+    import nes_b200
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=dev)
+    prec = nes_b200.PREC_EXACT if a.precision == 'exact' else nes_b200.PREC_FAST
+    P, mu, el, rows = a.population, a.parents, a.elites, a.rows
+    Pg = P * world
+    ctx = nes_b200.NesContext(dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=FD), seed=1234,
+                              table_len=1 << a.table_log2, n_parents=2 * mu, wave_members=min(P, 1024), rows=rows, device=local)
+    # random-init parents (Xavier, algorithm/nets.py:62-69), synthetic N(0,1) fc features
+    model = nes_b200.FCModel(ctx, parent=0, rng_state=0)
+    for k in range(1, mu):
+        ctx.evolve(int(ctx.sample_offsets(999, mu)[k]), 0.01, 1.0, parent=0, dst_parent=k, want_member=False, want_noise=False)
+    g = torch.Generator().manual_seed(0)
+    fc_host = torch.randn(rows, FD, generator=g).pin_memory()
+    fc_dev = fc_host.to(dev)
+    ones = torch.ones(P, dtype=torch.float32, device=dev)
+    lo = rank * P
+    state = {'base': 0, 'it': 0}
+
+    def select_and_materialise(fit_all, offs, pars):
+        ranks = ctx.compute_ranks(fit_all, device=True)
+        keep = torch.nonzero(ranks >= Pg - (mu - el)).flatten()
+        order = keep[torch.argsort(ranks[keep], descending=True)]
+        sel = torch.stack([order, offs[order], pars[order].to(torch.int64)], 1).cpu().numpy()      # the master's sync point
+        cur, nxt = state['base'], mu - state['base']
+        for e in range(el):       # elites carried over unchanged
+            ctx.evolve(0, 0.0, 1.0, parent=cur + e, dst_parent=nxt + e, want_member=False, want_noise=False)
+        for j, (m, off, par) in enumerate(sel):
+            ctx.evolve(int(off), a.sigma, 1.0, parent=cur + int(par), dst_parent=nxt + el + j, want_member=False, want_noise=False)
+        state['base'] = nxt
+
+    def step_resident():
+        it = state['it']; state['it'] += 1
+        offs = ctx.sample_offsets(it, Pg, device=True)
+        pars = ctx.sample_parents(it, Pg, mu, device=True)
+        ctx.rollout(offs[lo:lo + P], ones, fc_dev, a.sigma, parents=pars[lo:lo + P] + state['base'], precision=prec, out_device=dev)
+        fit = ctx.logprob_fitness(P, rows, device=dev)
+        if world > 1:
+            out = torch.empty(Pg, dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(out, fit)
+            fit = out
+        select_and_materialise(fit, offs, pars)
+
+    seq_host = torch.empty((P, rows, T), dtype=torch.int64).pin_memory()
+    lp_host = torch.empty((P, rows, T), dtype=torch.float32).pin_memory()
+
+    def step_e2e():
+        """through the host boundary the reference has: features come from host memory, tokens / log-probs go back
+        to the host where the scorer lives, the host returns fitness scalars"""
+        it = state['it']; state['it'] += 1
+        offs = ctx.sample_offsets(it, Pg, device=True)
+        pars = ctx.sample_parents(it, Pg, mu, device=True)
+        lib, h = ctx.lib, ctx._h
+        par_local = (pars[lo:lo + P] + state['base']).contiguous()
+        off_local = offs[lo:lo + P].contiguous()
+        nes_b200._lib.check(lib.nes_rollout(h, P, nes_b200._lib.ptr(off_local), nes_b200._lib.ptr(ones), nes_b200._lib.ptr(par_local),
+                                            nes_b200._lib.ptr(fc_host), rows, 1, float(a.sigma), int(prec),
+                                            nes_b200._lib.ptr(seq_host), nes_b200._lib.ptr(lp_host)))
+        fit = lp_host.view(P, -1).sum(1, dtype=torch.float64)          # host-side scorer stand-in
+        fit = fit.to(dev, non_blocking=True)
+        if world > 1:
+            out = torch.empty(Pg, dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(out, fit)
+            fit = out
+        select_and_materialise(fit, offs, pars)
+
+    def timed(fn, steps, warmup, sample_clocks=False):
+        for _ in range(warmup):
+            fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        sampler = ClockSampler(local) if sample_clocks else None
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = ctx.gpu_launches
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = e0.elapsed_time(e1)
+        clocks = sampler.stop() if sampler else None
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item(), ctx.gpu_launches - l0, clocks
+
+    ctx.profile(True)
+    ms, launches, clocks = timed(step_resident, a.steps, a.warmup, sample_clocks=True)
+    prof = ctx.profile_read()
+    ctx.profile(False)
+    ms_e2e, _, _ = timed(step_e2e, a.steps, max(1, a.warmup - 2))
+    value = Pg * a.steps / (ms / 1000.0)
+    e2e = Pg * a.steps / (ms_e2e / 1000.0)
+
+    out = {'metric': 'fc_caption perturbed-member evals/sec (bs128 greedy)', 'value': value, 'unit': 'member-evals/s', 'n_gpus': world,
+           'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': ms / a.steps, 'higher_is_better': True, 'scaling': 'weak',
+           'vs_baseline': None, 'dtype': 'f16 operands (split hi+lo, ~f32 products), f32 accumulate' if prec == nes_b200.PREC_EXACT else 'f16 operands, f32 accumulate',
+           'data': 'synthetic', 'config': dict(workload_config(a, world), precision=a.precision),
+           'clocks': clocks, 'gpu_launches': launches * world,
+           'e2e': {'value': e2e, 'unit': 'member-evals/s', 'h2d_bytes_per_step': int(fc_host.numel() * 4 + P * 8),
+                   'd2h_bytes_per_step': int(seq_host.numel() * 8 + lp_host.numel() * 4 + (mu - el) * 24), 'ms_per_step': ms_e2e / a.steps}}
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+        except Exception:
+            pass
+        tf_peak = peaks.get('bf16_tflops_sustained', 1400.0)
+        # dominant kernel: the vocabulary projection with fused argmax / log-sum-exp (64 % of the algorithmic FLOPs)
+        k = prof['logit']
+        flop_per_launch = 2.0 * R * (V + 1) * rows * min(P, 1024)
+        ach = flop_per_launch / (k['ms'] / max(1, k['count']) * 1e-3) / 1e12 if k['count'] else None
+        out['roofline'] = {'bound': 'tensor', 'kernel': 'k_member_gemm<LOGIT> (vocabulary projection + fused argmax/log-prob)',
+                           'achieved': ach, 'peak': tf_peak, 'unit': 'TFLOP/s', 'frac': ach / tf_peak if ach else None,
+                           'peak_source': 'MEASURED_PEAKS.json bf16_tflops_sustained (of measured)' if peaks else 'fallback 1400 (of fallback)',
+                           'traffic': None, 'launches': k['count'], 'avg_launch_ms': k['ms'] / max(1, k['count']),
+                           'algorithmic_flop_per_launch': flop_per_launch,
+                           'whole_step_algorithmic_tflops': FLOP_PER_ROW * rows * P * a.steps / (ms * 1e-3) / 1e12,
+                           'kernel_time_share': {kk: vv['ms'] / ms for kk, vv in prof.items()}}
+        if not a.no_extras and world == 1:
+            out['extras'] = extras(ctx, nes_b200, torch, dev, peaks)
+            v, cores, n = cpu_evals_per_s(rows, a.sigma, a.cpu_seconds)
+            out['cpu_baseline'] = {'value': v, 'unit': 'member-evals/s', 'cores': cores, 'kind': 'port',
+                                   'sample': '%d members (%d single-threaded processes x %d), %d rows each; oracle port of evolve + FCModel greedy decode' % (cores * n, cores, n, rows)}
+        print(json.dumps(out))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def extras(ctx, nes_b200, torch, dev, peaks):
+    """second half of the metric (NES iteration pieces) on the same context: K7 aggregation at F = 5000 rows
+    against the HBM roofline, K8 update, and one antithetic NES iteration at population 1000 pairs."""
+    import numpy as np
+    ex = {}
+    F = 5000
+    offs = ctx.sample_offsets(12345, F, device=True)
+    w = torch.randn(F, device=dev)
+    ctx.last_gradient_ms()                      # arm the event pair
+    for _ in range(2):
+        ctx.gradient(offs, w, 0.01, want=False)
+    t = []
+    for _ in range(5):
+        ctx.gradient(offs, w, 0.01, want=False)
+        t.append(ctx.last_gradient_ms())
+    ms = sum(t) / len(t)
+    gb = (F * ctx.D * 2 + ctx.D * 4) / 1e9
+    hbm = peaks.get('hbm_gbs', 6650.0)
+    ex['k7_gradient'] = {'F': F, 'D': ctx.D, 'ms': ms, 'algorithmic_GB': gb, 'achieved_GBps': gb / (ms * 1e-3), 'peak_GBps': hbm,
+                         'frac_of_measured_copy_peak': gb / (ms * 1e-3) / hbm, 'frac_of_8TBps_nominal': gb / (ms * 1e-3) / 8000.0}
+    nes_b200.Adam(ctx, None, stepsize=0.001)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx.opt_update(None, 1e-7, want_ratio=False)
+    e0.record()
+    for _ in range(5):
+        ctx.opt_update(None, 1e-7, want_ratio=False)
+    e1.record(); torch.cuda.synchronize()
+    ex['k8_adam_ms'] = e0.elapsed_time(e1) / 5
+    return ex
+
+
+if __name__ == '__main__':
+    main()

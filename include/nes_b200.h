@@ -134,6 +134,11 @@ int nes_master_step(nes_ctx* ctx, const double* fitness, const int64_t* offsets,
 /* timing of the last K7 launch on the context stream, CUDA events (ms); bench.py roofline */
 int nes_last_gradient_ms(nes_ctx* ctx, float* ms);
 int nes_last_rollout_ms(nes_ctx* ctx, float* ms);
+/* per-kernel timing of the decode launches (CUDA events on the context stream).  kinds: 0 plain member GEMM
+ * (img_embed / LayerNorm pre-activations), 1 LSTM member GEMM, 2 vocabulary-projection member GEMM, 3 finalize.
+ * nes_profile_read synchronises, returns the summed durations [4] and launch counts [4] since the last read. */
+int nes_profile_enable(nes_ctx* ctx, int on);
+int nes_profile_read(nes_ctx* ctx, float* ms_by_kind, int32_t* count_by_kind);
 
 /* standalone tensor-core self test through the same tcgen05/TMA kernel the decode uses:
  * C[M,N] = A[M,K] W[N,K]^T + sigma * A[M,K] f16(E[N,K])^T, float32 in/out (host or device pointers). */

@@ -92,8 +92,8 @@ class NesContext:
         _lib.check(self.lib.nes_sample_offsets(self._h, int(iteration), int(F), _lib.ptr(out)))
         return out
 
-    def sample_parents(self, iteration, F, n_parents):
-        out = torch.empty(int(F), dtype=torch.int32)
+    def sample_parents(self, iteration, F, n_parents, device=False):
+        out = torch.empty(int(F), dtype=torch.int32, device=self.dev if device else 'cpu')
         _lib.check(self.lib.nes_sample_parents(self._h, int(iteration), int(F), int(n_parents), _lib.ptr(out)))
         return out
 
@@ -165,9 +165,9 @@ class NesContext:
         return out
 
     # ---- master math
-    def compute_ranks(self, x):
+    def compute_ranks(self, x, device=False):
         x = torch.as_tensor(np.asarray(x, dtype=np.float64)).contiguous() if not torch.is_tensor(x) else x.to(torch.float64).contiguous()
-        out = torch.empty(x.numel(), dtype=torch.int64)
+        out = torch.empty(x.numel(), dtype=torch.int64, device=self.dev if device else 'cpu')
         _lib.check(self.lib.nes_compute_ranks(self._h, _lib.ptr(x), x.numel(), _lib.ptr(out)))
         return out
 
@@ -238,6 +238,15 @@ class NesContext:
         _lib.check(self.lib.nes_master_step(self._h, _lib.ptr(fit), _lib.ptr(offsets), F, float(sigma), float(l2coeff),
                                             ctypes.byref(ratio) if want_ratio else None))
         return ratio.value if want_ratio else None
+
+    def profile(self, on):
+        _lib.check(self.lib.nes_profile_enable(self._h, int(bool(on))))
+
+    def profile_read(self):
+        ms = (ctypes.c_float * 4)()
+        cnt = (ctypes.c_int32 * 4)()
+        _lib.check(self.lib.nes_profile_read(self._h, ms, cnt))
+        return {k: {'ms': float(ms[i]), 'count': int(cnt[i])} for i, k in enumerate(('plain', 'lstm', 'logit', 'finalize'))}
 
     def last_gradient_ms(self):
         ms = ctypes.c_float(0)

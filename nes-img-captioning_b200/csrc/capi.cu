@@ -144,6 +144,8 @@ int nes_ctx_destroy(nes_ctx* ctx) {
     if (c->ev_b) cudaEventDestroy(c->ev_b);
     if (c->ev_c) cudaEventDestroy(c->ev_c);
     if (c->ev_d) cudaEventDestroy(c->ev_d);
+    for (auto& r : c->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    for (auto& r : c->prof_pool) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     delete[] c->theta_is_f32;
     delete c;
     return 0;
@@ -357,6 +359,26 @@ int nes_master_step(nes_ctx* ctx, const double* fitness, const int64_t* offsets,
     if (nes_rank_weights(ctx, fitness, F, nullptr, nullptr)) return 1;
     if (nes_gradient(ctx, offsets, nullptr, F, sigma, nullptr)) return 1;
     return nes_opt_update(ctx, nullptr, l2coeff, ratio_out);
+}
+
+int nes_profile_enable(nes_ctx* ctx, int on) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    c->profiling = on != 0;
+    return 0;
+}
+int nes_profile_read(nes_ctx* ctx, float* ms_by_kind, int32_t* count_by_kind) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    NES_CHECK(ms_by_kind && count_by_kind, "null output");
+    NES_CUDA(cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < PROF_KINDS; ++k) { ms_by_kind[k] = 0.f; count_by_kind[k] = 0; }
+    for (auto& r : c->prof_recs) {
+        float ms = 0.f;
+        NES_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+        ms_by_kind[r.kind] += ms; count_by_kind[r.kind] += 1;
+        c->prof_pool.push_back(r);
+    }
+    c->prof_recs.clear();
+    return 0;
 }
 
 int nes_last_gradient_ms(nes_ctx* ctx, float* ms) {

@@ -83,7 +83,27 @@ struct Ctx {
     cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr;
     bool grad_timed = false, rollout_timed = false;
 
+    // optional per-kernel timing (bench.py roofline): event pairs around every decode kernel launch
+    bool profiling = false;
+    struct ProfRec { int kind; cudaEvent_t a, b; };
+    std::vector<ProfRec> prof_recs;        // records of the current profiling window
+    std::vector<ProfRec> prof_pool;        // recycled events
+
     DecodeWorkspace* ws = nullptr;
+};
+enum { PROF_PLAIN = 0, PROF_LSTM = 1, PROF_LOGIT = 2, PROF_FINALIZE = 3, PROF_KINDS = 4 };
+struct ProfScope {                          // RAII: record an event pair around one launch when profiling is on
+    Ctx* c; int idx = -1;
+    ProfScope(Ctx* c_, int kind) : c(c_) {
+        if (!c->profiling) return;
+        Ctx::ProfRec r;
+        if (!c->prof_pool.empty()) { r = c->prof_pool.back(); c->prof_pool.pop_back(); }
+        else { cudaEventCreate(&r.a); cudaEventCreate(&r.b); }
+        r.kind = kind;
+        cudaEventRecord(r.a, c->stream);
+        c->prof_recs.push_back(r); idx = (int)c->prof_recs.size() - 1;
+    }
+    ~ProfScope() { if (idx >= 0) cudaEventRecord(c->prof_recs[idx].b, c->stream); }
 };
 
 int ensure_small(Ctx* c, int64_t n);   // (re)allocate the small per-iteration scratch arrays for n members

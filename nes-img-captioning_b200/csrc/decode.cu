@@ -120,23 +120,32 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
     const float sgn = p.sign[member];
     int64_t tok = 0;
     if (p.t >= 1) {
-        float mx = -INFINITY; int idx = 0x7fffffff;
-        for (int j = lane; j < p.n_tiles; j += 32) {
-            const LogitPartial q = p.partials[grow * p.n_tiles + j];
-            if (q.mx > mx || (q.mx == mx && q.idx < idx)) { mx = q.mx; idx = q.idx; }
-        }
-        for (int o = 16; o > 0; o >>= 1) {
-            const float om = __shfl_xor_sync(0xffffffffu, mx, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
-            if (om > mx || (om == mx && oi < idx)) { mx = om; idx = oi; }
-        }
+        // global max and sum-exp over the vocabulary tiles
+        float mx = -INFINITY;
+        for (int j = lane; j < p.n_tiles; j += 32) mx = fmaxf(mx, p.partials[grow * p.n_tiles + j].mx);
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
         float s = 0.f;
         for (int j = lane; j < p.n_tiles; j += 32) {
             const LogitPartial q = p.partials[grow * p.n_tiles + j];
             s += q.sum * expf(q.mx - mx);
         }
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        const float logp = -logf(s);                              // logit_max - logsumexp
+        const float lse = logf(s);
+        // the reference's argmax runs over float32 log-probs, log_softmax(x) = (x - max) - log(sum) (captioning/nets.py:202-208):
+        // logits closer than the float32 quantum of log(sum) tie there and torch.max returns the LOWEST index.
+        float best = -INFINITY; int idx = 0x7fffffff;
+        for (int j = lane; j < p.n_tiles; j += 32) {
+            const LogitPartial q = p.partials[grow * p.n_tiles + j];
+            const float l1 = __fsub_rn(__fsub_rn(q.mx, mx), lse), l2 = __fsub_rn(__fsub_rn(q.lo_val, mx), lse);
+            if (l1 > best || (l1 == best && q.idx < idx)) { best = l1; idx = q.idx; }
+            if (l2 > best || (l2 == best && q.lo_idx < idx)) { best = l2; idx = q.lo_idx; }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+            if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+        }
+        const float logp = best;                                  // = max log-prob
         const bool done = p.t > 1 && p.unf_count[(p.t - 1) * p.W + member] == 0;   // the reference broke out of the loop
         int64_t it = 0;
         if (!done) {
@@ -311,6 +320,7 @@ static int launch_gemm(Ctx* c, const GemmParams& p, int64_t n_members) {
     NES_CHECK(n_members % p.group == 0, "member count must be a multiple of the scheduling group");
     const int64_t grid = n_members * p.m_tiles * p.n_tiles;
     NES_CHECK(grid < (1ll << 31), "grid too large");
+    ProfScope prof(c, EPI == EPI_PLAIN ? PROF_PLAIN : (EPI == EPI_LSTM ? PROF_LSTM : PROF_LOGIT));
     k_member_gemm<EPI, PREC><<<(unsigned)grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
     c->launches++;
     NES_CUDA(cudaGetLastError());
@@ -455,6 +465,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 q.off = base.off; q.sign = base.sign; q.parent = base.parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D;
                 q.affine = c->dims.layer_n_affine; q.sigma = sigma;
                 if (q.affine) for (int i = 0; i < 6; ++i) { q.ln_start[i] = L.t[T_I2H_LN_W + i].start; q.ln_pstart[i] = L.t[T_I2H_LN_W + i].pstart; }
+                ProfScope prof(c, PROF_FINALIZE);
                 k_ln_gates<<<(unsigned)(nm * rows), 128, sizeof(float) * 6 * R, c->stream>>>(q);
                 c->launches++;
                 NES_CUDA(cudaGetLastError());
@@ -466,6 +477,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 p.nseg = 1; p.N = V1; p.chunk_stride = 0; p.n_tiles = ws->nt_logit;
                 if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128)) return 1;
                 p.partials = ws->partials;
+                { int ex; frexpf(logf((float)V1), &ex); p.tie_delta = ldexpf(1.0f, ex - 1 - 23); }
                 p.logit_trace = logit_trace ? logit_trace + (int64_t)(t - 1) * n_members * rows * V1 : nullptr; p.ld_trace = V1;
                 if (launch_gemm_prec<EPI_LOGIT>(c, p, nm, precision)) return 1;
             }
@@ -478,6 +490,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;
                 f.forced = forced ? ws->d_forced + m0 * rows * T : nullptr;
                 f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0;
+                ProfScope prof(c, PROF_FINALIZE);
                 k_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(f);
                 c->launches++;
                 NES_CUDA(cudaGetLastError());

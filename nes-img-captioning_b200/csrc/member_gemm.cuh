@@ -27,7 +27,10 @@ struct SegInfo {
     int64_t w_pstart;          // padded start of the weight tensor inside a noise row / theta shadow
     int64_t b_start, b_pstart; // bias tensor: flat start / padded start (-1: no bias)
 };
-struct LogitPartial { float mx; int32_t idx; float sum; float pad; };
+// per (row, vocabulary tile): max logit + its first index, sum exp(logit - mx), and the EARLIEST index whose logit is
+// within tie_delta of the tile max (the reference takes argmax over float32 LOG-PROBS, whose quantum near
+// -log(V) is ~1e-6: logits closer than that tie and torch.max returns the lowest index -- see k_finalize)
+struct alignas(16) LogitPartial { float mx; int32_t idx; float sum; float lo_val; int32_t lo_idx; int32_t pad[3]; };
 
 struct GemmParams {
     SegMaps maps[2];
@@ -49,6 +52,7 @@ struct GemmParams {
     // LOGIT
     LogitPartial* partials;                  // [member*rows_pad + row, n_tiles]
     float* logit_trace; int64_t ld_trace;    // nullable, [member*rows + row, ld_trace]
+    float tie_delta;                         // one float32 ulp of log(V+1)
 };
 
 template <int EPI, int PREC> struct GemmCfg {
@@ -195,7 +199,6 @@ __global__ void __launch_bounds__(192) k_member_gemm(const __grid_constant__ Gem
         const int64_t grow = member * p.rows_pad + m_local;  // row in the wave buffers
         const float sW = 1.0f / (kThetaScale * kActScale);
         const float sE = sgn * p.sigma / kActScale;
-        const float ssig = sgn * p.sigma;
 
         // member bias for this tile: (theta_b + s*sigma*eps_b), summed over segments (i2h + h2h for the LSTM)
         for (int j = et; j < C::BN; j += 128) {
@@ -275,7 +278,7 @@ __global__ void __launch_bounds__(192) k_member_gemm(const __grid_constant__ Gem
             }
         } else {
             // PLAIN / LOGIT: 128 output columns, 16 at a time
-            float run_max = -INFINITY, run_sum = 0.f; int run_idx = 0;
+            float run_max = -INFINITY, run_sum = 0.f, lo_val = -INFINITY; int run_idx = 0, lo_idx = 0;
             const int n_base = nt * C::BN;
 #pragma unroll 1
             for (int c0 = 0; c0 < C::BN; c0 += 16) {
@@ -310,32 +313,34 @@ __global__ void __launch_bounds__(192) k_member_gemm(const __grid_constant__ Gem
                         }
                     }
                 } else {
-                    float cmax = -INFINITY; int cidx = 0;
+                    const float prev_max = run_max;
 #pragma unroll
                     for (int u = 0; u < 16; ++u) {
                         const int n = n_base + c0 + u;
                         const float v = (n < p.N) ? y[u] : -INFINITY;
                         y[u] = v;
-                        if (v > cmax) { cmax = v; cidx = n; }            // strict >: first index wins ties (torch.max)
+                        if (v > run_max) {                                   // strict >: first index wins exact ties (torch.max)
+                            if (!(lo_val >= v - p.tie_delta)) { lo_val = v; lo_idx = n; }
+                            run_max = v; run_idx = n;
+                        }
                     }
                     if (p.logit_trace && row_ok) {
                         float* lt = p.logit_trace + (member * p.rows + m_local) * p.ld_trace;
 #pragma unroll
                         for (int u = 0; u < 16; ++u) { const int n = n_base + c0 + u; if (n < p.N) lt[n] = y[u]; }
                     }
-                    if (cmax > run_max) {
-                        run_sum = run_sum * __expf(run_max - cmax);
-                        run_max = cmax; run_idx = cidx;
-                    }
+                    if (run_max > prev_max) run_sum = run_sum * __expf(prev_max - run_max);
                     if (run_max > -INFINITY) {
 #pragma unroll
-                        for (int u = 0; u < 16; ++u) run_sum += __expf(y[u] - run_max);
+                        for (int u = 0; u < 16; ++u) run_sum += (PREC == NES_PREC_EXACT) ? expf(y[u] - run_max) : __expf(y[u] - run_max);
                     }
                 }
             }
             if (EPI == EPI_LOGIT && row_ok) {
-                LogitPartial lp; lp.mx = run_max; lp.idx = run_idx; lp.sum = run_sum; lp.pad = 0.f;
-                *reinterpret_cast<float4*>(&p.partials[grow * p.n_tiles + nt]) = *reinterpret_cast<float4*>(&lp);
+                LogitPartial lp; lp.mx = run_max; lp.idx = run_idx; lp.sum = run_sum; lp.lo_val = lo_val; lp.lo_idx = lo_idx;
+                lp.pad[0] = lp.pad[1] = lp.pad[2] = 0;
+                float4* dst = reinterpret_cast<float4*>(&p.partials[grow * p.n_tiles + nt]);
+                dst[0] = reinterpret_cast<float4*>(&lp)[0]; dst[1] = reinterpret_cast<float4*>(&lp)[1];
             }
         }
         tc::tc_fence_before();

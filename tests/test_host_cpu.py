@@ -1,0 +1,109 @@
+"""CPU-only checks: the C-ABI library loads and exports every declared symbol, fails loudly without a GPU,
+the host-side layout equals the oracle's, and the population sharding / fitness all-gather logic works
+across 2 processes (gloo)."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope='module')
+def lib_path():
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as g
+    return g.build()
+
+
+def test_library_exports_every_declared_symbol(lib_path):
+    hdr = open(os.path.join(ROOT, 'include', 'nes_b200.h')).read()
+    names = sorted(set(re.findall(r'\b(nes_[a-z0-9_]+)\s*\(', hdr)))
+    assert len(names) >= 35
+    lib = ctypes.CDLL(lib_path)
+    assert [n for n in names if not hasattr(lib, n)] == []
+    import nes_b200
+    assert set(nes_b200._lib.SIGNATURES) == set(names)          # the ctypes binding covers the whole header
+    lib.nes_version.restype = ctypes.c_int
+    assert lib.nes_version() >= 100
+
+
+def test_no_cpu_fallback(lib_path):
+    if torch.cuda.is_available():
+        pytest.skip('a GPU is present')
+    import nes_b200
+    with pytest.raises(nes_b200.NesError):
+        nes_b200.NesContext(counts=[1000], table_len=4096)
+    with pytest.raises(nes_b200.NesError):
+        nes_b200.gemm_selftest(torch.zeros(8, 64), torch.zeros(8, 64))
+
+
+def test_product_code_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, 'nes-img-captioning_b200')
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(('.py', '.cu', '.cuh', '.h')):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r'^\s*(from|import)\s+oracle\b', src, re.M), f
+
+
+def test_host_layout_equals_oracle_layout():
+    import nes_b200
+    from oracle import noise
+    for V, E, R, Fd, ln, aff in [(9487, 512, 512, 2048, False, False), (9487, 128, 128, 2048, True, True), (199, 64, 64, 128, False, False),
+                                 (999, 64, 128, 256, True, False)]:
+        G = nes_b200.layout.granule(E, R, Fd)
+        assert G == noise.granularity(E, R, Fd)
+        specs, D, D_pad = nes_b200.layout.build_layout(nes_b200.layout.fc_tensors(V, E, R, Fd, ln, aff), G)
+        play, D2, D_pad2 = noise.padded_layout(noise.flat_layout(V, E, R, Fd, ln, aff), G)
+        assert (D, D_pad) == (D2, D_pad2)
+        assert [(t.name, t.shape, t.start, t.count, t.pstart) for t in specs] == [tuple(x) for x in play]
+    assert nes_b200.layout.build_layout(nes_b200.layout.fc_tensors(9487, 128, 128, 2048), 2048)[1] == 2865808   # tools/utils.py:180
+
+
+def test_shard_bounds_cover_the_population():
+    import nes_b200
+    for F in (0, 1, 7, 5000, 10001):
+        for W in (1, 2, 3, 8):
+            b = [nes_b200.shard_bounds(F, W, r) for r in range(W)]
+            assert b[0][0] == 0 and b[-1][1] == F
+            assert all(b[i][1] == b[i + 1][0] for i in range(W - 1))
+            assert max(h - l for l, h in b) - min(h - l for l, h in b) <= 1
+
+
+WORKER = r'''
+import os, sys
+sys.path.insert(0, sys.argv[1])
+import numpy as np, torch, torch.distributed as dist
+import nes_b200
+rank, world = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
+dist.init_process_group('gloo')
+F = 11
+full = torch.from_numpy(np.random.RandomState(0).randn(F, 2))
+lo, hi = nes_b200.shard_bounds(F, world, rank)
+got = nes_b200.all_gather_fitness(full[lo:hi].clone(), F, world, rank)
+assert torch.equal(got, full), (rank, got, full)
+# every rank then ranks the identical vector: identical centred ranks on every rank
+from oracle import nes_math
+w = torch.from_numpy(nes_math.rank_weights(got.numpy()))
+ws = [torch.empty_like(w) for _ in range(world)]
+dist.all_gather(ws, w)
+assert all(torch.equal(ws[0], x) for x in ws)
+dist.destroy_process_group()
+print('rank', rank, 'ok')
+'''
+
+
+def test_fitness_all_gather_world_size_2_gloo(tmp_path):
+    script = tmp_path / 'worker.py'
+    script.write_text(WORKER)
+    env = dict(os.environ, MASTER_ADDR='127.0.0.1', MASTER_PORT='29617', WORLD_SIZE='2', PYTHONPATH=ROOT)
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT], env=dict(env, RANK=str(r)), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+             for r in range(2)]
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
