@@ -187,6 +187,14 @@ def main():
     lo = rank * P
     state = {'base': 0, 'it': 0}
 
+    def sample_generation(it):
+        """(offset, parent) of every offspring of generation `it`, grouped by parent: members of one parent are
+        adjacent, so their CTAs hit the same theta tiles in L2 (the order of offspring carries no meaning in ES)"""
+        offs = ctx.sample_offsets(it, Pg, device=True)
+        pars = ctx.sample_parents(it, Pg, mu, device=True)
+        pars, perm = torch.sort(pars, stable=True)
+        return offs[perm].contiguous(), pars.contiguous()
+
     def select_and_materialise(fit_all, offs, pars):
         ranks = ctx.compute_ranks(fit_all, device=True)
         keep = torch.nonzero(ranks >= Pg - (mu - el)).flatten()
@@ -201,8 +209,7 @@ def main():
 
     def step_resident():
         it = state['it']; state['it'] += 1
-        offs = ctx.sample_offsets(it, Pg, device=True)
-        pars = ctx.sample_parents(it, Pg, mu, device=True)
+        offs, pars = sample_generation(it)
         ctx.rollout(offs[lo:lo + P], ones, fc_dev, a.sigma, parents=pars[lo:lo + P] + state['base'], precision=prec, out_device=dev)
         fit = ctx.logprob_fitness(P, rows, device=dev)
         if world > 1:
@@ -218,8 +225,7 @@ def main():
         """through the host boundary the reference has: features come from host memory, tokens / log-probs go back
         to the host where the scorer lives, the host returns fitness scalars"""
         it = state['it']; state['it'] += 1
-        offs = ctx.sample_offsets(it, Pg, device=True)
-        pars = ctx.sample_parents(it, Pg, mu, device=True)
+        offs, pars = sample_generation(it)
         lib, h = ctx.lib, ctx._h
         par_local = (pars[lo:lo + P] + state['base']).contiguous()
         off_local = offs[lo:lo + P].contiguous()

@@ -28,18 +28,34 @@ static PFN_encodeTiled get_encode() {
     }
     return fn;
 }
-// fp16 matrix viewed as [rows, K] row-major, box = 64 columns x box_rows rows, 128-byte swizzle
-static int make_map(CUtensorMap* m, const void* base, int64_t rows, int64_t K, int box_rows) {
+// fp16 matrix viewed as [rows, K] row-major, box = bk columns x box_rows rows, swizzle span = one box row (128 B / 64 B).
+// n_chunks > 1: 3-D view [n_chunks, rows - (n_chunks-1)*chunk_stride, K] whose outer dimension steps chunk_stride rows
+// (the 5 gate blocks of an LSTM weight matrix), so one request gathers the box_rows-row slab of every gate.
+static int make_map(CUtensorMap* m, const void* base, int64_t rows, int64_t K, int box_rows, int bk, int n_chunks = 1, int64_t chunk_stride = 0) {
     PFN_encodeTiled enc = get_encode();
     NES_CHECK(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
     NES_CHECK(K % 64 == 0, "inner dimension must be a multiple of 64");
-    NES_CHECK(rows >= 1, "empty tensor map");
-    cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
-    cuuint64_t gstr[1] = {(cuuint64_t)K * 2};
-    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    NES_CHECK(bk == 64 || bk == 32, "k-block must be 32 or 64 elements");
+    const CUtensorMapSwizzle swz = bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    CUresult r;
+    if (n_chunks <= 1) {
+        NES_CHECK(rows >= 1, "empty tensor map");
+        cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+        cuuint64_t gstr[1] = {(cuuint64_t)K * 2};
+        cuuint32_t box[2] = {(cuuint32_t)bk, (cuuint32_t)box_rows};
+        cuuint32_t estr[2] = {1u, 1u};
+        r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+        const int64_t rows1 = rows - (int64_t)(n_chunks - 1) * chunk_stride;
+        NES_CHECK(rows1 >= 1 && chunk_stride >= 1, "empty chunked tensor map");
+        cuuint64_t gdim[3] = {(cuuint64_t)K, (cuuint64_t)rows1, (cuuint64_t)n_chunks};
+        cuuint64_t gstr[2] = {(cuuint64_t)K * 2, (cuuint64_t)chunk_stride * K * 2};
+        cuuint32_t box[3] = {(cuuint32_t)bk, (cuuint32_t)box_rows, (cuuint32_t)n_chunks};
+        cuuint32_t estr[3] = {1u, 1u, 1u};
+        r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
     NES_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed");
     return 0;
 }
@@ -60,16 +76,17 @@ struct DecodeWorkspace {
     int64_t* d_off = nullptr; float* d_sign = nullptr; int32_t* d_parent = nullptr;
     int64_t* d_seq = nullptr; float* d_lp = nullptr; int64_t out_cap = 0;
     int64_t* d_forced = nullptr; int64_t forced_cap = 0;
-    std::map<std::tuple<const void*, int64_t, int64_t, int>, CUtensorMap> maps;
+    std::map<std::tuple<const void*, int64_t, int64_t, int, int, int, int64_t>, CUtensorMap> maps;
     bool attrs_set = false;
 };
 
-static int get_map(DecodeWorkspace* ws, CUtensorMap* out, const void* base, int64_t rows, int64_t K, int box_rows) {
-    auto key = std::make_tuple(base, rows, K, box_rows);
+static int get_map(DecodeWorkspace* ws, CUtensorMap* out, const void* base, int64_t rows, int64_t K, int box_rows, int bk,
+                   int n_chunks = 1, int64_t chunk_stride = 0) {
+    auto key = std::make_tuple(base, rows, K, box_rows, bk, n_chunks, chunk_stride);
     auto it = ws->maps.find(key);
     if (it == ws->maps.end()) {
         CUtensorMap m;
-        if (make_map(&m, base, rows, K, box_rows)) return 1;
+        if (make_map(&m, base, rows, K, box_rows, bk, n_chunks, chunk_stride)) return 1;
         it = ws->maps.emplace(key, m).first;
     }
     *out = it->second;
@@ -284,7 +301,7 @@ int decode_create(Ctx* c, int wave_members, int rows) {
     if (dmalloc(&ws->x_hi, WR * ws->E) || dmalloc(&ws->x_lo, WR * ws->E)) return 1;
     for (int b = 0; b < 2; ++b) if (dmalloc(&ws->h_hi[b], WR * ws->R) || dmalloc(&ws->h_lo[b], WR * ws->R)) return 1;
     if (dmalloc(&ws->c_state, WR * ws->R)) return 1;
-    if (dmalloc(&ws->partials, WR * ws->nt_logit)) return 1;
+    if (dmalloc(&ws->partials, WR)) return 1;
     if (dmalloc(&ws->unfinished, WR) || dmalloc(&ws->unf_count, (int64_t)(ws->T + 2) * ws->W)) return 1;
     if (d.layer_n) { if (dmalloc(&ws->pre_i, WR * 5 * ws->R) || dmalloc(&ws->pre_h, WR * 5 * ws->R)) return 1; }
     // zero everything once: padding rows of the operand buffers must stay finite forever
@@ -309,37 +326,47 @@ void decode_destroy(Ctx* c) {
     c->ws = nullptr;
 }
 
+static int sm_count(Ctx* c) {
+    static int n[64] = {0};
+    if (!n[c->device]) { if (cudaDeviceGetAttribute(&n[c->device], cudaDevAttrMultiProcessorCount, c->device) != cudaSuccess || n[c->device] < 1) n[c->device] = 148; }
+    return n[c->device];
+}
 template <int EPI, int PREC>
-static int launch_gemm(Ctx* c, const GemmParams& p, int64_t n_members) {
+static int launch_gemm(Ctx* c, GemmParams& p, int64_t n_members) {
     using C = GemmCfg<EPI, PREC>;
     static bool attr_done = false;
     if (!attr_done) {
         NES_CUDA(cudaFuncSetAttribute(k_member_gemm<EPI, PREC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         attr_done = true;
     }
-    NES_CHECK(n_members % p.group == 0, "member count must be a multiple of the scheduling group");
-    const int64_t grid = n_members * p.m_tiles * p.n_tiles;
-    NES_CHECK(grid < (1ll << 31), "grid too large");
+    const int64_t units = n_members * p.m_tiles;
+    NES_CHECK(units >= 1 && units < (1ll << 31), "bad unit count");
+    p.n_units = (int32_t)units;
+    // persistent: one CTA per SM, CTA b owns units b, b + grid, ... and sweeps every weight tile of each
+    const int sms = sm_count(c);
+    const unsigned grid = (unsigned)(units < sms ? units : sms);
     ProfScope prof(c, EPI == EPI_PLAIN ? PROF_PLAIN : (EPI == EPI_LSTM ? PROF_LSTM : PROF_LOGIT));
-    k_member_gemm<EPI, PREC><<<(unsigned)grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
+    k_member_gemm<EPI, PREC><<<grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
     c->launches++;
     NES_CUDA(cudaGetLastError());
     return 0;
 }
 template <int EPI>
-static int launch_gemm_prec(Ctx* c, const GemmParams& p, int64_t n_members, int prec) {
+static int launch_gemm_prec(Ctx* c, GemmParams& p, int64_t n_members, int prec) {
     return prec == NES_PREC_EXACT ? launch_gemm<EPI, NES_PREC_EXACT>(c, p, n_members) : launch_gemm<EPI, NES_PREC_FAST>(c, p, n_members);
 }
 
 // fill one GEMM segment: activations A (hi/lo buffers with `a_rows` rows), weight tensor wt, bias tensor bt (-1 none)
 static int fill_seg(Ctx* c, GemmParams& p, int s, const __half* a_hi, const __half* a_lo, int64_t a_rows, int K, int a_shared,
-                    int wt, int bt, int box_rows) {
+                    int wt, int bt, int box_rows, int prec, int n_chunks = 1, int64_t chunk_stride = 0) {
+    const int bk = prec == NES_PREC_EXACT ? GemmCfg<EPI_PLAIN, NES_PREC_EXACT>::BK : GemmCfg<EPI_PLAIN, NES_PREC_FAST>::BK;
     DecodeWorkspace* ws = c->ws;
     const Layout& L = c->lay;
-    if (get_map(ws, &p.maps[s].a_hi, a_hi, a_rows, K, 128) || get_map(ws, &p.maps[s].a_lo, a_lo, a_rows, K, 128)) return 1;
+    if (get_map(ws, &p.maps[s].a_hi, a_hi, a_rows, K, 128, bk) || get_map(ws, &p.maps[s].a_lo, a_lo, a_rows, K, 128, bk)) return 1;
     const int64_t th_rows = (int64_t)c->n_parents * L.D_pad / K;
-    if (get_map(ws, &p.maps[s].w_hi, c->theta_hi, th_rows, K, box_rows) || get_map(ws, &p.maps[s].w_lo, c->theta_lo, th_rows, K, box_rows)) return 1;
-    if (get_map(ws, &p.maps[s].eps, c->table, c->table_len / K, K, box_rows)) return 1;
+    if (get_map(ws, &p.maps[s].w_hi, c->theta_hi, th_rows, K, box_rows, bk, n_chunks, chunk_stride) ||
+        get_map(ws, &p.maps[s].w_lo, c->theta_lo, th_rows, K, box_rows, bk, n_chunks, chunk_stride)) return 1;
+    if (get_map(ws, &p.maps[s].eps, c->table, c->table_len / K, K, box_rows, bk, n_chunks, chunk_stride)) return 1;
     p.seg[s].K = K; p.seg[s].a_shared = a_shared; p.seg[s].w_pstart = L.t[wt].pstart;
     p.seg[s].b_start = bt >= 0 ? L.t[bt].start : -1;
     p.seg[s].b_pstart = bt >= 0 ? L.t[bt].pstart : -1;
@@ -423,19 +450,18 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
 
         GemmParams base{};
         base.rows = rows; base.rows_pad = rows_pad; base.m_tiles = m_tiles;
-        base.group = 1;
         base.D = L.D; base.D_pad = L.D_pad;
         base.off = ws->d_off + m0; base.sign = ws->d_sign + m0; base.parent = ws->d_parent + m0;
         base.theta32 = c->theta32; base.table = c->table; base.sigma = sigma;
-        // antithetic pairs (+eps, -eps adjacent) share their eps tiles through L2 when scheduled together
-        if (nm % 2 == 0) base.group = 2;
+        // antithetic pairs (+eps, -eps adjacent members) run on neighbouring SMs at the same tile index and share
+        // their eps tiles through L2
 
         const int64_t a_rows_w = (int64_t)ws->W * ws->rows_pad;
         // ---- t = 0 : x0 = img_embed(fc)
         {
             GemmParams p = base;
             p.nseg = 1; p.N = E; p.chunk_stride = 0; p.n_tiles = (E + 127) / 128;
-            if (fill_seg(c, p, 0, ws->fc_hi, ws->fc_lo, ws->fc_members * ws->rows_pad, Fd, shared_batch ? 1 : 0, T_IMG_W, T_IMG_B, 128)) return 1;
+            if (fill_seg(c, p, 0, ws->fc_hi, ws->fc_lo, ws->fc_members * ws->rows_pad, Fd, shared_batch ? 1 : 0, T_IMG_W, T_IMG_B, 128, precision)) return 1;
             p.out_hi = ws->x_hi; p.out_lo = ws->x_lo;
             if (launch_gemm_prec<EPI_PLAIN>(c, p, nm, precision)) return 1;
         }
@@ -446,16 +472,16 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             if (!c->dims.layer_n) {
                 GemmParams p = base;
                 p.nseg = 2; p.N = R; p.chunk_stride = R; p.n_tiles = R / 16;
-                if (fill_seg(c, p, 0, ws->x_hi, ws->x_lo, a_rows_w, E, 0, T_I2H_W, T_I2H_B, 16)) return 1;
-                if (fill_seg(c, p, 1, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_H2H_W, T_H2H_B, 16)) return 1;
+                if (fill_seg(c, p, 0, ws->x_hi, ws->x_lo, a_rows_w, E, 0, T_I2H_W, T_I2H_B, 16, precision, 5, R)) return 1;
+                if (fill_seg(c, p, 1, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_H2H_W, T_H2H_B, 16, precision, 5, R)) return 1;
                 p.c_state = ws->c_state; p.out_hi = ws->h_hi[hb ^ 1]; p.out_lo = ws->h_lo[hb ^ 1]; p.h_trace = ht;
                 if (launch_gemm_prec<EPI_LSTM>(c, p, nm, precision)) return 1;
             } else {
                 for (int s = 0; s < 2; ++s) {
                     GemmParams p = base;
                     p.nseg = 1; p.N = 5 * R; p.chunk_stride = 0; p.n_tiles = (5 * R + 127) / 128;
-                    if (s == 0) { if (fill_seg(c, p, 0, ws->x_hi, ws->x_lo, a_rows_w, E, 0, T_I2H_W, T_I2H_B, 128)) return 1; }
-                    else        { if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_H2H_W, T_H2H_B, 128)) return 1; }
+                    if (s == 0) { if (fill_seg(c, p, 0, ws->x_hi, ws->x_lo, a_rows_w, E, 0, T_I2H_W, T_I2H_B, 128, precision)) return 1; }
+                    else        { if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_H2H_W, T_H2H_B, 128, precision)) return 1; }
                     p.out_f32 = s == 0 ? ws->pre_i : ws->pre_h; p.ld_out = 5 * R;
                     if (launch_gemm_prec<EPI_PLAIN>(c, p, nm, precision)) return 1;
                 }
@@ -475,7 +501,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             if (t >= 1) {
                 GemmParams p = base;
                 p.nseg = 1; p.N = V1; p.chunk_stride = 0; p.n_tiles = ws->nt_logit;
-                if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128)) return 1;
+                if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128, precision)) return 1;
                 p.partials = ws->partials;
                 { int ex; frexpf(logf((float)V1), &ex); p.tie_delta = ldexpf(1.0f, ex - 1 - 23); }
                 p.logit_trace = logit_trace ? logit_trace + (int64_t)(t - 1) * n_members * rows * V1 : nullptr; p.ld_trace = V1;
@@ -483,7 +509,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             }
             if (t < T || t >= 1) {
                 FinalizeParams f{};
-                f.partials = ws->partials; f.n_tiles = ws->nt_logit; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
+                f.partials = ws->partials; f.n_tiles = 1; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
                 f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table;
                 f.D = L.D; f.emb_start = L.t[T_EMB_W].start; f.emb_pstart = L.t[T_EMB_W].pstart; f.sigma = sigma;
                 f.unfinished = ws->unfinished; f.unf_count = ws->unf_count; f.W = ws->W;
@@ -555,11 +581,12 @@ extern "C" int nes_gemm_selftest(int device, int M, int N, int K, const float* A
     k_split_scaled<<<256, 256>>>(dE, e16, nullptr, (int64_t)N * K, Np * K, 1.0f);
     NES_CUDA(cudaGetLastError());
     GemmParams p{};
-    if (make_map(&p.maps[0].a_hi, a_hi, Mp, K, 128) || make_map(&p.maps[0].a_lo, a_lo, Mp, K, 128) || make_map(&p.maps[0].w_hi, w_hi, Np, K, 128) ||
-        make_map(&p.maps[0].w_lo, w_lo, Np, K, 128) || make_map(&p.maps[0].eps, e16, Np, K, 128)) return 1;
+    const int bk = precision == NES_PREC_EXACT ? GemmCfg<EPI_PLAIN, NES_PREC_EXACT>::BK : GemmCfg<EPI_PLAIN, NES_PREC_FAST>::BK;
+    if (make_map(&p.maps[0].a_hi, a_hi, Mp, K, 128, bk) || make_map(&p.maps[0].a_lo, a_lo, Mp, K, 128, bk) || make_map(&p.maps[0].w_hi, w_hi, Np, K, 128, bk) ||
+        make_map(&p.maps[0].w_lo, w_lo, Np, K, 128, bk) || make_map(&p.maps[0].eps, e16, Np, K, 128, bk)) return 1;
     p.maps[1] = p.maps[0];
     p.nseg = 1; p.seg[0].K = K; p.seg[0].a_shared = 0; p.seg[0].w_pstart = 0; p.seg[0].b_start = -1; p.seg[0].b_pstart = -1;
-    p.rows = M; p.rows_pad = (int)Mp; p.m_tiles = (int)(Mp / 128); p.n_tiles = (int)(Np / 128); p.group = 1; p.N = N; p.chunk_stride = 0;
+    p.rows = M; p.rows_pad = (int)Mp; p.m_tiles = (int)(Mp / 128); p.n_tiles = (int)(Np / 128); p.N = N; p.chunk_stride = 0;
     p.D = 0; p.D_pad = 0; p.off = d_off; p.sign = d_sign; p.parent = nullptr; p.theta32 = nullptr; p.table = nullptr; p.sigma = sigma;
     p.out_f32 = dC; p.ld_out = N;
     Ctx tmp; tmp.stream = 0;

@@ -1,11 +1,20 @@
 // Population GEMM for perturbed members, factored as  y_m = x_m theta^T + s_m sigma x_m eps_m^T
-// (member m = theta + s_m*sigma*eps_m is never materialised).  One CTA computes a 128-row x BN-column
-// output tile of ONE member: TMA streams the activation tile, the matching theta tile (split-fp16 shadow,
-// L2 resident, shared by every member) and the member's eps tile straight out of the HBM noise table;
-// theta and eps tiles sit back to back in shared memory so ONE tcgen05.mma of N = 2*BN (3*BN in EXACT
-// mode) produces both partial products into adjacent TMEM column ranges; the epilogue combines them in
-// fp32 with the exact scale factors and applies the fused tail (bias + maxout-LSTM cell, or online
-// arg-max / log-sum-exp over the vocabulary tile, or a plain store).
+// (member m = theta + s_m*sigma*eps_m is never materialised).
+//
+// Persistent, warp-specialised tcgen05 kernel, one CTA per SM.  A CTA owns whole "units" (one member x one
+// 128-row block of its batch) and sweeps every weight tile j of the layer for that unit, so
+//   * all CTAs walk j in lock step: the theta tile j (split-fp16 shadow) is fetched from HBM once and then hit
+//     in L2 by every member of the same parent; the eps tile streams straight out of the HBM noise table and
+//     is shared through L2 by the antithetic partner running on the neighbouring SM;
+//   * the vocabulary arg-max / log-sum-exp of a row lives in ONE thread's registers across all tiles, so
+//     neither logits nor per-tile partials ever reach HBM;
+//   * TMEM holds two accumulator buffers: the epilogue of tile j overlaps the MMAs of tile j+1.
+// Roles: warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2..5 = epilogue (one TMEM lane
+// quarter each).  theta and eps tiles sit back to back in shared memory so ONE tcgen05.mma of N = 2*BN
+// produces both partial products into adjacent TMEM column ranges [theta-acc | eps-acc]; in EXACT mode the
+// low-order products (x_hi*theta_lo, x_lo*theta_hi, x_lo*eps) accumulate into the same columns.  The
+// epilogue combines the two ranges in fp32 with the exact scale factors and applies the fused tail
+// (bias + maxout-LSTM cell, or online arg-max / log-sum-exp, or a plain store).
 //
 // Reference math: captioning/nets.py:98-134 (LSTMCore.forward), :195-208 (img_embed, logit, log_softmax, max).
 #pragma once
@@ -17,9 +26,9 @@ namespace nes {
 enum { EPI_PLAIN = 0, EPI_LSTM = 1, EPI_LOGIT = 2 };
 
 struct alignas(64) SegMaps {
-    CUtensorMap a_hi, a_lo;    // activations [rows_total, K] fp16 (x * 2^5 split hi/lo), box 64 x 128
-    CUtensorMap w_hi, w_lo;    // theta shadow viewed as [n_parents*D_pad/K, K], box 64 x chunk_rows
-    CUtensorMap eps;           // noise table viewed as [L/K, K], box 64 x chunk_rows
+    CUtensorMap a_hi, a_lo;    // activations [rows_total, K] fp16 (x * 2^5 split hi/lo), box BK x 128
+    CUtensorMap w_hi, w_lo;    // theta shadow viewed as [n_parents*D_pad/K, K], box BK x chunk_rows
+    CUtensorMap eps;           // noise table viewed as [L/K, K], box BK x chunk_rows
 };
 struct SegInfo {
     int32_t K;
@@ -27,16 +36,17 @@ struct SegInfo {
     int64_t w_pstart;          // padded start of the weight tensor inside a noise row / theta shadow
     int64_t b_start, b_pstart; // bias tensor: flat start / padded start (-1: no bias)
 };
-// per (row, vocabulary tile): max logit + its first index, sum exp(logit - mx), and the EARLIEST index whose logit is
-// within tie_delta of the tile max (the reference takes argmax over float32 LOG-PROBS, whose quantum near
-// -log(V) is ~1e-6: logits closer than that tie and torch.max returns the lowest index -- see k_finalize)
+// per row, over the WHOLE vocabulary: max logit + its first index, sum exp(logit - mx), and the EARLIEST index
+// whose logit is within tie_delta of the max (the reference takes argmax over float32 LOG-PROBS, whose quantum
+// near -log(V) is ~1e-6: logits closer than that tie and torch.max returns the lowest index -- see k_finalize)
 struct alignas(16) LogitPartial { float mx; int32_t idx; float sum; float lo_val; int32_t lo_idx; int32_t pad[3]; };
 
 struct GemmParams {
     SegMaps maps[2];
     SegInfo seg[2];
     int32_t nseg;
-    int32_t rows, rows_pad, m_tiles, n_tiles, group;   // geometry / scheduling
+    int32_t rows, rows_pad, m_tiles, n_tiles;          // geometry
+    int32_t n_units;                                   // n_members * m_tiles
     int32_t N;                 // valid output columns per chunk (R for LSTM, N otherwise)
     int32_t chunk_stride;      // weight rows between chunks (R for LSTM)
     int64_t D, D_pad;
@@ -50,25 +60,34 @@ struct GemmParams {
     float* c_state;                          // [member*rows_pad + row, R] in place
     float* h_trace;                          // nullable, [member*rows + row, R]
     // LOGIT
-    LogitPartial* partials;                  // [member*rows_pad + row, n_tiles]
+    LogitPartial* partials;                  // [member*rows_pad + row]
     float* logit_trace; int64_t ld_trace;    // nullable, [member*rows + row, ld_trace]
     float tie_delta;                         // one float32 ulp of log(V+1)
 };
 
 template <int EPI, int PREC> struct GemmCfg {
-    static constexpr int BM = 128, BK = 64;
+    static constexpr int BM = 128;
+    static constexpr int BK = (PREC == NES_PREC_EXACT) ? 32 : 64;   // k-block: 64-byte / 128-byte swizzled rows
+    static constexpr int SWZ = BK * 2;                              // swizzle span in bytes
     static constexpr int NCH = (EPI == EPI_LSTM) ? 5 : 1;           // weight-row chunks gathered per tile
     static constexpr int CR  = (EPI == EPI_LSTM) ? 16 : 128;        // rows per chunk
     static constexpr int BN  = NCH * CR;                            // 80 or 128
-    static constexpr int NB  = (PREC == NES_PREC_EXACT) ? 3 : 2;    // B sub-tiles: [theta_lo] theta_hi eps
+    static constexpr int NB  = (PREC == NES_PREC_EXACT) ? 3 : 2;    // B sub-tiles: theta_hi eps [theta_lo]
     static constexpr int NA  = (PREC == NES_PREC_EXACT) ? 2 : 1;    // A sub-tiles: x_hi [x_lo]
-    static constexpr int A_BYTES = BM * BK * 2;                     // 16 KB
+    static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = NA * A_BYTES + NB * B_BYTES;
-    static constexpr int STAGES = (PREC == NES_PREC_EXACT) ? (EPI == EPI_LSTM ? 3 : 2) : (EPI == EPI_LSTM ? 3 : 2);
-    static constexpr int TMEM_COLS = (NB * BN <= 256) ? 256 : 512;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 1024 /*barriers, bias*/;
+    static constexpr int CTRL_BYTES = 2048;                         // barriers, tmem slot, bias[2][BN]
+    static constexpr int SMEM_MAX = 227 * 1024;
+    static constexpr int STAGES_FIT = (SMEM_MAX - 1024 - CTRL_BYTES) / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
+    static constexpr int ACC_STRIDE = 256;                          // TMEM columns between the two accumulator buffers
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + CTRL_BYTES;
     static constexpr int THREADS = 192;                             // warp0 TMA, warp1 MMA, warps 2-5 epilogue
+    static_assert(STAGES >= 2, "pipeline needs at least two stages");
+    static_assert(2 * BN <= ACC_STRIDE, "accumulator buffer too narrow");
+    static_assert(STAGE_BYTES % 1024 == 0 && A_BYTES % 1024 == 0 && B_BYTES % 1024 == 0, "swizzle atoms need 1024-byte alignment");
 };
 
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + expf(-x)); }
@@ -79,34 +98,23 @@ __device__ __forceinline__ void split_half_dev(float x, float scale, __half& hi,
 }
 
 template <int EPI, int PREC>
-__global__ void __launch_bounds__(192) k_member_gemm(const __grid_constant__ GemmParams p) {
+__global__ void __launch_bounds__(192, 1) k_member_gemm(const __grid_constant__ GemmParams p) {
     using C = GemmCfg<EPI, PREC>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* ctrl = smem + C::STAGES * C::STAGE_BYTES;
-    uint64_t* full_bar  = reinterpret_cast<uint64_t*>(ctrl);
-    uint64_t* empty_bar = full_bar + C::STAGES;
-    uint64_t* acc_bar   = empty_bar + C::STAGES;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
-    float* s_bias = reinterpret_cast<float*>(ctrl + 128);            // BN floats (<= 512 B)
+    uint64_t* full_bar   = reinterpret_cast<uint64_t*>(ctrl);
+    uint64_t* empty_bar  = full_bar + C::STAGES;
+    uint64_t* tfull_bar  = empty_bar + C::STAGES;     // [2] accumulator buffer complete (MMA -> epilogue)
+    uint64_t* tempty_bar = tfull_bar + 2;             // [2] accumulator buffer drained  (epilogue -> MMA)
+    uint32_t* tmem_slot  = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    float* s_bias = reinterpret_cast<float*>(ctrl + 512);            // [2][BN] floats (<= 1 KB)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    // ---- tile coordinates: CTAs of one weight-sharing group are adjacent (L2 reuse of theta / eps tiles)
-    const int per_group = p.group * p.m_tiles;
-    const int64_t gid = blockIdx.x / ((int64_t)p.n_tiles * per_group);
-    const int rem = (int)(blockIdx.x - gid * (int64_t)p.n_tiles * per_group);
-    const int nt = rem / per_group;
-    const int sub = rem % per_group;
-    const int64_t member = gid * p.group + sub / p.m_tiles;
-    const int mt = sub % p.m_tiles;
-    const int64_t off = p.off[member];
-    const float sgn = p.sign[member];
-    const int par = p.parent ? p.parent[member] : 0;
-
     if (threadIdx.x == 0) {
         for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
-        tc::mbar_init(acc_bar, 1);
+        for (int b = 0; b < 2; ++b) { tc::mbar_init(&tfull_bar[b], 1); tc::mbar_init(&tempty_bar[b], 4); }
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
@@ -120,34 +128,41 @@ __global__ void __launch_bounds__(192) k_member_gemm(const __grid_constant__ Gem
         if (lane == 0) {
             for (int s = 0; s < p.nseg; ++s) {
                 tc::prefetch_tmap(&p.maps[s].a_hi); tc::prefetch_tmap(&p.maps[s].w_hi); tc::prefetch_tmap(&p.maps[s].eps);
+                if (PREC == NES_PREC_EXACT) { tc::prefetch_tmap(&p.maps[s].a_lo); tc::prefetch_tmap(&p.maps[s].w_lo); }
             }
             int stage = 0; uint32_t phase = 0;
-            for (int s = 0; s < p.nseg; ++s) {
-                const SegMaps& mp = p.maps[s];
-                const SegInfo& sg = p.seg[s];
-                const int32_t a_row = (int32_t)((sg.a_shared ? 0 : member * p.rows_pad) + mt * C::BM);
-                const int32_t w_row0 = (int32_t)(((int64_t)par * p.D_pad + sg.w_pstart) / sg.K) + nt * C::CR;
-                const int32_t e_row0 = (int32_t)((off + sg.w_pstart) / sg.K) + nt * C::CR;
-                for (int kb = 0; kb < sg.K / C::BK; ++kb) {
-                    tc::mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t* st = smem + stage * C::STAGE_BYTES;
-                    tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
-                    tc::tma_load_2d(st, &mp.a_hi, &full_bar[stage], kb * C::BK, a_row);
-                    if (PREC == NES_PREC_EXACT) tc::tma_load_2d(st + C::A_BYTES, &mp.a_lo, &full_bar[stage], kb * C::BK, a_row);
-                    uint8_t* sb = st + C::NA * C::A_BYTES;
-#pragma unroll
-                    for (int c = 0; c < C::NCH; ++c) {
-                        const int32_t dr = c * p.chunk_stride;
-                        int sub_tile = 0;
-                        if (PREC == NES_PREC_EXACT) {
-                            tc::tma_load_2d(sb + (sub_tile * C::BN + c * C::CR) * 128, &mp.w_lo, &full_bar[stage], kb * C::BK, w_row0 + dr);
-                            ++sub_tile;
+            for (int u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+                const int64_t member = u / p.m_tiles;
+                const int mt = u % p.m_tiles;
+                const int64_t off = p.off[member];
+                const int par = p.parent ? p.parent[member] : 0;
+                for (int nt = 0; nt < p.n_tiles; ++nt) {
+                    for (int s = 0; s < p.nseg; ++s) {
+                        const SegMaps& mp = p.maps[s];
+                        const SegInfo& sg = p.seg[s];
+                        const int32_t a_row = (int32_t)((sg.a_shared ? 0 : member * p.rows_pad) + mt * C::BM);
+                        const int32_t w_row0 = (int32_t)(((int64_t)par * p.D_pad + sg.w_pstart) / sg.K) + nt * C::CR;
+                        const int32_t e_row0 = (int32_t)((off + sg.w_pstart) / sg.K) + nt * C::CR;
+                        const int nkb = sg.K / C::BK;
+                        for (int kb = 0; kb < nkb; ++kb) {
+                            tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+                            uint8_t* st = smem + stage * C::STAGE_BYTES;
+                            tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                            tc::tma_load_2d(st, &mp.a_hi, &full_bar[stage], kb * C::BK, a_row);
+                            if (PREC == NES_PREC_EXACT) tc::tma_load_2d(st + C::A_BYTES, &mp.a_lo, &full_bar[stage], kb * C::BK, a_row);
+                            uint8_t* sb = st + C::NA * C::A_BYTES;      // [theta_hi | eps | theta_lo]
+                            if (C::NCH > 1) {       // the gate blocks of this tile in one 3-D request per operand
+                                tc::tma_load_3d(sb, &mp.w_hi, &full_bar[stage], kb * C::BK, w_row0, 0);
+                                tc::tma_load_3d(sb + C::B_BYTES, &mp.eps, &full_bar[stage], kb * C::BK, e_row0, 0);
+                                if (PREC == NES_PREC_EXACT) tc::tma_load_3d(sb + 2 * C::B_BYTES, &mp.w_lo, &full_bar[stage], kb * C::BK, w_row0, 0);
+                            } else {
+                                tc::tma_load_2d(sb, &mp.w_hi, &full_bar[stage], kb * C::BK, w_row0);
+                                tc::tma_load_2d(sb + C::B_BYTES, &mp.eps, &full_bar[stage], kb * C::BK, e_row0);
+                                if (PREC == NES_PREC_EXACT) tc::tma_load_2d(sb + 2 * C::B_BYTES, &mp.w_lo, &full_bar[stage], kb * C::BK, w_row0);
+                            }
+                            if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                         }
-                        tc::tma_load_2d(sb + (sub_tile * C::BN + c * C::CR) * 128, &mp.w_hi, &full_bar[stage], kb * C::BK, w_row0 + dr);
-                        ++sub_tile;
-                        tc::tma_load_2d(sb + (sub_tile * C::BN + c * C::CR) * 128, &mp.eps, &full_bar[stage], kb * C::BK, e_row0 + dr);
                     }
-                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
@@ -155,191 +170,201 @@ __global__ void __launch_bounds__(192) k_member_gemm(const __grid_constant__ Gem
         // =========================== MMA issuer (one thread) ===========================
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            bool first = true;
-            for (int s = 0; s < p.nseg; ++s) {
-                for (int kb = 0; kb < p.seg[s].K / C::BK; ++kb) {
-                    tc::mbar_wait(&full_bar[stage], phase);
+            uint32_t it = 0;                                  // tile counter of this CTA
+            constexpr uint32_t idesc2 = tc::make_idesc_f16(128, 2 * C::BN);
+            constexpr uint32_t idesc1 = tc::make_idesc_f16(128, C::BN);
+            for (int u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+                for (int nt = 0; nt < p.n_tiles; ++nt, ++it) {
+                    const uint32_t buf = it & 1;
+                    tc::mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);     // epilogue has drained this buffer
                     tc::tc_fence_after();
-                    const uint32_t sa = tc::smem_u32(smem + stage * C::STAGE_BYTES);
-                    const uint32_t sb = sa + C::NA * C::A_BYTES;
+                    const uint32_t d_tmem = tmem_base + buf * C::ACC_STRIDE;
+                    bool first = true;
+                    for (int s = 0; s < p.nseg; ++s) {
+                        const int nkb = p.seg[s].K / C::BK;
+                        for (int kb = 0; kb < nkb; ++kb) {
+                            tc::mbar_wait(&full_bar[stage], phase);
+                            tc::tc_fence_after();
+                            const uint32_t sa = tc::smem_u32(smem + stage * C::STAGE_BYTES);
+                            const uint32_t sb = sa + C::NA * C::A_BYTES;
 #pragma unroll
-                    for (int k = 0; k < C::BK / 16; ++k) {
-                        const uint64_t a_hi = tc::make_smem_desc_sw128(sa + k * 32);
-                        const uint32_t acc = (first && k == 0) ? 0u : 1u;
-                        // x_hi * [theta_lo | theta_hi | eps]  (FAST: [theta_hi | eps])
-                        constexpr int NTOT = C::NB * C::BN;
-#pragma unroll
-                        for (int n0 = 0; n0 < NTOT; n0 += 256) {
-                            const int nn = (NTOT - n0) < 256 ? (NTOT - n0) : 256;
-                            tc::umma_f16(tmem_base + n0, a_hi, tc::make_smem_desc_sw128(sb + n0 * 128 + k * 32),
-                                         tc::make_idesc_f16(128, nn), acc);
-                        }
-                        if (PREC == NES_PREC_EXACT) {
-                            // x_lo * [theta_hi | eps]  -> columns [BN, 3BN)
-                            const uint64_t a_lo = tc::make_smem_desc_sw128(sa + C::A_BYTES + k * 32);
-                            constexpr int N2 = 2 * C::BN;
-                            tc::umma_f16(tmem_base + C::BN, a_lo, tc::make_smem_desc_sw128(sb + C::BN * 128 + k * 32),
-                                         tc::make_idesc_f16(128, N2), 1u);
+                            for (int k = 0; k < C::BK / 16; ++k) {
+                                const uint64_t a_hi = tc::make_smem_desc<C::SWZ>(sa + k * 32);
+                                // x_hi * [theta_hi | eps] -> [theta-acc | eps-acc]
+                                tc::umma_f16(d_tmem, a_hi, tc::make_smem_desc<C::SWZ>(sb + k * 32), idesc2, (first && k == 0) ? 0u : 1u);
+                                if (PREC == NES_PREC_EXACT) {
+                                    // x_hi * theta_lo -> theta-acc ;  x_lo * [theta_hi | eps] -> both
+                                    tc::umma_f16(d_tmem, a_hi, tc::make_smem_desc<C::SWZ>(sb + 2 * C::B_BYTES + k * 32), idesc1, 1u);
+                                    const uint64_t a_lo = tc::make_smem_desc<C::SWZ>(sa + C::A_BYTES + k * 32);
+                                    tc::umma_f16(d_tmem, a_lo, tc::make_smem_desc<C::SWZ>(sb + k * 32), idesc2, 1u);
+                                }
+                            }
+                            first = false;
+                            tc::umma_commit(&empty_bar[stage]);      // frees the smem stage once these MMAs retire
+                            if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                         }
                     }
-                    first = false;
-                    tc::umma_commit(&empty_bar[stage]);      // frees the smem stage once these MMAs retire
-                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                    tc::umma_commit(&tfull_bar[buf]);                // accumulators of this tile complete
                 }
             }
-            tc::umma_commit(acc_bar);                        // accumulators complete
         }
     } else {
         // =========================== epilogue (warps 2..5 = TMEM lane quarters 2,3,0,1) ===========================
         const int q = warp & 3;
         const int et = (warp - 2) * 32 + lane;               // 0..127 among epilogue threads
         const int row = q * 32 + lane;                       // accumulator row = TMEM lane
-        const int m_local = mt * C::BM + row;                // row within the member's batch
-        const bool row_ok = m_local < p.rows;
-        const int64_t grow = member * p.rows_pad + m_local;  // row in the wave buffers
         const float sW = 1.0f / (kThetaScale * kActScale);
-        const float sE = sgn * p.sigma / kActScale;
-
-        // member bias for this tile: (theta_b + s*sigma*eps_b), summed over segments (i2h + h2h for the LSTM)
-        for (int j = et; j < C::BN; j += 128) {
-            const int c = j / C::CR, u = j % C::CR;
-            const int n = c * p.chunk_stride + nt * C::CR + u;          // index inside the bias tensor
-            const bool ok = (nt * C::CR + u) < p.N;
-            float b = 0.f;
-            if (ok) {
-                for (int s = 0; s < p.nseg; ++s) {
-                    if (p.seg[s].b_start >= 0) {
-                        const float tb = p.theta32[(int64_t)par * p.D + p.seg[s].b_start + n];
-                        const float eb = __half2float(p.table[off + p.seg[s].b_pstart + n]);
-                        const float nz = __fmul_rn(p.sigma, eb);
-                        b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
-                    }
-                }
-            }
-            s_bias[j] = b;
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-
-        tc::mbar_wait(acc_bar, 0);
-        tc::tc_fence_after();
-        const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
-        constexpr int COL_HI = (PREC == NES_PREC_EXACT) ? C::BN : 0;
-        constexpr int COL_EPS = (C::NB - 1) * C::BN;
-
-        if (EPI == EPI_LSTM) {
-            // columns: chunk c (0 in, 1 forget, 2 out, 3/4 maxout candidates) x 16 hidden units
-            const int j0 = nt * 16;
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                float pre[5][8];
-#pragma unroll
-                for (int c = 0; c < 5; ++c) {
-                    float vh[8], ve[8];
-                    tc::tmem_ld8(trow + COL_HI + c * 16 + half * 8, vh);
-                    tc::tmem_ld8(trow + COL_EPS + c * 16 + half * 8, ve);
-                    if (PREC == NES_PREC_EXACT) {
-                        float vl[8];
-                        tc::tmem_ld8(trow + c * 16 + half * 8, vl);
-                        tc::tmem_ld_wait();
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) vh[u] += vl[u];
-                    } else {
-                        tc::tmem_ld_wait();
-                    }
-#pragma unroll
-                    for (int u = 0; u < 8; ++u) pre[c][u] = vh[u] * sW + ve[u] * sE + s_bias[c * 16 + half * 8 + u];
-                }
-                if (row_ok) {
-                    float* cp = p.c_state + grow * p.N + j0 + half * 8;
-                    float cprev[8];
-                    *reinterpret_cast<float4*>(&cprev[0]) = *reinterpret_cast<const float4*>(cp);
-                    *reinterpret_cast<float4*>(&cprev[4]) = *reinterpret_cast<const float4*>(cp + 4);
-                    float cn[8], hn[8];
-#pragma unroll
-                    for (int u = 0; u < 8; ++u) {
-                        const float ig = sigmoid_f(pre[0][u]), fg = sigmoid_f(pre[1][u]), og = sigmoid_f(pre[2][u]);
-                        const float cand = fmaxf(pre[3][u], pre[4][u]);
-                        cn[u] = __fadd_rn(__fmul_rn(fg, cprev[u]), __fmul_rn(ig, cand));
-                        hn[u] = og * tanhf(cn[u]);
-                    }
-                    *reinterpret_cast<float4*>(cp) = *reinterpret_cast<float4*>(&cn[0]);
-                    *reinterpret_cast<float4*>(cp + 4) = *reinterpret_cast<float4*>(&cn[4]);
-                    __half hh[8], hl[8];
-#pragma unroll
-                    for (int u = 0; u < 8; ++u) split_half_dev(hn[u], kActScale, hh[u], hl[u]);
-                    *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + j0 + half * 8) = *reinterpret_cast<uint4*>(hh);
-                    if (p.out_lo) *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + j0 + half * 8) = *reinterpret_cast<uint4*>(hl);
-                    if (p.h_trace) {
-                        float* ht = p.h_trace + (member * p.rows + m_local) * (int64_t)p.N + j0 + half * 8;
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) ht[u] = hn[u];
-                    }
-                }
-            }
-        } else {
-            // PLAIN / LOGIT: 128 output columns, 16 at a time
+        constexpr int COL_EPS = C::BN;
+        uint32_t it = 0;
+        for (int u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+            const int64_t member = u / p.m_tiles;
+            const int mt = u % p.m_tiles;
+            const int64_t off = p.off[member];
+            const float sgn = p.sign[member];
+            const int par = p.parent ? p.parent[member] : 0;
+            const int m_local = mt * C::BM + row;                // row within the member's batch
+            const bool row_ok = m_local < p.rows;
+            const int64_t grow = member * p.rows_pad + m_local;  // row in the wave buffers
+            const float sE = sgn * p.sigma / kActScale;
+            // running arg-max / log-sum-exp of this row over the whole vocabulary (LOGIT)
             float run_max = -INFINITY, run_sum = 0.f, lo_val = -INFINITY; int run_idx = 0, lo_idx = 0;
-            const int n_base = nt * C::BN;
-#pragma unroll 1
-            for (int c0 = 0; c0 < C::BN; c0 += 16) {
-                float vh[16], ve[16];
-                tc::tmem_ld16(trow + COL_HI + c0, vh);
-                tc::tmem_ld16(trow + COL_EPS + c0, ve);
-                if (PREC == NES_PREC_EXACT) {
-                    float vl[16];
-                    tc::tmem_ld16(trow + c0, vl);
-                    tc::tmem_ld_wait();
-#pragma unroll
-                    for (int u = 0; u < 16; ++u) vh[u] += vl[u];
-                } else {
-                    tc::tmem_ld_wait();
+
+            for (int nt = 0; nt < p.n_tiles; ++nt, ++it) {
+                const uint32_t buf = it & 1;
+                float* bias = s_bias + buf * C::BN;
+                // member bias for this tile: (theta_b + s*sigma*eps_b), summed over segments (i2h + h2h for the LSTM)
+                for (int j = et; j < C::BN; j += 128) {
+                    const int c = j / C::CR, uu = j % C::CR;
+                    const int n = c * p.chunk_stride + nt * C::CR + uu;         // index inside the bias tensor
+                    const bool ok = (nt * C::CR + uu) < p.N;
+                    float b = 0.f;
+                    if (ok) {
+                        for (int s = 0; s < p.nseg; ++s) {
+                            if (p.seg[s].b_start >= 0) {
+                                const float tb = p.theta32[(int64_t)par * p.D + p.seg[s].b_start + n];
+                                const float eb = __half2float(p.table[off + p.seg[s].b_pstart + n]);
+                                const float nz = __fmul_rn(p.sigma, eb);
+                                b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
+                            }
+                        }
+                    }
+                    bias[j] = b;
                 }
-                float y[16];
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                float cprev[16];                                  // LSTM: this row's cell state, fetched while the MMAs run
+                if (EPI == EPI_LSTM && row_ok) {
+                    const float4* cp4 = reinterpret_cast<const float4*>(p.c_state + grow * p.N + nt * 16);
 #pragma unroll
-                for (int u = 0; u < 16; ++u) y[u] = vh[u] * sW + ve[u] * sE + s_bias[c0 + u];
-                if (EPI == EPI_PLAIN) {
-                    if (row_ok) {
+                    for (int v4 = 0; v4 < 4; ++v4) *reinterpret_cast<float4*>(&cprev[4 * v4]) = cp4[v4];
+                }
+
+                tc::mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
+                tc::tc_fence_after();
+                const uint32_t trow = tmem_base + buf * C::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
+
+                if (EPI == EPI_LSTM) {
+                    // columns: chunk c (0 in, 1 forget, 2 out, 3/4 maxout candidates) x 16 hidden units
+                    const int j0 = nt * 16;
 #pragma unroll
-                        for (int u = 0; u < 16; ++u) {
-                            const int n = n_base + c0 + u;
-                            if (n < p.N) {
-                                if (p.out_f32) p.out_f32[grow * p.ld_out + n] = y[u];
-                                if (p.out_hi) {
-                                    __half a, b; split_half_dev(y[u], kActScale, a, b);
-                                    p.out_hi[grow * p.N + n] = a;
-                                    if (p.out_lo) p.out_lo[grow * p.N + n] = b;
-                                }
+                    for (int half = 0; half < 2; ++half) {
+                        float pre[5][8];
+#pragma unroll
+                        for (int c = 0; c < 5; ++c) {
+                            float vh[8], ve[8];
+                            tc::tmem_ld8(trow + c * 16 + half * 8, vh);
+                            tc::tmem_ld8(trow + COL_EPS + c * 16 + half * 8, ve);
+                            tc::tmem_ld_wait();
+#pragma unroll
+                            for (int uu = 0; uu < 8; ++uu) pre[c][uu] = vh[uu] * sW + ve[uu] * sE + bias[c * 16 + half * 8 + uu];
+                        }
+                        if (row_ok) {
+                            float* cp = p.c_state + grow * p.N + j0 + half * 8;
+                            float cn[8], hn[8];
+#pragma unroll
+                            for (int uu = 0; uu < 8; ++uu) {
+                                const float ig = sigmoid_f(pre[0][uu]), fg = sigmoid_f(pre[1][uu]), og = sigmoid_f(pre[2][uu]);
+                                const float cand = fmaxf(pre[3][uu], pre[4][uu]);
+                                cn[uu] = __fadd_rn(__fmul_rn(fg, cprev[half * 8 + uu]), __fmul_rn(ig, cand));
+                                hn[uu] = og * tanhf(cn[uu]);
+                            }
+                            *reinterpret_cast<float4*>(cp) = *reinterpret_cast<float4*>(&cn[0]);
+                            *reinterpret_cast<float4*>(cp + 4) = *reinterpret_cast<float4*>(&cn[4]);
+                            __half hh[8], hl[8];
+#pragma unroll
+                            for (int uu = 0; uu < 8; ++uu) split_half_dev(hn[uu], kActScale, hh[uu], hl[uu]);
+                            *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + j0 + half * 8) = *reinterpret_cast<uint4*>(hh);
+                            if (p.out_lo) *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + j0 + half * 8) = *reinterpret_cast<uint4*>(hl);
+                            if (p.h_trace) {
+                                float* ht = p.h_trace + (member * p.rows + m_local) * (int64_t)p.N + j0 + half * 8;
+#pragma unroll
+                                for (int uu = 0; uu < 8; ++uu) ht[uu] = hn[uu];
                             }
                         }
                     }
                 } else {
-                    const float prev_max = run_max;
+                    // PLAIN / LOGIT: 128 output columns, 32 at a time
+                    const int n_base = nt * C::BN;
+#pragma unroll 1
+                    for (int c0 = 0; c0 < C::BN; c0 += 32) {
+                        float vh[32], ve[32];
+                        tc::tmem_ld32(trow + c0, vh);
+                        tc::tmem_ld32(trow + COL_EPS + c0, ve);
+                        tc::tmem_ld_wait();
+                        float y[32];
 #pragma unroll
-                    for (int u = 0; u < 16; ++u) {
-                        const int n = n_base + c0 + u;
-                        const float v = (n < p.N) ? y[u] : -INFINITY;
-                        y[u] = v;
-                        if (v > run_max) {                                   // strict >: first index wins exact ties (torch.max)
-                            if (!(lo_val >= v - p.tie_delta)) { lo_val = v; lo_idx = n; }
-                            run_max = v; run_idx = n;
+                        for (int uu = 0; uu < 32; ++uu) y[uu] = vh[uu] * sW + ve[uu] * sE + bias[c0 + uu];
+                        if (EPI == EPI_PLAIN) {
+                            if (row_ok) {
+#pragma unroll
+                                for (int uu = 0; uu < 32; ++uu) {
+                                    const int n = n_base + c0 + uu;
+                                    if (n < p.N) {
+                                        if (p.out_f32) p.out_f32[grow * p.ld_out + n] = y[uu];
+                                        if (p.out_hi) {
+                                            __half a, b; split_half_dev(y[uu], kActScale, a, b);
+                                            p.out_hi[grow * p.N + n] = a;
+                                            if (p.out_lo) p.out_lo[grow * p.N + n] = b;
+                                        }
+                                    }
+                                }
+                            }
+                        } else {
+                            const float prev_max = run_max;
+#pragma unroll
+                            for (int uu = 0; uu < 32; ++uu) {
+                                const int n = n_base + c0 + uu;
+                                const float v = (n < p.N) ? y[uu] : -INFINITY;
+                                y[uu] = v;
+                                if (v > run_max) {                                   // strict >: first index wins exact ties (torch.max)
+                                    if (!(lo_val >= v - p.tie_delta)) {              // the tie candidate fell out of the window
+                                        if (run_max >= v - p.tie_delta) { lo_val = run_max; lo_idx = run_idx; }   // the previous max is still inside, and earlier
+                                        else { lo_val = v; lo_idx = n; }
+                                    }
+                                    run_max = v; run_idx = n;
+                                }
+                            }
+                            if (p.logit_trace && row_ok) {
+                                float* lt = p.logit_trace + (member * p.rows + m_local) * p.ld_trace;
+#pragma unroll
+                                for (int uu = 0; uu < 32; ++uu) { const int n = n_base + c0 + uu; if (n < p.N) lt[n] = y[uu]; }
+                            }
+                            if (run_max > prev_max) run_sum = run_sum * __expf(prev_max - run_max);
+                            if (run_max > -INFINITY) {
+#pragma unroll
+                                for (int uu = 0; uu < 32; ++uu) run_sum += (PREC == NES_PREC_EXACT) ? expf(y[uu] - run_max) : __expf(y[uu] - run_max);
+                            }
                         }
                     }
-                    if (p.logit_trace && row_ok) {
-                        float* lt = p.logit_trace + (member * p.rows + m_local) * p.ld_trace;
-#pragma unroll
-                        for (int u = 0; u < 16; ++u) { const int n = n_base + c0 + u; if (n < p.N) lt[n] = y[u]; }
-                    }
-                    if (run_max > prev_max) run_sum = run_sum * __expf(prev_max - run_max);
-                    if (run_max > -INFINITY) {
-#pragma unroll
-                        for (int u = 0; u < 16; ++u) run_sum += (PREC == NES_PREC_EXACT) ? expf(y[u] - run_max) : __expf(y[u] - run_max);
-                    }
                 }
+                // this accumulator buffer may be overwritten by the MMAs of tile it+2
+                tc::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(&tempty_bar[buf]);
             }
             if (EPI == EPI_LOGIT && row_ok) {
                 LogitPartial lp; lp.mx = run_max; lp.idx = run_idx; lp.sum = run_sum; lp.lo_val = lo_val; lp.lo_idx = lo_idx;
                 lp.pad[0] = lp.pad[1] = lp.pad[2] = 0;
-                float4* dst = reinterpret_cast<float4*>(&p.partials[grow * p.n_tiles + nt]);
+                float4* dst = reinterpret_cast<float4*>(&p.partials[grow]);
                 dst[0] = reinterpret_cast<float4*>(&lp)[0]; dst[1] = reinterpret_cast<float4*>(&lp)[1];
             }
         }
