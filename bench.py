@@ -41,6 +41,7 @@ def parse():
     ap.add_argument('--table-log2', type=int, default=28)
     ap.add_argument('--cpu-seconds', type=float, default=15.0)
     ap.add_argument('--no-extras', action='store_true')
+    ap.add_argument('--debug-same-offset', action='store_true', help='experiment only: every member reads the same noise row (eps L2-resident)')
     return ap.parse_args()
 
 
@@ -192,6 +193,8 @@ def main():
         adjacent, so their CTAs hit the same theta tiles in L2 (the order of offspring carries no meaning in ES)"""
         offs = ctx.sample_offsets(it, Pg, device=True)
         pars = ctx.sample_parents(it, Pg, mu, device=True)
+        if a.debug_same_offset:
+            offs = offs[:1].expand(Pg).contiguous()
         pars, perm = torch.sort(pars, stable=True)
         return offs[perm].contiguous(), pars.contiguous()
 

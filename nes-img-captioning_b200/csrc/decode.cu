@@ -7,6 +7,7 @@
 //              logits = logit(h) -> argmax, log-prob    LOGIT member GEMM + k_finalize
 // Finished-mask, early break and the seq / seq_logprobs writes follow :233-243.
 #include "member_gemm.cuh"
+#include <cstdlib>
 #include <map>
 #include <tuple>
 
@@ -301,7 +302,7 @@ int decode_create(Ctx* c, int wave_members, int rows) {
     if (dmalloc(&ws->x_hi, WR * ws->E) || dmalloc(&ws->x_lo, WR * ws->E)) return 1;
     for (int b = 0; b < 2; ++b) if (dmalloc(&ws->h_hi[b], WR * ws->R) || dmalloc(&ws->h_lo[b], WR * ws->R)) return 1;
     if (dmalloc(&ws->c_state, WR * ws->R)) return 1;
-    if (dmalloc(&ws->partials, WR)) return 1;
+    if (dmalloc(&ws->partials, 2 * WR)) return 1;
     if (dmalloc(&ws->unfinished, WR) || dmalloc(&ws->unf_count, (int64_t)(ws->T + 2) * ws->W)) return 1;
     if (d.layer_n) { if (dmalloc(&ws->pre_i, WR * 5 * ws->R) || dmalloc(&ws->pre_h, WR * 5 * ws->R)) return 1; }
     // zero everything once: padding rows of the operand buffers must stay finite forever
@@ -342,6 +343,7 @@ static int launch_gemm(Ctx* c, GemmParams& p, int64_t n_members) {
     const int64_t units = n_members * p.m_tiles;
     NES_CHECK(units >= 1 && units < (1ll << 31), "bad unit count");
     p.n_units = (int32_t)units;
+    { static int dbg = -1; if (dbg < 0) { const char* e = getenv("NES_DEBUG"); dbg = e ? atoi(e) : 0; } p.debug = dbg; }
     // persistent: one CTA per SM, CTA b owns units b, b + grid, ... and sweeps every weight tile of each
     const int sms = sm_count(c);
     const unsigned grid = (unsigned)(units < sms ? units : sms);
@@ -509,7 +511,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             }
             if (t < T || t >= 1) {
                 FinalizeParams f{};
-                f.partials = ws->partials; f.n_tiles = 1; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
+                f.partials = ws->partials; f.n_tiles = 2; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
                 f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table;
                 f.D = L.D; f.emb_start = L.t[T_EMB_W].start; f.emb_pstart = L.t[T_EMB_W].pstart; f.sigma = sigma;
                 f.unfinished = ws->unfinished; f.unf_count = ws->unf_count; f.W = ws->W;

@@ -9,8 +9,8 @@
 //   * the vocabulary arg-max / log-sum-exp of a row lives in ONE thread's registers across all tiles, so
 //     neither logits nor per-tile partials ever reach HBM;
 //   * TMEM holds two accumulator buffers: the epilogue of tile j overlaps the MMAs of tile j+1.
-// Roles: warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2..5 = epilogue (one TMEM lane
-// quarter each).  theta and eps tiles sit back to back in shared memory so ONE tcgen05.mma of N = 2*BN
+// Roles: warps 0 and 10 = TMA producers (alternate stages), warp 1 = MMA issuer (one thread), warps 2..9 =
+// epilogue (TMEM lane quarter = warp & 3, two warps per quarter split the tile's columns).  theta and eps tiles sit back to back in shared memory so ONE tcgen05.mma of N = 2*BN
 // produces both partial products into adjacent TMEM column ranges [theta-acc | eps-acc]; in EXACT mode the
 // low-order products (x_hi*theta_lo, x_lo*theta_hi, x_lo*eps) accumulate into the same columns.  The
 // epilogue combines the two ranges in fp32 with the exact scale factors and applies the fused tail
@@ -60,9 +60,10 @@ struct GemmParams {
     float* c_state;                          // [member*rows_pad + row, R] in place
     float* h_trace;                          // nullable, [member*rows + row, R]
     // LOGIT
-    LogitPartial* partials;                  // [member*rows_pad + row]
+    LogitPartial* partials;                  // [member*rows_pad + row][2]: one per column half (epilogue warp pair)
     float* logit_trace; int64_t ld_trace;    // nullable, [member*rows + row, ld_trace]
     float tie_delta;                         // one float32 ulp of log(V+1)
+    int32_t debug;                           // experiments: bit 0 = skip the epilogue work (timing only, wrong results)
 };
 
 template <int EPI, int PREC> struct GemmCfg {
@@ -84,7 +85,7 @@ template <int EPI, int PREC> struct GemmCfg {
     static constexpr int ACC_STRIDE = 256;                          // TMEM columns between the two accumulator buffers
     static constexpr int TMEM_COLS = 512;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + CTRL_BYTES;
-    static constexpr int THREADS = 192;                             // warp0 TMA, warp1 MMA, warps 2-5 epilogue
+    static constexpr int THREADS = 352;                             // warps 0 and 10 TMA (alternate stages), warp 1 MMA, warps 2-9 epilogue
     static_assert(STAGES >= 2, "pipeline needs at least two stages");
     static_assert(2 * BN <= ACC_STRIDE, "accumulator buffer too narrow");
     static_assert(STAGE_BYTES % 1024 == 0 && A_BYTES % 1024 == 0 && B_BYTES % 1024 == 0, "swizzle atoms need 1024-byte alignment");
@@ -98,7 +99,7 @@ __device__ __forceinline__ void split_half_dev(float x, float scale, __half& hi,
 }
 
 template <int EPI, int PREC>
-__global__ void __launch_bounds__(192, 1) k_member_gemm(const __grid_constant__ GemmParams p) {
+__global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ GemmParams p) {
     using C = GemmCfg<EPI, PREC>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -114,7 +115,7 @@ __global__ void __launch_bounds__(192, 1) k_member_gemm(const __grid_constant__ 
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
-        for (int b = 0; b < 2; ++b) { tc::mbar_init(&tfull_bar[b], 1); tc::mbar_init(&tempty_bar[b], 4); }
+        for (int b = 0; b < 2; ++b) { tc::mbar_init(&tfull_bar[b], 1); tc::mbar_init(&tempty_bar[b], 8); }
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
@@ -123,14 +124,16 @@ __global__ void __launch_bounds__(192, 1) k_member_gemm(const __grid_constant__ 
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
-        // =========================== TMA producer ===========================
+    if (warp == 0 || warp == 10) {
+        // ===== TMA producers: a stage costs one thread ~450 cycles of barrier + issue latency (measured, tools/tma_bw.cu),
+        // ===== more than the MMAs of a small stage take, so two warps fill alternate stages
+        const int pid = warp == 0 ? 0 : 1;
         if (lane == 0) {
             for (int s = 0; s < p.nseg; ++s) {
                 tc::prefetch_tmap(&p.maps[s].a_hi); tc::prefetch_tmap(&p.maps[s].w_hi); tc::prefetch_tmap(&p.maps[s].eps);
                 if (PREC == NES_PREC_EXACT) { tc::prefetch_tmap(&p.maps[s].a_lo); tc::prefetch_tmap(&p.maps[s].w_lo); }
             }
-            int stage = 0; uint32_t phase = 0;
+            int stage = 0; uint32_t phase = 0; uint32_t q = 0;
             for (int u = blockIdx.x; u < p.n_units; u += gridDim.x) {
                 const int64_t member = u / p.m_tiles;
                 const int mt = u % p.m_tiles;
@@ -145,6 +148,7 @@ __global__ void __launch_bounds__(192, 1) k_member_gemm(const __grid_constant__ 
                         const int32_t e_row0 = (int32_t)((off + sg.w_pstart) / sg.K) + nt * C::CR;
                         const int nkb = sg.K / C::BK;
                         for (int kb = 0; kb < nkb; ++kb) {
+                            if (((q++) & 1) != pid) { if (++stage == C::STAGES) { stage = 0; phase ^= 1; } continue; }
                             tc::mbar_wait(&empty_bar[stage], phase ^ 1);
                             uint8_t* st = smem + stage * C::STAGE_BYTES;
                             tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
@@ -209,110 +213,114 @@ __global__ void __launch_bounds__(192, 1) k_member_gemm(const __grid_constant__ 
             }
         }
     } else {
-        // =========================== epilogue (warps 2..5 = TMEM lane quarters 2,3,0,1) ===========================
+        // ======= epilogue: warps 2..9.  TMEM lane quarter = warp & 3 (rows), column half = (warp - 2) >> 2 =======
         const int q = warp & 3;
-        const int et = (warp - 2) * 32 + lane;               // 0..127 among epilogue threads
+        const int hf = (warp - 2) >> 2;                      // which half of the tile's columns / hidden units
+        const int et = (warp - 2) * 32 + lane;               // 0..255 among epilogue threads
         const int row = q * 32 + lane;                       // accumulator row = TMEM lane
         const float sW = 1.0f / (kThetaScale * kActScale);
         constexpr int COL_EPS = C::BN;
+        constexpr float kLog2e = 1.4426950408889634f;
+        // member bias of tile (u, nt), element et: theta_b + s*sigma*eps_b, summed over segments (i2h + h2h for the LSTM).
+        // Loaded one tile AHEAD into a register so the dependent global loads never sit on the epilogue's critical path.
+        auto bias_val = [&](int u, int nt) -> float {
+            if (u >= p.n_units || et >= C::BN) return 0.f;
+            const int64_t member = u / p.m_tiles;
+            const int c = et / C::CR, uu = et % C::CR;
+            if (nt * C::CR + uu >= p.N) return 0.f;
+            const int n = c * p.chunk_stride + nt * C::CR + uu;          // index inside the bias tensor
+            const int64_t off = p.off[member];
+            const float sgn = p.sign[member];
+            const int par = p.parent ? p.parent[member] : 0;
+            float b = 0.f;
+            for (int s = 0; s < p.nseg; ++s) {
+                if (p.seg[s].b_start >= 0) {
+                    const float tb = p.theta32[(int64_t)par * p.D + p.seg[s].b_start + n];
+                    const float nz = __fmul_rn(p.sigma, __half2float(p.table[off + p.seg[s].b_pstart + n]));
+                    b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
+                }
+            }
+            return b;
+        };
+        float b_cur = bias_val(blockIdx.x, 0);
         uint32_t it = 0;
         for (int u = blockIdx.x; u < p.n_units; u += gridDim.x) {
             const int64_t member = u / p.m_tiles;
             const int mt = u % p.m_tiles;
-            const int64_t off = p.off[member];
             const float sgn = p.sign[member];
-            const int par = p.parent ? p.parent[member] : 0;
             const int m_local = mt * C::BM + row;                // row within the member's batch
             const bool row_ok = m_local < p.rows;
             const int64_t grow = member * p.rows_pad + m_local;  // row in the wave buffers
             const float sE = sgn * p.sigma / kActScale;
-            // running arg-max / log-sum-exp of this row over the whole vocabulary (LOGIT)
+            // running arg-max / log-sum-exp of this row over this thread's half of every vocabulary tile (LOGIT)
             float run_max = -INFINITY, run_sum = 0.f, lo_val = -INFINITY; int run_idx = 0, lo_idx = 0;
 
             for (int nt = 0; nt < p.n_tiles; ++nt, ++it) {
                 const uint32_t buf = it & 1;
                 float* bias = s_bias + buf * C::BN;
-                // member bias for this tile: (theta_b + s*sigma*eps_b), summed over segments (i2h + h2h for the LSTM)
-                for (int j = et; j < C::BN; j += 128) {
-                    const int c = j / C::CR, uu = j % C::CR;
-                    const int n = c * p.chunk_stride + nt * C::CR + uu;         // index inside the bias tensor
-                    const bool ok = (nt * C::CR + uu) < p.N;
-                    float b = 0.f;
-                    if (ok) {
-                        for (int s = 0; s < p.nseg; ++s) {
-                            if (p.seg[s].b_start >= 0) {
-                                const float tb = p.theta32[(int64_t)par * p.D + p.seg[s].b_start + n];
-                                const float eb = __half2float(p.table[off + p.seg[s].b_pstart + n]);
-                                const float nz = __fmul_rn(p.sigma, eb);
-                                b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
-                            }
-                        }
-                    }
-                    bias[j] = b;
-                }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-                float cprev[16];                                  // LSTM: this row's cell state, fetched while the MMAs run
+                if (et < C::BN) bias[et] = b_cur;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                b_cur = (nt + 1 < p.n_tiles) ? bias_val(u, nt + 1) : bias_val(u + gridDim.x, 0);
+                float cprev[8];                                   // LSTM: this row's cell state, fetched while the MMAs run
                 if (EPI == EPI_LSTM && row_ok) {
-                    const float4* cp4 = reinterpret_cast<const float4*>(p.c_state + grow * p.N + nt * 16);
-#pragma unroll
-                    for (int v4 = 0; v4 < 4; ++v4) *reinterpret_cast<float4*>(&cprev[4 * v4]) = cp4[v4];
+                    const float4* cp4 = reinterpret_cast<const float4*>(p.c_state + grow * p.N + nt * 16 + hf * 8);
+                    *reinterpret_cast<float4*>(&cprev[0]) = cp4[0];
+                    *reinterpret_cast<float4*>(&cprev[4]) = cp4[1];
                 }
-
                 tc::mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
                 tc::tc_fence_after();
                 const uint32_t trow = tmem_base + buf * C::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
-
+                if (!(p.debug & 1)) {
                 if (EPI == EPI_LSTM) {
-                    // columns: chunk c (0 in, 1 forget, 2 out, 3/4 maxout candidates) x 16 hidden units
-                    const int j0 = nt * 16;
+                    // columns: chunk c (0 in, 1 forget, 2 out, 3/4 maxout candidates) x 16 hidden units; this warp owns 8 of them
+                    const int j0 = nt * 16 + hf * 8;
+                    float pre[5][8];
 #pragma unroll
-                    for (int half = 0; half < 2; ++half) {
-                        float pre[5][8];
+                    for (int c = 0; c < 5; ++c) {
+                        float vh[8], ve[8];
+                        tc::tmem_ld8(trow + c * 16 + hf * 8, vh);
+                        tc::tmem_ld8(trow + COL_EPS + c * 16 + hf * 8, ve);
+                        tc::tmem_ld_wait();
 #pragma unroll
-                        for (int c = 0; c < 5; ++c) {
-                            float vh[8], ve[8];
-                            tc::tmem_ld8(trow + c * 16 + half * 8, vh);
-                            tc::tmem_ld8(trow + COL_EPS + c * 16 + half * 8, ve);
-                            tc::tmem_ld_wait();
+                        for (int uu = 0; uu < 8; ++uu) pre[c][uu] = vh[uu] * sW + ve[uu] * sE + bias[c * 16 + hf * 8 + uu];
+                    }
+                    if (row_ok) {
+                        float cn[8], hn[8];
 #pragma unroll
-                            for (int uu = 0; uu < 8; ++uu) pre[c][uu] = vh[uu] * sW + ve[uu] * sE + bias[c * 16 + half * 8 + uu];
+                        for (int uu = 0; uu < 8; ++uu) {
+                            const float ig = sigmoid_f(pre[0][uu]), fg = sigmoid_f(pre[1][uu]), og = sigmoid_f(pre[2][uu]);
+                            const float cand = fmaxf(pre[3][uu], pre[4][uu]);
+                            cn[uu] = __fadd_rn(__fmul_rn(fg, cprev[uu]), __fmul_rn(ig, cand));
+                            hn[uu] = og * tanhf(cn[uu]);
                         }
-                        if (row_ok) {
-                            float* cp = p.c_state + grow * p.N + j0 + half * 8;
-                            float cn[8], hn[8];
+                        float* cp = p.c_state + grow * p.N + j0;
+                        *reinterpret_cast<float4*>(cp) = *reinterpret_cast<float4*>(&cn[0]);
+                        *reinterpret_cast<float4*>(cp + 4) = *reinterpret_cast<float4*>(&cn[4]);
+                        __half hh[8], hl[8];
 #pragma unroll
-                            for (int uu = 0; uu < 8; ++uu) {
-                                const float ig = sigmoid_f(pre[0][uu]), fg = sigmoid_f(pre[1][uu]), og = sigmoid_f(pre[2][uu]);
-                                const float cand = fmaxf(pre[3][uu], pre[4][uu]);
-                                cn[uu] = __fadd_rn(__fmul_rn(fg, cprev[half * 8 + uu]), __fmul_rn(ig, cand));
-                                hn[uu] = og * tanhf(cn[uu]);
-                            }
-                            *reinterpret_cast<float4*>(cp) = *reinterpret_cast<float4*>(&cn[0]);
-                            *reinterpret_cast<float4*>(cp + 4) = *reinterpret_cast<float4*>(&cn[4]);
-                            __half hh[8], hl[8];
+                        for (int uu = 0; uu < 8; ++uu) split_half_dev(hn[uu], kActScale, hh[uu], hl[uu]);
+                        *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + j0) = *reinterpret_cast<uint4*>(hh);
+                        if (p.out_lo) *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + j0) = *reinterpret_cast<uint4*>(hl);
+                        if (p.h_trace) {
+                            float* ht = p.h_trace + (member * p.rows + m_local) * (int64_t)p.N + j0;
 #pragma unroll
-                            for (int uu = 0; uu < 8; ++uu) split_half_dev(hn[uu], kActScale, hh[uu], hl[uu]);
-                            *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + j0 + half * 8) = *reinterpret_cast<uint4*>(hh);
-                            if (p.out_lo) *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + j0 + half * 8) = *reinterpret_cast<uint4*>(hl);
-                            if (p.h_trace) {
-                                float* ht = p.h_trace + (member * p.rows + m_local) * (int64_t)p.N + j0 + half * 8;
-#pragma unroll
-                                for (int uu = 0; uu < 8; ++uu) ht[uu] = hn[uu];
-                            }
+                            for (int uu = 0; uu < 8; ++uu) ht[uu] = hn[uu];
                         }
                     }
                 } else {
-                    // PLAIN / LOGIT: 128 output columns, 32 at a time
+                    // PLAIN / LOGIT: this warp owns 64 of the tile's 128 output columns, 32 at a time
                     const int n_base = nt * C::BN;
 #pragma unroll 1
-                    for (int c0 = 0; c0 < C::BN; c0 += 32) {
-                        float vh[32], ve[32];
-                        tc::tmem_ld32(trow + c0, vh);
-                        tc::tmem_ld32(trow + COL_EPS + c0, ve);
-                        tc::tmem_ld_wait();
+                    for (int c0 = hf * 64; c0 < hf * 64 + 64; c0 += 32) {
                         float y[32];
+                        {
+                            float vh[32], ve[32];
+                            tc::tmem_ld32(trow + c0, vh);
+                            tc::tmem_ld32(trow + COL_EPS + c0, ve);
+                            tc::tmem_ld_wait();
 #pragma unroll
-                        for (int uu = 0; uu < 32; ++uu) y[uu] = vh[uu] * sW + ve[uu] * sE + bias[c0 + uu];
+                            for (int uu = 0; uu < 32; ++uu) y[uu] = vh[uu] * sW + ve[uu] * sE + bias[c0 + uu];
+                        }
                         if (EPI == EPI_PLAIN) {
                             if (row_ok) {
 #pragma unroll
@@ -329,42 +337,57 @@ __global__ void __launch_bounds__(192, 1) k_member_gemm(const __grid_constant__ 
                                 }
                             }
                         } else {
-                            const float prev_max = run_max;
+                            if (n_base + c0 + 32 > p.N) {                            // ragged last tile: mask the columns past V+1
 #pragma unroll
-                            for (int uu = 0; uu < 32; ++uu) {
-                                const int n = n_base + c0 + uu;
-                                const float v = (n < p.N) ? y[uu] : -INFINITY;
-                                y[uu] = v;
-                                if (v > run_max) {                                   // strict >: first index wins exact ties (torch.max)
-                                    if (!(lo_val >= v - p.tie_delta)) {              // the tie candidate fell out of the window
-                                        if (run_max >= v - p.tie_delta) { lo_val = run_max; lo_idx = run_idx; }   // the previous max is still inside, and earlier
-                                        else { lo_val = v; lo_idx = n; }
-                                    }
-                                    run_max = v; run_idx = n;
-                                }
+                                for (int uu = 0; uu < 32; ++uu) if (n_base + c0 + uu >= p.N) y[uu] = -INFINITY;
                             }
                             if (p.logit_trace && row_ok) {
                                 float* lt = p.logit_trace + (member * p.rows + m_local) * p.ld_trace;
 #pragma unroll
                                 for (int uu = 0; uu < 32; ++uu) { const int n = n_base + c0 + uu; if (n < p.N) lt[n] = y[uu]; }
                             }
-                            if (run_max > prev_max) run_sum = run_sum * __expf(prev_max - run_max);
-                            if (run_max > -INFINITY) {
+                            float cm = y[0];
 #pragma unroll
-                                for (int uu = 0; uu < 32; ++uu) run_sum += (PREC == NES_PREC_EXACT) ? expf(y[uu] - run_max) : __expf(y[uu] - run_max);
+                            for (int uu = 1; uu < 32; ++uu) cm = fmaxf(cm, y[uu]);
+                            if (cm > run_max) {                                      // rare after the first tiles: a new running max in this chunk
+                                const float prev_max = run_max;
+#pragma unroll
+                                for (int uu = 0; uu < 32; ++uu) {
+                                    const float v = y[uu];
+                                    if (v > run_max) {                               // strict >: first index wins exact ties (torch.max)
+                                        if (!(lo_val >= v - p.tie_delta)) {          // the tie candidate fell out of the window
+                                            if (run_max >= v - p.tie_delta) { lo_val = run_max; lo_idx = run_idx; }   // previous max still inside, and earlier
+                                            else { lo_val = v; lo_idx = n_base + c0 + uu; }
+                                        }
+                                        run_max = v; run_idx = n_base + c0 + uu;
+                                    }
+                                }
+                                run_sum *= tc::ex2_approx((prev_max - run_max) * kLog2e);
+                            }
+                            if (run_max > -INFINITY) {
+                                const float ml2 = run_max * kLog2e;
+                                float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                                for (int uu = 0; uu < 32; uu += 2) {
+                                    s0 += tc::ex2_approx(fmaf(y[uu], kLog2e, -ml2));
+                                    s1 += tc::ex2_approx(fmaf(y[uu + 1], kLog2e, -ml2));
+                                }
+                                run_sum += s0 + s1;
                             }
                         }
                     }
                 }
+                }   // !debug
                 // this accumulator buffer may be overwritten by the MMAs of tile it+2
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&tempty_bar[buf]);
             }
             if (EPI == EPI_LOGIT && row_ok) {
+                if (p.debug & 1) { run_max = 0.f; run_sum = 1.f + 1e-3f * (float)(grow % 977); run_idx = 1; lo_val = 0.f; lo_idx = 1; }
                 LogitPartial lp; lp.mx = run_max; lp.idx = run_idx; lp.sum = run_sum; lp.lo_val = lo_val; lp.lo_idx = lo_idx;
                 lp.pad[0] = lp.pad[1] = lp.pad[2] = 0;
-                float4* dst = reinterpret_cast<float4*>(&p.partials[grow]);
+                float4* dst = reinterpret_cast<float4*>(&p.partials[grow * 2 + hf]);
                 dst[0] = reinterpret_cast<float4*>(&lp)[0]; dst[1] = reinterpret_cast<float4*>(&lp)[1];
             }
         }

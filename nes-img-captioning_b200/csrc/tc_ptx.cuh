@@ -125,6 +125,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
 // ---- descriptors ----------------------------------------------------------------------------------
 // K-major operand tile in shared memory, 128-byte swizzle (what TMA SWIZZLE_128B writes): rows of 64 fp16
 // (128 B), 8-row groups 1024 B apart.  start address / LBO / SBO are in 16-byte units.
