@@ -37,7 +37,7 @@ def parse():
     ap.add_argument('--elites', type=int, default=3)
     ap.add_argument('--rows', type=int, default=128)
     ap.add_argument('--sigma', type=float, default=0.005)
-    ap.add_argument('--precision', default='exact', choices=['exact', 'fast'])
+    ap.add_argument('--precision', default='hybrid', choices=['hybrid', 'exact', 'fast'])
     ap.add_argument('--table-log2', type=int, default=28)
     ap.add_argument('--cpu-seconds', type=float, default=15.0)
     ap.add_argument('--no-extras', action='store_true')
@@ -172,7 +172,7 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group('nccl', device_id=dev)
-    prec = nes_b200.PREC_EXACT if a.precision == 'exact' else nes_b200.PREC_FAST
+    prec = {'exact': nes_b200.PREC_EXACT, 'fast': nes_b200.PREC_FAST, 'hybrid': nes_b200.PREC_HYBRID}[a.precision]
     P, mu, el, rows = a.population, a.parents, a.elites, a.rows
     Pg = P * world
     ctx = nes_b200.NesContext(dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=FD), seed=1234,
@@ -272,6 +272,7 @@ def main():
 
     ms, launches, clocks = timed(step_resident, a.steps, a.warmup, sample_clocks=True, profile=True)
     prof = ctx.profile_read()
+    hstats = ctx.hybrid_stats()
     ctx.profile(False)
     ms_e2e, _, _ = timed(step_e2e, a.steps, max(1, a.warmup - 2))
     value = Pg * a.steps / (ms / 1000.0)
@@ -279,7 +280,8 @@ def main():
 
     out = {'metric': 'fc_caption perturbed-member evals/sec (bs128 greedy)', 'value': value, 'unit': 'member-evals/s', 'n_gpus': world,
            'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': ms / a.steps, 'higher_is_better': True, 'scaling': 'weak',
-           'vs_baseline': None, 'dtype': 'f16 operands (split hi+lo, ~f32 products), f32 accumulate' if prec == nes_b200.PREC_EXACT else 'f16 operands, f32 accumulate',
+           'vs_baseline': None, 'dtype': {'exact': 'f16 operands split hi+lo (~f32 products), f32 accumulate', 'fast': 'f16 operands, f32 accumulate',
+                                        'hybrid': 'LSTM: f16 operands split hi+lo (~f32 products); vocabulary projection: f16 operands + f32 re-evaluation of the arg-max candidates; f32 accumulate'}[a.precision],
            'data': 'synthetic', 'config': dict(workload_config(a, world), precision=a.precision),
            'clocks': clocks, 'gpu_launches': launches * world,
            'e2e': {'value': e2e, 'unit': 'member-evals/s', 'h2d_bytes_per_step': int(fc_host.numel() * 4 + P * 8),
@@ -302,6 +304,7 @@ def main():
                            'algorithmic_flop_per_launch': flop_per_launch,
                            'whole_step_algorithmic_tflops': FLOP_PER_ROW * rows * P * a.steps / (ms * 1e-3) / 1e12,
                            'kernel_time_share': {kk: vv['ms'] / ms for kk, vv in prof.items()}}
+        out['hybrid_stats'] = hstats
         if not a.no_extras and world == 1:
             out['extras'] = extras(ctx, nes_b200, torch, dev, peaks)
             v, cores, n = cpu_evals_per_s(rows, a.sigma, a.cpu_seconds)

@@ -44,6 +44,9 @@ typedef struct nes_fc_dims {
 /* precision of the population GEMMs */
 #define NES_PREC_FAST  0   /* fp16 operands (theta_hi, x_hi, eps exact), fp32 accumulate          */
 #define NES_PREC_EXACT 1   /* split-fp16 (hi+lo) theta and activations: ~fp32 products, 5 MMAs    */
+#define NES_PREC_HYBRID 2  /* EXACT, except the vocabulary projection: fp16-operand logits with a  */
+                           /* rigorous error bound + exact fp32 re-evaluation of the arg-max      */
+                           /* candidates (same tokens as EXACT; log-probs within ~1e-5)           */
 
 /* optimizer kinds (algorithm/nic_nes/optimizers.py) */
 #define NES_OPT_SGD  0
@@ -135,10 +138,14 @@ int nes_master_step(nes_ctx* ctx, const double* fitness, const int64_t* offsets,
 int nes_last_gradient_ms(nes_ctx* ctx, float* ms);
 int nes_last_rollout_ms(nes_ctx* ctx, float* ms);
 /* per-kernel timing of the decode launches (CUDA events on the context stream).  kinds: 0 plain member GEMM
- * (img_embed / LayerNorm pre-activations), 1 LSTM member GEMM, 2 vocabulary-projection member GEMM, 3 finalize.
- * nes_profile_read synchronises, returns the summed durations [4] and launch counts [4] since the last read. */
+ * (img_embed / LayerNorm pre-activations), 1 LSTM member GEMM, 2 vocabulary-projection member GEMM, 3 finalize / margin /
+ * refine, 4 masked split-fp16 fallback of the HYBRID vocabulary projection.
+ * nes_profile_read synchronises, returns the summed durations [5] and launch counts [5] since the last read. */
 int nes_profile_enable(nes_ctx* ctx, int on);
 int nes_profile_read(nes_ctx* ctx, float* ms_by_kind, int32_t* count_by_kind);
+/* HYBRID bookkeeping, counted while profiling is enabled: out4 = {rows refined, candidate logits re-evaluated in fp32,
+ * rows whose candidate list overflowed (their unit took the split-fp16 fallback), 0}. */
+int nes_hybrid_stats(nes_ctx* ctx, int64_t* out4, int reset);
 
 /* standalone tensor-core self test through the same tcgen05/TMA kernel the decode uses:
  * C[M,N] = A[M,K] W[N,K]^T + sigma * A[M,K] f16(E[N,K])^T, float32 in/out (host or device pointers). */

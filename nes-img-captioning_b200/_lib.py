@@ -53,6 +53,7 @@ SIGNATURES = {
     'nes_last_rollout_ms': (c_i32, [c_vp, ctypes.POINTER(c_f32)]),
     'nes_profile_enable': (c_i32, [c_vp, c_i32]),
     'nes_profile_read': (c_i32, [c_vp, ctypes.POINTER(c_f32), ctypes.POINTER(c_i32)]),
+    'nes_hybrid_stats': (c_i32, [c_vp, ctypes.POINTER(c_i64), c_i32]),
     'nes_gemm_selftest': (c_i32, [c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_f32, c_i32, c_vp]),
 }
 

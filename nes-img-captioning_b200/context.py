@@ -8,7 +8,7 @@ import torch
 from . import _lib
 from .layout import build_layout, fc_tensors, granule
 
-PREC_FAST, PREC_EXACT = 0, 1
+PREC_FAST, PREC_EXACT, PREC_HYBRID = 0, 1, 2
 OPT_SGD, OPT_ADAM = 0, 1
 
 
@@ -243,10 +243,15 @@ class NesContext:
         _lib.check(self.lib.nes_profile_enable(self._h, int(bool(on))))
 
     def profile_read(self):
-        ms = (ctypes.c_float * 4)()
-        cnt = (ctypes.c_int32 * 4)()
+        ms = (ctypes.c_float * 5)()
+        cnt = (ctypes.c_int32 * 5)()
         _lib.check(self.lib.nes_profile_read(self._h, ms, cnt))
-        return {k: {'ms': float(ms[i]), 'count': int(cnt[i])} for i, k in enumerate(('plain', 'lstm', 'logit', 'finalize'))}
+        return {k: {'ms': float(ms[i]), 'count': int(cnt[i])} for i, k in enumerate(('plain', 'lstm', 'logit', 'finalize', 'fallback'))}
+
+    def hybrid_stats(self, reset=True):
+        out = (ctypes.c_int64 * 4)()
+        _lib.check(self.lib.nes_hybrid_stats(self._h, out, int(reset)))
+        return {'rows_refined': int(out[0]), 'candidates': int(out[1]), 'rows_overflowed': int(out[2])}
 
     def last_gradient_ms(self):
         ms = ctypes.c_float(0)

@@ -70,6 +70,10 @@ static int ctx_common_init(Ctx* c, int device, uint64_t seed, int64_t table_len,
     NES_CUDA(cudaMalloc((void**)&c->opt_m, sizeof(double) * D));
     NES_CUDA(cudaMalloc((void**)&c->opt_v, sizeof(double) * D));
     NES_CUDA(cudaMalloc((void**)&c->d_lay, sizeof(Layout)));
+    NES_CUDA(cudaMalloc((void**)&c->d_theta_rowmax, sizeof(float) * n_parents));
+    NES_CUDA(cudaMalloc((void**)&c->d_eps_rowmax, sizeof(float)));
+    NES_CUDA(cudaMemset(c->d_theta_rowmax, 0, sizeof(float) * n_parents));
+    NES_CUDA(cudaMemset(c->d_eps_rowmax, 0, sizeof(float)));
     c->norm_blocks = 148 * 8;
     NES_CUDA(cudaMalloc((void**)&c->d_norm_partials, sizeof(double) * 2 * c->norm_blocks));
     NES_CUDA(cudaMalloc((void**)&c->d_norms, sizeof(double) * 2));
@@ -138,7 +142,7 @@ int nes_ctx_destroy(nes_ctx* ctx) {
     cudaStreamSynchronize(c->stream);
     decode_destroy(c);
     void* ptrs[] = {c->table, c->theta64, c->theta32, c->theta_hi, c->theta_lo, c->grad, c->opt_m, c->opt_v, c->d_lay, c->d_norm_partials,
-                    c->d_norms, c->d_G64, c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks};
+                    c->d_norms, c->d_G64, c->d_theta_rowmax, c->d_eps_rowmax, c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->ev_a) cudaEventDestroy(c->ev_a);
     if (c->ev_b) cudaEventDestroy(c->ev_b);
@@ -379,6 +383,12 @@ int nes_profile_read(nes_ctx* ctx, float* ms_by_kind, int32_t* count_by_kind) {
     }
     c->prof_recs.clear();
     return 0;
+}
+
+int nes_hybrid_stats(nes_ctx* ctx, int64_t* out4, int reset) {
+    NEED_CTX(ctx);
+    NES_CHECK(out4, "null output");
+    return decode_hybrid_stats(CTX(ctx), out4, reset);
 }
 
 int nes_last_gradient_ms(nes_ctx* ctx, float* ms) {

@@ -64,6 +64,9 @@ struct Ctx {
     __half* theta_lo = nullptr;
     uint8_t* theta_is_f32 = nullptr;  // host flags [n_parents]: master theta still has float32 provenance
     Layout* d_lay = nullptr;          // device copy of lay
+    float* d_theta_rowmax = nullptr;  // [n_parents] max row 2-norm of logit.weight (HYBRID error bound)
+    float* d_eps_rowmax = nullptr;    // [1] max 2-norm over the rows of the [L/R, R] view of the noise table
+    bool eps_rowmax_valid = false;
 
     // master math
     float*  grad = nullptr;           // [D]
@@ -91,7 +94,7 @@ struct Ctx {
 
     DecodeWorkspace* ws = nullptr;
 };
-enum { PROF_PLAIN = 0, PROF_LSTM = 1, PROF_LOGIT = 2, PROF_FINALIZE = 3, PROF_KINDS = 4 };
+enum { PROF_PLAIN = 0, PROF_LSTM = 1, PROF_LOGIT = 2, PROF_FINALIZE = 3, PROF_FALLBACK = 4, PROF_KINDS = 5 };
 struct ProfScope {                          // RAII: record an event pair around one launch when profiling is on
     Ctx* c; int idx = -1;
     ProfScope(Ctx* c_, int kind) : c(c_) {
@@ -112,6 +115,7 @@ int ensure_small(Ctx* c, int64_t n);   // (re)allocate the small per-iteration s
 int launch_fill_table(Ctx* c);
 int launch_sample_offsets(Ctx* c, uint64_t iteration, int64_t F, int64_t* d_out);
 int launch_sample_parents(Ctx* c, uint64_t iteration, int64_t F, int32_t n_parents, int32_t* d_out);
+int launch_bound_norms(Ctx* c, int parent);       // parent >= 0: theta_rowmax[parent]; parent < 0: eps_rowmax (decode.cu)
 int launch_theta_shadow(Ctx* c, int parent);      // theta32 -> theta_hi/lo (padded)
 int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64);
 int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, float* d_member, float* d_noise, int dst_parent);
@@ -129,6 +133,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                    const float* fc, int rows, int shared_batch, float sigma, int precision,
                    const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace);
 int decode_logprob_fitness(Ctx* c, int64_t n_members, int rows, double* out);
+int decode_hybrid_stats(Ctx* c, int64_t* out4, int reset);
 
 }  // namespace nes
 

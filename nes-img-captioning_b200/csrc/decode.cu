@@ -6,7 +6,7 @@
 //              (h, c) = core(x_t, (h, c))              LSTM member GEMM
 //              logits = logit(h) -> argmax, log-prob    LOGIT member GEMM + k_finalize
 // Finished-mask, early break and the seq / seq_logprobs writes follow :233-243.
-#include "member_gemm.cuh"
+#include "hybrid.cuh"
 #include <cstdlib>
 #include <map>
 #include <tuple>
@@ -71,6 +71,8 @@ struct DecodeWorkspace {
     float* c_state = nullptr;
     float *pre_i = nullptr, *pre_h = nullptr;               // LayerNorm path
     LogitPartial* partials = nullptr;
+    CandPartial* cand = nullptr; float* margin = nullptr; int32_t* pre_tok = nullptr; float* pre_lp = nullptr; uint8_t* unit_flag = nullptr;   // HYBRID
+    unsigned long long* stats = nullptr;
     uint8_t* unfinished = nullptr; int32_t* unf_count = nullptr;
     // per call
     int64_t cap_members = 0;
@@ -113,6 +115,7 @@ __global__ void __launch_bounds__(256) k_split_rows(const float* __restrict__ sr
 
 struct FinalizeParams {
     const LogitPartial* partials; int n_tiles;
+    const int32_t* pre_tok; const float* pre_lp; const uint8_t* unit_flag; int m_tiles;   // HYBRID: refined arg-max unless the unit is flagged
     int rows, rows_pad, T, E, t;                 // t in 1..T (0: <bos> gather only)
     int64_t n_members;
     const int64_t* off; const float* sign; const int32_t* parent;
@@ -138,6 +141,9 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
     const float sgn = p.sign[member];
     int64_t tok = 0;
     if (p.t >= 1) {
+        float best = -INFINITY; int idx = 0x7fffffff;
+        if (p.pre_tok && !p.unit_flag[member * p.m_tiles + r / 128]) { idx = p.pre_tok[grow]; best = p.pre_lp[grow]; }
+        else {
         // global max and sum-exp over the vocabulary tiles
         float mx = -INFINITY;
         for (int j = lane; j < p.n_tiles; j += 32) mx = fmaxf(mx, p.partials[grow * p.n_tiles + j].mx);
@@ -151,7 +157,6 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
         const float lse = logf(s);
         // the reference's argmax runs over float32 log-probs, log_softmax(x) = (x - max) - log(sum) (captioning/nets.py:202-208):
         // logits closer than the float32 quantum of log(sum) tie there and torch.max returns the LOWEST index.
-        float best = -INFINITY; int idx = 0x7fffffff;
         for (int j = lane; j < p.n_tiles; j += 32) {
             const LogitPartial q = p.partials[grow * p.n_tiles + j];
             const float l1 = __fsub_rn(__fsub_rn(q.mx, mx), lse), l2 = __fsub_rn(__fsub_rn(q.lo_val, mx), lse);
@@ -162,6 +167,7 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
             const float ob = __shfl_xor_sync(0xffffffffu, best, o);
             const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
             if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+        }
         }
         const float logp = best;                                  // = max log-prob
         const bool done = p.t > 1 && p.unf_count[(p.t - 1) * p.W + member] == 0;   // the reference broke out of the loop
@@ -303,6 +309,8 @@ int decode_create(Ctx* c, int wave_members, int rows) {
     for (int b = 0; b < 2; ++b) if (dmalloc(&ws->h_hi[b], WR * ws->R) || dmalloc(&ws->h_lo[b], WR * ws->R)) return 1;
     if (dmalloc(&ws->c_state, WR * ws->R)) return 1;
     if (dmalloc(&ws->partials, 2 * WR)) return 1;
+    if (dmalloc(&ws->cand, 2 * WR) || dmalloc(&ws->margin, WR) || dmalloc(&ws->pre_tok, WR) || dmalloc(&ws->pre_lp, WR) || dmalloc(&ws->unit_flag, WR / 128) || dmalloc(&ws->stats, 4)) return 1;
+    NES_CUDA(cudaMemsetAsync(ws->stats, 0, 32, c->stream));
     if (dmalloc(&ws->unfinished, WR) || dmalloc(&ws->unf_count, (int64_t)(ws->T + 2) * ws->W)) return 1;
     if (d.layer_n) { if (dmalloc(&ws->pre_i, WR * 5 * ws->R) || dmalloc(&ws->pre_h, WR * 5 * ws->R)) return 1; }
     // zero everything once: padding rows of the operand buffers must stay finite forever
@@ -320,7 +328,7 @@ void decode_destroy(Ctx* c) {
     DecodeWorkspace* ws = c->ws;
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
-                    ws->pre_i, ws->pre_h, ws->partials, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
+                    ws->pre_i, ws->pre_h, ws->partials, ws->cand, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
                     ws->d_lp, ws->d_forced};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
@@ -347,7 +355,7 @@ static int launch_gemm(Ctx* c, GemmParams& p, int64_t n_members) {
     // persistent: one CTA per SM, CTA b owns units b, b + grid, ... and sweeps every weight tile of each
     const int sms = sm_count(c);
     const unsigned grid = (unsigned)(units < sms ? units : sms);
-    ProfScope prof(c, EPI == EPI_PLAIN ? PROF_PLAIN : (EPI == EPI_LSTM ? PROF_LSTM : PROF_LOGIT));
+    ProfScope prof(c, EPI == EPI_PLAIN ? PROF_PLAIN : (EPI == EPI_LSTM ? PROF_LSTM : (p.unit_mask ? PROF_FALLBACK : PROF_LOGIT)));
     k_member_gemm<EPI, PREC><<<grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
     c->launches++;
     NES_CUDA(cudaGetLastError());
@@ -402,11 +410,16 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     DecodeWorkspace* ws = c->ws;
     NES_CHECK(ws != nullptr, "context has no decode workspace");
     NES_CHECK(rows >= 1 && rows <= ws->rows_cap, "rows exceeds the workspace capacity given to nes_ctx_create_fc");
-    NES_CHECK(precision == NES_PREC_FAST || precision == NES_PREC_EXACT, "unknown precision");
+    NES_CHECK(precision == NES_PREC_FAST || precision == NES_PREC_EXACT || precision == NES_PREC_HYBRID, "unknown precision");
     NES_CHECK(n_members >= 0, "negative member count");
     const bool tracing = h_trace || logit_trace || forced;
+    // HYBRID = split-fp16 everywhere except the vocabulary projection, which runs on fp16 operands with an exact
+    // fp32 re-evaluation of the arg-max candidates (hybrid.cuh); a logit trace needs the accurate logits themselves
+    const bool hybrid = precision == NES_PREC_HYBRID && !logit_trace;
+    if (precision == NES_PREC_HYBRID) precision = NES_PREC_EXACT;
     NES_CHECK(!tracing || n_members <= ws->W, "trace mode handles a single wave");
     if (n_members == 0) return 0;
+    if (hybrid && !c->eps_rowmax_valid && launch_bound_norms(c, -1)) return 1;
     const Layout& L = c->lay;
     const int E = ws->E, R = ws->R, Fd = ws->Fd, V1 = ws->V1, T = ws->T;
     const int rows_pad = (rows + 127) / 128 * 128, m_tiles = rows_pad / 128;
@@ -503,9 +516,33 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             if (t >= 1) {
                 GemmParams p = base;
                 p.nseg = 1; p.N = V1; p.chunk_stride = 0; p.n_tiles = ws->nt_logit;
-                if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128, precision)) return 1;
-                p.partials = ws->partials;
                 { int ex; frexpf(logf((float)V1), &ex); p.tie_delta = ldexpf(1.0f, ex - 1 - 23); }
+                p.partials = ws->partials;
+                if (hybrid) {
+                    // (1) per-row error bound, (2) fp16-operand logits + candidate lists, (3) fp32 re-evaluation of the candidates
+                    MarginParams mg{};
+                    mg.h_hi = ws->h_hi[hb]; mg.h_lo = ws->h_lo[hb]; mg.R = R; mg.rows = rows; mg.rows_pad = rows_pad; mg.n_members = nm;
+                    mg.parent = base.parent; mg.theta_rowmax = c->d_theta_rowmax; mg.eps_rowmax = c->d_eps_rowmax; mg.sigma = sigma; mg.margin = ws->margin;
+                    { ProfScope prof(c, PROF_FINALIZE);
+                      k_row_margin<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(mg); c->launches++; }
+                    NES_CUDA(cudaGetLastError());
+                    GemmParams pc = p;
+                    if (fill_seg(c, pc, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128, NES_PREC_FAST)) return 1;
+                    pc.cand = ws->cand; pc.margin = ws->margin;
+                    if (launch_gemm<EPI_LOGITC, NES_PREC_FAST>(c, pc, nm)) return 1;
+                    NES_CUDA(cudaMemsetAsync(ws->unit_flag, 0, (size_t)nm * m_tiles, c->stream));
+                    RefineParams rf{};
+                    rf.cand = ws->cand; rf.margin = ws->margin; rf.h_hi = ws->h_hi[hb]; rf.h_lo = ws->h_lo[hb]; rf.R = R; rf.V1 = V1;
+                    rf.rows = rows; rf.rows_pad = rows_pad; rf.m_tiles = m_tiles; rf.n_members = nm;
+                    rf.off = base.off; rf.sign = base.sign; rf.parent = base.parent; rf.theta32 = c->theta32; rf.table = c->table; rf.D = L.D;
+                    rf.w_start = L.t[T_LOGIT_W].start; rf.w_pstart = L.t[T_LOGIT_W].pstart; rf.b_start = L.t[T_LOGIT_B].start; rf.b_pstart = L.t[T_LOGIT_B].pstart;
+                    rf.sigma = sigma; rf.tok = ws->pre_tok; rf.lp = ws->pre_lp; rf.unit_flag = ws->unit_flag; rf.stats = c->profiling ? ws->stats : nullptr;
+                    { ProfScope prof(c, PROF_FINALIZE);
+                      k_refine<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(rf); c->launches++; }
+                    NES_CUDA(cudaGetLastError());
+                    p.unit_mask = ws->unit_flag;      // (4) units whose candidate list overflowed: the split-fp16 kernel, everything else skips
+                }
+                if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128, precision)) return 1;
                 p.logit_trace = logit_trace ? logit_trace + (int64_t)(t - 1) * n_members * rows * V1 : nullptr; p.ld_trace = V1;
                 if (launch_gemm_prec<EPI_LOGIT>(c, p, nm, precision)) return 1;
             }
@@ -518,6 +555,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;
                 f.forced = forced ? ws->d_forced + m0 * rows * T : nullptr;
                 f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0;
+                if (hybrid && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; }
                 ProfScope prof(c, PROF_FINALIZE);
                 k_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(f);
                 c->launches++;
@@ -528,6 +566,31 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     if (c->rollout_timed) NES_CUDA(cudaEventRecord(c->ev_d, c->stream));
     if (seq)  NES_CUDA(cudaMemcpyAsync(seq, ws->d_seq, sizeof(int64_t) * n_members * rows * T, cudaMemcpyDefault, c->stream));
     if (logp) NES_CUDA(cudaMemcpyAsync(logp, ws->d_lp, sizeof(float) * n_members * rows * T, cudaMemcpyDefault, c->stream));
+    return 0;
+}
+
+int launch_bound_norms(Ctx* c, int parent) {
+    if (!c->is_fc) return 0;
+    const int R = c->dims.rnn_size, V1 = c->dims.vocab_size + 1;
+    if (parent >= 0) {
+        NES_CUDA(cudaMemsetAsync(c->d_theta_rowmax + parent, 0, sizeof(float), c->stream));
+        k_rowmax_theta<<<148, 256, 0, c->stream>>>(c->theta32 + (int64_t)parent * c->lay.D + c->lay.t[T_LOGIT_W].start, V1, R, c->d_theta_rowmax + parent);
+    } else {
+        NES_CUDA(cudaMemsetAsync(c->d_eps_rowmax, 0, sizeof(float), c->stream));
+        k_rowmax_eps<<<148 * 8, 256, 0, c->stream>>>(c->table, c->table_len / R, R, c->d_eps_rowmax);
+        c->eps_rowmax_valid = true;
+    }
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int decode_hybrid_stats(Ctx* c, int64_t* out4, int reset) {
+    DecodeWorkspace* ws = c->ws;
+    NES_CHECK(ws != nullptr, "context has no decode workspace");
+    NES_CUDA(cudaMemcpyAsync(out4, ws->stats, 32, cudaMemcpyDeviceToHost, c->stream));
+    NES_CUDA(cudaStreamSynchronize(c->stream));
+    if (reset) NES_CUDA(cudaMemsetAsync(ws->stats, 0, 32, c->stream));
     return 0;
 }
 

@@ -1,0 +1,166 @@
+// HYBRID vocabulary projection: helpers around the fp16-operand logit GEMM (k_member_gemm<EPI_LOGITC, FAST>).
+//
+// The reference picks the next token as argmax of float32 log-softmax(logit(h)) (captioning/nets.py:202-208).  Only the
+// arg-max and its log-prob are needed, so the 64 % of the FLOPs spent in the vocabulary projection do not need
+// split-fp16 accuracy everywhere: single-fp16 operands give every logit with a RIGOROUS error bound
+//     |l~ - l| <= 2^-11 (1 + 2^-11) |x|_2 (|w_j|_2 + |theta_j|_2)  +  fp32 accumulation,      w_j = theta_j +- sigma eps_j
+// (both operands are rounded to 11 significant bits, Cauchy-Schwarz), with |theta_j|_2 <= max row norm of logit.weight
+// (k_rowmax_theta, per parent) and |eps_j|_2 <= max row norm of the [L/R, R] view of the table (k_rowmax_eps).  Every
+// column within margin = 2 * bound of the approximate max is kept (the kMaxCand largest per half row) and k_refine
+// re-evaluates exactly those columns in fp32 from the float32 theta and the exact fp16 eps -- the same member weight
+// theta +- f32(sigma)*eps the reference forms (algorithm/nets.py:113).  Rows with more candidates than fit flag their
+// unit, which is then recomputed by the split-fp16 kernel (masked launch), so the result never depends on the bound
+// being tight, only on it being an upper bound.
+#pragma once
+#include "member_gemm.cuh"
+
+namespace nes {
+
+__device__ __forceinline__ float warp_sum(float v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
+__device__ __forceinline__ float warp_max(float v) { for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o)); return v; }
+__device__ __forceinline__ void atomic_max_pos(float* addr, float v) { atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v)); }   // v >= 0
+
+// max over the rows of logit.weight [V1, R] (float32 theta of one parent) of the row 2-norm; *out zeroed by the caller
+__global__ void __launch_bounds__(256) k_rowmax_theta(const float* __restrict__ w, int64_t n_rows, int R, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    float best = 0.f;
+    for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < n_rows; r += (int64_t)gridDim.x * 8) {
+        float s = 0.f;
+        for (int k = lane; k < R; k += 32) { const float v = w[r * R + k]; s = fmaf(v, v, s); }
+        best = fmaxf(best, warp_sum(s));
+    }
+    if (lane == 0) atomic_max_pos(out, sqrtf(best) * 1.0001f);
+}
+// max over the rows of the [L/R, R] view of the fp16 noise table of the row 2-norm
+__global__ void __launch_bounds__(256) k_rowmax_eps(const __half* __restrict__ table, int64_t n_rows, int R, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    float best = 0.f;
+    for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < n_rows; r += (int64_t)gridDim.x * 8) {
+        float s = 0.f;
+        for (int k = lane * 8; k < R; k += 256) {
+            const uint4 v = *reinterpret_cast<const uint4*>(table + r * R + k);
+            const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { const float2 f = __half22float2(h[e]); s = fmaf(f.x, f.x, s); s = fmaf(f.y, f.y, s); }
+        }
+        best = fmaxf(best, warp_sum(s));
+    }
+    if (lane == 0) atomic_max_pos(out, sqrtf(best) * 1.0001f);
+}
+
+struct MarginParams {
+    const __half *h_hi, *h_lo; int R; int rows, rows_pad; int64_t n_members;
+    const int32_t* parent; const float* theta_rowmax; const float* eps_rowmax; float sigma; float* margin;
+};
+// one warp per (member, row): margin = 2 * error bound of the fp16-operand logits of that row
+__global__ void __launch_bounds__(128) k_row_margin(const MarginParams p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (wid >= p.n_members * p.rows) return;
+    const int64_t member = wid / p.rows;
+    const int64_t grow = member * p.rows_pad + (wid % p.rows);
+    float s = 0.f;
+    for (int k = lane * 8; k < p.R; k += 256) {
+        const uint4 a = *reinterpret_cast<const uint4*>(p.h_hi + grow * p.R + k), b = *reinterpret_cast<const uint4*>(p.h_lo + grow * p.R + k);
+        const __half2 *ha = reinterpret_cast<const __half2*>(&a), *hb = reinterpret_cast<const __half2*>(&b);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float2 fa = __half22float2(ha[e]), fb = __half22float2(hb[e]);
+            const float x0 = (fa.x + fb.x) * (1.0f / kActScale), x1 = (fa.y + fb.y) * (1.0f / kActScale);
+            s = fmaf(x0, x0, s); s = fmaf(x1, x1, s);
+        }
+    }
+    s = warp_sum(s);
+    if (lane == 0) {
+        const int par = p.parent ? p.parent[member] : 0;
+        const float wsum = 2.f * p.theta_rowmax[par] + fabsf(p.sigma) * p.eps_rowmax[0];
+        // 2^-11 relative rounding of both operands, +10 % for the fp32 accumulation of K <= 4096 terms, x2 (two logits compared)
+        p.margin[grow] = 2.f * 1.1f * 4.8828125e-4f * sqrtf(s) * 1.0001f * (wsum + 1e-4f) + 1e-30f;
+    }
+}
+
+struct RefineParams {
+    const CandPartial* cand; const float* margin;
+    const __half *h_hi, *h_lo; int R, V1; int rows, rows_pad, m_tiles; int64_t n_members;
+    const int64_t* off; const float* sign; const int32_t* parent;
+    const float* theta32; const __half* table; int64_t D;
+    int64_t w_start, w_pstart, b_start, b_pstart;     // logit.weight / logit.bias: flat and padded starts
+    float sigma;
+    int32_t* tok; float* lp;                          // [member*rows_pad + row]: arg-max column and its log-prob
+    uint8_t* unit_flag;                               // [n_members*m_tiles]: 1 -> recompute this unit with the split-fp16 kernel
+    unsigned long long* stats;                        // nullable: [0] rows refined, [1] candidates evaluated, [2] rows overflowed
+};
+// one warp per (member, row): merge the two half-row candidate lists, re-evaluate every candidate logit in fp32 with
+// the member weight theta +- f32(sigma)*eps (algorithm/nets.py:113), pick the reference's argmax of float32 log-probs
+// (lowest index among equal rounded log-probs, captioning/nets.py:202-208)
+__global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (wid >= p.n_members * p.rows) return;
+    const int64_t member = wid / p.rows;
+    const int r = (int)(wid % p.rows);
+    const int64_t grow = member * p.rows_pad + r;
+    const CandPartial* cp = p.cand + grow * 2;
+    const float m0 = cp[0].mx, m1 = cp[1].mx;
+    const float M = fmaxf(m0, m1);
+    const float thr = M - p.margin[grow];
+    if (fmaxf(cp[0].dropped, cp[1].dropped) >= thr) {          // a dropped logit is still a candidate: more than the lists hold
+        if (lane == 0) { p.unit_flag[member * p.m_tiles + r / 128] = 1; if (p.stats) atomicAdd(&p.stats[2], 1ull); }
+        return;
+    }
+    const float S = cp[0].sum * expf(m0 - M) + cp[1].sum * expf(m1 - M);
+    // lane k < 2*kMaxCand holds candidate slot (half k / kMaxCand, entry k % kMaxCand)
+    int my_idx = -1;
+    if (lane < 2 * kMaxCand) {
+        const int hf = lane / kMaxCand, e = lane % kMaxCand;
+        if (e < cp[hf].n && cp[hf].v[e] >= thr) my_idx = cp[hf].idx[e];
+    }
+    const float sgn = p.sign[member];
+    const int64_t off = p.off[member];
+    const int par = p.parent ? p.parent[member] : 0;
+    float my_val = -INFINITY;
+    for (int c = 0; c < 2 * kMaxCand; ++c) {
+        const int j = __shfl_sync(0xffffffffu, my_idx, c);
+        if (j < 0) continue;                                   // warp-uniform
+        const float* tw = p.theta32 + (int64_t)par * p.D + p.w_start + (int64_t)j * p.R;
+        const __half* ew = p.table + off + p.w_pstart + (int64_t)j * p.R;
+        float acc = 0.f;
+        for (int k = lane * 8; k < p.R; k += 256) {
+            const uint4 a = *reinterpret_cast<const uint4*>(p.h_hi + grow * p.R + k), b = *reinterpret_cast<const uint4*>(p.h_lo + grow * p.R + k);
+            const uint4 ev = *reinterpret_cast<const uint4*>(ew + k);
+            const __half *ha = reinterpret_cast<const __half*>(&a), *hb = reinterpret_cast<const __half*>(&b), *he = reinterpret_cast<const __half*>(&ev);
+            float tv[8];                                           // scalar loads: parent*D need not be 16-byte aligned
+#pragma unroll
+            for (int e = 0; e < 8; ++e) tv[e] = tw[k + e];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const float x = (__half2float(ha[e]) + __half2float(hb[e])) * (1.0f / kActScale);
+                const float nz = __fmul_rn(p.sigma, __half2float(he[e]));
+                const float w = sgn > 0.f ? __fadd_rn(tv[e], nz) : __fsub_rn(tv[e], nz);
+                acc = fmaf(x, w, acc);
+            }
+        }
+        acc = warp_sum(acc);
+        const float tb = p.theta32[(int64_t)par * p.D + p.b_start + j];
+        const float nzb = __fmul_rn(p.sigma, __half2float(p.table[off + p.b_pstart + j]));
+        const float v = acc + (sgn > 0.f ? __fadd_rn(tb, nzb) : __fsub_rn(tb, nzb));
+        if (lane == c) my_val = v;
+    }
+    const float vmax = warp_max(my_val);
+    // log_softmax(x) = (x - max) - log(sum exp(x - max)); the sum comes from the approximate logits (relative to M)
+    const float lse = __fadd_rn(__fsub_rn(M, vmax), logf(S));
+    float best = -INFINITY; int idx = 0x7fffffff;
+    if (my_idx >= 0) { best = __fsub_rn(__fsub_rn(my_val, vmax), lse); idx = my_idx; }
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+    }
+    if (lane == 0) { p.tok[grow] = idx; p.lp[grow] = best; }
+    if (p.stats) {
+        const unsigned n = __popc(__ballot_sync(0xffffffffu, my_idx >= 0));
+        if (lane == 0) { atomicAdd(&p.stats[0], 1ull); atomicAdd(&p.stats[1], (unsigned long long)n); }
+    }
+}
+
+}  // namespace nes

@@ -42,6 +42,7 @@ int launch_fill_table(Ctx* c) {
     k_fill_table<<<grid, 256, 0, c->stream>>>(c->table, n_blocks, (uint32_t)c->seed, (uint32_t)(c->seed >> 32));
     c->launches++;
     NES_CUDA(cudaGetLastError());
+    if (c->is_fc) return launch_bound_norms(c, -1);
     return 0;
 }
 
@@ -113,6 +114,7 @@ int launch_theta_shadow(Ctx* c, int parent) {
                                                 c->theta_lo + (int64_t)parent * c->lay.D_pad, c->d_lay);
     c->launches++;
     NES_CUDA(cudaGetLastError());
+    if (c->is_fc) return launch_bound_norms(c, parent);
     return 0;
 }
 

@@ -21,16 +21,18 @@ def _members(offs):
     return offs2, signs
 
 
+@pytest.mark.parametrize('prec', [1, 2], ids=['exact', 'hybrid'])
 @pytest.mark.parametrize('name', ['g1', 'g2', 'g3', 'g4', 'g5', 'g6'])
-def test_tokens_and_logprobs_match_reference_golden_exact_mode(name, golden, golden_mod):
-    """token ids bit-exact, log-probs to float32 round-off, against what the REAL reference produced"""
+def test_tokens_and_logprobs_match_reference_golden_exact_mode(name, prec, golden, golden_mod):
+    """token ids bit-exact, log-probs to float32 round-off, against what the REAL reference produced; in both the
+    split-fp16 mode and the HYBRID mode bench.py headlines (fp16-operand logits + exact re-evaluation of the candidates)"""
     import nes_b200
     c = golden_mod.CASES[name]
     dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
     ctx = _ctx_for(c, golden_mod, L)
     ctx.set_theta(theta)
     offs2, signs = _members(offs)
-    seq, lp = ctx.rollout(offs2, signs, fc, c['sigma'], precision=nes_b200.PREC_EXACT)
+    seq, lp = ctx.rollout(offs2, signs, fc, c['sigma'], precision=prec)
     want_seq = golden[name + '_seq'].reshape(-1, c['B'], 16).astype(np.int64)
     want_lp = golden[name + '_logprobs'].reshape(-1, c['B'], 16)
     assert seq.dtype == torch.int64 and tuple(seq.shape) == want_seq.shape
@@ -39,6 +41,7 @@ def test_tokens_and_logprobs_match_reference_golden_exact_mode(name, golden, gol
     # the unperturbed theta through the single-individual API (FCModel.__call__)
     model = nes_b200.FCModel(ctx, from_param_file=None, options=None, rng_state=1)
     model.set_from_vector(theta)
+    model.precision = prec
     s0, lp0 = model(torch.from_numpy(fc), greedy=True)
     want0 = golden[name + '_seq_theta'].astype(np.int64)
     assert np.array_equal(s0.numpy(), want0), 'mismatching tokens: %d of %d' % ((s0.numpy() != want0).sum(), want0.size)
@@ -121,8 +124,11 @@ def test_fast_mode_token_agreement_is_reported(golden, golden_mod, capsys):
     ctx.close()
 
 
-def test_early_break_zeroes_later_logprobs():
-    """all rows emit token 0 at the first step -> the reference breaks (nets.py:242-243): later columns stay 0"""
+@pytest.mark.parametrize('prec', [1, 2], ids=['exact', 'hybrid'])
+def test_early_break_zeroes_later_logprobs(prec):
+    """all rows emit token 0 at the first step -> the reference breaks (nets.py:242-243): later columns stay 0.
+    With zero weights every other logit ties exactly, so in HYBRID mode the candidate lists overflow and the unit
+    takes the split-fp16 fallback: this is the test of that path."""
     import nes_b200
     mo = dict(vocab_size=63, input_encoding_size=64, rnn_size=64, fc_feat_size=64)
     ctx = nes_b200.NesContext(mo, seed=1, table_len=1 << 20, wave_members=4, rows=3)
@@ -132,7 +138,7 @@ def test_early_break_zeroes_later_logprobs():
     theta[lay['logit.bias'].start] = 5.0
     ctx.set_theta(theta)
     fc = np.ones((3, 64), dtype=np.float32)
-    seq, lp = ctx.rollout(np.zeros(2, dtype=np.int64), np.array([1., -1.], dtype=np.float32), fc, 0.0)
+    seq, lp = ctx.rollout(np.zeros(2, dtype=np.int64), np.array([1., -1.], dtype=np.float32), fc, 0.0, precision=prec)
     s_ref, lp_ref = fc_caption.decode_greedy(dims, theta, fc)
     for m in range(2):
         assert np.array_equal(seq[m].numpy(), s_ref) and (seq[m] == 0).all()
@@ -152,7 +158,7 @@ def test_es_parents_per_member_batches_and_waves(golden_mod):
     offs_all = ctx.sample_offsets(3, P).numpy()
     parents = ctx.sample_parents(3, P, 2).numpy()
     fcs = np.stack([noise.table_slice(50 + i, 0, c['B'] * c['Fd']).astype(np.float32).reshape(c['B'], c['Fd']) for i in range(P)])
-    seq, lp = ctx.rollout(offs_all, np.ones(P, dtype=np.float32), fcs, 0.02, parents=parents, shared_batch=False)
+    seq, lp = ctx.rollout(offs_all, np.ones(P, dtype=np.float32), fcs, 0.02, parents=parents, shared_batch=False, precision=nes_b200.PREC_HYBRID)
     for i in range(P):
         base = theta if parents[i] == 0 else theta_b
         th, _ = noise.member_theta(base, noise.noise_row(golden_mod.TABLE_SEED, offs_all[i], play, D), 0.02, +1)
