@@ -139,8 +139,8 @@ int nes_last_gradient_ms(nes_ctx* ctx, float* ms);
 int nes_last_rollout_ms(nes_ctx* ctx, float* ms);
 /* per-kernel timing of the decode launches (CUDA events on the context stream).  kinds: 0 plain member GEMM
  * (img_embed / LayerNorm pre-activations), 1 LSTM member GEMM, 2 vocabulary-projection member GEMM, 3 finalize / margin /
- * refine, 4 masked split-fp16 fallback of the HYBRID vocabulary projection.
- * nes_profile_read synchronises, returns the summed durations [5] and launch counts [5] since the last read. */
+ * refine, 4 masked split-fp16 fallback of the HYBRID vocabulary projection, 5 materialisation of the wave's member weights.
+ * nes_profile_read synchronises, returns the summed durations [6] and launch counts [6] since the last read. */
 int nes_profile_enable(nes_ctx* ctx, int on);
 int nes_profile_read(nes_ctx* ctx, float* ms_by_kind, int32_t* count_by_kind);
 /* HYBRID bookkeeping, counted while profiling is enabled: out4 = {rows refined, candidate logits re-evaluated in fp32,

@@ -243,10 +243,10 @@ class NesContext:
         _lib.check(self.lib.nes_profile_enable(self._h, int(bool(on))))
 
     def profile_read(self):
-        ms = (ctypes.c_float * 5)()
-        cnt = (ctypes.c_int32 * 5)()
+        ms = (ctypes.c_float * 6)()
+        cnt = (ctypes.c_int32 * 6)()
         _lib.check(self.lib.nes_profile_read(self._h, ms, cnt))
-        return {k: {'ms': float(ms[i]), 'count': int(cnt[i])} for i, k in enumerate(('plain', 'lstm', 'logit', 'finalize', 'fallback'))}
+        return {k: {'ms': float(ms[i]), 'count': int(cnt[i])} for i, k in enumerate(('plain', 'lstm', 'logit', 'finalize', 'fallback', 'materialise'))}
 
     def hybrid_stats(self, reset=True):
         out = (ctypes.c_int64 * 4)()

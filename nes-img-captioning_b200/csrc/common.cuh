@@ -94,7 +94,7 @@ struct Ctx {
 
     DecodeWorkspace* ws = nullptr;
 };
-enum { PROF_PLAIN = 0, PROF_LSTM = 1, PROF_LOGIT = 2, PROF_FINALIZE = 3, PROF_FALLBACK = 4, PROF_KINDS = 5 };
+enum { PROF_PLAIN = 0, PROF_LSTM = 1, PROF_LOGIT = 2, PROF_FINALIZE = 3, PROF_FALLBACK = 4, PROF_MATERIALISE = 5, PROF_KINDS = 6 };
 struct ProfScope {                          // RAII: record an event pair around one launch when profiling is on
     Ctx* c; int idx = -1;
     ProfScope(Ctx* c_, int kind) : c(c_) {

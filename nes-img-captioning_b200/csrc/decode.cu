@@ -71,7 +71,12 @@ struct DecodeWorkspace {
     float* c_state = nullptr;
     float *pre_i = nullptr, *pre_h = nullptr;               // LayerNorm path
     LogitPartial* partials = nullptr;
-    CandPartial* cand = nullptr; float* margin = nullptr; int32_t* pre_tok = nullptr; float* pre_lp = nullptr; uint8_t* unit_flag = nullptr;   // HYBRID
+    CandHead* heads = nullptr; CandEntry* entries = nullptr;                                       // HYBRID candidate lists
+    // materialised member weights of the wave (dense.cuh): LSTM split fp16 per segment, vocabulary projection single fp16
+    bool dense_lstm = false, dense_logit = false; int ntl = 0, ntv = 0;
+    __half *wl_hi[2] = {nullptr, nullptr}, *wl_lo[2] = {nullptr, nullptr}; float* wl_bias = nullptr;
+    __half* wv16 = nullptr; float* wv_bias = nullptr;
+    float* margin = nullptr; int32_t* pre_tok = nullptr; float* pre_lp = nullptr; uint8_t* unit_flag = nullptr;   // HYBRID
     unsigned long long* stats = nullptr;
     uint8_t* unfinished = nullptr; int32_t* unf_count = nullptr;
     // per call
@@ -309,7 +314,24 @@ int decode_create(Ctx* c, int wave_members, int rows) {
     for (int b = 0; b < 2; ++b) if (dmalloc(&ws->h_hi[b], WR * ws->R) || dmalloc(&ws->h_lo[b], WR * ws->R)) return 1;
     if (dmalloc(&ws->c_state, WR * ws->R)) return 1;
     if (dmalloc(&ws->partials, 2 * WR)) return 1;
-    if (dmalloc(&ws->cand, 2 * WR) || dmalloc(&ws->margin, WR) || dmalloc(&ws->pre_tok, WR) || dmalloc(&ws->pre_lp, WR) || dmalloc(&ws->unit_flag, WR / 128) || dmalloc(&ws->stats, 4)) return 1;
+    {
+        const char* e = getenv("NES_FACTORED");                       // experiments / tests: keep every layer in the factored form
+        const bool factored = e && atoi(e) != 0;
+        ws->dense_lstm = !factored && !d.layer_n;
+        ws->dense_logit = !factored && ws->R <= 512;
+        ws->ntl = (ws->R + kLstmTileUnits - 1) / kLstmTileUnits;
+        ws->ntv = (ws->V1 + 255) / 256;
+        if (ws->dense_lstm) {
+            const int64_t rows_l = (int64_t)ws->W * ws->ntl * kLstmTileCols;
+            if (dmalloc(&ws->wl_hi[0], rows_l * ws->E) || dmalloc(&ws->wl_lo[0], rows_l * ws->E) ||
+                dmalloc(&ws->wl_hi[1], rows_l * ws->R) || dmalloc(&ws->wl_lo[1], rows_l * ws->R) || dmalloc(&ws->wl_bias, rows_l)) return 1;
+        }
+        if (ws->dense_logit) {
+            if (dmalloc(&ws->wv16, (int64_t)ws->W * ws->V1 * ws->R) || dmalloc(&ws->wv_bias, (int64_t)ws->W * ws->V1) ||
+                dmalloc(&ws->heads, 2 * WR) || dmalloc(&ws->entries, 2 * WR * kCandCap)) return 1;
+        }
+    }
+    if (dmalloc(&ws->margin, WR) || dmalloc(&ws->pre_tok, WR) || dmalloc(&ws->pre_lp, WR) || dmalloc(&ws->unit_flag, WR / 128) || dmalloc(&ws->stats, 4)) return 1;
     NES_CUDA(cudaMemsetAsync(ws->stats, 0, 32, c->stream));
     if (dmalloc(&ws->unfinished, WR) || dmalloc(&ws->unf_count, (int64_t)(ws->T + 2) * ws->W)) return 1;
     if (d.layer_n) { if (dmalloc(&ws->pre_i, WR * 5 * ws->R) || dmalloc(&ws->pre_h, WR * 5 * ws->R)) return 1; }
@@ -328,7 +350,7 @@ void decode_destroy(Ctx* c) {
     DecodeWorkspace* ws = c->ws;
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
-                    ws->pre_i, ws->pre_h, ws->partials, ws->cand, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
+                    ws->pre_i, ws->pre_h, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
                     ws->d_lp, ws->d_forced};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
@@ -340,6 +362,7 @@ static int sm_count(Ctx* c) {
     if (!n[c->device]) { if (cudaDeviceGetAttribute(&n[c->device], cudaDevAttrMultiProcessorCount, c->device) != cudaSuccess || n[c->device] < 1) n[c->device] = 148; }
     return n[c->device];
 }
+static int env_debug();
 template <int EPI, int PREC>
 static int launch_gemm(Ctx* c, GemmParams& p, int64_t n_members) {
     using C = GemmCfg<EPI, PREC>;
@@ -351,7 +374,7 @@ static int launch_gemm(Ctx* c, GemmParams& p, int64_t n_members) {
     const int64_t units = n_members * p.m_tiles;
     NES_CHECK(units >= 1 && units < (1ll << 31), "bad unit count");
     p.n_units = (int32_t)units;
-    { static int dbg = -1; if (dbg < 0) { const char* e = getenv("NES_DEBUG"); dbg = e ? atoi(e) : 0; } p.debug = dbg; }
+    p.debug = env_debug();
     // persistent: one CTA per SM, CTA b owns units b, b + grid, ... and sweeps every weight tile of each
     const int sms = sm_count(c);
     const unsigned grid = (unsigned)(units < sms ? units : sms);
@@ -364,6 +387,64 @@ static int launch_gemm(Ctx* c, GemmParams& p, int64_t n_members) {
 template <int EPI>
 static int launch_gemm_prec(Ctx* c, GemmParams& p, int64_t n_members, int prec) {
     return prec == NES_PREC_EXACT ? launch_gemm<EPI, NES_PREC_EXACT>(c, p, n_members) : launch_gemm<EPI, NES_PREC_FAST>(c, p, n_members);
+}
+
+static int env_debug() { static int dbg = -1; if (dbg < 0) { const char* e = getenv("NES_DEBUG"); dbg = e ? atoi(e) : 0; } return dbg; }
+template <int EPI>
+static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
+    using C = DenseCfg<EPI>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        NES_CUDA(cudaFuncSetAttribute(k_member_dense<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        attr_done = true;
+    }
+    const int64_t units = n_members * p.m_tiles;
+    NES_CHECK(units >= 1 && units < (1ll << 31), "bad unit count");
+    p.n_units = (int32_t)units;
+    p.debug = env_debug();
+    const int sms = sm_count(c);
+    const unsigned grid = (unsigned)(units < sms ? units : sms);
+    ProfScope prof(c, EPI == DEN_LSTM ? PROF_LSTM : PROF_LOGIT);
+    k_member_dense<EPI><<<grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// member weights of one wave, materialised once per rollout (dense.cuh)
+static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit) {
+    DecodeWorkspace* ws = c->ws;
+    const Layout& L = c->lay;
+    ProfScope prof(c, PROF_MATERIALISE);
+    auto mat = [&](int wt, int K, int out_rows, int mode, int src_rows, __half* hi, __half* lo) {
+        MatParams q{};
+        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D;
+        q.w_start = L.t[wt].start; q.w_pstart = L.t[wt].pstart; q.K = K; q.out_rows = out_rows; q.mode = mode; q.R = ws->R; q.src_rows = src_rows;
+        q.sigma = sigma; q.hi = hi; q.lo = lo; q.n_members = nm;
+        k_materialise<<<148 * 16, 256, 0, c->stream>>>(q);
+        c->launches++;
+    };
+    auto matb = [&](int b0, int b1, int out_cols, int mode, int src_n, float* out) {
+        MatBiasParams q{};
+        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D;
+        q.b_start[0] = L.t[b0].start; q.b_pstart[0] = L.t[b0].pstart; q.nb = 1;
+        if (b1 >= 0) { q.b_start[1] = L.t[b1].start; q.b_pstart[1] = L.t[b1].pstart; q.nb = 2; }
+        q.out_cols = out_cols; q.mode = mode; q.R = ws->R; q.src_n = src_n; q.sigma = sigma; q.out = out; q.n_members = nm;
+        k_materialise_bias<<<148 * 4, 256, 0, c->stream>>>(q);
+        c->launches++;
+    };
+    if (lstm) {
+        const int rows_l = ws->ntl * kLstmTileCols;
+        mat(T_I2H_W, ws->E, rows_l, 1, 5 * ws->R, ws->wl_hi[0], ws->wl_lo[0]);
+        mat(T_H2H_W, ws->R, rows_l, 1, 5 * ws->R, ws->wl_hi[1], ws->wl_lo[1]);
+        matb(T_I2H_B, T_H2H_B, rows_l, 1, 5 * ws->R, ws->wl_bias);
+    }
+    if (logit) {
+        mat(T_LOGIT_W, ws->R, ws->V1, 0, ws->V1, ws->wv16, nullptr);
+        matb(T_LOGIT_B, -1, ws->V1, 0, ws->V1, ws->wv_bias);
+    }
+    NES_CUDA(cudaGetLastError());
+    return 0;
 }
 
 // fill one GEMM segment: activations A (hi/lo buffers with `a_rows` rows), weight tensor wt, bias tensor bt (-1 none)
@@ -415,8 +496,9 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     const bool tracing = h_trace || logit_trace || forced;
     // HYBRID = split-fp16 everywhere except the vocabulary projection, which runs on fp16 operands with an exact
     // fp32 re-evaluation of the arg-max candidates (hybrid.cuh); a logit trace needs the accurate logits themselves
-    const bool hybrid = precision == NES_PREC_HYBRID && !logit_trace;
+    const bool hybrid = precision == NES_PREC_HYBRID && !logit_trace && ws->dense_logit;
     if (precision == NES_PREC_HYBRID) precision = NES_PREC_EXACT;
+    const bool dense_lstm = ws->dense_lstm && precision == NES_PREC_EXACT;     // split-fp16 LSTM on materialised member weights
     NES_CHECK(!tracing || n_members <= ws->W, "trace mode handles a single wave");
     if (n_members == 0) return 0;
     if (hybrid && !c->eps_rowmax_valid && launch_bound_norms(c, -1)) return 1;
@@ -462,6 +544,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
         NES_CUDA(cudaMemsetAsync(ws->h_hi[0], 0, sizeof(__half) * WR * R, c->stream));
         NES_CUDA(cudaMemsetAsync(ws->h_lo[0], 0, sizeof(__half) * WR * R, c->stream));
         NES_CUDA(cudaMemsetAsync(ws->unf_count, 0, sizeof(int32_t) * (T + 2) * ws->W, c->stream));
+        if ((dense_lstm || hybrid) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid)) return 1;
 
         GemmParams base{};
         base.rows = rows; base.rows_pad = rows_pad; base.m_tiles = m_tiles;
@@ -484,7 +567,20 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
         for (int t = 0; t <= T; ++t) {
             // ---- (h, c) = core(x_t, (h, c))
             float* ht = h_trace ? h_trace + (int64_t)t * n_members * rows * R : nullptr;
-            if (!c->dims.layer_n) {
+            if (dense_lstm) {
+                DenseParams p{};
+                const int bk = DenseCfg<DEN_LSTM>::BK;
+                const int64_t b_rows_all = (int64_t)ws->W * ws->ntl * kLstmTileCols;
+                if (get_map(ws, &p.a_hi[0], ws->x_hi, a_rows_w, E, 128, bk) || get_map(ws, &p.a_lo[0], ws->x_lo, a_rows_w, E, 128, bk) ||
+                    get_map(ws, &p.a_hi[1], ws->h_hi[hb], a_rows_w, R, 128, bk) || get_map(ws, &p.a_lo[1], ws->h_lo[hb], a_rows_w, R, 128, bk) ||
+                    get_map(ws, &p.b_hi[0], ws->wl_hi[0], b_rows_all, E, kLstmTileCols, bk) || get_map(ws, &p.b_lo[0], ws->wl_lo[0], b_rows_all, E, kLstmTileCols, bk) ||
+                    get_map(ws, &p.b_hi[1], ws->wl_hi[1], b_rows_all, R, kLstmTileCols, bk) || get_map(ws, &p.b_lo[1], ws->wl_lo[1], b_rows_all, R, kLstmTileCols, bk)) return 1;
+                p.K[0] = E; p.K[1] = R; p.nseg = 2;
+                p.rows = rows; p.rows_pad = rows_pad; p.m_tiles = m_tiles; p.n_tiles = ws->ntl; p.N = R;
+                p.b_rows = ws->ntl * kLstmTileCols; p.bias = ws->wl_bias; p.bias_stride = ws->ntl * kLstmTileCols;
+                p.c_state = ws->c_state; p.out_hi = ws->h_hi[hb ^ 1]; p.out_lo = ws->h_lo[hb ^ 1]; p.h_trace = ht;
+                if (launch_dense<DEN_LSTM>(c, p, nm)) return 1;
+            } else if (!c->dims.layer_n) {
                 GemmParams p = base;
                 p.nseg = 2; p.N = R; p.chunk_stride = R; p.n_tiles = R / 16;
                 if (fill_seg(c, p, 0, ws->x_hi, ws->x_lo, a_rows_w, E, 0, T_I2H_W, T_I2H_B, 16, precision, 5, R)) return 1;
@@ -526,13 +622,21 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     { ProfScope prof(c, PROF_FINALIZE);
                       k_row_margin<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(mg); c->launches++; }
                     NES_CUDA(cudaGetLastError());
-                    GemmParams pc = p;
-                    if (fill_seg(c, pc, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128, NES_PREC_FAST)) return 1;
-                    pc.cand = ws->cand; pc.margin = ws->margin;
-                    if (launch_gemm<EPI_LOGITC, NES_PREC_FAST>(c, pc, nm)) return 1;
+                    {
+                        DenseParams pc{};
+                        const int bk = DenseCfg<DEN_LOGITC>::BK;
+                        if (get_map(ws, &pc.a_hi[0], ws->h_hi[hb], a_rows_w, R, 128, bk) ||
+                            get_map(ws, &pc.b_hi[0], ws->wv16, (int64_t)ws->W * V1, R, 256, bk)) return 1;
+                        pc.a_lo[0] = pc.a_hi[0]; pc.b_lo[0] = pc.b_hi[0];
+                        pc.K[0] = R; pc.K[1] = 0; pc.nseg = 1;
+                        pc.rows = rows; pc.rows_pad = rows_pad; pc.m_tiles = m_tiles; pc.n_tiles = ws->ntv; pc.N = V1;
+                        pc.b_rows = V1; pc.bias = ws->wv_bias; pc.bias_stride = V1;
+                        pc.heads = ws->heads; pc.entries = ws->entries; pc.margin = ws->margin;
+                        if (launch_dense<DEN_LOGITC>(c, pc, nm)) return 1;
+                    }
                     NES_CUDA(cudaMemsetAsync(ws->unit_flag, 0, (size_t)nm * m_tiles, c->stream));
                     RefineParams rf{};
-                    rf.cand = ws->cand; rf.margin = ws->margin; rf.h_hi = ws->h_hi[hb]; rf.h_lo = ws->h_lo[hb]; rf.R = R; rf.V1 = V1;
+                    rf.heads = ws->heads; rf.entries = ws->entries; rf.margin = ws->margin; rf.h_hi = ws->h_hi[hb]; rf.h_lo = ws->h_lo[hb]; rf.R = R; rf.V1 = V1;
                     rf.rows = rows; rf.rows_pad = rows_pad; rf.m_tiles = m_tiles; rf.n_members = nm;
                     rf.off = base.off; rf.sign = base.sign; rf.parent = base.parent; rf.theta32 = c->theta32; rf.table = c->table; rf.D = L.D;
                     rf.w_start = L.t[T_LOGIT_W].start; rf.w_pstart = L.t[T_LOGIT_W].pstart; rf.b_start = L.t[T_LOGIT_B].start; rf.b_pstart = L.t[T_LOGIT_B].pstart;

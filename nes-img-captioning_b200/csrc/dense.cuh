@@ -1,0 +1,431 @@
+// Member GEMMs on MATERIALISED member weights, for the two layers whose weights are reused by every decode step.
+//
+// The factored kernel (member_gemm.cuh) never forms theta +- sigma*eps; that is the right trade for a weight that is
+// used once per generation (img_embed), but the LSTM weights are used 17 times and logit.weight 16 times per
+// generation, and in split-fp16 the factored form costs 5 MMA passes per k-step (x_hi*[theta_hi|eps], x_hi*theta_lo,
+// x_lo*[theta_hi|eps]) and three operand tiles per stage.  With 180 GB of HBM a wave of 1000 members can simply hold
+//     W_m = fl32(theta_p +- fl32(sigma*eps_m))            (exactly the reference's member weights, algorithm/nets.py:113)
+// as split fp16 (LSTM: W*2^8 = hi + lo, 10.8 MB per member) or single fp16 (vocabulary projection of the HYBRID
+// scheme, 9.7 MB per member), written once per generation by k_materialise.  The decode GEMMs then are plain
+//     LSTM   : acc = x_hi*W_hi + x_lo*W_hi + x_hi*W_lo   -> ONE 240-column accumulator (48 hidden units x 5 gates),
+//              3 MMAs of N = 240 per k-step, TMEM double-buffered, maxout-LSTM cell fused in the epilogue;
+//     LOGITC : acc = x_hi*W16, N = 256, the member's x block (128 x K fp16) stays RESIDENT in shared memory for all 38
+//              vocabulary tiles (the factored kernel re-fetched it per tile: L2 -> SM traffic was its bound),
+//              online max / sum-exp per row in registers, arg-max candidates appended to a per-row list in HBM.
+// Same roles as the factored kernel: warps 0 and 10 TMA producers, warp 1 MMA issuer, warps 2..9 epilogue.
+//
+// Reference math: captioning/nets.py:98-134 (LSTMCore.forward), :202-208 (logit, log_softmax, max).
+#pragma once
+#include "member_gemm.cuh"
+
+namespace nes {
+
+enum { DEN_LSTM = 0, DEN_LOGITC = 1 };
+constexpr int kLstmTileUnits = 48;          // hidden units per LSTM tile; accumulator column = gate * 48 + unit
+constexpr int kLstmTileCols = 5 * kLstmTileUnits;
+constexpr int kCandCap = 64;                // candidate entries per half row (append-only; overflow -> split-fp16 fallback)
+
+struct alignas(16) CandHead { float mx; float sum; int32_t n; int32_t pad; };
+struct alignas(8) CandEntry { float v; int32_t idx; };
+
+struct alignas(64) DenseParams {
+    CUtensorMap a_hi[2], a_lo[2];           // activations of segment s: [rows_total, K_s] fp16, box BK x 128
+    CUtensorMap b_hi[2], b_lo[2];           // materialised weights of segment s: [W * b_rows, K_s] fp16, box BK x BN
+    int32_t K[2]; int32_t nseg;
+    int32_t rows, rows_pad, m_tiles, n_tiles, n_units;
+    int32_t N;                              // valid outputs: R (LSTM hidden units) or V+1 (LOGITC)
+    int32_t b_rows;                         // weight rows per member in the materialised buffer
+    const float* bias; int32_t bias_stride; // [W][bias_stride] member bias in accumulator-column order
+    float* c_state; __half* out_hi; __half* out_lo; float* h_trace;       // LSTM
+    CandHead* heads; CandEntry* entries; const float* margin;            // LOGITC
+    int32_t debug;
+};
+
+template <int EPI> struct DenseCfg {
+    static constexpr bool LSTM = EPI == DEN_LSTM;
+    static constexpr int BM = 128;
+    static constexpr int BK = LSTM ? 32 : 64;
+    static constexpr int SWZ = BK * 2;
+    static constexpr int BN = LSTM ? kLstmTileCols : 256;
+    static constexpr int NA = LSTM ? 2 : 1;
+    static constexpr int NB = LSTM ? 2 : 1;
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int ARES_KB = LSTM ? 0 : 8;                         // resident A k-blocks (LOGITC needs K <= 512)
+    static constexpr int ARES_BYTES = ARES_KB * A_BYTES;
+    static constexpr int STAGE_BYTES = (LSTM ? NA * A_BYTES : 0) + NB * B_BYTES;
+    static constexpr int CTRL_BYTES = 2048;                              // barriers [0,512), tmem slot, bias [512, 1536)
+    static constexpr int SMEM_MAX = 227 * 1024;
+    static constexpr int STAGES_FIT = (SMEM_MAX - 1024 - CTRL_BYTES - ARES_BYTES) / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_FIT > 6 ? 6 : STAGES_FIT;
+    static constexpr int ACC_STRIDE = 256;
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int SMEM_BYTES = ARES_BYTES + STAGES * STAGE_BYTES + 1024 + CTRL_BYTES;
+    static constexpr int THREADS = 352;
+    static_assert(STAGES >= 3, "pipeline too shallow");
+    static_assert(BN <= ACC_STRIDE && BN % 16 == 0, "accumulator shape");
+    static_assert(STAGE_BYTES % 1024 == 0 && A_BYTES % 1024 == 0 && B_BYTES % 1024 == 0, "swizzle atoms need 1024-byte alignment");
+    static_assert(SMEM_BYTES <= SMEM_MAX, "shared memory budget");
+};
+
+template <int EPI>
+__global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__ DenseParams p) {
+    using C = DenseCfg<EPI>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* ares = smem;                                             // LOGITC: resident x block, ARES_KB k-blocks
+    uint8_t* ring = smem + C::ARES_BYTES;
+    uint8_t* ctrl = ring + C::STAGES * C::STAGE_BYTES;
+    uint64_t* full_bar   = reinterpret_cast<uint64_t*>(ctrl);
+    uint64_t* empty_bar  = full_bar + C::STAGES;
+    uint64_t* tfull_bar  = empty_bar + C::STAGES;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint64_t* afull_bar  = tempty_bar + 2;                            // [8] resident A k-block landed
+    uint64_t* aempty_bar = afull_bar + 8;                             // [8] last MMA of the unit that reads it retired
+    uint32_t* tmem_slot  = reinterpret_cast<uint32_t*>(aempty_bar + 8);
+    float* s_bias = reinterpret_cast<float*>(ctrl + 512);             // [BN]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+        for (int b = 0; b < 2; ++b) { tc::mbar_init(&tfull_bar[b], 1); tc::mbar_init(&tempty_bar[b], 8); }
+        for (int k = 0; k < 8; ++k) { tc::mbar_init(&afull_bar[k], 1); tc::mbar_init(&aempty_bar[k], 1); }
+        tc::fence_barrier_init();
+    }
+    if (warp == 1) tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0 || warp == 10) {
+        // =========================== TMA producers (two warps fill alternate stages) ===========================
+        const int pid = warp == 0 ? 0 : 1;
+        if (lane == 0) {
+            for (int s = 0; s < p.nseg; ++s) {
+                tc::prefetch_tmap(&p.a_hi[s]); tc::prefetch_tmap(&p.b_hi[s]);
+                if (C::LSTM) { tc::prefetch_tmap(&p.a_lo[s]); tc::prefetch_tmap(&p.b_lo[s]); }
+            }
+            int stage = 0; uint32_t phase = 0; uint32_t q = 0; uint32_t uc = 0;
+            for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++uc) {
+                const int64_t member = u / p.m_tiles;
+                const int mt = u % p.m_tiles;
+                const int32_t a_row = (int32_t)(member * p.rows_pad + mt * C::BM);
+                const int32_t b_row0 = (int32_t)(member * p.b_rows);
+                if (!C::LSTM && pid == 0) {
+                    // the unit's x block: k-block kb may be overwritten once the previous unit's last tile has consumed it
+                    const int nkb = p.K[0] / C::BK;
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        if (uc > 0) tc::mbar_wait(&aempty_bar[kb], (uc - 1) & 1);
+                        tc::mbar_expect_tx(&afull_bar[kb], C::A_BYTES);
+                        tc::tma_load_2d(ares + kb * C::A_BYTES, &p.a_hi[0], &afull_bar[kb], kb * C::BK, a_row);
+                    }
+                }
+                for (int nt = 0; nt < p.n_tiles; ++nt) {
+                    for (int s = 0; s < p.nseg; ++s) {
+                        const int nkb = p.K[s] / C::BK;
+                        for (int kb = 0; kb < nkb; ++kb) {
+                            if (((q++) & 1) != pid) { if (++stage == C::STAGES) { stage = 0; phase ^= 1; } continue; }
+                            tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+                            uint8_t* st = ring + stage * C::STAGE_BYTES;
+                            tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                            if (C::LSTM) {
+                                tc::tma_load_2d(st, &p.a_hi[s], &full_bar[stage], kb * C::BK, a_row);
+                                tc::tma_load_2d(st + C::A_BYTES, &p.a_lo[s], &full_bar[stage], kb * C::BK, a_row);
+                                uint8_t* sb = st + 2 * C::A_BYTES;
+                                tc::tma_load_2d(sb, &p.b_hi[s], &full_bar[stage], kb * C::BK, b_row0 + nt * C::BN);
+                                tc::tma_load_2d(sb + C::B_BYTES, &p.b_lo[s], &full_bar[stage], kb * C::BK, b_row0 + nt * C::BN);
+                            } else {
+                                tc::tma_load_2d(st, &p.b_hi[s], &full_bar[stage], kb * C::BK, b_row0 + nt * C::BN);
+                            }
+                            if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // =========================== MMA issuer (one thread) ===========================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0; uint32_t it = 0; uint32_t uc = 0;
+            constexpr uint32_t idesc = tc::make_idesc_f16(128, C::BN);
+            for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++uc) {
+                for (int nt = 0; nt < p.n_tiles; ++nt, ++it) {
+                    const uint32_t buf = it & 1;
+                    tc::mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);
+                    tc::tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + buf * C::ACC_STRIDE;
+                    bool first = true;
+                    for (int s = 0; s < p.nseg; ++s) {
+                        const int nkb = p.K[s] / C::BK;
+                        for (int kb = 0; kb < nkb; ++kb) {
+                            if (!C::LSTM && nt == 0) tc::mbar_wait(&afull_bar[kb], uc & 1);
+                            tc::mbar_wait(&full_bar[stage], phase);
+                            tc::tc_fence_after();
+                            const uint32_t st = tc::smem_u32(ring + stage * C::STAGE_BYTES);
+#pragma unroll
+                            for (int k = 0; k < C::BK / 16; ++k) {
+                                if (C::LSTM) {
+                                    const uint64_t a_hi = tc::make_smem_desc<C::SWZ>(st + k * 32);
+                                    const uint64_t a_lo = tc::make_smem_desc<C::SWZ>(st + C::A_BYTES + k * 32);
+                                    const uint64_t b_hi = tc::make_smem_desc<C::SWZ>(st + 2 * C::A_BYTES + k * 32);
+                                    const uint64_t b_lo = tc::make_smem_desc<C::SWZ>(st + 2 * C::A_BYTES + C::B_BYTES + k * 32);
+                                    tc::umma_f16(d_tmem, a_hi, b_hi, idesc, (first && k == 0) ? 0u : 1u);
+                                    tc::umma_f16(d_tmem, a_lo, b_hi, idesc, 1u);
+                                    tc::umma_f16(d_tmem, a_hi, b_lo, idesc, 1u);
+                                } else {
+                                    const uint64_t a = tc::make_smem_desc<C::SWZ>(tc::smem_u32(ares + kb * C::A_BYTES) + k * 32);
+                                    tc::umma_f16(d_tmem, a, tc::make_smem_desc<C::SWZ>(st + k * 32), idesc, (first && k == 0) ? 0u : 1u);
+                                }
+                            }
+                            first = false;
+                            tc::umma_commit(&empty_bar[stage]);
+                            if (!C::LSTM && nt == p.n_tiles - 1) tc::umma_commit(&aempty_bar[kb]);
+                            if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                        }
+                    }
+                    tc::umma_commit(&tfull_bar[buf]);
+                }
+            }
+        }
+    } else {
+        // ======= epilogue: warps 2..9.  TMEM lane quarter = warp & 3 (rows), column half = (warp - 2) >> 2 =======
+        const int q = warp & 3;
+        const int hf = (warp - 2) >> 2;
+        const int et = (warp - 2) * 32 + lane;               // 0..255 among epilogue threads
+        const int row = q * 32 + lane;
+        const float sW = 1.0f / (kThetaScale * kActScale);
+        constexpr float kLog2e = 1.4426950408889634f;
+        // member bias of tile (u, nt), accumulator column et; fetched one tile ahead
+        auto bias_val = [&](int u, int nt) -> float {
+            if (u >= p.n_units || et >= C::BN) return 0.f;
+            const int64_t member = u / p.m_tiles;
+            const int col = nt * C::BN + et;
+            return col < p.bias_stride ? p.bias[member * p.bias_stride + col] : 0.f;
+        };
+        float b_cur = bias_val(blockIdx.x, 0);
+        uint32_t it = 0;
+        for (int u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+            const int64_t member = u / p.m_tiles;
+            const int mt = u % p.m_tiles;
+            const int m_local = mt * C::BM + row;
+            const bool row_ok = m_local < p.rows;
+            const int64_t grow = member * p.rows_pad + m_local;
+            float run_max = -INFINITY, run_sum = 0.f; int n_cand = 0;
+            const float margin = (!C::LSTM && row_ok) ? p.margin[grow] : 0.f;
+            CandEntry* ent = C::LSTM ? nullptr : p.entries + (grow * 2 + hf) * (int64_t)kCandCap;
+
+            for (int nt = 0; nt < p.n_tiles; ++nt, ++it) {
+                const uint32_t buf = it & 1;
+                asm volatile("bar.sync 1, 256;" ::: "memory");           // everyone is done with the previous tile's bias
+                if (et < C::BN) s_bias[et] = b_cur;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                b_cur = (nt + 1 < p.n_tiles) ? bias_val(u, nt + 1) : bias_val(u + gridDim.x, 0);
+                float cprev[24];
+                if (C::LSTM) {
+#pragma unroll
+                    for (int sb = 0; sb < 3; ++sb) {
+                        const int j0 = nt * kLstmTileUnits + hf * 24 + sb * 8;
+                        if (row_ok && j0 < p.N) {
+                            const float4* cp4 = reinterpret_cast<const float4*>(p.c_state + grow * p.N + j0);
+                            *reinterpret_cast<float4*>(&cprev[sb * 8]) = cp4[0];
+                            *reinterpret_cast<float4*>(&cprev[sb * 8 + 4]) = cp4[1];
+                        } else {
+#pragma unroll
+                            for (int uu = 0; uu < 8; ++uu) cprev[sb * 8 + uu] = 0.f;
+                        }
+                    }
+                }
+                tc::mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
+                tc::tc_fence_after();
+                const uint32_t trow = tmem_base + buf * C::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
+                if (!(p.debug & 1)) {
+                if (C::LSTM) {
+#pragma unroll
+                    for (int sb = 0; sb < 3; ++sb) {
+                        const int cu = hf * 24 + sb * 8;                 // first unit of this sub-batch inside the tile
+                        const int j0 = nt * kLstmTileUnits + cu;        // hidden unit index
+                        float pre[5][8];
+#pragma unroll
+                        for (int c = 0; c < 5; ++c) tc::tmem_ld8(trow + c * kLstmTileUnits + cu, pre[c]);
+                        tc::tmem_ld_wait();
+                        if (row_ok && j0 < p.N) {
+                            float cn[8], hn[8];
+#pragma unroll
+                            for (int uu = 0; uu < 8; ++uu) {
+                                float g[5];
+#pragma unroll
+                                for (int c = 0; c < 5; ++c) g[c] = pre[c][uu] * sW + s_bias[c * kLstmTileUnits + cu + uu];
+                                const float ig = sigmoid_f(g[0]), fg = sigmoid_f(g[1]), og = sigmoid_f(g[2]);
+                                const float cand = fmaxf(g[3], g[4]);
+                                cn[uu] = __fadd_rn(__fmul_rn(fg, cprev[sb * 8 + uu]), __fmul_rn(ig, cand));
+                                hn[uu] = og * tanhf(cn[uu]);
+                            }
+                            float* cp = p.c_state + grow * p.N + j0;
+                            *reinterpret_cast<float4*>(cp) = *reinterpret_cast<float4*>(&cn[0]);
+                            *reinterpret_cast<float4*>(cp + 4) = *reinterpret_cast<float4*>(&cn[4]);
+                            __half hh[8], hl[8];
+#pragma unroll
+                            for (int uu = 0; uu < 8; ++uu) split_half_dev(hn[uu], kActScale, hh[uu], hl[uu]);
+                            *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + j0) = *reinterpret_cast<uint4*>(hh);
+                            *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + j0) = *reinterpret_cast<uint4*>(hl);
+                            if (p.h_trace) {
+                                float* ht = p.h_trace + (member * p.rows + m_local) * (int64_t)p.N + j0;
+#pragma unroll
+                                for (int uu = 0; uu < 8; ++uu) ht[uu] = hn[uu];
+                            }
+                        }
+                    }
+                } else {
+                    // LOGITC: this warp owns 128 of the tile's 256 vocabulary columns, 32 at a time
+                    const int n_base = nt * C::BN;
+#pragma unroll 1
+                    for (int c0 = hf * 128; c0 < hf * 128 + 128; c0 += 32) {
+                        float y[32];
+                        tc::tmem_ld32(trow + c0, y);
+                        tc::tmem_ld_wait();
+#pragma unroll
+                        for (int uu = 0; uu < 32; ++uu) y[uu] = fmaf(y[uu], sW, s_bias[c0 + uu]);
+                        if (n_base + c0 + 32 > p.N) {                            // ragged last tile: mask the columns past V+1
+#pragma unroll
+                            for (int uu = 0; uu < 32; ++uu) if (n_base + c0 + uu >= p.N) y[uu] = -INFINITY;
+                        }
+                        float cm = y[0];
+#pragma unroll
+                        for (int uu = 1; uu < 32; ++uu) cm = fmaxf(cm, y[uu]);
+                        if (cm >= run_max - margin && cm > -INFINITY && row_ok) {
+                            // some column of this chunk is within the error margin of the running max: append it.  The list
+                            // is a superset of the final candidates (the threshold only rises); k_refine filters it.
+                            const float prev_max = run_max;
+                            run_max = fmaxf(run_max, cm);
+                            const float thr = run_max - margin;
+#pragma unroll
+                            for (int uu = 0; uu < 32; ++uu) {
+                                if (y[uu] >= thr) {
+                                    if (n_cand < kCandCap) { CandEntry e; e.v = y[uu]; e.idx = n_base + c0 + uu; ent[n_cand] = e; }
+                                    ++n_cand;
+                                }
+                            }
+                            if (run_max > prev_max) run_sum *= tc::ex2_approx((prev_max - run_max) * kLog2e);
+                        }
+                        if (run_max > -INFINITY) {
+                            const float ml2 = run_max * kLog2e;
+                            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                            for (int uu = 0; uu < 32; uu += 2) {
+                                s0 += tc::ex2_approx(fmaf(y[uu], kLog2e, -ml2));
+                                s1 += tc::ex2_approx(fmaf(y[uu + 1], kLog2e, -ml2));
+                            }
+                            run_sum += s0 + s1;
+                        }
+                    }
+                }
+                }   // !debug
+                tc::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(&tempty_bar[buf]);
+            }
+            if (!C::LSTM && row_ok) {
+                CandHead hd; hd.mx = run_max; hd.sum = run_sum; hd.n = n_cand; hd.pad = 0;
+                *reinterpret_cast<float4*>(&p.heads[grow * 2 + hf]) = *reinterpret_cast<float4*>(&hd);
+            }
+        }
+        tc::tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) { tc::tc_fence_after(); tc::tmem_dealloc(tmem_base, C::TMEM_COLS); }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_materialise: member weights W = fl32(theta_p +- fl32(sigma * eps)) of one weight matrix, for every member of the
+// wave, as fp16 operands scaled by 2^8 (hi, and lo = the rounding remainder when `lo` is given).
+//   mode 0: output row j = weight row j                      (logit.weight [V+1, R])
+//   mode 1: output row tile*240 + gate*48 + u = weight row gate*R + tile*48 + u, zero rows past R   (i2h / h2h [5R, K])
+struct MatParams {
+    const int64_t* off; const float* sign; const int32_t* parent;
+    const float* theta32; const __half* table; int64_t D;
+    int64_t w_start, w_pstart;
+    int32_t K, out_rows, mode, R, src_rows;
+    float sigma;
+    __half* hi; __half* lo;
+    int64_t n_members;
+};
+__global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
+    const int kv = p.K / 8;
+    const int64_t per_member = (int64_t)p.out_rows * kv;
+    const int64_t total = p.n_members * per_member;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t member = i / per_member;
+        const int64_t rem = i - member * per_member;
+        const int r = (int)(rem / kv);
+        const int k = (int)(rem - (int64_t)r * kv) * 8;
+        int src = r;
+        if (p.mode == 1) {
+            const int tile = r / kLstmTileCols, c = (r % kLstmTileCols) / kLstmTileUnits, u = r % kLstmTileUnits;
+            const int unit = tile * kLstmTileUnits + u;
+            src = unit < p.R ? c * p.R + unit : -1;
+        } else if (r >= p.src_rows) src = -1;
+        __half hh[8], hl[8];
+        if (src >= 0) {
+            const float sgn = p.sign[member];
+            const float* tw = p.theta32 + (int64_t)(p.parent ? p.parent[member] : 0) * p.D + p.w_start + (int64_t)src * p.K + k;
+            const uint4 ev = *reinterpret_cast<const uint4*>(p.table + p.off[member] + p.w_pstart + (int64_t)src * p.K + k);
+            const __half* eh = reinterpret_cast<const __half*>(&ev);
+            float tv[8];
+            if ((reinterpret_cast<uintptr_t>(tw) & 15) == 0) {
+                *reinterpret_cast<float4*>(&tv[0]) = reinterpret_cast<const float4*>(tw)[0];
+                *reinterpret_cast<float4*>(&tv[4]) = reinterpret_cast<const float4*>(tw)[1];
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) tv[e] = tw[e];
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const float nz = __fmul_rn(p.sigma, __half2float(eh[e]));
+                const float w = sgn > 0.f ? __fadd_rn(tv[e], nz) : __fsub_rn(tv[e], nz);
+                split_half_dev(w, kThetaScale, hh[e], hl[e]);
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { hh[e] = __float2half_rn(0.f); hl[e] = hh[e]; }
+        }
+        const int64_t o = (member * p.out_rows + r) * (int64_t)p.K + k;
+        *reinterpret_cast<uint4*>(p.hi + o) = *reinterpret_cast<uint4*>(hh);
+        if (p.lo) *reinterpret_cast<uint4*>(p.lo + o) = *reinterpret_cast<uint4*>(hl);
+    }
+}
+// member biases in accumulator-column order: LSTM (mode 1) = (b_i2h +- sigma eps) + (b_h2h +- sigma eps); logit (mode 0)
+struct MatBiasParams {
+    const int64_t* off; const float* sign; const int32_t* parent;
+    const float* theta32; const __half* table; int64_t D;
+    int64_t b_start[2], b_pstart[2]; int32_t nb;
+    int32_t out_cols, mode, R, src_n;
+    float sigma; float* out; int64_t n_members;
+};
+__global__ void __launch_bounds__(256) k_materialise_bias(const MatBiasParams p) {
+    const int64_t total = p.n_members * p.out_cols;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t member = i / p.out_cols;
+        const int col = (int)(i - member * p.out_cols);
+        int n = col;
+        if (p.mode == 1) {
+            const int tile = col / kLstmTileCols, c = (col % kLstmTileCols) / kLstmTileUnits, u = col % kLstmTileUnits;
+            const int unit = tile * kLstmTileUnits + u;
+            n = unit < p.R ? c * p.R + unit : -1;
+        } else if (col >= p.src_n) n = -1;
+        float b = 0.f;
+        if (n >= 0) {
+            const float sgn = p.sign[member];
+            const int64_t par = p.parent ? p.parent[member] : 0;
+            const int64_t off = p.off[member];
+            for (int s = 0; s < p.nb; ++s) {
+                const float tb = p.theta32[par * p.D + p.b_start[s] + n];
+                const float nz = __fmul_rn(p.sigma, __half2float(p.table[off + p.b_pstart[s] + n]));
+                b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
+            }
+        }
+        p.out[i] = b;
+    }
+}
+
+}  // namespace nes

@@ -1,18 +1,19 @@
-// HYBRID vocabulary projection: helpers around the fp16-operand logit GEMM (k_member_gemm<EPI_LOGITC, FAST>).
+// HYBRID vocabulary projection: helpers around the fp16-operand logit GEMM (k_member_dense<DEN_LOGITC>, dense.cuh).
 //
 // The reference picks the next token as argmax of float32 log-softmax(logit(h)) (captioning/nets.py:202-208).  Only the
 // arg-max and its log-prob are needed, so the 64 % of the FLOPs spent in the vocabulary projection do not need
 // split-fp16 accuracy everywhere: single-fp16 operands give every logit with a RIGOROUS error bound
-//     |l~ - l| <= 2^-11 (1 + 2^-11) |x|_2 (|w_j|_2 + |theta_j|_2)  +  fp32 accumulation,      w_j = theta_j +- sigma eps_j
-// (both operands are rounded to 11 significant bits, Cauchy-Schwarz), with |theta_j|_2 <= max row norm of logit.weight
-// (k_rowmax_theta, per parent) and |eps_j|_2 <= max row norm of the [L/R, R] view of the table (k_rowmax_eps).  Every
-// column within margin = 2 * bound of the approximate max is kept (the kMaxCand largest per half row) and k_refine
-// re-evaluates exactly those columns in fp32 from the float32 theta and the exact fp16 eps -- the same member weight
-// theta +- f32(sigma)*eps the reference forms (algorithm/nets.py:113).  Rows with more candidates than fit flag their
+//     |l~ - l| <= (2 * 2^-11 + 2^-22) |x|_2 |w_j|_2  +  fp32 accumulation,      w_j = theta_j +- sigma eps_j
+// (x and the materialised w_j are each rounded to 11 significant bits, Cauchy-Schwarz), with |w_j|_2 <= |theta_j|_2 +
+// sigma |eps_j|_2, |theta_j|_2 <= max row norm of logit.weight (k_rowmax_theta, per parent) and |eps_j|_2 <= max row norm
+// of the [L/R, R] view of the table (k_rowmax_eps).  Every column within margin = 2 * bound of the running max is appended
+// to the row's candidate list (a superset of the columns within the margin of the final max, since the running max only
+// rises) and k_refine re-evaluates the survivors in fp32 from the float32 theta and the exact fp16 eps -- the same member
+// weight theta +- f32(sigma)*eps the reference forms (algorithm/nets.py:113).  Rows whose list overflowed flag their
 // unit, which is then recomputed by the split-fp16 kernel (masked launch), so the result never depends on the bound
 // being tight, only on it being an upper bound.
 #pragma once
-#include "member_gemm.cuh"
+#include "dense.cuh"
 
 namespace nes {
 
@@ -73,14 +74,14 @@ __global__ void __launch_bounds__(128) k_row_margin(const MarginParams p) {
     s = warp_sum(s);
     if (lane == 0) {
         const int par = p.parent ? p.parent[member] : 0;
-        const float wsum = 2.f * p.theta_rowmax[par] + fabsf(p.sigma) * p.eps_rowmax[0];
+        const float wsum = 2.f * (p.theta_rowmax[par] + fabsf(p.sigma) * p.eps_rowmax[0]);
         // 2^-11 relative rounding of both operands, +10 % for the fp32 accumulation of K <= 4096 terms, x2 (two logits compared)
         p.margin[grow] = 2.f * 1.1f * 4.8828125e-4f * sqrtf(s) * 1.0001f * (wsum + 1e-4f) + 1e-30f;
     }
 }
 
 struct RefineParams {
-    const CandPartial* cand; const float* margin;
+    const CandHead* heads; const CandEntry* entries; const float* margin;
     const __half *h_hi, *h_lo; int R, V1; int rows, rows_pad, m_tiles; int64_t n_members;
     const int64_t* off; const float* sign; const int32_t* parent;
     const float* theta32; const __half* table; int64_t D;
@@ -90,38 +91,52 @@ struct RefineParams {
     uint8_t* unit_flag;                               // [n_members*m_tiles]: 1 -> recompute this unit with the split-fp16 kernel
     unsigned long long* stats;                        // nullable: [0] rows refined, [1] candidates evaluated, [2] rows overflowed
 };
-// one warp per (member, row): merge the two half-row candidate lists, re-evaluate every candidate logit in fp32 with
-// the member weight theta +- f32(sigma)*eps (algorithm/nets.py:113), pick the reference's argmax of float32 log-probs
-// (lowest index among equal rounded log-probs, captioning/nets.py:202-208)
+// one warp per (member, row): filter the two half-row candidate lists by the final threshold, re-evaluate every survivor
+// in fp32 with the member weight theta +- f32(sigma)*eps (algorithm/nets.py:113), pick the reference's argmax of float32
+// log-probs (lowest index among equal rounded log-probs, captioning/nets.py:202-208)
 __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
-    const int lane = threadIdx.x & 31;
-    const int64_t wid = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    __shared__ int s_idx[4][32];
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + wq;
     if (wid >= p.n_members * p.rows) return;
     const int64_t member = wid / p.rows;
     const int r = (int)(wid % p.rows);
     const int64_t grow = member * p.rows_pad + r;
-    const CandPartial* cp = p.cand + grow * 2;
-    const float m0 = cp[0].mx, m1 = cp[1].mx;
-    const float M = fmaxf(m0, m1);
+    const CandHead h0 = p.heads[grow * 2], h1 = p.heads[grow * 2 + 1];
+    const float M = fmaxf(h0.mx, h1.mx);
     const float thr = M - p.margin[grow];
-    if (fmaxf(cp[0].dropped, cp[1].dropped) >= thr) {          // a dropped logit is still a candidate: more than the lists hold
+    int count = 0;
+    bool overflow = h0.n > kCandCap || h1.n > kCandCap;
+    if (!overflow) {
+        for (int hf = 0; hf < 2; ++hf) {
+            const int n = hf ? h1.n : h0.n;
+            const CandEntry* ent = p.entries + (grow * 2 + hf) * (int64_t)kCandCap;
+            for (int e0 = 0; e0 < n; e0 += 32) {
+                const int e = e0 + lane;
+                CandEntry ce; ce.v = -INFINITY; ce.idx = 0;
+                if (e < n) ce = ent[e];
+                const bool ok = e < n && ce.v >= thr;
+                const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                const int pos = count + __popc(bal & ((1u << lane) - 1u));
+                if (ok && pos < 32) s_idx[wq][pos] = ce.idx;
+                count += __popc(bal);
+            }
+        }
+        overflow = count > 32;
+    }
+    if (overflow) {                                            // more candidates than the lists / one warp hold
         if (lane == 0) { p.unit_flag[member * p.m_tiles + r / 128] = 1; if (p.stats) atomicAdd(&p.stats[2], 1ull); }
         return;
     }
-    const float S = cp[0].sum * expf(m0 - M) + cp[1].sum * expf(m1 - M);
-    // lane k < 2*kMaxCand holds candidate slot (half k / kMaxCand, entry k % kMaxCand)
-    int my_idx = -1;
-    if (lane < 2 * kMaxCand) {
-        const int hf = lane / kMaxCand, e = lane % kMaxCand;
-        if (e < cp[hf].n && cp[hf].v[e] >= thr) my_idx = cp[hf].idx[e];
-    }
+    __syncwarp();
+    const float S = h0.sum * expf(h0.mx - M) + h1.sum * expf(h1.mx - M);
+    const int my_idx = lane < count ? s_idx[wq][lane] : -1;
     const float sgn = p.sign[member];
     const int64_t off = p.off[member];
     const int par = p.parent ? p.parent[member] : 0;
     float my_val = -INFINITY;
-    for (int c = 0; c < 2 * kMaxCand; ++c) {
+    for (int c = 0; c < count; ++c) {
         const int j = __shfl_sync(0xffffffffu, my_idx, c);
-        if (j < 0) continue;                                   // warp-uniform
         const float* tw = p.theta32 + (int64_t)par * p.D + p.w_start + (int64_t)j * p.R;
         const __half* ew = p.table + off + p.w_pstart + (int64_t)j * p.R;
         float acc = 0.f;
@@ -157,10 +172,7 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
         if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
     }
     if (lane == 0) { p.tok[grow] = idx; p.lp[grow] = best; }
-    if (p.stats) {
-        const unsigned n = __popc(__ballot_sync(0xffffffffu, my_idx >= 0));
-        if (lane == 0) { atomicAdd(&p.stats[0], 1ull); atomicAdd(&p.stats[1], (unsigned long long)n); }
-    }
+    if (p.stats && lane == 0) { atomicAdd(&p.stats[0], 1ull); atomicAdd(&p.stats[1], (unsigned long long)count); }
 }
 
 }  // namespace nes

@@ -23,7 +23,7 @@
 
 namespace nes {
 
-enum { EPI_PLAIN = 0, EPI_LSTM = 1, EPI_LOGIT = 2, EPI_LOGITC = 3 };   // LOGITC: fp16-operand logits + arg-max candidate list (HYBRID)
+enum { EPI_PLAIN = 0, EPI_LSTM = 1, EPI_LOGIT = 2 };
 
 struct alignas(64) SegMaps {
     CUtensorMap a_hi, a_lo;    // activations [rows_total, K] fp16 (x * 2^5 split hi/lo), box BK x 128
@@ -40,17 +40,6 @@ struct SegInfo {
 // whose logit is within tie_delta of the max (the reference takes argmax over float32 LOG-PROBS, whose quantum
 // near -log(V) is ~1e-6: logits closer than that tie and torch.max returns the lowest index -- see k_finalize)
 struct alignas(16) LogitPartial { float mx; int32_t idx; float sum; float lo_val; int32_t lo_idx; int32_t pad[3]; };
-
-// HYBRID vocabulary projection: the logits are computed with single-fp16 operands (error <= margin/2 per logit, a
-// rigorous bound from |x|, |theta|, |eps|), so every column whose approximate logit is within `margin` of the
-// approximate max is kept as a candidate and re-evaluated in fp32 by k_refine; more than kMaxCand of them -> the unit
-// falls back to the split-fp16 kernel.
-// The number of logits within d of the max of n Gaussians is geometric-tailed, P(>= k others) = (1 - exp(-d/gap))^k, and
-// while the running max is still low many more pass through the window, so the list keeps the kMaxCand LARGEST in-window
-// values and remembers the largest value it ever had to drop: only if that value is still inside the final window
-// (i.e. more than kMaxCand true candidates in this half row, ~1e-7 at d/gap = 0.14) does the unit fall back.
-constexpr int kMaxCand = 8;
-struct alignas(16) CandPartial { float mx; float sum; int32_t n; float dropped; float v[kMaxCand]; int32_t idx[kMaxCand]; int32_t pad[4]; };
 
 struct GemmParams {
     SegMaps maps[2];
@@ -74,8 +63,6 @@ struct GemmParams {
     LogitPartial* partials;                  // [member*rows_pad + row][2]: one per column half (epilogue warp pair)
     float* logit_trace; int64_t ld_trace;    // nullable, [member*rows + row, ld_trace]
     float tie_delta;                         // one float32 ulp of log(V+1)
-    CandPartial* cand;                       // LOGITC: [member*rows_pad + row][2]
-    const float* margin;                     // LOGITC: [member*rows_pad + row]
     const uint8_t* unit_mask;                // nullable: only units with a non-zero flag are computed (HYBRID fallback)
     int32_t debug;                           // experiments: bit 0 = skip the epilogue work (timing only, wrong results)
 };
@@ -166,9 +153,12 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                             if (((q++) & 1) != pid) { if (++stage == C::STAGES) { stage = 0; phase ^= 1; } continue; }
                             tc::mbar_wait(&empty_bar[stage], phase ^ 1);
                             uint8_t* st = smem + stage * C::STAGE_BYTES;
-                            tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                            const bool skip_a = (p.debug & 2) && nt > 0;      // experiment: emulate a smem-resident A operand (wrong results)
+                            tc::mbar_expect_tx(&full_bar[stage], skip_a ? C::NB * C::B_BYTES : C::STAGE_BYTES);
+                            if (!skip_a) {
                             tc::tma_load_2d(st, &mp.a_hi, &full_bar[stage], kb * C::BK, a_row);
                             if (PREC == NES_PREC_EXACT) tc::tma_load_2d(st + C::A_BYTES, &mp.a_lo, &full_bar[stage], kb * C::BK, a_row);
+                            }
                             uint8_t* sb = st + C::NA * C::A_BYTES;      // [theta_hi | eps | theta_lo]
                             if (C::NCH > 1) {       // the gate blocks of this tile in one 3-D request per operand
                                 tc::tma_load_3d(sb, &mp.w_hi, &full_bar[stage], kb * C::BK, w_row0, 0);
@@ -272,10 +262,6 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
             const float sE = sgn * p.sigma / kActScale;
             // running arg-max / log-sum-exp of this row over this thread's half of every vocabulary tile (LOGIT)
             float run_max = -INFINITY, run_sum = 0.f, lo_val = -INFINITY; int run_idx = 0, lo_idx = 0;
-            float cand_v[kMaxCand]; int cand_i[kMaxCand]; int n_cand = 0; float dropped = -INFINITY;
-#pragma unroll
-            for (int k = 0; k < kMaxCand; ++k) { cand_v[k] = -INFINITY; cand_i[k] = 0; }
-            const float margin = (EPI == EPI_LOGITC && row_ok) ? p.margin[grow] : 0.f;
 
             for (int nt = 0; nt < p.n_tiles; ++nt, ++it) {
                 const uint32_t buf = it & 1;
@@ -371,39 +357,6 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                             float cm = y[0];
 #pragma unroll
                             for (int uu = 1; uu < 32; ++uu) cm = fmaxf(cm, y[uu]);
-                            if (EPI == EPI_LOGITC) {
-                                if (cm >= run_max - margin) {                        // rare: some column of this chunk is a candidate
-                                    const float prev_max = run_max;
-                                    run_max = fmaxf(run_max, cm);
-                                    const float thr = run_max - margin;
-                                    int keep = 0;                                    // drop the candidates that fell out of the window
-#pragma unroll
-                                    for (int k = 0; k < kMaxCand; ++k) {
-                                        if (k < n_cand && cand_v[k] >= thr) { const float tv = cand_v[k]; const int ti = cand_i[k]; cand_v[keep] = tv; cand_i[keep] = ti; ++keep; }
-                                    }
-                                    n_cand = keep;
-#pragma unroll
-                                    for (int uu = 0; uu < 32; ++uu) {
-                                        if (y[uu] >= thr) {
-                                            if (n_cand < kMaxCand) {
-#pragma unroll
-                                                for (int k = 0; k < kMaxCand; ++k) if (k == n_cand) { cand_v[k] = y[uu]; cand_i[k] = n_base + c0 + uu; }
-                                                ++n_cand;
-                                            } else {                                 // full: keep the largest, remember what was dropped
-                                                float mn = cand_v[0]; int mk = 0;
-#pragma unroll
-                                                for (int k = 1; k < kMaxCand; ++k) if (cand_v[k] < mn) { mn = cand_v[k]; mk = k; }
-                                                if (y[uu] > mn) {
-                                                    dropped = fmaxf(dropped, mn);
-#pragma unroll
-                                                    for (int k = 0; k < kMaxCand; ++k) if (k == mk) { cand_v[k] = y[uu]; cand_i[k] = n_base + c0 + uu; }
-                                                } else dropped = fmaxf(dropped, y[uu]);
-                                            }
-                                        }
-                                    }
-                                    if (run_max > prev_max) run_sum *= tc::ex2_approx((prev_max - run_max) * kLog2e);
-                                }
-                            } else
                             if (cm > run_max) {                                      // rare after the first tiles: a new running max in this chunk
                                 const float prev_max = run_max;
 #pragma unroll
@@ -437,15 +390,6 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&tempty_bar[buf]);
-            }
-            if (EPI == EPI_LOGITC && row_ok) {
-                CandPartial cp; cp.mx = run_max; cp.sum = run_sum; cp.n = n_cand; cp.dropped = dropped;
-#pragma unroll
-                for (int k = 0; k < kMaxCand; ++k) { cp.v[k] = cand_v[k]; cp.idx[k] = cand_i[k]; }
-                cp.pad[0] = cp.pad[1] = cp.pad[2] = cp.pad[3] = 0;
-                float4* dst = reinterpret_cast<float4*>(&p.cand[grow * 2 + hf]);
-#pragma unroll
-                for (int k = 0; k < (int)(sizeof(CandPartial) / 16); ++k) dst[k] = reinterpret_cast<float4*>(&cp)[k];
             }
             if (EPI == EPI_LOGIT && row_ok) {
                 if (p.debug & 1) { run_max = 0.f; run_sum = 1.f + 1e-3f * (float)(grow % 977); run_idx = 1; lo_val = 0.f; lo_idx = 1; }

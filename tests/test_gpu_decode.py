@@ -49,6 +49,23 @@ def test_tokens_and_logprobs_match_reference_golden_exact_mode(name, prec, golde
     ctx.close()
 
 
+@pytest.mark.parametrize('name', ['g1', 'g3', 'g6'])
+def test_factored_lstm_path_still_matches_golden(name, golden, golden_mod, monkeypatch):
+    """NES_FACTORED=1 keeps every layer in the factored theta*x + sigma*eps*x form (no materialised member weights):
+    the split-fp16 member GEMM the dense kernels replaced must stay bit-exact on tokens too"""
+    monkeypatch.setenv('NES_FACTORED', '1')
+    c = golden_mod.CASES[name]
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    ctx = _ctx_for(c, golden_mod, L)
+    ctx.set_theta(theta)
+    offs2, signs = _members(offs)
+    seq, lp = ctx.rollout(offs2, signs, fc, c['sigma'], precision=1)
+    want_seq = golden[name + '_seq'].reshape(-1, c['B'], 16).astype(np.int64)
+    assert np.array_equal(seq.numpy(), want_seq)
+    assert np.allclose(lp.numpy(), golden[name + '_logprobs'].reshape(-1, c['B'], 16), rtol=1e-4, atol=1e-5)
+    ctx.close()
+
+
 @pytest.mark.parametrize('name,prec,tol', [('g1', 1, 2e-5), ('g3', 1, 2e-5), ('g1', 0, 1e-3), ('g3', 0, 1e-3), ('g5', 0, 1e-2), ('g5', 1, 2e-5)])
 def test_hidden_states_and_logits_teacher_forced(name, prec, tol, golden_mod):
     """per-step h and logits against the oracle trace when both follow the oracle's token path:
