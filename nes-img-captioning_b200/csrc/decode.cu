@@ -403,7 +403,9 @@ static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
     p.n_units = (int32_t)units;
     p.debug = env_debug();
     const int sms = sm_count(c);
-    const unsigned grid = (unsigned)(units < sms ? units : sms);
+    const int64_t items = EPI == DEN_LSTM ? units * p.n_tiles : units;     // see k_member_dense: LSTM work items are (unit, tile) pairs
+    NES_CHECK(items < (1ll << 31), "too many work items");
+    const unsigned grid = (unsigned)(items < sms ? items : sms);
     ProfScope prof(c, EPI == DEN_LSTM ? PROF_LSTM : PROF_LOGIT);
     k_member_dense<EPI><<<grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
     c->launches++;
@@ -421,7 +423,7 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D;
         q.w_start = L.t[wt].start; q.w_pstart = L.t[wt].pstart; q.K = K; q.out_rows = out_rows; q.mode = mode; q.R = ws->R; q.src_rows = src_rows;
         q.sigma = sigma; q.hi = hi; q.lo = lo; q.n_members = nm;
-        k_materialise<<<148 * 16, 256, 0, c->stream>>>(q);
+        k_materialise<<<dim3((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(nm < 32768 ? nm : 32768)), 256, 0, c->stream>>>(q);
         c->launches++;
     };
     auto matb = [&](int b0, int b1, int out_cols, int mode, int src_n, float* out) {

@@ -97,6 +97,10 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
     __syncthreads();
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // work items: LSTM = (unit, weight tile) pairs in tile-minor order, so the CTAs that run concurrently share a unit's
+    // activation block through L2 (it is fetched from HBM once, not once per tile); LOGITC = whole units, because the
+    // running arg-max / sum-exp of a row lives in one thread's registers across all vocabulary tiles
+    const int n_items = C::LSTM ? p.n_units * p.n_tiles : p.n_units;
 
     if (warp == 0 || warp == 10) {
         // =========================== TMA producers (two warps fill alternate stages) ===========================
@@ -107,7 +111,9 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                 if (C::LSTM) { tc::prefetch_tmap(&p.a_lo[s]); tc::prefetch_tmap(&p.b_lo[s]); }
             }
             int stage = 0; uint32_t phase = 0; uint32_t q = 0; uint32_t uc = 0;
-            for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++uc) {
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++uc) {
+                const int u = C::LSTM ? item / p.n_tiles : item;
+                const int nt0 = C::LSTM ? item - u * p.n_tiles : 0, nt1 = C::LSTM ? nt0 + 1 : p.n_tiles;
                 const int64_t member = u / p.m_tiles;
                 const int mt = u % p.m_tiles;
                 const int32_t a_row = (int32_t)(member * p.rows_pad + mt * C::BM);
@@ -121,7 +127,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                         tc::tma_load_2d(ares + kb * C::A_BYTES, &p.a_hi[0], &afull_bar[kb], kb * C::BK, a_row);
                     }
                 }
-                for (int nt = 0; nt < p.n_tiles; ++nt) {
+                for (int nt = nt0; nt < nt1; ++nt) {
                     for (int s = 0; s < p.nseg; ++s) {
                         const int nkb = p.K[s] / C::BK;
                         for (int kb = 0; kb < nkb; ++kb) {
@@ -149,8 +155,9 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0; uint32_t it = 0; uint32_t uc = 0;
             constexpr uint32_t idesc = tc::make_idesc_f16(128, C::BN);
-            for (int u = blockIdx.x; u < p.n_units; u += gridDim.x, ++uc) {
-                for (int nt = 0; nt < p.n_tiles; ++nt, ++it) {
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++uc) {
+                const int nt0 = C::LSTM ? item % p.n_tiles : 0, nt1 = C::LSTM ? nt0 + 1 : p.n_tiles;
+                for (int nt = nt0; nt < nt1; ++nt, ++it) {
                     const uint32_t buf = it & 1;
                     tc::mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);
                     tc::tc_fence_after();
@@ -203,9 +210,11 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
             const int col = nt * C::BN + et;
             return col < p.bias_stride ? p.bias[member * p.bias_stride + col] : 0.f;
         };
-        float b_cur = bias_val(blockIdx.x, 0);
+        float b_cur = C::LSTM ? bias_val(blockIdx.x / p.n_tiles, blockIdx.x % p.n_tiles) : bias_val(blockIdx.x, 0);
         uint32_t it = 0;
-        for (int u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int u = C::LSTM ? item / p.n_tiles : item;
+            const int nt0 = C::LSTM ? item - u * p.n_tiles : 0, nt1 = C::LSTM ? nt0 + 1 : p.n_tiles;
             const int64_t member = u / p.m_tiles;
             const int mt = u % p.m_tiles;
             const int m_local = mt * C::BM + row;
@@ -215,12 +224,16 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
             const float margin = (!C::LSTM && row_ok) ? p.margin[grow] : 0.f;
             CandEntry* ent = C::LSTM ? nullptr : p.entries + (grow * 2 + hf) * (int64_t)kCandCap;
 
-            for (int nt = 0; nt < p.n_tiles; ++nt, ++it) {
+            for (int nt = nt0; nt < nt1; ++nt, ++it) {
                 const uint32_t buf = it & 1;
                 asm volatile("bar.sync 1, 256;" ::: "memory");           // everyone is done with the previous tile's bias
                 if (et < C::BN) s_bias[et] = b_cur;
                 asm volatile("bar.sync 1, 256;" ::: "memory");
-                b_cur = (nt + 1 < p.n_tiles) ? bias_val(u, nt + 1) : bias_val(u + gridDim.x, 0);
+                {
+                    const int nx = item + (int)gridDim.x;                  // first tile of this CTA's next work item
+                    b_cur = (nt + 1 < nt1) ? bias_val(u, nt + 1)
+                          : (C::LSTM ? bias_val(nx / p.n_tiles, nx % p.n_tiles) : bias_val(nx, 0));
+                }
                 float cprev[24];
                 if (C::LSTM) {
 #pragma unroll
@@ -350,48 +363,57 @@ struct MatParams {
     __half* hi; __half* lo;
     int64_t n_members;
 };
+constexpr int kMatRowsPerBlock = 32;
+// grid = (ceil(out_rows / 32), members): one block writes 32 output rows of one member; a row is covered by K/8 threads
+// (16 bytes of eps each), so all index arithmetic is 32-bit and per row, not per element
 __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
     const int kv = p.K / 8;
-    const int64_t per_member = (int64_t)p.out_rows * kv;
-    const int64_t total = p.n_members * per_member;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t member = i / per_member;
-        const int64_t rem = i - member * per_member;
-        const int r = (int)(rem / kv);
-        const int k = (int)(rem - (int64_t)r * kv) * 8;
-        int src = r;
-        if (p.mode == 1) {
-            const int tile = r / kLstmTileCols, c = (r % kLstmTileCols) / kLstmTileUnits, u = r % kLstmTileUnits;
-            const int unit = tile * kLstmTileUnits + u;
-            src = unit < p.R ? c * p.R + unit : -1;
-        } else if (r >= p.src_rows) src = -1;
-        __half hh[8], hl[8];
-        if (src >= 0) {
-            const float sgn = p.sign[member];
-            const float* tw = p.theta32 + (int64_t)(p.parent ? p.parent[member] : 0) * p.D + p.w_start + (int64_t)src * p.K + k;
-            const uint4 ev = *reinterpret_cast<const uint4*>(p.table + p.off[member] + p.w_pstart + (int64_t)src * p.K + k);
-            const __half* eh = reinterpret_cast<const __half*>(&ev);
-            float tv[8];
-            if ((reinterpret_cast<uintptr_t>(tw) & 15) == 0) {
-                *reinterpret_cast<float4*>(&tv[0]) = reinterpret_cast<const float4*>(tw)[0];
-                *reinterpret_cast<float4*>(&tv[4]) = reinterpret_cast<const float4*>(tw)[1];
-            } else {
+    const int tpr = kv < 256 ? kv : 256;                 // threads per row
+    const int rpi = 256 / tpr;                           // rows per iteration
+    const int lr = threadIdx.x / tpr, kvi = threadIdx.x - lr * tpr;
+    if (lr >= rpi) return;
+    const int r_end = min(p.out_rows, ((int)blockIdx.x + 1) * kMatRowsPerBlock);
+    for (int64_t member = blockIdx.y; member < p.n_members; member += gridDim.y) {
+        const float sgn = p.sign[member];
+        const float* tbase = p.theta32 + (int64_t)(p.parent ? p.parent[member] : 0) * p.D + p.w_start;
+        const __half* ebase = p.table + p.off[member] + p.w_pstart;
+        for (int r = blockIdx.x * kMatRowsPerBlock + lr; r < r_end; r += rpi) {
+            int src = r;
+            if (p.mode == 1) {
+                const int tile = r / kLstmTileCols, rr = r - tile * kLstmTileCols;
+                const int c = rr / kLstmTileUnits, u = rr - c * kLstmTileUnits;
+                const int unit = tile * kLstmTileUnits + u;
+                src = unit < p.R ? c * p.R + unit : -1;
+            } else if (r >= p.src_rows) src = -1;
+            for (int k = kvi * 8; k < p.K; k += tpr * 8) {
+                __half hh[8], hl[8];
+                if (src >= 0) {
+                    const float* tw = tbase + (int64_t)src * p.K + k;
+                    const uint4 ev = *reinterpret_cast<const uint4*>(ebase + (int64_t)src * p.K + k);
+                    const __half* eh = reinterpret_cast<const __half*>(&ev);
+                    float tv[8];
+                    if ((reinterpret_cast<uintptr_t>(tw) & 15) == 0) {
+                        *reinterpret_cast<float4*>(&tv[0]) = reinterpret_cast<const float4*>(tw)[0];
+                        *reinterpret_cast<float4*>(&tv[4]) = reinterpret_cast<const float4*>(tw)[1];
+                    } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) tv[e] = tw[e];
+                        for (int e = 0; e < 8; ++e) tv[e] = tw[e];
+                    }
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const float nz = __fmul_rn(p.sigma, __half2float(eh[e]));
+                        const float w = sgn > 0.f ? __fadd_rn(tv[e], nz) : __fsub_rn(tv[e], nz);
+                        split_half_dev(w, kThetaScale, hh[e], hl[e]);
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) { hh[e] = __float2half_rn(0.f); hl[e] = hh[e]; }
+                }
+                const int64_t o = (member * p.out_rows + r) * (int64_t)p.K + k;
+                *reinterpret_cast<uint4*>(p.hi + o) = *reinterpret_cast<uint4*>(hh);
+                if (p.lo) *reinterpret_cast<uint4*>(p.lo + o) = *reinterpret_cast<uint4*>(hl);
             }
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const float nz = __fmul_rn(p.sigma, __half2float(eh[e]));
-                const float w = sgn > 0.f ? __fadd_rn(tv[e], nz) : __fsub_rn(tv[e], nz);
-                split_half_dev(w, kThetaScale, hh[e], hl[e]);
-            }
-        } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) { hh[e] = __float2half_rn(0.f); hl[e] = hh[e]; }
         }
-        const int64_t o = (member * p.out_rows + r) * (int64_t)p.K + k;
-        *reinterpret_cast<uint4*>(p.hi + o) = *reinterpret_cast<uint4*>(hh);
-        if (p.lo) *reinterpret_cast<uint4*>(p.lo + o) = *reinterpret_cast<uint4*>(hl);
     }
 }
 // member biases in accumulator-column order: LSTM (mode 1) = (b_i2h +- sigma eps) + (b_h2h +- sigma eps); logit (mode 0)
