@@ -292,18 +292,7 @@ def main():
             peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
         except Exception:
             pass
-        tf_peak = peaks.get('bf16_tflops_sustained', 1400.0)
-        # dominant kernel: the vocabulary projection with fused argmax / log-sum-exp (64 % of the algorithmic FLOPs)
-        k = prof['logit']
-        flop_per_launch = 2.0 * R * (V + 1) * rows * min(P, 1024)
-        ach = flop_per_launch / (k['ms'] / max(1, k['count']) * 1e-3) / 1e12 if k['count'] else None
-        out['roofline'] = {'bound': 'tensor', 'kernel': 'k_member_gemm<LOGIT> (vocabulary projection + fused argmax/log-prob)',
-                           'achieved': ach, 'peak': tf_peak, 'unit': 'TFLOP/s', 'frac': ach / tf_peak if ach else None,
-                           'peak_source': 'MEASURED_PEAKS.json bf16_tflops_sustained (of measured)' if peaks else 'fallback 1400 (of fallback)',
-                           'traffic': None, 'launches': k['count'], 'avg_launch_ms': k['ms'] / max(1, k['count']),
-                           'algorithmic_flop_per_launch': flop_per_launch,
-                           'whole_step_algorithmic_tflops': FLOP_PER_ROW * rows * P * a.steps / (ms * 1e-3) / 1e12,
-                           'kernel_time_share': {kk: vv['ms'] / ms for kk, vv in prof.items()}}
+        out['roofline'] = rooflines(prof, a, min(P, 1024), rows, ms, peaks)
         out['hybrid_stats'] = hstats
         if not a.no_extras and world == 1:
             out['extras'] = extras(ctx, nes_b200, torch, dev, peaks)
@@ -314,6 +303,49 @@ def main():
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def rooflines(prof, a, wave, rows, ms_total, peaks):
+    """per-kernel roofline of the two member GEMMs; the headline object is the one with the larger share of the step.
+    Algorithmic work per launch: LSTM step = 2*rows*(E+R)*5R FLOP per member; its bytes are the
+    member's LSTM weights at float32 size (the precision the path computes in: split-fp16 hi+lo is 4 B/element) plus
+    the activations in / (h, c) out.  Vocabulary projection = 2*rows*R*(V+1) FLOP per member; HYBRID streams the member's
+    fp16 logit weights (2 B/element) plus the fp16 activations."""
+    hbm = peaks.get('hbm_gbs', 6650.0)
+    tfl = peaks.get('bf16_tflops_sustained', 1400.0)
+    src = 'MEASURED_PEAKS.json' if peaks else 'B200_PROFILING.md fallback'
+    traffic = {}
+    try:
+        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'r1_traffic.json')))
+    except Exception:
+        pass
+    dense_lstm = a.precision in ('hybrid', 'exact') and os.environ.get('NES_FACTORED', '0') in ('', '0')
+    dense_logit = a.precision == 'hybrid' and dense_lstm
+    ks = {}
+    for name, key, flop, nbytes, dense, kern in (
+            ('lstm', 'lstm', 2.0 * rows * (E + R) * 5 * R * wave, wave * (5.0 * R * (E + R) * 4 + rows * (E + R) * 4 + rows * R * 8), dense_lstm,
+             'k_member_dense<LSTM> (split-fp16 LSTM step on materialised member weights, fused maxout cell)' if dense_lstm else 'k_member_gemm<LSTM> (factored theta*x + sigma*eps*x, fused maxout cell)'),
+            ('logit', 'logit', 2.0 * rows * R * (V + 1) * wave, wave * ((V + 1.0) * R * 2 + rows * R * 2), dense_logit,
+             'k_member_dense<LOGITC> (fp16 vocabulary projection, smem-resident x block, fused max / sum-exp / candidate lists)' if dense_logit else 'k_member_gemm<LOGIT> (factored vocabulary projection + fused argmax/log-prob)')):
+        k = prof[key]
+        if not k['count']:
+            continue
+        t = k['ms'] / k['count'] * 1e-3
+        if dense:
+            ach, peak, unit, bound = nbytes / t / 1e9, hbm, 'GB/s', 'hbm'
+        else:
+            ach, peak, unit, bound = flop / t / 1e12, tfl, 'TFLOP/s', 'tensor'
+        tr = traffic.get(kern.split(' ')[0])
+        ks[name] = {'bound': bound, 'kernel': kern, 'achieved': ach, 'peak': peak, 'unit': unit, 'frac': ach / peak,
+                    'peak_source': src + (' hbm_gbs' if dense else ' bf16_tflops_sustained'),
+                    'traffic': tr, 'launches': k['count'], 'avg_launch_ms': t * 1e3,
+                    'algorithmic_bytes_per_launch': nbytes, 'algorithmic_flop_per_launch': flop,
+                    'algorithmic_tflops': flop / t / 1e12, 'time_share': k['ms'] / ms_total}
+    top = max(ks, key=lambda n: ks[n]['time_share'])
+    out = dict(ks[top])
+    out['other_kernels'] = {n: v for n, v in ks.items() if n != top}
+    out['kernel_time_share'] = {kk: vv['ms'] / ms_total for kk, vv in prof.items()}
+    return out
 
 
 def extras(ctx, nes_b200, torch, dev, peaks):

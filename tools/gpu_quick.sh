@@ -4,11 +4,4 @@ tag=${1:-q}
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -q --timeout 600 -x > gpurun_out/${tag}_gputests.log 2>&1; echo "tests rc=$?"; tail -15 gpurun_out/${tag}_gputests.log
 timeout 600 python bench.py --no-extras > gpurun_out/${tag}_bench_hybrid.json 2> gpurun_out/${tag}_bench_hybrid.err; echo "bench rc=$?"; tail -3 gpurun_out/${tag}_bench_hybrid.err
-python - <<PY
-import json
-try:
-    d=json.loads(open('gpurun_out/${tag}_bench_hybrid.json').read().strip().splitlines()[-1]); r=d['roofline']
-    sh=r['kernel_time_share']; ms=d['ms_per_step']
-    print('hybrid evals/s %.0f ms %.1f e2e %.0f clk %s logit_ms %.2f lstm_ms %.2f frac %.3f shares %s hyb %s'%(d['value'],ms,d['e2e']['value'],d['clocks']['sm_mhz'],r['avg_launch_ms'],sh['lstm']*ms/17,r['frac'],{k:round(v,3) for k,v in sh.items()}, d['hybrid_stats']))
-except Exception as e: print('failed',e)
-PY
+python tools/show_bench.py gpurun_out/${tag}_bench_hybrid.json hybrid
