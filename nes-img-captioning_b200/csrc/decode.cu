@@ -577,7 +577,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     get_map(ws, &p.a_hi[1], ws->h_hi[hb], a_rows_w, R, 128, bk) || get_map(ws, &p.a_lo[1], ws->h_lo[hb], a_rows_w, R, 128, bk) ||
                     get_map(ws, &p.b_hi[0], ws->wl_hi[0], b_rows_all, E, kLstmTileCols, bk) || get_map(ws, &p.b_lo[0], ws->wl_lo[0], b_rows_all, E, kLstmTileCols, bk) ||
                     get_map(ws, &p.b_hi[1], ws->wl_hi[1], b_rows_all, R, kLstmTileCols, bk) || get_map(ws, &p.b_lo[1], ws->wl_lo[1], b_rows_all, R, kLstmTileCols, bk)) return 1;
-                p.K[0] = E; p.K[1] = R; p.nseg = 2;
+                p.K[0] = E; p.K[1] = R; p.nseg = t == 0 ? 1 : 2;      // t = 0: h = 0, the h2h product vanishes (its bias is in wl_bias)
                 p.rows = rows; p.rows_pad = rows_pad; p.m_tiles = m_tiles; p.n_tiles = ws->ntl; p.N = R;
                 p.b_rows = ws->ntl * kLstmTileCols; p.bias = ws->wl_bias; p.bias_stride = ws->ntl * kLstmTileCols;
                 p.c_state = ws->c_state; p.out_hi = ws->h_hi[hb ^ 1]; p.out_lo = ws->h_lo[hb ^ 1]; p.h_trace = ht;

@@ -185,6 +185,32 @@ def test_es_parents_per_member_batches_and_waves(golden_mod):
     ctx.close()
 
 
+@pytest.mark.parametrize('V,E,R,Fd,B', [(333, 64, 64, 128, 200), (700, 128, 192, 64, 37), (520, 64, 320, 128, 130)])
+@pytest.mark.parametrize('prec', [1, 2], ids=['exact', 'hybrid'])
+def test_ragged_shapes_against_oracle(V, E, R, Fd, B, prec):
+    """more rows than one 128-row block (config 4 runs 512), ragged last block, rnn sizes whose last 48-unit LSTM tile
+    is partly padding, vocabulary sizes that end inside a 256-column tile, E != R"""
+    import nes_b200
+    dims = fc_caption.Dims(V, E, R, Fd)
+    G = noise.granularity(E, R, Fd)
+    play, D, D_pad = noise.padded_layout(dims.layout(), G)
+    L = D_pad + 15 * G
+    ctx = nes_b200.NesContext(dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd), seed=77, table_len=L, wave_members=2, rows=B)
+    theta = fc_caption.xavier_theta(dims, 5)
+    ctx.set_theta(theta)
+    fc = noise.table_slice(9, 0, B * Fd).astype(np.float32).reshape(B, Fd)
+    offs = ctx.sample_offsets(1, 2).numpy()
+    offs3 = np.array([offs[0], offs[0], offs[1]], dtype=np.int64)
+    signs = np.array([1.0, -1.0, 1.0], dtype=np.float32)
+    seq, lp = ctx.rollout(offs3, signs, fc, 0.02, precision=prec)          # 3 members, wave of 2
+    for i in range(3):
+        th, _ = noise.member_theta(theta, noise.noise_row(77, offs3[i], play, D), 0.02, int(signs[i]))
+        s, l = fc_caption.decode_greedy(dims, th, fc)
+        assert np.array_equal(seq[i].numpy(), s), 'member %d: %d tokens differ' % (i, (seq[i].numpy() != s).sum())
+        assert np.allclose(lp[i].numpy(), l, rtol=1e-4, atol=1e-5)
+    ctx.close()
+
+
 def test_rollout_rejects_bad_arguments():
     import nes_b200
     mo = dict(vocab_size=63, input_encoding_size=64, rnn_size=64, fc_feat_size=64)
