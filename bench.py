@@ -376,6 +376,28 @@ def extras(ctx, nes_b200, torch, dev, peaks):
         ctx.opt_update(None, 1e-7, want_ratio=False)
     e1.record(); torch.cuda.synchronize()
     ex['k8_adam_ms'] = e0.elapsed_time(e1) / 5
+    # second half of BASELINE.json's metric: one NIC-NES iteration (nic_nes_master.py:120-137 + nic_nes_worker.py:131-154):
+    # sample offsets -> F antithetic pairs = 2F rollouts on the shared batch -> fitness -> centred ranks -> K7 -> L2 + Adam
+    Fp = min(500, ctx.n_slots if hasattr(ctx, 'n_slots') else 500)
+    g = torch.Generator().manual_seed(1)
+    fc = torch.randn(128, FD, generator=g).to(dev)
+    signs = torch.tensor([1.0, -1.0], dtype=torch.float32, device=dev).repeat(Fp)
+    prec = nes_b200.PREC_HYBRID
+
+    def nes_iter(it):
+        offs = ctx.sample_offsets(it, Fp, device=True)
+        ctx.rollout(offs.repeat_interleave(2), signs, fc, 0.01, precision=prec, out_device=dev)
+        fit = ctx.logprob_fitness(2 * Fp, 128, device=dev).reshape(Fp, 2)
+        ctx.master_step(fit, offs, 0.01, 1e-7, want_ratio=False)
+    for i in range(2):
+        nes_iter(100 + i)
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(3):
+        nes_iter(200 + i)
+    e1.record(); torch.cuda.synchronize()
+    ex['nes_iteration'] = {'pairs': Fp, 'rollouts': 2 * Fp, 'rows': 128, 'optimizer': 'adam', 'precision': 'hybrid',
+                           'ms': e0.elapsed_time(e1) / 3, 'rollouts_per_s': 2 * Fp * 3 / (e0.elapsed_time(e1) * 1e-3)}
     return ex
 
 
