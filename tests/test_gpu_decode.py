@@ -211,6 +211,62 @@ def test_ragged_shapes_against_oracle(V, E, R, Fd, B, prec):
     ctx.close()
 
 
+@pytest.mark.parametrize('prec', [1, 2], ids=['exact', 'hybrid'])
+def test_more_units_than_sms_against_oracle(prec):
+    """450 members > 2 x 148 SMs: every persistent CTA walks several units (resident x block re-loaded behind the last
+    tile, accumulator / stage phases wrapping), two waves of 256; every member checked against the oracle"""
+    import nes_b200
+    V, E, R, Fd, B, P = 299, 64, 64, 64, 4, 450
+    dims = fc_caption.Dims(V, E, R, Fd)
+    G = noise.granularity(E, R, Fd)
+    play, D, D_pad = noise.padded_layout(dims.layout(), G)
+    L = D_pad + 1023 * G
+    ctx = nes_b200.NesContext(dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd), seed=5, table_len=L, n_parents=3, wave_members=256, rows=B)
+    thetas = [fc_caption.xavier_theta(dims, 40 + k) for k in range(3)]
+    for k in range(3):
+        ctx.set_theta(thetas[k], k)
+    fc = noise.table_slice(3, 0, B * Fd).astype(np.float32).reshape(B, Fd)
+    offs = ctx.sample_offsets(2, P).numpy()
+    parents = ctx.sample_parents(2, P, 3).numpy()
+    signs = np.where(np.arange(P) % 2 == 0, 1.0, -1.0).astype(np.float32)
+    seq, lp = ctx.rollout(offs, signs, fc, 0.03, parents=parents, precision=prec)
+    bad = 0
+    for i in range(P):
+        th, _ = noise.member_theta(thetas[parents[i]], noise.noise_row(5, offs[i], play, D), 0.03, int(signs[i]))
+        s, l = fc_caption.decode_greedy(dims, th, fc)
+        bad += int(not np.array_equal(seq[i].numpy(), s))
+        assert np.allclose(lp[i].numpy(), l, rtol=1e-4, atol=1e-5), i
+    assert bad == 0, '%d of %d members decode differently from the oracle' % (bad, P)
+    # determinism: the same call again gives the same bits
+    seq2, lp2 = ctx.rollout(offs, signs, fc, 0.03, parents=parents, precision=prec)
+    assert torch.equal(seq, seq2) and torch.equal(lp, lp2)
+    ctx.close()
+
+
+@pytest.mark.parametrize('rows', [128])
+def test_full_size_population_hybrid_equals_exact(rows):
+    """BASELINE.json configs[1] shapes (E = R = 512, V = 9487, 128 rows), 320 members over 10 parents: the HYBRID mode
+    the bench headlines must give the same token ids as the split-fp16 EXACT mode for every member, and the same
+    log-probs to float32 round-off (size-independent property; the oracle would need minutes at this size)"""
+    import nes_b200
+    mo = dict(vocab_size=9487, input_encoding_size=512, rnn_size=512, fc_feat_size=2048)
+    P, mu = 320, 10
+    ctx = nes_b200.NesContext(mo, seed=1234, table_len=1 << 26, n_parents=mu, wave_members=P, rows=rows)
+    nes_b200.FCModel(ctx, parent=0, rng_state=0)
+    for k in range(1, mu):
+        ctx.evolve(int(ctx.sample_offsets(999, mu)[k]), 0.01, 1.0, parent=0, dst_parent=k, want_member=False, want_noise=False)
+    fc = torch.randn(rows, 2048, generator=torch.Generator().manual_seed(0))
+    offs = ctx.sample_offsets(1, P)
+    parents = ctx.sample_parents(1, P, mu)
+    signs = torch.ones(P)
+    seq_h, lp_h = ctx.rollout(offs, signs, fc, 0.005, parents=parents, precision=nes_b200.PREC_HYBRID)
+    seq_e, lp_e = ctx.rollout(offs, signs, fc, 0.005, parents=parents, precision=nes_b200.PREC_EXACT)
+    assert torch.equal(seq_h, seq_e), '%d tokens differ' % int((seq_h != seq_e).sum())
+    assert torch.allclose(lp_h, lp_e, rtol=1e-4, atol=1e-5)
+    assert len(torch.unique(seq_h[:, :, 0])) > 1                      # not a degenerate decode
+    ctx.close()
+
+
 def test_rollout_rejects_bad_arguments():
     import nes_b200
     mo = dict(vocab_size=63, input_encoding_size=64, rnn_size=64, fc_feat_size=64)
