@@ -147,6 +147,22 @@ int nes_profile_read(nes_ctx* ctx, float* ms_by_kind, int32_t* count_by_kind);
  * rows whose candidate list overflowed (their unit took the split-fp16 fallback), 0}. */
 int nes_hybrid_stats(nes_ctx* ctx, int64_t* out4, int reset);
 
+/* CIDEr-D reward of decoded captions.  Replaces the per-rollout Python scorer call of
+ * CaptPolicy.compute_ciders (src/captioning/policies.py:145-193 -> cider/pyciderevalcap/ciderD/ciderD_scorer.py:120-213).
+ * nes_cider_set_tables uploads what depends only on the batch (prepared by the host in the reference's float64 operation
+ * order, nes-img-captioning_b200/cider.py): idf[ngram] = ref_len - log(max(1, df)) for the n-grams with df > 1 (packed keys:
+ * n | t0<<3 | t1<<18 | t2<<33 | t3<<48, tokens < 32768; absent n-grams take idf_default), and per image its reference
+ * captions as CSR lists of (key, tf*idf) in dict order with their four norms and length; penalty[d + 64] =
+ * e**(-(d*d)/(2 sigma^2)) for d = len(hyp) - len(ref).  All pointers host memory.
+ * nes_cider_scores scores n_members x rows captions (seq int64 [n_members, rows, T] host or device; NULL = the tokens of
+ * the last nes_rollout, resident on the device); row r is scored against image r / rows_per_img; scores float64
+ * [n_members, rows] = the per-caption `scores` array of CiderD.compute_score, bit-identical. */
+int nes_cider_set_tables(nes_ctx* ctx, const uint64_t* idf_keys, const double* idf_vals, int64_t n_idf, double idf_default,
+                         const int32_t* img_ref_ptr, int32_t n_img, const int32_t* ref_ent_ptr, int32_t n_refs,
+                         const uint64_t* ent_key, const double* ent_w, const double* ref_norm, const int32_t* ref_len,
+                         const double* penalty);
+int nes_cider_scores(nes_ctx* ctx, const int64_t* seq, int64_t n_members, int rows, int T, int rows_per_img, double* scores);
+
 /* standalone tensor-core self test through the same tcgen05/TMA kernel the decode uses:
  * C[M,N] = A[M,K] W[N,K]^T + sigma * A[M,K] f16(E[N,K])^T, float32 in/out (host or device pointers). */
 int nes_gemm_selftest(int device, int M, int N, int K, const float* A, const float* W, const float* E,

@@ -6,8 +6,9 @@ from ._lib import NesError
 from .context import NesContext, PREC_EXACT, PREC_FAST, PREC_HYBRID, OPT_ADAM, OPT_SGD, gemm_selftest
 from .nets import FCModel, ModelOptions, Mutation, PolicyNet
 from .policies import CaptPolicy, Net, Policy, PolicyFactory, PolicyOptions, SuppDataset
+from .cider import CiderD
 from .master import (Adam, NESMaster, Optimizer, SGD, all_gather_fitness, nes_iteration, shard_bounds)
 
 __all__ = ['NesContext', 'NesError', 'FCModel', 'ModelOptions', 'Mutation', 'PolicyNet', 'CaptPolicy', 'Net', 'Policy',
            'PolicyFactory', 'PolicyOptions', 'SuppDataset', 'Adam', 'SGD', 'Optimizer', 'NESMaster', 'nes_iteration',
-           'shard_bounds', 'all_gather_fitness', 'PREC_EXACT', 'PREC_FAST', 'PREC_HYBRID', 'OPT_ADAM', 'OPT_SGD', 'gemm_selftest']
+           'shard_bounds', 'all_gather_fitness', 'CiderD', 'PREC_EXACT', 'PREC_FAST', 'PREC_HYBRID', 'OPT_ADAM', 'OPT_SGD', 'gemm_selftest']

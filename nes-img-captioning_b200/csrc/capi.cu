@@ -141,6 +141,7 @@ int nes_ctx_destroy(nes_ctx* ctx) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     decode_destroy(c);
+    cider_destroy(c);
     void* ptrs[] = {c->table, c->theta64, c->theta32, c->theta_hi, c->theta_lo, c->grad, c->opt_m, c->opt_v, c->d_lay, c->d_norm_partials,
                     c->d_norms, c->d_G64, c->d_theta_rowmax, c->d_eps_rowmax, c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks};
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -273,6 +274,19 @@ int nes_logprob_fitness(nes_ctx* ctx, int64_t n_members, int rows, double* out) 
     NES_CHECK(out, "null output");
     if (decode_logprob_fitness(c, n_members, rows, out)) return 1;
     return finish_output(c, out);
+}
+
+int nes_cider_set_tables(nes_ctx* ctx, const uint64_t* idf_keys, const double* idf_vals, int64_t n_idf, double idf_default,
+                         const int32_t* img_ref_ptr, int32_t n_img, const int32_t* ref_ent_ptr, int32_t n_refs,
+                         const uint64_t* ent_key, const double* ent_w, const double* ref_norm, const int32_t* ref_len, const double* penalty) {
+    NEED_CTX(ctx);
+    return cider_set_tables(CTX(ctx), idf_keys, idf_vals, n_idf, idf_default, img_ref_ptr, n_img, ref_ent_ptr, n_refs, ent_key, ent_w, ref_norm, ref_len, penalty);
+}
+
+int nes_cider_scores(nes_ctx* ctx, const int64_t* seq, int64_t n_members, int rows, int T, int rows_per_img, double* scores) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    if (cider_scores(c, seq, n_members, rows, T, rows_per_img, scores)) return 1;
+    return finish_output(c, scores);
 }
 
 int nes_compute_ranks(nes_ctx* ctx, const double* x, int64_t n, int64_t* ranks) {

@@ -45,6 +45,7 @@ constexpr float kActScale   = 32.0f;      // x_hi + x_lo = x * 2^5
 
 // ---------------------------------------------------------------------------------------------
 struct DecodeWorkspace;   // decode.cu
+struct CiderTables;       // cider.cu
 
 struct Ctx {
     int device = 0;
@@ -93,6 +94,7 @@ struct Ctx {
     std::vector<ProfRec> prof_pool;        // recycled events
 
     DecodeWorkspace* ws = nullptr;
+    CiderTables* cider = nullptr;
 };
 enum { PROF_PLAIN = 0, PROF_LSTM = 1, PROF_LOGIT = 2, PROF_FINALIZE = 3, PROF_FALLBACK = 4, PROF_MATERIALISE = 5, PROF_KINDS = 6 };
 struct ProfScope {                          // RAII: record an event pair around one launch when profiling is on
@@ -134,6 +136,14 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                    const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace);
 int decode_logprob_fitness(Ctx* c, int64_t n_members, int rows, double* out);
 int decode_hybrid_stats(Ctx* c, int64_t* out4, int reset);
+const int64_t* decode_resident_seq(Ctx* c, int64_t n_members, int rows, int* T);   // device seq of the last rollout (nullptr if not resident)
+
+// cider.cu
+int cider_set_tables(Ctx* c, const uint64_t* idf_keys, const double* idf_vals, int64_t n_idf, double idf_default,
+                     const int32_t* img_ref_ptr, int32_t n_img, const int32_t* ref_ent_ptr, int32_t n_refs,
+                     const uint64_t* ent_key, const double* ent_w, const double* ref_norm, const int32_t* ref_len, const double* penalty);
+int cider_scores(Ctx* c, const int64_t* seq, int64_t n_members, int rows, int T, int rows_per_img, double* scores);
+void cider_destroy(Ctx* c);
 
 }  // namespace nes
 

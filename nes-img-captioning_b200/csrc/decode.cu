@@ -700,6 +700,13 @@ int decode_hybrid_stats(Ctx* c, int64_t* out4, int reset) {
     return 0;
 }
 
+const int64_t* decode_resident_seq(Ctx* c, int64_t n_members, int rows, int* T) {
+    DecodeWorkspace* ws = c->ws;
+    if (!ws || !ws->d_seq || n_members * rows * ws->T > ws->out_cap) return nullptr;
+    *T = ws->T;
+    return ws->d_seq;
+}
+
 int decode_logprob_fitness(Ctx* c, int64_t n_members, int rows, double* out) {
     DecodeWorkspace* ws = c->ws;
     NES_CHECK(ws && ws->d_lp && n_members * rows * ws->T <= ws->out_cap, "no rollout results resident for that many members");

@@ -9,6 +9,7 @@ from enum import Enum
 import numpy as np
 import torch
 
+from .cider import CiderD
 from .context import NesContext, PREC_EXACT
 from .nets import FCModel, ModelOptions, PolicyNet
 
@@ -131,9 +132,25 @@ class CaptPolicy(Policy):
         return seq, lp
 
     def rollout(self, placeholder, data, config):
-        assert self.scorer is not None, 'CaptPolicy.rollout needs a scorer callable (CIDEr-D is off the CUDA path)'
+        """fitness of this individual on the batch (captioning/policies.py:86-128, `greedy` fitness = CIDEr-D * 100).
+        scorer = nes_b200.CiderD(ctx, ...): scored on the device from the resident tokens; any other callable
+        scorer(seq [rows, T] numpy, data) -> float runs on the host like the reference's."""
+        assert self.scorer is not None, 'CaptPolicy.rollout needs a scorer (nes_b200.CiderD or a callable)'
+        if isinstance(self.scorer, CiderD):
+            return float(self.rollout_population_fitness(np.zeros(1, dtype=np.int64), np.ones(1, dtype=np.float32), data, 0.0,
+                                                         parents=np.array([self.policy_net.parent], dtype=np.int32))[0])
         seq, _ = self.rollout_tokens(data)
         return float(self.scorer(seq.numpy(), data))
+
+    def rollout_population_fitness(self, offsets, signs, data, sigma, parents=None):
+        """CIDEr-D * 100 of every member (float64 numpy [P]): decode on the device, score the resident tokens on the device
+        against data['gts'] (list over images of int arrays [n_refs, T]); only P x rows float64 scores travel to the host."""
+        assert isinstance(self.scorer, CiderD), 'needs scorer = nes_b200.CiderD(ctx, ...)'
+        fc = torch.from_numpy(np.ascontiguousarray(self._unique_rows(data['fc_feats'])))
+        self.scorer.set_refs(data['gts'], seq_per_img=self.seq_per_img, rows_per_img=1)
+        P = len(offsets)
+        self.ctx.rollout(offsets, signs, fc, sigma, parents=parents, precision=self.precision, out_device=self.ctx.dev)
+        return self.scorer.fitness(P, fc.shape[0])
 
     def rollout_population(self, offsets, signs, data, sigma, parents=None, out_device='cpu'):
         """all members at once -> seq int64 [P, rows, T], logprobs float32 [P, rows, T] (unique rows)."""
