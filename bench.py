@@ -398,6 +398,33 @@ def extras(ctx, nes_b200, torch, dev, peaks):
     e1.record(); torch.cuda.synchronize()
     ex['nes_iteration'] = {'pairs': Fp, 'rollouts': 2 * Fp, 'rows': 128, 'optimizer': 'adam', 'precision': 'hybrid',
                            'ms': e0.elapsed_time(e1) / 3, 'rollouts_per_s': 2 * Fp * 3 / (e0.elapsed_time(e1) * 1e-3)}
+    # CIDEr-D reward of one generation's captions: 1000 members x 128 captions against 5 synthetic references per
+    # image, on the device from the resident tokens; the reference scores them one rollout at a time in Python
+    rs = np.random.RandomState(0)
+    gts = []
+    for i in range(128):
+        refs = np.zeros((5, T), dtype=np.int64)
+        for j in range(5):
+            ln = rs.randint(6, T)
+            refs[j, :ln] = rs.randint(1, V + 1, ln)
+        gts.append(refs)
+    sc = nes_b200.CiderD(ctx, df='corpus').set_refs(gts, seq_per_img=5)
+    n_m = 2 * Fp
+    sc.scores(None, n_m, 128, device=dev)
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(3):
+        sc.scores(None, n_m, 128, device=dev)
+    e1.record(); torch.cuda.synchronize()
+    ms_c = e0.elapsed_time(e1) / 3
+    from oracle import cider as ocider
+    seq_host = rs.randint(0, V + 1, (128, T))
+    t0 = time.perf_counter()
+    for i in range(3):
+        ocider.cider_scores(seq_host, gts)
+    cpu_s = (time.perf_counter() - t0) / 3
+    ex['cider_d'] = {'captions': n_m * 128, 'ms': ms_c, 'captions_per_s': n_m * 128 / (ms_c * 1e-3),
+                     'cpu_port_captions_per_s_one_core': 128 / cpu_s, 'refs_per_image': 5}
     return ex
 
 

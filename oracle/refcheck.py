@@ -75,6 +75,20 @@ def check_optimizers(ref, D=513, steps=5, seed=0):
     return True
 
 
+def check_cider(seed=0):
+    """oracle/cider.py against the real pyciderevalcap scorer fed like CaptPolicy.compute_ciders (captioning/policies.py:145-193)"""
+    import os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tests', 'golden'))
+    import make_golden_cider as mg
+    from . import cider
+    for c in mg.CASES.values():
+        seq, gts = mg.case_inputs(c)
+        score_r, scores_r = mg.reference_scores(seq, gts, c['spi'])
+        score_o, scores_o = cider.cider_scores(seq, gts, c['spi'])
+        assert score_r == score_o and np.array_equal(scores_r, scores_o)
+    return True
+
+
 def main():
     if not _refimport.available():
         print('reference not present; nothing checked'); return 1
@@ -89,8 +103,8 @@ def main():
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)
     assert fc_caption.Dims(9487, 128, 128, 2048).num_params() == 2865808
     assert fc_caption.Dims(9487, 512, 512, 2048).num_params() == 13400848
-    check_master_math(ref); check_optimizers(ref)
-    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers OK' % n)
+    check_master_math(ref); check_optimizers(ref); check_cider()
+    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D OK' % n)
     return 0
 
 
