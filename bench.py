@@ -189,26 +189,13 @@ def main():
     state = {'base': 0, 'it': 0}
 
     def sample_generation(it):
-        """(offset, parent) of every offspring of generation `it`, grouped by parent: members of one parent are
-        adjacent, so their CTAs hit the same theta tiles in L2 (the order of offspring carries no meaning in ES)"""
-        offs = ctx.sample_offsets(it, Pg, device=True)
-        pars = ctx.sample_parents(it, Pg, mu, device=True)
+        offs, pars = nes_b200.es_sample_generation(ctx, it, Pg, mu)
         if a.debug_same_offset:
             offs = offs[:1].expand(Pg).contiguous()
-        pars, perm = torch.sort(pars, stable=True)
-        return offs[perm].contiguous(), pars.contiguous()
+        return offs, pars
 
     def select_and_materialise(fit_all, offs, pars):
-        ranks = ctx.compute_ranks(fit_all, device=True)
-        keep = torch.nonzero(ranks >= Pg - (mu - el)).flatten()
-        order = keep[torch.argsort(ranks[keep], descending=True)]
-        sel = torch.stack([order, offs[order], pars[order].to(torch.int64)], 1).cpu().numpy()      # the master's sync point
-        cur, nxt = state['base'], mu - state['base']
-        for e in range(el):       # elites carried over unchanged
-            ctx.evolve(0, 0.0, 1.0, parent=cur + e, dst_parent=nxt + e, want_member=False, want_noise=False)
-        for j, (m, off, par) in enumerate(sel):
-            ctx.evolve(int(off), a.sigma, 1.0, parent=cur + int(par), dst_parent=nxt + el + j, want_member=False, want_noise=False)
-        state['base'] = nxt
+        state['base'] = nes_b200.es_select_and_materialise(ctx, fit_all, offs, pars, mu, el, state['base'], a.sigma)
 
     def step_resident():
         it = state['it']; state['it'] += 1

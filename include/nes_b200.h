@@ -163,6 +163,16 @@ int nes_cider_set_tables(nes_ctx* ctx, const uint64_t* idf_keys, const double* i
                          const double* penalty);
 int nes_cider_scores(nes_ctx* ctx, const int64_t* seq, int64_t n_members, int rows, int T, int rows_per_img, double* scores);
 
+/* Log-prob-shaped fitness criteria on the resident rollout results (src/captioning/fitness.py:43-132 called at
+ * src/captioning/policies.py:119-123): out[m] = sum f(logprob) * reward * mask / sum mask over the member's rows x T.
+ * scores float64 [n_members, rows] = per-caption CIDEr-D (host or device; NULL = the result of the last nes_cider_scores). */
+enum { NES_FIT_SC_LOSS = 0,          /* LogFitnessCriterion     -logprob                                  */
+       NES_FIT_GREEDY_LOGPROB = 1,   /* AltLogFitnessCriterion  log10(p + 1/9) + log10(9)                 */
+       NES_FIT_GREEDY_AVGPROB = 2,   /* AvgLogFitnessCriterion  0.5 + 0.5 * (log10(p + 1/9) + log10(9))   */
+       NES_FIT_GREEDY_EXPPROB = 3,   /* ExpFitnessCriterion     (exp(p) - 1) / (e - 1)                    */
+       NES_FIT_GREEDY_LINPROB = 4 }; /* LinFitnessCriterion     p                                         */
+int nes_shaped_fitness(nes_ctx* ctx, int kind, int64_t n_members, int rows, const double* scores, double* out);
+
 /* standalone tensor-core self test through the same tcgen05/TMA kernel the decode uses:
  * C[M,N] = A[M,K] W[N,K]^T + sigma * A[M,K] f16(E[N,K])^T, float32 in/out (host or device pointers). */
 int nes_gemm_selftest(int device, int M, int N, int K, const float* A, const float* W, const float* E,

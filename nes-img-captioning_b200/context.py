@@ -164,6 +164,19 @@ class NesContext:
         _lib.check(self.lib.nes_logprob_fitness(self._h, int(n_members), int(rows), _lib.ptr(out)))
         return out
 
+    FITNESS_KINDS = {'sc_loss': 0, 'greedy_logprob': 1, 'greedy_avgprob': 2, 'greedy_expprob': 3, 'greedy_linprob': 4}
+
+    def shaped_fitness(self, kind, n_members, rows, scores=None, device='cpu'):
+        """log-prob-shaped fitness (src/captioning/fitness.py) of the resident rollout: kind = the reference's Fitness value
+        ('greedy_logprob', 'greedy_expprob', 'greedy_linprob', 'greedy_avgprob', 'sc_loss'); scores float64 [n_members, rows]
+        per-caption CIDEr-D or None = the last CiderD.scores result still on the device.  -> float64 [n_members]"""
+        if scores is not None:
+            scores = torch.as_tensor(scores, dtype=torch.float64).contiguous()
+            assert scores.numel() == int(n_members) * int(rows)
+        out = torch.empty(int(n_members), dtype=torch.float64, device=device)
+        _lib.check(self.lib.nes_shaped_fitness(self._h, int(self.FITNESS_KINDS[kind]), int(n_members), int(rows), _lib.ptr(scores), _lib.ptr(out)))
+        return out
+
     # ---- master math
     def compute_ranks(self, x, device=False):
         x = torch.as_tensor(np.asarray(x, dtype=np.float64)).contiguous() if not torch.is_tensor(x) else x.to(torch.float64).contiguous()

@@ -289,6 +289,12 @@ int nes_cider_scores(nes_ctx* ctx, const int64_t* seq, int64_t n_members, int ro
     return finish_output(c, scores);
 }
 
+int nes_shaped_fitness(nes_ctx* ctx, int kind, int64_t n_members, int rows, const double* scores, double* out) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    if (cider_shaped_fitness(c, kind, n_members, rows, scores, out)) return 1;
+    return finish_output(c, out);
+}
+
 int nes_compute_ranks(nes_ctx* ctx, const double* x, int64_t n, int64_t* ranks) {
     NEED_CTX(ctx); Ctx* c = CTX(ctx);
     NES_CHECK(n >= 0 && (n == 0 || (x && ranks)), "bad arguments");

@@ -147,6 +147,78 @@ __global__ void __launch_bounds__(128) k_cider(const CiderParams p) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// log-prob-shaped fitness criteria (src/captioning/fitness.py:43-132 as called at captioning/policies.py:119-123):
+//   out = sum_{r,t} f(logprob[r,t]) * reward[r] * mask[r,t] / sum mask,   mask[r,0] = 1, mask[r,t] = seq[r,t-1] > 0
+// element values in float32 like the reference's torch ops, the sum in float64 (the reference sums in float32: results agree
+// to float32 round-off, tested at 1e-5 relative).  One block per member.
+__global__ void __launch_bounds__(256) k_shaped_fitness(int kind, const float* __restrict__ lp, const int64_t* __restrict__ seq,
+                                                        const double* __restrict__ scores, int rows, int T, double* __restrict__ out) {
+    __shared__ double sh[2][8];
+    const int64_t m = blockIdx.x;
+    const float* l = lp + m * rows * T;
+    const int64_t* s = seq + m * rows * T;
+    const float log10_9 = (float)0.95424250943932487;               // np.log10(10 - 1) added to a float32 tensor
+    double acc = 0.0, msum = 0.0;
+    for (int i = threadIdx.x; i < rows * T; i += 256) {
+        const int r = i / T, t = i - r * T;
+        const float mask = (t == 0 || s[i - 1] > 0) ? 1.f : 0.f;
+        const float reward = (float)scores[m * rows + r];
+        const float x = l[i];
+        float v;
+        if (kind == NES_FIT_SC_LOSS) v = __fmul_rn(__fmul_rn(-x, reward), mask);
+        else if (kind == NES_FIT_GREEDY_LOGPROB || kind == NES_FIT_GREEDY_AVGPROB) {
+            const float pf = __fadd_rn(log10f(__fadd_rn(expf(x), (float)(1.0 / 9.0))), log10_9);
+            if (kind == NES_FIT_GREEDY_LOGPROB) v = __fmul_rn(__fmul_rn(pf, reward), mask);
+            else v = __fadd_rn(__fmul_rn(__fmul_rn(0.5f, reward), mask), __fmul_rn(__fmul_rn(__fmul_rn(0.5f, pf), reward), mask));
+        } else if (kind == NES_FIT_GREEDY_EXPPROB) v = __fmul_rn(__fmul_rn(__fdiv_rn(__fsub_rn(expf(expf(x)), 1.f), (float)(2.718281828459045 - 1.0)), reward), mask);
+        else v = __fmul_rn(__fmul_rn(expf(x), reward), mask);          // NES_FIT_GREEDY_LINPROB
+        acc += (double)v; msum += (double)mask;
+    }
+    for (int o = 16; o > 0; o >>= 1) { acc += __shfl_xor_sync(0xffffffffu, acc, o); msum += __shfl_xor_sync(0xffffffffu, msum, o); }
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = acc; sh[1][threadIdx.x >> 5] = msum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0, b = 0;
+        for (int q = 0; q < 8; ++q) { a += sh[0][q]; b += sh[1][q]; }
+        out[m] = (double)((float)a / (float)b);
+    }
+}
+
+int cider_shaped_fitness(Ctx* c, int kind, int64_t n_members, int rows, const double* scores, double* out) {
+    CiderTables* t = c->cider;
+    NES_CHECK(kind >= NES_FIT_SC_LOSS && kind <= NES_FIT_GREEDY_LINPROB, "unknown fitness kind");
+    NES_CHECK(n_members >= 0 && out, "bad arguments");
+    if (n_members == 0) return 0;
+    int T = 0;
+    const int64_t* d_seq = decode_resident_seq(c, n_members, rows, &T);
+    const float* d_lp = decode_resident_logprobs(c, n_members, rows);
+    NES_CHECK(d_seq && d_lp, "no rollout results resident for that many members");
+    const double* d_scores = nullptr;
+    double* tmp = nullptr;
+    if (scores) {
+        cudaPointerAttributes at{};
+        const bool on_dev = cudaPointerGetAttributes(&at, scores) == cudaSuccess && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
+        cudaGetLastError();
+        if (on_dev) d_scores = scores;
+        else {
+            NES_CUDA(cudaMallocAsync((void**)&tmp, sizeof(double) * n_members * rows, c->stream));
+            NES_CUDA(cudaMemcpyAsync(tmp, scores, sizeof(double) * n_members * rows, cudaMemcpyDefault, c->stream));
+            d_scores = tmp;
+        }
+    } else {
+        NES_CHECK(t && t->d_scores && t->scores_cap >= n_members * rows, "no CIDEr-D scores resident: call nes_cider_scores first or pass scores");
+        d_scores = t->d_scores;
+    }
+    if (ensure_small(c, n_members)) return 1;
+    k_shaped_fitness<<<(unsigned)n_members, 256, 0, c->stream>>>(kind, d_lp, d_seq, d_scores, rows, T, c->d_fitness);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    if (tmp) NES_CUDA(cudaFreeAsync(tmp, c->stream));
+    NES_CUDA(cudaMemcpyAsync(out, c->d_fitness, sizeof(double) * n_members, cudaMemcpyDefault, c->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 static void cider_free(CiderTables* t) {
     void* ptrs[] = {t->idf_keys, t->idf_vals, t->img_ref_ptr, t->ref_ent_ptr, t->ent_key, t->ent_w, t->ref_norm, t->ref_len, t->penalty};
     for (void* q : ptrs) if (q) cudaFree(q);

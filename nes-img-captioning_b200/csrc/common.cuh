@@ -136,7 +136,8 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                    const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace);
 int decode_logprob_fitness(Ctx* c, int64_t n_members, int rows, double* out);
 int decode_hybrid_stats(Ctx* c, int64_t* out4, int reset);
-const int64_t* decode_resident_seq(Ctx* c, int64_t n_members, int rows, int* T);   // device seq of the last rollout (nullptr if not resident)
+const int64_t* decode_resident_seq(Ctx* c, int64_t n_members, int rows, int* T);
+const float* decode_resident_logprobs(Ctx* c, int64_t n_members, int rows);   // device seq of the last rollout (nullptr if not resident)
 
 // cider.cu
 int cider_set_tables(Ctx* c, const uint64_t* idf_keys, const double* idf_vals, int64_t n_idf, double idf_default,
@@ -144,6 +145,7 @@ int cider_set_tables(Ctx* c, const uint64_t* idf_keys, const double* idf_vals, i
                      const uint64_t* ent_key, const double* ent_w, const double* ref_norm, const int32_t* ref_len, const double* penalty);
 int cider_scores(Ctx* c, const int64_t* seq, int64_t n_members, int rows, int T, int rows_per_img, double* scores);
 void cider_destroy(Ctx* c);
+int cider_shaped_fitness(Ctx* c, int kind, int64_t n_members, int rows, const double* scores, double* out);
 
 }  // namespace nes
 

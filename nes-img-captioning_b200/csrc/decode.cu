@@ -707,6 +707,12 @@ const int64_t* decode_resident_seq(Ctx* c, int64_t n_members, int rows, int* T) 
     return ws->d_seq;
 }
 
+const float* decode_resident_logprobs(Ctx* c, int64_t n_members, int rows) {
+    DecodeWorkspace* ws = c->ws;
+    if (!ws || !ws->d_lp || n_members * rows * ws->T > ws->out_cap) return nullptr;
+    return ws->d_lp;
+}
+
 int decode_logprob_fitness(Ctx* c, int64_t n_members, int rows, double* out) {
     DecodeWorkspace* ws = c->ws;
     NES_CHECK(ws && ws->d_lp && n_members * rows * ws->T <= ws->out_cap, "no rollout results resident for that many members");

@@ -152,3 +152,63 @@ def nes_iteration(ctx: NesContext, optimizer: Optimizer, iteration, F, fc, sigma
     ratio = ctx.master_step(fit, offsets, sigma, l2coeff)
     optimizer.t += 1
     return ratio, fit
+
+
+# ---------------------------------------------------------------------------------------------
+# NIC-ES generation (ESWorker.fitness nic_es_worker.py:142-192 + ESMaster.selection nic_es_master.py:155-167), in process
+class ESMaster:
+    """Only the math of the reference's ESMaster."""
+
+    @staticmethod
+    def selection(fitness, pop_size, num_elites):
+        """indices of the pop_size - num_elites best offspring, best first, and all scores sorted descending
+        (nic_es_master.py:155-167: Python's stable sort with reverse=True, so equal fitnesses keep their submission order).
+        fitness: torch float64 [n] (any device) or array-like.  Returns (LongTensor indices, sorted scores) on fitness's device."""
+        fit = fitness if torch.is_tensor(fitness) else torch.as_tensor(np.asarray(fitness, dtype=np.float64))
+        order = torch.sort(-fit.to(torch.float64), stable=True).indices
+        return order[:max(0, int(pop_size) - int(num_elites))], fit[order]
+
+
+def es_sample_generation(ctx: NesContext, iteration, n_offspring, mu):
+    """(offset, parent) of every offspring of a generation, identical on every rank (shared seed), grouped by parent: members
+    of one parent are adjacent so that their CTAs hit the same theta tiles in L2 (offspring order carries no meaning in ES)."""
+    offs = ctx.sample_offsets(iteration, n_offspring, device=True)
+    pars = ctx.sample_parents(iteration, n_offspring, mu, device=True)
+    pars, perm = torch.sort(pars, stable=True)
+    return offs[perm].contiguous(), pars.contiguous()
+
+
+def es_select_and_materialise(ctx: NesContext, fitness_all, offs, pars, mu, num_elites, base, sigma):
+    """truncation selection on the gathered fitnesses, then the next generation's parents are written into the other half of
+    the context's 2*mu parent slots: the first num_elites parents carried over unchanged, then the selected offspring
+    re-derived from (parent, offset) -- no weights ever leave the device.  Returns the new base slot."""
+    keep, _ = ESMaster.selection(fitness_all, mu, num_elites)
+    sel = torch.stack([keep, offs[keep], pars[keep].to(torch.int64)], 1).cpu().numpy()      # the master's one sync point
+    nxt = mu - base
+    for e in range(num_elites):
+        ctx.evolve(0, 0.0, 1.0, parent=base + e, dst_parent=nxt + e, want_member=False, want_noise=False)
+    for j, (_, off, par) in enumerate(sel):
+        ctx.evolve(int(off), sigma, 1.0, parent=base + int(par), dst_parent=nxt + num_elites + j, want_member=False, want_noise=False)
+    return nxt
+
+
+def es_generation(ctx: NesContext, iteration, n_local, mu, num_elites, fc, sigma, base=0, fitness_fn=None,
+                  world_size=1, rank=0, precision=PREC_EXACT, group=None):
+    """One NIC-ES generation on a context created with n_parents = 2*mu (current parents in slots [base, base+mu)).
+    Every rank evaluates n_local offspring of the n_local*world_size sampled; fitness_fn(seq, logprobs) -> float64 [n_local]
+    (None: sum of greedy log-probs, computed on the device).  Returns (new base, all fitnesses, offsets, parents)."""
+    assert ctx.n_parents >= 2 * mu and base in (0, mu)
+    n_all = n_local * world_size
+    offs, pars = es_sample_generation(ctx, iteration, n_all, mu)
+    lo = rank * n_local
+    ones = torch.ones(n_local, dtype=torch.float32, device=ctx.dev)
+    seq, lp = ctx.rollout(offs[lo:lo + n_local], ones, fc, sigma, parents=pars[lo:lo + n_local] + base, precision=precision, out_device=ctx.dev)
+    rows = seq.shape[1]
+    fit = ctx.logprob_fitness(n_local, rows, device=ctx.dev) if fitness_fn is None else torch.as_tensor(fitness_fn(seq, lp), dtype=torch.float64).to(ctx.dev)
+    if world_size > 1:
+        import torch.distributed as dist
+        out = torch.empty(n_all, dtype=torch.float64, device=ctx.dev)
+        dist.all_gather_into_tensor(out, fit.contiguous(), group=group)
+        fit = out
+    new_base = es_select_and_materialise(ctx, fit, offs, pars, mu, num_elites, base, sigma)
+    return new_base, fit, offs, pars

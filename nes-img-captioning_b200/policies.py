@@ -150,7 +150,12 @@ class CaptPolicy(Policy):
         self.scorer.set_refs(data['gts'], seq_per_img=self.seq_per_img, rows_per_img=1)
         P = len(offsets)
         self.ctx.rollout(offsets, signs, fc, sigma, parents=parents, precision=self.precision, out_device=self.ctx.dev)
-        return self.scorer.fitness(P, fc.shape[0])
+        kind = self.options.fitness or 'greedy'
+        if kind == 'greedy':
+            return self.scorer.fitness(P, fc.shape[0])                      # float(cider * 100), policies.py:125
+        assert kind in self.ctx.FITNESS_KINDS and kind != 'sc_loss', 'fitness %r needs sampled decode, which is not on the B200 path' % kind
+        self.scorer.scores(None, P, fc.shape[0], device=self.ctx.dev)       # per-caption CIDEr-D stays on the device
+        return self.ctx.shaped_fitness(kind, P, fc.shape[0]).numpy()        # crit(logprobs, seq, ciders), policies.py:119-123
 
     def rollout_population(self, offsets, signs, data, sigma, parents=None, out_device='cpu'):
         """all members at once -> seq int64 [P, rows, T], logprobs float32 [P, rows, T] (unique rows)."""

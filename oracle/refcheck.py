@@ -89,6 +89,28 @@ def check_cider(seed=0):
     return True
 
 
+def check_shaped_fitness(seed=0):
+    """oracle/fitness.py against the imported captioning.fitness criteria"""
+    from captioning import fitness as rf
+    from . import fitness as of
+    cls = {'greedy_logprob': rf.AltLogFitnessCriterion, 'greedy_expprob': rf.ExpFitnessCriterion, 'greedy_linprob': rf.LinFitnessCriterion,
+           'greedy_avgprob': rf.AvgLogFitnessCriterion, 'sc_loss': rf.LogFitnessCriterion}
+    rs = np.random.RandomState(seed)
+    rows, T = 40, 16
+    seq = rs.randint(0, 9, (rows, T))
+    for r in range(rows):
+        z = np.nonzero(seq[r] == 0)[0]
+        if len(z):
+            seq[r, z[0]:] = 0
+    lp = -np.abs(rs.randn(rows, T)).astype(np.float32) * 3
+    sc = np.abs(rs.randn(rows)) * 2
+    for k, c in cls.items():
+        ciders = np.repeat(sc[:, None], T, 1)
+        want = float(c()(torch.from_numpy(lp), torch.from_numpy(seq), torch.from_numpy(ciders.copy()).float()).item())
+        assert of.shaped_fitness(k, lp, seq, sc) == want, k
+    return True
+
+
 def main():
     if not _refimport.available():
         print('reference not present; nothing checked'); return 1
@@ -103,8 +125,8 @@ def main():
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)
     assert fc_caption.Dims(9487, 128, 128, 2048).num_params() == 2865808
     assert fc_caption.Dims(9487, 512, 512, 2048).num_params() == 13400848
-    check_master_math(ref); check_optimizers(ref); check_cider()
-    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D OK' % n)
+    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness()
+    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses OK' % n)
     return 0
 
 

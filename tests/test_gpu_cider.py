@@ -126,3 +126,26 @@ def test_capt_policy_rollout_with_device_scorer_equals_host_scorer():
     offs = pol.ctx.sample_offsets(1, 3).numpy()
     f3 = pol.rollout_population_fitness(np.repeat(offs, 2), np.tile(np.array([1.0, -1.0], dtype=np.float32), 3), data, 0.05)
     assert f3.shape == (6,) and np.isfinite(f3).all()
+
+
+@pytest.mark.parametrize('kind', ['greedy_logprob', 'greedy_expprob', 'greedy_linprob', 'greedy_avgprob', 'sc_loss'])
+def test_shaped_fitness_against_the_pinned_oracle(kind, ctx):
+    """src/captioning/fitness.py criteria on the resident log-probs / tokens with CIDEr-D rewards: device (float32 elements,
+    float64 sum) vs the oracle (the reference's torch float32 ops, bit-identical to the imported reference): 1e-5 relative"""
+    import nes_b200
+    from oracle import fitness as ofit
+    dims = fc_caption.Dims(199, 64, 64, 128)
+    ctx.set_theta(fc_caption.xavier_theta(dims, 2))
+    fc = noise.table_slice(12, 0, 8 * 128).astype(np.float32).reshape(8, 128)
+    offs = ctx.sample_offsets(5, 4).numpy()
+    seq, lp = ctx.rollout(offs, np.ones(4, dtype=np.float32), fc, 0.05, precision=nes_b200.PREC_HYBRID)
+    rs = np.random.RandomState(7)
+    gts = [np.concatenate([seq[rs.randint(4), i].numpy()[None], rs.randint(0, 199, (2, 16))]) for i in range(8)]
+    sc = nes_b200.CiderD(ctx, df='corpus').set_refs(gts)
+    scores = sc.scores(None, 4, 8).numpy()
+    got = ctx.shaped_fitness(kind, 4, 8).numpy()                            # rewards = the scores just computed, still resident
+    got2 = ctx.shaped_fitness(kind, 4, 8, scores=scores).numpy()            # rewards passed from the host
+    for m in range(4):
+        want = ofit.shaped_fitness(kind, lp[m].numpy(), seq[m].numpy(), scores[m])
+        assert abs(got[m] - want) <= 1e-5 * max(abs(want), 1e-3), (m, got[m], want)
+        assert got2[m] == got[m]

@@ -107,3 +107,16 @@ def test_fitness_all_gather_world_size_2_gloo(tmp_path):
              for r in range(2)]
     outs = [p.communicate(timeout=240)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
+
+
+def test_es_selection_is_the_references_stable_descending_sort():
+    """ESMaster.selection (nic_es_master.py:155-167): scored_models.sort(key=fitness, reverse=True) keeps equal fitnesses in
+    submission order; the top pop_size - num_elites become parents"""
+    import nes_b200
+    fit = [3.0, 7.0, 7.0, -1.0, 7.0, 5.0, 3.0]
+    want = sorted(range(len(fit)), key=lambda i: fit[i], reverse=True)        # Python's own stable reverse sort
+    keep, scores = nes_b200.ESMaster.selection(torch.tensor(fit, dtype=torch.float64), 6, 2)
+    assert keep.tolist() == want[:4] == [1, 2, 4, 5]
+    assert scores.tolist() == sorted(fit, reverse=True)
+    keep, _ = nes_b200.ESMaster.selection(np.array(fit), 3, 3)
+    assert keep.numel() == 0
