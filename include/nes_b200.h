@@ -90,6 +90,12 @@ int nes_get_theta(nes_ctx* ctx, int parent, void* out, int as_f64);
 int nes_evolve(nes_ctx* ctx, int parent, int64_t offset, float sign, float sigma,
                float* member_out, float* noise_out, int dst_parent);
 
+/* Safe mutations (PolicyNet.evolve, algorithm/nets.py:104-111).  NES_MUT_PROPORTIONAL (the reference's "SM-PROPORTIONAL", shipped in
+ * experiments/mscoco_es.json): noise = sigma * eps (.) |theta_p|, exact zeros of theta_p replaced by mean|theta_p|.  Applies to
+ * nes_evolve and nes_rollout (HYBRID precision, no layer_n); K7 scales its result by the scale of parent 0. */
+enum { NES_MUT_DEFAULT = 0, NES_MUT_PROPORTIONAL = 1 };
+int nes_set_mutation(nes_ctx* ctx, int kind);
+
 /* ---- population rollout (NESWorker.fitness nic_nes_worker.py:131-154 / ESWorker.fitness
  *      nic_es_worker.py:142-175 -> CaptPolicy.rollout captioning/policies.py:86-116 ->
  *      FCModel._sample(greedy) captioning/nets.py:183-245), CIDEr scoring excluded --------------- */

@@ -97,6 +97,17 @@ class NesContext:
         _lib.check(self.lib.nes_sample_parents(self._h, int(iteration), int(F), int(n_parents), _lib.ptr(out)))
         return out
 
+    # ---- safe mutations (src/algorithm/nets.py:104-111)
+    MUTATIONS = {'': 0, 'SM-PROPORTIONAL': 1}
+
+    def set_mutation(self, kind):
+        """'' (default) or 'SM-PROPORTIONAL' (noise scaled by |theta_p|, zeros by mean|theta_p|); the gradient-based safe
+        mutations (SM-G-SUM / SM-G-ABS) need autograd and are not on the B200 path"""
+        if kind not in self.MUTATIONS:
+            raise NotImplementedError('mutation %r is not on the B200 path (SURVEY 8f-3)' % (kind,))
+        _lib.check(self.lib.nes_set_mutation(self._h, self.MUTATIONS[kind]))
+        self.mutation = kind
+
     # ---- theta
     def set_theta(self, vector, parent=0):
         """vector: numpy / torch, float32 or float64, host or device, length D (asserted like

@@ -143,7 +143,7 @@ int nes_ctx_destroy(nes_ctx* ctx) {
     decode_destroy(c);
     cider_destroy(c);
     void* ptrs[] = {c->table, c->theta64, c->theta32, c->theta_hi, c->theta_lo, c->grad, c->opt_m, c->opt_v, c->d_lay, c->d_norm_partials,
-                    c->d_norms, c->d_G64, c->d_theta_rowmax, c->d_eps_rowmax, c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks};
+                    c->d_norms, c->d_G64, c->d_theta_rowmax, c->d_eps_rowmax, c->scale32, c->d_scale_max, c->d_abs_partials, c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->ev_a) cudaEventDestroy(c->ev_a);
     if (c->ev_b) cudaEventDestroy(c->ev_b);
@@ -287,6 +287,11 @@ int nes_cider_scores(nes_ctx* ctx, const int64_t* seq, int64_t n_members, int ro
     NEED_CTX(ctx); Ctx* c = CTX(ctx);
     if (cider_scores(c, seq, n_members, rows, T, rows_per_img, scores)) return 1;
     return finish_output(c, scores);
+}
+
+int nes_set_mutation(nes_ctx* ctx, int kind) {
+    NEED_CTX(ctx);
+    return set_mutation(CTX(ctx), kind);
 }
 
 int nes_shaped_fitness(nes_ctx* ctx, int kind, int64_t n_members, int rows, const double* scores, double* out) {

@@ -39,6 +39,13 @@ struct Layout {
 enum { T_IMG_W = 0, T_IMG_B, T_EMB_W, T_LOGIT_W, T_LOGIT_B, T_I2H_W, T_I2H_B, T_H2H_W, T_H2H_B,
        T_I2H_LN_W, T_I2H_LN_B, T_H2H_LN_W, T_H2H_LN_B, T_C_LN_W, T_C_LN_B };
 
+constexpr int kAbsBlocks = 296;
+// the perturbation of one parameter: f32(sigma) * eps, times the safe-mutation scale when one is set (algorithm/nets.py:101-111)
+__device__ __forceinline__ float mut_noise(float sigma, float eps, const float* __restrict__ scale, int64_t idx) {
+    const float nz = __fmul_rn(sigma, eps);
+    return scale ? __fmul_rn(nz, scale[idx]) : nz;
+}
+
 // theta / activation scaling of the split-fp16 operands (exact powers of two)
 constexpr float kThetaScale = 256.0f;     // theta_hi + theta_lo = theta * 2^8
 constexpr float kActScale   = 32.0f;      // x_hi + x_lo = x * 2^5
@@ -68,6 +75,13 @@ struct Ctx {
     float* d_theta_rowmax = nullptr;  // [n_parents] max row 2-norm of logit.weight (HYBRID error bound)
     float* d_eps_rowmax = nullptr;    // [1] max 2-norm over the rows of the [L/R, R] view of the noise table
     bool eps_rowmax_valid = false;
+
+    // safe mutations (algorithm/nets.py:104-111).  NES_MUT_PROPORTIONAL: noise = sigma*eps (.) s_p with s_p = |theta_p|, exact zeros
+    // replaced by mean|theta_p|; s_p is refreshed whenever parent p changes (launch_theta_shadow)
+    int mut_kind = 0;
+    float* scale32 = nullptr;         // [n_parents, D] (nullptr: default mutation)
+    float* d_scale_max = nullptr;     // [n_parents] max of s_p (HYBRID error bound)
+    double* d_abs_partials = nullptr; // [kAbsBlocks]
 
     // master math
     float*  grad = nullptr;           // [D]
@@ -119,6 +133,8 @@ int launch_sample_offsets(Ctx* c, uint64_t iteration, int64_t F, int64_t* d_out)
 int launch_sample_parents(Ctx* c, uint64_t iteration, int64_t F, int32_t n_parents, int32_t* d_out);
 int launch_bound_norms(Ctx* c, int parent);       // parent >= 0: theta_rowmax[parent]; parent < 0: eps_rowmax (decode.cu)
 int launch_theta_shadow(Ctx* c, int parent);      // theta32 -> theta_hi/lo (padded)
+int launch_prop_scale(Ctx* c, int parent);        // theta32 -> scale32 (SM-PROPORTIONAL)
+int set_mutation(Ctx* c, int kind);
 int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64);
 int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, float* d_member, float* d_noise, int dst_parent);
 

@@ -76,6 +76,7 @@ struct DecodeWorkspace {
     bool dense_lstm = false, dense_logit = false; int ntl = 0, ntv = 0;
     __half *wl_hi[2] = {nullptr, nullptr}, *wl_lo[2] = {nullptr, nullptr}; float* wl_bias = nullptr;
     __half* wv16 = nullptr; float* wv_bias = nullptr;
+    __half *wi_hi = nullptr, *wi_lo = nullptr; float* wi_bias = nullptr;      // img_embed, only with a safe-mutation scale (lazy)
     float* margin = nullptr; int32_t* pre_tok = nullptr; float* pre_lp = nullptr; uint8_t* unit_flag = nullptr;   // HYBRID
     unsigned long long* stats = nullptr;
     uint8_t* unfinished = nullptr; int32_t* unf_count = nullptr;
@@ -121,10 +122,11 @@ __global__ void __launch_bounds__(256) k_split_rows(const float* __restrict__ sr
 struct FinalizeParams {
     const LogitPartial* partials; int n_tiles;
     const int32_t* pre_tok; const float* pre_lp; const uint8_t* unit_flag; int m_tiles;   // HYBRID: refined arg-max unless the unit is flagged
+    int pre_always;                                                                        // flagged units were recomputed into pre_tok too (k_exact_rows)
     int rows, rows_pad, T, E, t;                 // t in 1..T (0: <bos> gather only)
     int64_t n_members;
     const int64_t* off; const float* sign; const int32_t* parent;
-    const float* theta32; const __half* table; int64_t D;
+    const float* theta32; const __half* table; int64_t D; const float* scale;
     int64_t emb_start, emb_pstart;
     float sigma;
     uint8_t* unfinished; int32_t* unf_count;     // [T+1, W]
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
     int64_t tok = 0;
     if (p.t >= 1) {
         float best = -INFINITY; int idx = 0x7fffffff;
-        if (p.pre_tok && !p.unit_flag[member * p.m_tiles + r / 128]) { idx = p.pre_tok[grow]; best = p.pre_lp[grow]; }
+        if (p.pre_tok && (p.pre_always || !p.unit_flag[member * p.m_tiles + r / 128])) { idx = p.pre_tok[grow]; best = p.pre_lp[grow]; }
         else {
         // global max and sum-exp over the vocabulary tiles
         float mx = -INFINITY;
@@ -201,7 +203,7 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
         __half hh[8], hl[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-            const float nz = __fmul_rn(p.sigma, __half2float(eh[u]));
+            const float nz = mut_noise(p.sigma, __half2float(eh[u]), p.scale, (int64_t)par * p.D + p.emb_start + tok * p.E + e + u);
             const float x = sgn > 0.f ? __fadd_rn(te[e + u], nz) : __fsub_rn(te[e + u], nz);
             split_half_dev(x, kActScale, hh[u], hl[u]);
         }
@@ -350,7 +352,7 @@ void decode_destroy(Ctx* c) {
     DecodeWorkspace* ws = c->ws;
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
-                    ws->pre_i, ws->pre_h, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
+                    ws->pre_i, ws->pre_h, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
                     ws->d_lp, ws->d_forced};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
@@ -389,7 +391,7 @@ static int launch_gemm_prec(Ctx* c, GemmParams& p, int64_t n_members, int prec) 
     return prec == NES_PREC_EXACT ? launch_gemm<EPI, NES_PREC_EXACT>(c, p, n_members) : launch_gemm<EPI, NES_PREC_FAST>(c, p, n_members);
 }
 
-static int env_debug() { static int dbg = -1; if (dbg < 0) { const char* e = getenv("NES_DEBUG"); dbg = e ? atoi(e) : 0; } return dbg; }
+static int env_debug() { const char* e = getenv("NES_DEBUG"); return e ? atoi(e) : 0; }     // experiments / tests only
 template <int EPI>
 static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
     using C = DenseCfg<EPI>;
@@ -403,10 +405,10 @@ static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
     p.n_units = (int32_t)units;
     p.debug = env_debug();
     const int sms = sm_count(c);
-    const int64_t items = EPI == DEN_LSTM ? units * p.n_tiles : units;     // see k_member_dense: LSTM work items are (unit, tile) pairs
+    const int64_t items = EPI != DEN_LOGITC ? units * p.n_tiles : units;   // see k_member_dense: LSTM / PLAIN work items are (unit, tile) pairs
     NES_CHECK(items < (1ll << 31), "too many work items");
     const unsigned grid = (unsigned)(items < sms ? items : sms);
-    ProfScope prof(c, EPI == DEN_LSTM ? PROF_LSTM : PROF_LOGIT);
+    ProfScope prof(c, EPI == DEN_LSTM ? PROF_LSTM : (EPI == DEN_PLAIN ? PROF_PLAIN : PROF_LOGIT));
     k_member_dense<EPI><<<grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
     c->launches++;
     NES_CUDA(cudaGetLastError());
@@ -414,13 +416,13 @@ static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
 }
 
 // member weights of one wave, materialised once per rollout (dense.cuh)
-static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit) {
+static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit, bool img) {
     DecodeWorkspace* ws = c->ws;
     const Layout& L = c->lay;
     ProfScope prof(c, PROF_MATERIALISE);
     auto mat = [&](int wt, int K, int out_rows, int mode, int src_rows, __half* hi, __half* lo) {
         MatParams q{};
-        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D;
+        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32;
         q.w_start = L.t[wt].start; q.w_pstart = L.t[wt].pstart; q.K = K; q.out_rows = out_rows; q.mode = mode; q.R = ws->R; q.src_rows = src_rows;
         q.sigma = sigma; q.hi = hi; q.lo = lo; q.n_members = nm;
         k_materialise<<<dim3((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(nm < 32768 ? nm : 32768)), 256, 0, c->stream>>>(q);
@@ -428,7 +430,7 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
     };
     auto matb = [&](int b0, int b1, int out_cols, int mode, int src_n, float* out) {
         MatBiasParams q{};
-        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D;
+        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32;
         q.b_start[0] = L.t[b0].start; q.b_pstart[0] = L.t[b0].pstart; q.nb = 1;
         if (b1 >= 0) { q.b_start[1] = L.t[b1].start; q.b_pstart[1] = L.t[b1].pstart; q.nb = 2; }
         q.out_cols = out_cols; q.mode = mode; q.R = ws->R; q.src_n = src_n; q.sigma = sigma; q.out = out; q.n_members = nm;
@@ -440,6 +442,10 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         mat(T_I2H_W, ws->E, rows_l, 1, 5 * ws->R, ws->wl_hi[0], ws->wl_lo[0]);
         mat(T_H2H_W, ws->R, rows_l, 1, 5 * ws->R, ws->wl_hi[1], ws->wl_lo[1]);
         matb(T_I2H_B, T_H2H_B, rows_l, 1, 5 * ws->R, ws->wl_bias);
+    }
+    if (img) {
+        mat(T_IMG_W, ws->Fd, ws->E, 0, ws->E, ws->wi_hi, ws->wi_lo);
+        matb(T_IMG_B, -1, ws->E, 0, ws->E, ws->wi_bias);
     }
     if (logit) {
         mat(T_LOGIT_W, ws->R, ws->V1, 0, ws->V1, ws->wv16, nullptr);
@@ -501,6 +507,13 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     const bool hybrid = precision == NES_PREC_HYBRID && !logit_trace && ws->dense_logit;
     if (precision == NES_PREC_HYBRID) precision = NES_PREC_EXACT;
     const bool dense_lstm = ws->dense_lstm && precision == NES_PREC_EXACT;     // split-fp16 LSTM on materialised member weights
+    const bool scaled = c->scale32 != nullptr;                                 // safe-mutation scale: every member weight is materialised
+    if (scaled) {
+        NES_CHECK(hybrid && dense_lstm && !c->dims.layer_n, "a safe-mutation scale needs HYBRID precision on the dense kernels (no layer_n, no logit trace, R <= 512)");
+        if (!ws->wi_hi) {
+            if (dmalloc(&ws->wi_hi, (int64_t)ws->W * ws->E * ws->Fd) || dmalloc(&ws->wi_lo, (int64_t)ws->W * ws->E * ws->Fd) || dmalloc(&ws->wi_bias, (int64_t)ws->W * ws->E)) return 1;
+        }
+    }
     NES_CHECK(!tracing || n_members <= ws->W, "trace mode handles a single wave");
     if (n_members == 0) return 0;
     if (hybrid && !c->eps_rowmax_valid && launch_bound_norms(c, -1)) return 1;
@@ -546,7 +559,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
         NES_CUDA(cudaMemsetAsync(ws->h_hi[0], 0, sizeof(__half) * WR * R, c->stream));
         NES_CUDA(cudaMemsetAsync(ws->h_lo[0], 0, sizeof(__half) * WR * R, c->stream));
         NES_CUDA(cudaMemsetAsync(ws->unf_count, 0, sizeof(int32_t) * (T + 2) * ws->W, c->stream));
-        if ((dense_lstm || hybrid) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid)) return 1;
+        if ((dense_lstm || hybrid) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid, scaled)) return 1;
 
         GemmParams base{};
         base.rows = rows; base.rows_pad = rows_pad; base.m_tiles = m_tiles;
@@ -558,7 +571,18 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
 
         const int64_t a_rows_w = (int64_t)ws->W * ws->rows_pad;
         // ---- t = 0 : x0 = img_embed(fc)
-        {
+        if (scaled) {
+            DenseParams p{};
+            const int bk = DenseCfg<DEN_PLAIN>::BK;
+            if (get_map(ws, &p.a_hi[0], ws->fc_hi, ws->fc_members * ws->rows_pad, Fd, 128, bk) || get_map(ws, &p.a_lo[0], ws->fc_lo, ws->fc_members * ws->rows_pad, Fd, 128, bk) ||
+                get_map(ws, &p.b_hi[0], ws->wi_hi, (int64_t)ws->W * E, Fd, 256, bk) || get_map(ws, &p.b_lo[0], ws->wi_lo, (int64_t)ws->W * E, Fd, 256, bk)) return 1;
+            p.a_hi[1] = p.a_hi[0]; p.a_lo[1] = p.a_lo[0]; p.b_hi[1] = p.b_hi[0]; p.b_lo[1] = p.b_lo[0];
+            p.K[0] = Fd; p.K[1] = 0; p.nseg = 1; p.a_shared = shared_batch ? 1 : 0;
+            p.rows = rows; p.rows_pad = rows_pad; p.m_tiles = m_tiles; p.n_tiles = (E + 255) / 256; p.N = E;
+            p.b_rows = E; p.bias = ws->wi_bias; p.bias_stride = E;
+            p.out_hi = ws->x_hi; p.out_lo = ws->x_lo;
+            if (launch_dense<DEN_PLAIN>(c, p, nm)) return 1;
+        } else {
             GemmParams p = base;
             p.nseg = 1; p.N = E; p.chunk_stride = 0; p.n_tiles = (E + 127) / 128;
             if (fill_seg(c, p, 0, ws->fc_hi, ws->fc_lo, ws->fc_members * ws->rows_pad, Fd, shared_batch ? 1 : 0, T_IMG_W, T_IMG_B, 128, precision)) return 1;
@@ -620,7 +644,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     // (1) per-row error bound, (2) fp16-operand logits + candidate lists, (3) fp32 re-evaluation of the candidates
                     MarginParams mg{};
                     mg.h_hi = ws->h_hi[hb]; mg.h_lo = ws->h_lo[hb]; mg.R = R; mg.rows = rows; mg.rows_pad = rows_pad; mg.n_members = nm;
-                    mg.parent = base.parent; mg.theta_rowmax = c->d_theta_rowmax; mg.eps_rowmax = c->d_eps_rowmax; mg.sigma = sigma; mg.margin = ws->margin;
+                    mg.parent = base.parent; mg.theta_rowmax = c->d_theta_rowmax; mg.eps_rowmax = c->d_eps_rowmax; mg.scale_max = c->d_scale_max; mg.sigma = sigma; mg.margin = ws->margin;
                     { ProfScope prof(c, PROF_FINALIZE);
                       k_row_margin<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(mg); c->launches++; }
                     NES_CUDA(cudaGetLastError());
@@ -640,28 +664,36 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     RefineParams rf{};
                     rf.heads = ws->heads; rf.entries = ws->entries; rf.margin = ws->margin; rf.h_hi = ws->h_hi[hb]; rf.h_lo = ws->h_lo[hb]; rf.R = R; rf.V1 = V1;
                     rf.rows = rows; rf.rows_pad = rows_pad; rf.m_tiles = m_tiles; rf.n_members = nm;
-                    rf.off = base.off; rf.sign = base.sign; rf.parent = base.parent; rf.theta32 = c->theta32; rf.table = c->table; rf.D = L.D;
+                    rf.off = base.off; rf.sign = base.sign; rf.parent = base.parent; rf.theta32 = c->theta32; rf.table = c->table; rf.D = L.D; rf.scale = c->scale32;
                     rf.w_start = L.t[T_LOGIT_W].start; rf.w_pstart = L.t[T_LOGIT_W].pstart; rf.b_start = L.t[T_LOGIT_B].start; rf.b_pstart = L.t[T_LOGIT_B].pstart;
                     rf.sigma = sigma; rf.tok = ws->pre_tok; rf.lp = ws->pre_lp; rf.unit_flag = ws->unit_flag; rf.stats = c->profiling ? ws->stats : nullptr;
+                    rf.force_overflow = (env_debug() & 64) ? 1 : 0;
                     { ProfScope prof(c, PROF_FINALIZE);
                       k_refine<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(rf); c->launches++; }
                     NES_CUDA(cudaGetLastError());
                     p.unit_mask = ws->unit_flag;      // (4) units whose candidate list overflowed: the split-fp16 kernel, everything else skips
+                    if (scaled) {                     //     ... or, with scaled noise, every logit of those rows in fp32 (k_exact_rows)
+                        ProfScope prof(c, PROF_FALLBACK);
+                        k_exact_rows<<<(unsigned)(nm * rows), 256, sizeof(float) * V1, c->stream>>>(rf); c->launches++;
+                        NES_CUDA(cudaGetLastError());
+                    }
                 }
+                if (!(hybrid && scaled)) {
                 if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128, precision)) return 1;
                 p.logit_trace = logit_trace ? logit_trace + (int64_t)(t - 1) * n_members * rows * V1 : nullptr; p.ld_trace = V1;
                 if (launch_gemm_prec<EPI_LOGIT>(c, p, nm, precision)) return 1;
+                }
             }
             if (t < T || t >= 1) {
                 FinalizeParams f{};
                 f.partials = ws->partials; f.n_tiles = 2; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
-                f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table;
+                f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table; f.scale = c->scale32;
                 f.D = L.D; f.emb_start = L.t[T_EMB_W].start; f.emb_pstart = L.t[T_EMB_W].pstart; f.sigma = sigma;
                 f.unfinished = ws->unfinished; f.unf_count = ws->unf_count; f.W = ws->W;
                 f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;
                 f.forced = forced ? ws->d_forced + m0 * rows * T : nullptr;
                 f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0;
-                if (hybrid && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; }
+                if (hybrid && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = scaled ? 1 : 0; }
                 ProfScope prof(c, PROF_FINALIZE);
                 k_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(f);
                 c->launches++;

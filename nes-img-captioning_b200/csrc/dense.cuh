@@ -20,7 +20,7 @@
 
 namespace nes {
 
-enum { DEN_LSTM = 0, DEN_LOGITC = 1 };
+enum { DEN_LSTM = 0, DEN_LOGITC = 1, DEN_PLAIN = 2 };
 constexpr int kLstmTileUnits = 48;          // hidden units per LSTM tile; accumulator column = gate * 48 + unit
 constexpr int kLstmTileCols = 5 * kLstmTileUnits;
 constexpr int kCandCap = 64;                // candidate entries per half row (append-only; overflow -> split-fp16 fallback)
@@ -35,6 +35,7 @@ struct alignas(64) DenseParams {
     int32_t rows, rows_pad, m_tiles, n_tiles, n_units;
     int32_t N;                              // valid outputs: R (LSTM hidden units) or V+1 (LOGITC)
     int32_t b_rows;                         // weight rows per member in the materialised buffer
+    int32_t a_shared;                       // 1: every member reads activation rows [0, rows_pad) (shared fc batch, PLAIN)
     const float* bias; int32_t bias_stride; // [W][bias_stride] member bias in accumulator-column order
     float* c_state; __half* out_hi; __half* out_lo; float* h_trace;       // LSTM
     CandHead* heads; CandEntry* entries; const float* margin;            // LOGITC
@@ -43,17 +44,18 @@ struct alignas(64) DenseParams {
 
 template <int EPI> struct DenseCfg {
     static constexpr bool LSTM = EPI == DEN_LSTM;
+    static constexpr bool SPLIT = EPI != DEN_LOGITC;                     // split-fp16 operands streamed per stage (LSTM, PLAIN)
     static constexpr int BM = 128;
-    static constexpr int BK = LSTM ? 32 : 64;
+    static constexpr int BK = SPLIT ? 32 : 64;
     static constexpr int SWZ = BK * 2;
     static constexpr int BN = LSTM ? kLstmTileCols : 256;
-    static constexpr int NA = LSTM ? 2 : 1;
-    static constexpr int NB = LSTM ? 2 : 1;
+    static constexpr int NA = SPLIT ? 2 : 1;
+    static constexpr int NB = SPLIT ? 2 : 1;
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
-    static constexpr int ARES_KB = LSTM ? 0 : 8;                         // resident A k-blocks (LOGITC needs K <= 512)
+    static constexpr int ARES_KB = SPLIT ? 0 : 8;                        // resident A k-blocks (LOGITC needs K <= 512)
     static constexpr int ARES_BYTES = ARES_KB * A_BYTES;
-    static constexpr int STAGE_BYTES = (LSTM ? NA * A_BYTES : 0) + NB * B_BYTES;
+    static constexpr int STAGE_BYTES = (SPLIT ? NA * A_BYTES : 0) + NB * B_BYTES;
     static constexpr int CTRL_BYTES = 2048;                              // barriers [0,512), tmem slot, bias [512, 1536)
     static constexpr int SMEM_MAX = 227 * 1024;
     static constexpr int STAGES_FIT = (SMEM_MAX - 1024 - CTRL_BYTES - ARES_BYTES) / STAGE_BYTES;
@@ -100,7 +102,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
     // work items: LSTM = (unit, weight tile) pairs in tile-minor order, so the CTAs that run concurrently share a unit's
     // activation block through L2 (it is fetched from HBM once, not once per tile); LOGITC = whole units, because the
     // running arg-max / sum-exp of a row lives in one thread's registers across all vocabulary tiles
-    const int n_items = C::LSTM ? p.n_units * p.n_tiles : p.n_units;
+    const int n_items = C::SPLIT ? p.n_units * p.n_tiles : p.n_units;
 
     if (warp == 0 || warp == 10) {
         // =========================== TMA producers (two warps fill alternate stages) ===========================
@@ -108,17 +110,17 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
         if (lane == 0) {
             for (int s = 0; s < p.nseg; ++s) {
                 tc::prefetch_tmap(&p.a_hi[s]); tc::prefetch_tmap(&p.b_hi[s]);
-                if (C::LSTM) { tc::prefetch_tmap(&p.a_lo[s]); tc::prefetch_tmap(&p.b_lo[s]); }
+                if (C::SPLIT) { tc::prefetch_tmap(&p.a_lo[s]); tc::prefetch_tmap(&p.b_lo[s]); }
             }
             int stage = 0; uint32_t phase = 0; uint32_t q = 0; uint32_t uc = 0;
             for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++uc) {
-                const int u = C::LSTM ? item / p.n_tiles : item;
-                const int nt0 = C::LSTM ? item - u * p.n_tiles : 0, nt1 = C::LSTM ? nt0 + 1 : p.n_tiles;
+                const int u = C::SPLIT ? item / p.n_tiles : item;
+                const int nt0 = C::SPLIT ? item - u * p.n_tiles : 0, nt1 = C::SPLIT ? nt0 + 1 : p.n_tiles;
                 const int64_t member = u / p.m_tiles;
                 const int mt = u % p.m_tiles;
-                const int32_t a_row = (int32_t)(member * p.rows_pad + mt * C::BM);
+                const int32_t a_row = (int32_t)((p.a_shared ? 0 : member * p.rows_pad) + mt * C::BM);
                 const int32_t b_row0 = (int32_t)(member * p.b_rows);
-                if (!C::LSTM && pid == 0) {
+                if (!C::SPLIT && pid == 0) {
                     // the unit's x block: k-block kb may be overwritten once the previous unit's last tile has consumed it
                     const int nkb = p.K[0] / C::BK;
                     for (int kb = 0; kb < nkb; ++kb) {
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                             tc::mbar_wait(&empty_bar[stage], phase ^ 1);
                             uint8_t* st = ring + stage * C::STAGE_BYTES;
                             tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
-                            if (C::LSTM) {
+                            if (C::SPLIT) {
                                 tc::tma_load_2d(st, &p.a_hi[s], &full_bar[stage], kb * C::BK, a_row);
                                 tc::tma_load_2d(st + C::A_BYTES, &p.a_lo[s], &full_bar[stage], kb * C::BK, a_row);
                                 uint8_t* sb = st + 2 * C::A_BYTES;
@@ -156,7 +158,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
             int stage = 0; uint32_t phase = 0; uint32_t it = 0; uint32_t uc = 0;
             constexpr uint32_t idesc = tc::make_idesc_f16(128, C::BN);
             for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++uc) {
-                const int nt0 = C::LSTM ? item % p.n_tiles : 0, nt1 = C::LSTM ? nt0 + 1 : p.n_tiles;
+                const int nt0 = C::SPLIT ? item % p.n_tiles : 0, nt1 = C::SPLIT ? nt0 + 1 : p.n_tiles;
                 for (int nt = nt0; nt < nt1; ++nt, ++it) {
                     const uint32_t buf = it & 1;
                     tc::mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);
@@ -166,13 +168,13 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                     for (int s = 0; s < p.nseg; ++s) {
                         const int nkb = p.K[s] / C::BK;
                         for (int kb = 0; kb < nkb; ++kb) {
-                            if (!C::LSTM && nt == 0) tc::mbar_wait(&afull_bar[kb], uc & 1);
+                            if (!C::SPLIT && nt == 0) tc::mbar_wait(&afull_bar[kb], uc & 1);
                             tc::mbar_wait(&full_bar[stage], phase);
                             tc::tc_fence_after();
                             const uint32_t st = tc::smem_u32(ring + stage * C::STAGE_BYTES);
 #pragma unroll
                             for (int k = 0; k < C::BK / 16; ++k) {
-                                if (C::LSTM) {
+                                if (C::SPLIT) {
                                     const uint64_t a_hi = tc::make_smem_desc<C::SWZ>(st + k * 32);
                                     const uint64_t a_lo = tc::make_smem_desc<C::SWZ>(st + C::A_BYTES + k * 32);
                                     const uint64_t b_hi = tc::make_smem_desc<C::SWZ>(st + 2 * C::A_BYTES + k * 32);
@@ -187,7 +189,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                             }
                             first = false;
                             tc::umma_commit(&empty_bar[stage]);
-                            if (!C::LSTM && nt == p.n_tiles - 1) tc::umma_commit(&aempty_bar[kb]);
+                            if (!C::SPLIT && nt == p.n_tiles - 1) tc::umma_commit(&aempty_bar[kb]);
                             if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                         }
                     }
@@ -210,19 +212,19 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
             const int col = nt * C::BN + et;
             return col < p.bias_stride ? p.bias[member * p.bias_stride + col] : 0.f;
         };
-        float b_cur = C::LSTM ? bias_val(blockIdx.x / p.n_tiles, blockIdx.x % p.n_tiles) : bias_val(blockIdx.x, 0);
+        float b_cur = C::SPLIT ? bias_val(blockIdx.x / p.n_tiles, blockIdx.x % p.n_tiles) : bias_val(blockIdx.x, 0);
         uint32_t it = 0;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int u = C::LSTM ? item / p.n_tiles : item;
-            const int nt0 = C::LSTM ? item - u * p.n_tiles : 0, nt1 = C::LSTM ? nt0 + 1 : p.n_tiles;
+            const int u = C::SPLIT ? item / p.n_tiles : item;
+            const int nt0 = C::SPLIT ? item - u * p.n_tiles : 0, nt1 = C::SPLIT ? nt0 + 1 : p.n_tiles;
             const int64_t member = u / p.m_tiles;
             const int mt = u % p.m_tiles;
             const int m_local = mt * C::BM + row;
             const bool row_ok = m_local < p.rows;
             const int64_t grow = member * p.rows_pad + m_local;
             float run_max = -INFINITY, run_sum = 0.f; int n_cand = 0;
-            const float margin = (!C::LSTM && row_ok) ? p.margin[grow] : 0.f;
-            CandEntry* ent = C::LSTM ? nullptr : p.entries + (grow * 2 + hf) * (int64_t)kCandCap;
+            const float margin = (EPI == DEN_LOGITC && row_ok) ? p.margin[grow] : 0.f;
+            CandEntry* ent = EPI != DEN_LOGITC ? nullptr : p.entries + (grow * 2 + hf) * (int64_t)kCandCap;
 
             for (int nt = nt0; nt < nt1; ++nt, ++it) {
                 const uint32_t buf = it & 1;
@@ -232,7 +234,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                 {
                     const int nx = item + (int)gridDim.x;                  // first tile of this CTA's next work item
                     b_cur = (nt + 1 < nt1) ? bias_val(u, nt + 1)
-                          : (C::LSTM ? bias_val(nx / p.n_tiles, nx % p.n_tiles) : bias_val(nx, 0));
+                          : (C::SPLIT ? bias_val(nx / p.n_tiles, nx % p.n_tiles) : bias_val(nx, 0));
                 }
                 float cprev[24];
                 if (C::LSTM) {
@@ -289,6 +291,27 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                             }
                         }
                     }
+                } else if (EPI == DEN_PLAIN) {
+                    // PLAIN: y = acc * 2^-13 + bias, written as the next split-fp16 A operand; this warp owns 128 of the 256 columns
+                    const int n_base = nt * C::BN;
+#pragma unroll 1
+                    for (int c0 = hf * 128; c0 < hf * 128 + 128; c0 += 32) {
+                        float y[32];
+                        tc::tmem_ld32(trow + c0, y);
+                        tc::tmem_ld_wait();
+                        if (row_ok && n_base + c0 < p.N) {
+                            __half hh[32], hl[32];
+#pragma unroll
+                            for (int uu = 0; uu < 32; ++uu) split_half_dev(fmaf(y[uu], sW, s_bias[c0 + uu]), kActScale, hh[uu], hl[uu]);
+#pragma unroll
+                            for (int v4 = 0; v4 < 4; ++v4) {
+                                if (n_base + c0 + v4 * 8 < p.N) {
+                                    *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + n_base + c0 + v4 * 8) = *reinterpret_cast<uint4*>(&hh[v4 * 8]);
+                                    *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + n_base + c0 + v4 * 8) = *reinterpret_cast<uint4*>(&hl[v4 * 8]);
+                                }
+                            }
+                        }
+                    }
                 } else {
                     // LOGITC: this warp owns 128 of the tile's 256 vocabulary columns, 32 at a time
                     const int n_base = nt * C::BN;
@@ -338,7 +361,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&tempty_bar[buf]);
             }
-            if (!C::LSTM && row_ok) {
+            if (EPI == DEN_LOGITC && row_ok) {
                 CandHead hd; hd.mx = run_max; hd.sum = run_sum; hd.n = n_cand; hd.pad = 0;
                 *reinterpret_cast<float4*>(&p.heads[grow * 2 + hf]) = *reinterpret_cast<float4*>(&hd);
             }
@@ -357,6 +380,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
 struct MatParams {
     const int64_t* off; const float* sign; const int32_t* parent;
     const float* theta32; const __half* table; int64_t D;
+    const float* scale;                     // nullable: safe-mutation scale [n_parents, D]
     int64_t w_start, w_pstart;
     int32_t K, out_rows, mode, R, src_rows;
     float sigma;
@@ -375,7 +399,9 @@ __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
     const int r_end = min(p.out_rows, ((int)blockIdx.x + 1) * kMatRowsPerBlock);
     for (int64_t member = blockIdx.y; member < p.n_members; member += gridDim.y) {
         const float sgn = p.sign[member];
-        const float* tbase = p.theta32 + (int64_t)(p.parent ? p.parent[member] : 0) * p.D + p.w_start;
+        const int64_t pbase = (int64_t)(p.parent ? p.parent[member] : 0) * p.D + p.w_start;
+        const float* tbase = p.theta32 + pbase;
+        const float* sbase = p.scale ? p.scale + pbase : nullptr;
         const __half* ebase = p.table + p.off[member] + p.w_pstart;
         for (int r = blockIdx.x * kMatRowsPerBlock + lr; r < r_end; r += rpi) {
             int src = r;
@@ -401,7 +427,7 @@ __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
                     }
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
-                        const float nz = __fmul_rn(p.sigma, __half2float(eh[e]));
+                        const float nz = mut_noise(p.sigma, __half2float(eh[e]), sbase, (int64_t)src * p.K + k + e);
                         const float w = sgn > 0.f ? __fadd_rn(tv[e], nz) : __fsub_rn(tv[e], nz);
                         split_half_dev(w, kThetaScale, hh[e], hl[e]);
                     }
@@ -419,7 +445,7 @@ __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
 // member biases in accumulator-column order: LSTM (mode 1) = (b_i2h +- sigma eps) + (b_h2h +- sigma eps); logit (mode 0)
 struct MatBiasParams {
     const int64_t* off; const float* sign; const int32_t* parent;
-    const float* theta32; const __half* table; int64_t D;
+    const float* theta32; const __half* table; int64_t D; const float* scale;
     int64_t b_start[2], b_pstart[2]; int32_t nb;
     int32_t out_cols, mode, R, src_n;
     float sigma; float* out; int64_t n_members;
@@ -442,7 +468,7 @@ __global__ void __launch_bounds__(256) k_materialise_bias(const MatBiasParams p)
             const int64_t off = p.off[member];
             for (int s = 0; s < p.nb; ++s) {
                 const float tb = p.theta32[par * p.D + p.b_start[s] + n];
-                const float nz = __fmul_rn(p.sigma, __half2float(p.table[off + p.b_pstart[s] + n]));
+                const float nz = mut_noise(p.sigma, __half2float(p.table[off + p.b_pstart[s] + n]), p.scale, par * p.D + p.b_start[s] + n);
                 b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
             }
         }

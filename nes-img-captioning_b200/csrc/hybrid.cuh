@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(256) k_rowmax_eps(const __half* __restrict__ t
 
 struct MarginParams {
     const __half *h_hi, *h_lo; int R; int rows, rows_pad; int64_t n_members;
-    const int32_t* parent; const float* theta_rowmax; const float* eps_rowmax; float sigma; float* margin;
+    const int32_t* parent; const float* theta_rowmax; const float* eps_rowmax; const float* scale_max; float sigma; float* margin;
 };
 // one warp per (member, row): margin = 2 * error bound of the fp16-operand logits of that row
 __global__ void __launch_bounds__(128) k_row_margin(const MarginParams p) {
@@ -74,7 +74,8 @@ __global__ void __launch_bounds__(128) k_row_margin(const MarginParams p) {
     s = warp_sum(s);
     if (lane == 0) {
         const int par = p.parent ? p.parent[member] : 0;
-        const float wsum = 2.f * (p.theta_rowmax[par] + fabsf(p.sigma) * p.eps_rowmax[0]);
+        const float smax = p.scale_max ? p.scale_max[par] : 1.f;            // |eps_j (.) s|_2 <= max(s) |eps_j|_2
+        const float wsum = 2.f * (p.theta_rowmax[par] + fabsf(p.sigma) * p.eps_rowmax[0] * smax);
         // 2^-11 relative rounding of both operands, +10 % for the fp32 accumulation of K <= 4096 terms, x2 (two logits compared)
         p.margin[grow] = 2.f * 1.1f * 4.8828125e-4f * sqrtf(s) * 1.0001f * (wsum + 1e-4f) + 1e-30f;
     }
@@ -84,12 +85,13 @@ struct RefineParams {
     const CandHead* heads; const CandEntry* entries; const float* margin;
     const __half *h_hi, *h_lo; int R, V1; int rows, rows_pad, m_tiles; int64_t n_members;
     const int64_t* off; const float* sign; const int32_t* parent;
-    const float* theta32; const __half* table; int64_t D;
+    const float* theta32; const __half* table; int64_t D; const float* scale;
     int64_t w_start, w_pstart, b_start, b_pstart;     // logit.weight / logit.bias: flat and padded starts
     float sigma;
     int32_t* tok; float* lp;                          // [member*rows_pad + row]: arg-max column and its log-prob
     uint8_t* unit_flag;                               // [n_members*m_tiles]: 1 -> recompute this unit with the split-fp16 kernel
     unsigned long long* stats;                        // nullable: [0] rows refined, [1] candidates evaluated, [2] rows overflowed
+    int force_overflow;                               // NES_DEBUG bit 6 (64): every row takes the fallback (tests)
 };
 // one warp per (member, row): filter the two half-row candidate lists by the final threshold, re-evaluate every survivor
 // in fp32 with the member weight theta +- f32(sigma)*eps (algorithm/nets.py:113), pick the reference's argmax of float32
@@ -106,7 +108,7 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
     const float M = fmaxf(h0.mx, h1.mx);
     const float thr = M - p.margin[grow];
     int count = 0;
-    bool overflow = h0.n > kCandCap || h1.n > kCandCap;
+    bool overflow = h0.n > kCandCap || h1.n > kCandCap || p.force_overflow;
     if (!overflow) {
         for (int hf = 0; hf < 2; ++hf) {
             const int n = hf ? h1.n : h0.n;
@@ -150,14 +152,14 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
                 const float x = (__half2float(ha[e]) + __half2float(hb[e])) * (1.0f / kActScale);
-                const float nz = __fmul_rn(p.sigma, __half2float(he[e]));
+                const float nz = mut_noise(p.sigma, __half2float(he[e]), p.scale, (int64_t)par * p.D + p.w_start + (int64_t)j * p.R + k + e);
                 const float w = sgn > 0.f ? __fadd_rn(tv[e], nz) : __fsub_rn(tv[e], nz);
                 acc = fmaf(x, w, acc);
             }
         }
         acc = warp_sum(acc);
         const float tb = p.theta32[(int64_t)par * p.D + p.b_start + j];
-        const float nzb = __fmul_rn(p.sigma, __half2float(p.table[off + p.b_pstart + j]));
+        const float nzb = mut_noise(p.sigma, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j);
         const float v = acc + (sgn > 0.f ? __fadd_rn(tb, nzb) : __fsub_rn(tb, nzb));
         if (lane == c) my_val = v;
     }
@@ -173,6 +175,73 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
     }
     if (lane == 0) { p.tok[grow] = idx; p.lp[grow] = best; }
     if (p.stats && lane == 0) { atomicAdd(&p.stats[0], 1ull); atomicAdd(&p.stats[1], (unsigned long long)count); }
+}
+
+// Fallback of the HYBRID projection when member weights carry a safe-mutation scale (the factored split-fp16 kernel cannot
+// scale eps tiles on their way through TMA): every logit of every row of a flagged unit in plain fp32 on the CUDA cores, then
+// the reference's log_softmax / argmax (captioning/nets.py:202-208).  One block per row; rare (candidate list overflow).
+__global__ void __launch_bounds__(256) k_exact_rows(const RefineParams p) {
+    extern __shared__ float s_logit[];                    // [V1]
+    __shared__ float s_red[8]; __shared__ int s_idx[8];
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    const int64_t wid = blockIdx.x;
+    const int64_t member = wid / p.rows;
+    const int r = (int)(wid % p.rows);
+    if (!p.unit_flag[member * p.m_tiles + r / 128]) return;
+    const int64_t grow = member * p.rows_pad + r;
+    const float sgn = p.sign[member];
+    const int64_t off = p.off[member];
+    const int par = p.parent ? p.parent[member] : 0;
+    for (int j = wq; j < p.V1; j += 8) {
+        const float* tw = p.theta32 + (int64_t)par * p.D + p.w_start + (int64_t)j * p.R;
+        const __half* ew = p.table + off + p.w_pstart + (int64_t)j * p.R;
+        float acc = 0.f;
+        for (int k = lane; k < p.R; k += 32) {
+            const float x = (__half2float(p.h_hi[grow * p.R + k]) + __half2float(p.h_lo[grow * p.R + k])) * (1.0f / kActScale);
+            const float nz = mut_noise(p.sigma, __half2float(ew[k]), p.scale, (int64_t)par * p.D + p.w_start + (int64_t)j * p.R + k);
+            acc = fmaf(x, sgn > 0.f ? __fadd_rn(tw[k], nz) : __fsub_rn(tw[k], nz), acc);
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) {
+            const float tb = p.theta32[(int64_t)par * p.D + p.b_start + j];
+            const float nzb = mut_noise(p.sigma, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j);
+            s_logit[j] = acc + (sgn > 0.f ? __fadd_rn(tb, nzb) : __fsub_rn(tb, nzb));
+        }
+    }
+    __syncthreads();
+    float mx = -INFINITY;
+    for (int j = threadIdx.x; j < p.V1; j += 256) mx = fmaxf(mx, s_logit[j]);
+    mx = warp_max(mx);
+    if (lane == 0) s_red[wq] = mx;
+    __syncthreads();
+    mx = s_red[0];
+    for (int q = 1; q < 8; ++q) mx = fmaxf(mx, s_red[q]);
+    __syncthreads();
+    float sm = 0.f;
+    for (int j = threadIdx.x; j < p.V1; j += 256) sm += expf(s_logit[j] - mx);
+    sm = warp_sum(sm);
+    if (lane == 0) s_red[wq] = sm;
+    __syncthreads();
+    sm = 0.f;
+    for (int q = 0; q < 8; ++q) sm += s_red[q];
+    const float lse = logf(sm);
+    float best = -INFINITY; int idx = 0x7fffffff;
+    for (int j = threadIdx.x; j < p.V1; j += 256) {
+        const float l = __fsub_rn(__fsub_rn(s_logit[j], mx), lse);
+        if (l > best) { best = l; idx = j; }              // ascending j per thread: the first index wins ties
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+    }
+    __syncthreads();
+    if (lane == 0) { s_red[wq] = best; s_idx[wq] = idx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int q = 1; q < 8; ++q) if (s_red[q] > best || (s_red[q] == best && s_idx[q] < idx)) { best = s_red[q]; idx = s_idx[q]; }
+        p.tok[grow] = idx; p.lp[grow] = best;
+    }
 }
 
 }  // namespace nes

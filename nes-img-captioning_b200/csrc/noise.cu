@@ -114,6 +114,7 @@ int launch_theta_shadow(Ctx* c, int parent) {
                                                 c->theta_lo + (int64_t)parent * c->lay.D_pad, c->d_lay);
     c->launches++;
     NES_CUDA(cudaGetLastError());
+    if (c->mut_kind == NES_MUT_PROPORTIONAL && launch_prop_scale(c, parent)) return 1;
     if (c->is_fc) return launch_bound_norms(c, parent);
     return 0;
 }
@@ -142,10 +143,10 @@ int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64) {
 // noise = f32(sigma) * f32(eps) ; member = theta + noise  (sign<0: theta - noise, nic_nes_worker.py:151)
 __global__ void __launch_bounds__(256) k_evolve(const float* __restrict__ th, const __half* __restrict__ row, const Layout* __restrict__ lay,
                                                 float sign, float sigma, float* __restrict__ member, float* __restrict__ noise,
-                                                double* __restrict__ dst64, float* __restrict__ dst32) {
+                                                double* __restrict__ dst64, float* __restrict__ dst32, const float* __restrict__ scale) {
     const TensorDesc t = lay->t[blockIdx.y];
     for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < t.count; j += (int64_t)gridDim.x * blockDim.x) {
-        float nz = __fmul_rn(sigma, __half2float(row[t.pstart + j]));
+        float nz = mut_noise(sigma, __half2float(row[t.pstart + j]), scale, t.start + j);
         float th0 = th[t.start + j];
         float m = sign > 0.f ? __fadd_rn(th0, nz) : __fsub_rn(th0, nz);
         if (noise)  noise[t.start + j] = nz;
@@ -160,10 +161,67 @@ int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, f
     dim3 grid(148 * 2, c->lay.n);
     k_evolve<<<grid, 256, 0, c->stream>>>(c->theta32 + parent * D, c->table + offset, c->d_lay, sign, sigma, d_member, d_noise,
                                           dst_parent >= 0 ? c->theta64 + dst_parent * D : nullptr,
-                                          dst_parent >= 0 ? c->theta32 + dst_parent * D : nullptr);
+                                          dst_parent >= 0 ? c->theta32 + dst_parent * D : nullptr,
+                                          c->scale32 ? c->scale32 + parent * D : nullptr);
     c->launches++;
     NES_CUDA(cudaGetLastError());
     if (dst_parent >= 0) { c->theta_is_f32[dst_parent] = 1; return launch_theta_shadow(c, dst_parent); }
+    return 0;
+}
+
+// ---- SM-PROPORTIONAL scale (algorithm/nets.py:107-111): params = theta.clone(); params[params == 0] = mean(|theta|); noise *= |params|
+// The mean is accumulated in float64 in a fixed order and rounded to float32 (torch's float32 pairwise mean agrees to ~1 ulp;
+// it only enters through parameters that are exactly zero, i.e. untrained biases).
+__global__ void __launch_bounds__(256) k_abs_partial(const float* __restrict__ th, int64_t D, double* __restrict__ partials) {
+    __shared__ double sh[8];
+    double a = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < D; i += (int64_t)gridDim.x * 256) a += (double)fabsf(th[i]);
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) { double t = 0; for (int q = 0; q < 8; ++q) t += sh[q]; partials[blockIdx.x] = t; }
+}
+__global__ void __launch_bounds__(256) k_prop_scale(const float* __restrict__ th, int64_t D, const double* __restrict__ partials, int n_partials,
+                                                    float* __restrict__ scale, float* __restrict__ scale_max) {
+    double tot = 0.0;
+    for (int q = 0; q < n_partials; ++q) tot += partials[q];
+    const float mean = (float)(tot / (double)D);
+    float mx = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < D; i += (int64_t)gridDim.x * 256) {
+        const float v = th[i];
+        const float s = v == 0.0f ? fabsf(mean) : fabsf(v);
+        scale[i] = s; mx = fmaxf(mx, s);
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<int*>(scale_max), __float_as_int(mx));     // mx >= 0
+}
+int launch_prop_scale(Ctx* c, int parent) {
+    const int64_t D = c->lay.D;
+    NES_CHECK(c->scale32 && c->d_scale_max && c->d_abs_partials, "proportional mutation buffers missing");
+    const float* th = c->theta32 + (int64_t)parent * D;
+    k_abs_partial<<<kAbsBlocks, 256, 0, c->stream>>>(th, D, c->d_abs_partials);
+    NES_CUDA(cudaMemsetAsync(c->d_scale_max + parent, 0, sizeof(float), c->stream));
+    k_prop_scale<<<kAbsBlocks, 256, 0, c->stream>>>(th, D, c->d_abs_partials, kAbsBlocks, c->scale32 + (int64_t)parent * D, c->d_scale_max + parent);
+    c->launches += 2;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+int set_mutation(Ctx* c, int kind) {
+    NES_CHECK(kind == NES_MUT_DEFAULT || kind == NES_MUT_PROPORTIONAL, "only the default and SM-PROPORTIONAL mutations run on the device");
+    NES_CHECK(!(kind == NES_MUT_PROPORTIONAL && c->is_fc && c->dims.layer_n), "SM-PROPORTIONAL with layer_n is not supported");
+    if (kind == c->mut_kind) return 0;
+    NES_CUDA(cudaStreamSynchronize(c->stream));
+    if (kind == NES_MUT_PROPORTIONAL) {
+        NES_CUDA(cudaMalloc((void**)&c->scale32, sizeof(float) * (size_t)c->n_parents * c->lay.D));
+        NES_CUDA(cudaMalloc((void**)&c->d_scale_max, sizeof(float) * c->n_parents));
+        NES_CUDA(cudaMalloc((void**)&c->d_abs_partials, sizeof(double) * kAbsBlocks));
+        c->mut_kind = kind;
+        for (int p = 0; p < c->n_parents; ++p) if (launch_prop_scale(c, p)) return 1;
+    } else {
+        cudaFree(c->scale32); cudaFree(c->d_scale_max); cudaFree(c->d_abs_partials);
+        c->scale32 = nullptr; c->d_scale_max = nullptr; c->d_abs_partials = nullptr;
+        c->mut_kind = kind;
+    }
     return 0;
 }
 

@@ -5,7 +5,8 @@ Differences that follow from the design (documented in DESIGN.md):
   * evolve() draws its noise from the shared noise table (a fresh offset per call) instead of an
     unseeded torch.normal_ -- the returned vector is still float32 sigma*eps of length D;
   * set_from_vector() copies (the reference aliases the caller's memory, nets.py:163-165);
-  * only Mutation.DEFAULT runs on the CUDA path; safe mutations raise.
+  * Mutation.DEFAULT and Mutation.SAFE_PROPORTIONAL run on the CUDA path; the gradient / vector safe mutations raise
+    (SURVEY section 8f-3).
 """
 from collections import OrderedDict, namedtuple
 from enum import Enum
@@ -36,8 +37,9 @@ class PolicyNet:
     def __init__(self, ctx: NesContext, parent=0, options=None, vbn=False):
         self.ctx, self.parent = ctx, int(parent)
         self.mutations = Mutation((options and options.safe_mutations) or '')
-        if self.mutations != Mutation.DEFAULT:
-            raise NotImplementedError('safe mutations are not on the B200 path (SURVEY 8f-3)')
+        if self.mutations not in (Mutation.DEFAULT, Mutation.SAFE_PROPORTIONAL):
+            raise NotImplementedError('gradient / vector safe mutations are not on the B200 path (SURVEY 8f-3)')
+        ctx.set_mutation(self.mutations.value)        # context-wide: every parent slot mutates the same way
         if vbn:
             raise NotImplementedError('virtual batch norm is not on the B200 path (SURVEY 8f-3)')
         self.nb_learnable_params = ctx.D

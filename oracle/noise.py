@@ -165,10 +165,21 @@ def noise_row(seed, offset, playout, D):
     return eps
 
 
-def member_theta(theta, eps, sigma, sign):
+def proportional_scale(theta):
+    """SM-PROPORTIONAL (src/algorithm/nets.py:107-111): params = theta.clone(); params[params == 0] = mean(|theta|);
+    noise *= |params|.  The mean is taken in float64 and rounded to float32 (this build's rule; torch's float32 mean
+    agrees to ~1 ulp and only matters for parameters that are exactly zero)."""
+    theta = np.asarray(theta, dtype=np.float32)
+    mean = np.float32(np.abs(theta).astype(np.float64).sum() / theta.size)
+    return np.where(theta == 0, np.abs(mean), np.abs(theta)).astype(np.float32)
+
+
+def member_theta(theta, eps, sigma, sign, scale=None):
     """theta +/- float32(sigma)*eps in float32 (src/algorithm/nets.py:113,
-    src/algorithm/nic_nes/nic_nes_worker.py:151)."""
+    src/algorithm/nic_nes/nic_nes_worker.py:151); with a safe-mutation scale the noise is multiplied by it first (:104-111)."""
     noise = np.float32(sigma) * eps.astype(np.float32)
+    if scale is not None:
+        noise = noise * scale.astype(np.float32)
     return (theta + noise) if sign > 0 else (theta - noise), noise
 
 

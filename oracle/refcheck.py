@@ -111,6 +111,30 @@ def check_shaped_fitness(seed=0):
     return True
 
 
+def check_proportional(ref, seed=3):
+    """SM-PROPORTIONAL scale of oracle/noise.py against the reference's PolicyNet.evolve (algorithm/nets.py:101-119): the same
+    torch normal draw goes through both.  Non-zero parameters: bit-exact; exactly-zero parameters are scaled by mean|theta|,
+    where torch's float32 mean and this build's float64-accumulated mean may differ in the last bit (checked to 1e-6)."""
+    from algorithm.nets import Mutation
+    opt = ref.ModelOptions(vocab_size=199, input_encoding_size=64, rnn_size=64, fc_feat_size=128, safe_mutations='SM-PROPORTIONAL')
+    torch.manual_seed(seed)
+    model = ref.FCModel(options=opt)
+    assert model.mutations == Mutation.SAFE_PROPORTIONAL
+    theta = model.parameter_vector().numpy().copy()
+    torch.manual_seed(seed + 1)
+    raw = torch.empty(theta.size).normal_(mean=0.0, std=0.25).numpy().copy()       # what evolve draws first
+    torch.manual_seed(seed + 1)
+    got = model.evolve(0.25)
+    scale = noise.proportional_scale(theta)
+    want = raw * scale
+    nzm = theta != 0
+    assert nzm.sum() > 0 and (~nzm).sum() > 0
+    assert np.array_equal(got[nzm], want[nzm])
+    assert np.allclose(got[~nzm], want[~nzm], rtol=1e-6, atol=0)
+    assert np.array_equal(model.parameter_vector().numpy()[nzm], (theta + want)[nzm])
+    return True
+
+
 def main():
     if not _refimport.available():
         print('reference not present; nothing checked'); return 1
@@ -125,8 +149,8 @@ def main():
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)
     assert fc_caption.Dims(9487, 128, 128, 2048).num_params() == 2865808
     assert fc_caption.Dims(9487, 512, 512, 2048).num_params() == 13400848
-    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness()
-    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses OK' % n)
+    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref)
+    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL OK' % n)
     return 0
 
 

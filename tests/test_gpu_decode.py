@@ -299,6 +299,73 @@ def test_es_generation_against_oracle():
     ctx.close()
 
 
+def _prop_case():
+    V, E, R, Fd, B = 299, 64, 128, 128, 6
+    dims = fc_caption.Dims(V, E, R, Fd)
+    G = noise.granularity(E, R, Fd)
+    play, D, D_pad = noise.padded_layout(dims.layout(), G)
+    return V, E, R, Fd, B, dims, G, play, D, D_pad
+
+
+def test_proportional_mutation_evolve_and_rollout_against_oracle(monkeypatch):
+    """SM-PROPORTIONAL (algorithm/nets.py:104-111, shipped in experiments/mscoco_es.json): noise = sigma*eps (.) |theta|, zeros of
+    theta (the untrained biases) scaled by mean|theta|.  nes_evolve and the HYBRID rollout against the oracle; then the same
+    with every row forced through the fallback (NES_DEBUG=64: k_exact_rows)."""
+    import nes_b200
+    V, E, R, Fd, B, dims, G, play, D, D_pad = _prop_case()
+    ctx = nes_b200.NesContext(dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd), seed=31, table_len=D_pad + 63 * G, n_parents=2, wave_members=4, rows=B)
+    thetas = [fc_caption.xavier_theta(dims, 60), fc_caption.xavier_theta(dims, 61) * np.float32(3.0)]
+    ctx.set_theta(thetas[0], 0); ctx.set_theta(thetas[1], 1)
+    ctx.set_mutation('SM-PROPORTIONAL')
+    scales = [noise.proportional_scale(t) for t in thetas]
+    assert (thetas[0] == 0).sum() > 100                      # biases are zero: the mean|theta| branch is exercised
+    offs = ctx.sample_offsets(4, 5).numpy()
+    sigma = 0.3                                               # proportional noise is relative: sigma ~ O(0.1) like the shipped 0.005..0.5 range
+    member, nz = ctx.evolve(int(offs[0]), sigma, 1.0, parent=1)
+    want_m, want_nz = noise.member_theta(thetas[1], noise.noise_row(31, offs[0], play, D), sigma, +1, scale=scales[1])
+    assert np.array_equal(nz.numpy(), want_nz) and np.array_equal(member.numpy(), want_m)
+    fc = noise.table_slice(14, 0, B * Fd).astype(np.float32).reshape(B, Fd)
+    parents = np.array([0, 1, 1, 0, 1], dtype=np.int32)
+    signs = np.array([1, -1, 1, 1, -1], dtype=np.float32)
+    for dbg in ('0', '64'):
+        monkeypatch.setenv('NES_DEBUG', dbg)
+        seq, lp = ctx.rollout(offs, signs, fc, sigma, parents=parents, precision=nes_b200.PREC_HYBRID)      # 5 members, waves of 4
+        for i in range(5):
+            th, _ = noise.member_theta(thetas[parents[i]], noise.noise_row(31, offs[i], play, D), sigma, int(signs[i]), scale=scales[parents[i]])
+            s_, l_ = fc_caption.decode_greedy(dims, th, fc)
+            assert np.array_equal(seq[i].numpy(), s_), (dbg, i, (seq[i].numpy() != s_).sum())
+            assert np.allclose(lp[i].numpy(), l_, rtol=1e-4, atol=1e-5)
+    monkeypatch.setenv('NES_DEBUG', '0')
+    with pytest.raises(nes_b200.NesError):
+        ctx.rollout(offs, signs, fc, sigma, parents=parents, precision=nes_b200.PREC_EXACT)             # scaled noise: HYBRID only
+    # the member that survives selection carries the scaled noise too, and its own scale is refreshed
+    ctx.evolve(int(offs[1]), sigma, 1.0, parent=1, dst_parent=0, want_member=False, want_noise=False)
+    new0, _ = noise.member_theta(thetas[1], noise.noise_row(31, offs[1], play, D), sigma, +1, scale=scales[1])
+    assert np.array_equal(ctx.get_theta(0).numpy(), new0)
+    m2, _ = ctx.evolve(int(offs[2]), sigma, 1.0, parent=0)
+    want2, _ = noise.member_theta(new0, noise.noise_row(31, offs[2], play, D), sigma, +1, scale=noise.proportional_scale(new0))
+    assert np.array_equal(m2.numpy(), want2)
+    ctx.set_mutation('')
+    m3, _ = ctx.evolve(int(offs[2]), sigma, 1.0, parent=0)
+    assert np.array_equal(m3.numpy(), noise.member_theta(new0, noise.noise_row(31, offs[2], play, D), sigma, +1)[0])
+    ctx.close()
+
+
+def test_forced_fallback_of_the_hybrid_projection_matches_golden(golden, golden_mod, monkeypatch):
+    """NES_DEBUG=64 declares every candidate list overflowed: all units take the masked split-fp16 fallback and must still
+    reproduce the reference goldens (the path that runs when a list really overflows)"""
+    monkeypatch.setenv('NES_DEBUG', '64')
+    c = golden_mod.CASES['g1']
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    ctx = _ctx_for(c, golden_mod, L)
+    ctx.set_theta(theta)
+    offs2, signs = _members(offs)
+    seq, lp = ctx.rollout(offs2, signs, fc, c['sigma'], precision=2)
+    assert np.array_equal(seq.numpy(), golden['g1_seq'].reshape(-1, c['B'], 16).astype(np.int64))
+    assert np.allclose(lp.numpy(), golden['g1_logprobs'].reshape(-1, c['B'], 16), rtol=1e-4, atol=1e-5)
+    ctx.close()
+
+
 def test_rollout_rejects_bad_arguments():
     import nes_b200
     mo = dict(vocab_size=63, input_encoding_size=64, rnn_size=64, fc_feat_size=64)

@@ -165,3 +165,26 @@ def test_flat_context_generic_parameter_vector():
     ref = nes_math.gradient_estimate(fit, np.stack(rows))
     assert np.max(np.abs(g - ref)) <= 1e-5 * np.max(np.abs(ref))
     ctx.close()
+
+
+def test_gradient_with_proportional_scale():
+    """K7 under SM-PROPORTIONAL: g = sum_i w_i (sigma eps_i (.) s) / (2F) (nic_nes_master.py:178-182 on the scaled noise vectors
+    of algorithm/nets.py:104-111) -- the common scale is applied to the sum, within float32 round-off of the reference order"""
+    import nes_b200
+    from oracle import nes_math, noise
+    D = 5000
+    ctx = nes_b200.NesContext(counts=[D], seed=11, table_len=1 << 20)
+    theta = (np.random.RandomState(0).randn(D) * 0.05).astype(np.float32)
+    theta[::7] = 0.0
+    ctx.set_theta(theta)
+    ctx.set_mutation('SM-PROPORTIONAL')
+    F = 37
+    offs = ctx.sample_offsets(2, F).numpy()
+    fit = np.random.RandomState(1).randn(F, 2)
+    scale = noise.proportional_scale(theta)
+    play, D_, D_pad = noise.padded_layout([('t0', (D,), 0, D)], 64)
+    nz = np.stack([noise.member_theta(theta, noise.noise_row(11, o, play, D), 0.1, +1, scale=scale)[1] for o in offs])
+    want = nes_math.gradient_estimate(fit, nz)
+    got = nes_b200.NESMaster(ctx).gradient_estimate(fit, offs, 0.1)
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-9)
+    ctx.close()
