@@ -65,7 +65,12 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(',')])
+            self.rows.append((time.time(), [x.strip() for x in line.split(',')]))
+
+    def window(self, t0, t1):
+        """keep the samples taken inside the timed region (the sampler is started before the warm-up because nvidia-smi
+        needs up to a second to produce its first line on an 8-GPU box)"""
+        self.t0, self.t1 = t0, t1
 
     def stop(self):
         if not self.proc:
@@ -77,7 +82,11 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], None, set()
-        for r in self.rows:
+        t0, t1 = getattr(self, 't0', None), getattr(self, 't1', None)
+        rows = [r for t, r in self.rows if t0 is None or (t0 <= t <= t1 + 0.1)]
+        if not rows:                                   # region shorter than the sampling period: the samples nearest to it
+            rows = [r for _, r in self.rows[-3:]]
+        for r in rows:
             try:
                 sm.append(float(r[1])); mx = float(r[2])
                 for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), r[5:9]):
@@ -169,6 +178,9 @@ def main():
     import nes_b200
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    early_sampler = ClockSampler(local) if rank == 0 else None      # started now: nvidia-smi takes a while to print its first line
+    if early_sampler:
+        early_sampler.start()
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group('nccl', device_id=dev)
@@ -231,6 +243,7 @@ def main():
         select_and_materialise(fit, offs, pars)
 
     def timed(fn, steps, warmup, sample_clocks=False, profile=False):
+        sampler = early_sampler if sample_clocks else None
         for _ in range(warmup):
             fn()
         if world > 1:
@@ -238,16 +251,16 @@ def main():
         torch.cuda.synchronize()
         if profile:
             ctx.profile(True)          # per-kernel CUDA-event pairs cover the timed steps only
-        sampler = ClockSampler(local) if sample_clocks else None
-        if sampler:
-            sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = ctx.gpu_launches
+        w0 = time.time()
         e0.record()
         for _ in range(steps):
             fn()
         e1.record()
         torch.cuda.synchronize()
+        if sampler:
+            sampler.window(w0, time.time())
         if world > 1:
             dist.barrier()
         ms = e0.elapsed_time(e1)
