@@ -41,6 +41,7 @@ def parse():
     ap.add_argument('--table-log2', type=int, default=28)
     ap.add_argument('--cpu-seconds', type=float, default=15.0)
     ap.add_argument('--no-extras', action='store_true')
+    ap.add_argument('--sections', action='store_true', help='experiment: CUDA-event time of the phases of a step (sample / rollout / fitness+gather / selection)')
     ap.add_argument('--debug-same-offset', action='store_true', help='experiment only: every member reads the same noise row (eps L2-resident)')
     return ap.parse_args()
 
@@ -209,16 +210,27 @@ def main():
     def select_and_materialise(fit_all, offs, pars):
         state['base'] = nes_b200.es_select_and_materialise(ctx, fit_all, offs, pars, mu, el, state['base'], a.sigma)
 
+    sections = []
+
+    def mark():
+        if a.sections:
+            e = torch.cuda.Event(enable_timing=True); e.record(); sections.append(e)
+
     def step_resident():
         it = state['it']; state['it'] += 1
+        mark()
         offs, pars = sample_generation(it)
+        mark()
         ctx.rollout(offs[lo:lo + P], ones, fc_dev, a.sigma, parents=pars[lo:lo + P] + state['base'], precision=prec, out_device=dev)
+        mark()
         fit = ctx.logprob_fitness(P, rows, device=dev)
         if world > 1:
             out = torch.empty(Pg, dtype=torch.float64, device=dev)
             dist.all_gather_into_tensor(out, fit)
             fit = out
+        mark()
         select_and_materialise(fit, offs, pars)
+        mark()
 
     seq_host = torch.empty((P, rows, T), dtype=torch.int64).pin_memory()
     lp_host = torch.empty((P, rows, T), dtype=torch.float32).pin_memory()
@@ -270,8 +282,21 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item(), ctx.gpu_launches - l0, clocks
 
-    ms, launches, clocks = timed(step_resident, a.steps, a.warmup, sample_clocks=True, profile=True)
+    # pass 1: the timed region (no per-kernel events in the stream) -> value; pass 2: the same K steps again with a CUDA-event pair
+    # around every launch (nes_profile_*) -> per-kernel averages of the roofline object
+    ms, launches, clocks = timed(step_resident, a.steps, a.warmup, sample_clocks=True, profile=False)
+    ms_prof, _, _ = timed(step_resident, a.steps, 0, profile=True)
     prof = ctx.profile_read()
+    if a.sections and rank == 0:
+        n = 5
+        tail = sections[-n * a.steps:]
+        names = ['sample', 'rollout', 'fitness+gather', 'select+materialise']
+        acc = [0.0] * 4
+        for k in range(a.steps):
+            for j in range(4):
+                acc[j] += tail[k * n + j].elapsed_time(tail[k * n + j + 1])
+        between = sum(tail[k * n + 4].elapsed_time(tail[(k + 1) * n]) for k in range(a.steps - 1)) / max(1, a.steps - 1)
+        sys.stderr.write('sections ms/step: %s  between-steps %.2f\n' % ({nm: round(v / a.steps, 2) for nm, v in zip(names, acc)}, between))
     hstats = ctx.hybrid_stats()
     ctx.profile(False)
     ms_e2e, _, _ = timed(step_e2e, a.steps, max(1, a.warmup - 2))
@@ -292,7 +317,8 @@ def main():
             peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
         except Exception:
             pass
-        out['roofline'] = rooflines(prof, a, min(P, 1024), rows, ms, peaks)
+        out['roofline'] = rooflines(prof, a, min(P, 1024), rows, ms_prof, peaks)
+        out['roofline']['measured_in'] = 'a second pass of the same %d steps with per-launch CUDA-event pairs: %.2f ms/step (timed pass: %.2f)' % (a.steps, ms_prof / a.steps, ms / a.steps)
         out['hybrid_stats'] = hstats
         if not a.no_extras and world == 1:
             out['extras'] = extras(ctx, nes_b200, torch, dev, peaks)
