@@ -77,7 +77,9 @@ __global__ void __launch_bounds__(128) k_row_margin(const MarginParams p) {
         const float smax = p.scale_max ? p.scale_max[par] : 1.f;            // |eps_j (.) s|_2 <= max(s) |eps_j|_2
         const float wsum = 2.f * (p.theta_rowmax[par] + fabsf(p.sigma) * p.eps_rowmax[0] * smax);
         // 2^-11 relative rounding of both operands, +10 % for the fp32 accumulation of K <= 4096 terms, x2 (two logits compared)
-        p.margin[grow] = 2.f * 1.1f * 4.8828125e-4f * sqrtf(s) * 1.0001f * (wsum + 1e-4f) + 1e-30f;
+        // ... plus an absolute floor for the fp16 subnormal range (|32 h_k| or |256 w_jk| below 6e-5 round with an absolute, not a
+        // relative, error of 2^-25: at most sqrt(R) 2^-30 |w_j|_2 per logit, far below 1e-7)
+        p.margin[grow] = 2.f * 1.1f * 4.8828125e-4f * sqrtf(s) * 1.0001f * (wsum + 1e-4f) + 1e-7f;
     }
 }
 
