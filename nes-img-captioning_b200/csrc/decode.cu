@@ -77,6 +77,8 @@ struct DecodeWorkspace {
     __half *wl_hi[2] = {nullptr, nullptr}, *wl_lo[2] = {nullptr, nullptr}; float* wl_bias = nullptr;
     __half* wv16 = nullptr; float* wv_bias = nullptr;
     __half *wi_hi = nullptr, *wi_lo = nullptr; float* wi_bias = nullptr;      // img_embed, only with a safe-mutation scale (lazy)
+    bool dense_ln = false;                                                    // LayerNorm cell: dense PLAIN pre-activation GEMMs
+    __half *wn_hi[2] = {nullptr, nullptr}, *wn_lo[2] = {nullptr, nullptr}; float* wn_bias[2] = {nullptr, nullptr}; float* ln_par = nullptr;
     float* margin = nullptr; int32_t* pre_tok = nullptr; float* pre_lp = nullptr; uint8_t* unit_flag = nullptr;   // HYBRID
     unsigned long long* stats = nullptr;
     uint8_t* unfinished = nullptr; int32_t* unf_count = nullptr;
@@ -215,65 +217,53 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
 struct LnParams {
     const float *pre_i, *pre_h; float* c_state; __half *h_hi, *h_lo; float* h_trace;
     int rows, rows_pad, R; int64_t n_members;
-    const int64_t* off; const float* sign; const int32_t* parent; const float* theta32; const __half* table; int64_t D;
-    int affine; int64_t ln_start[6], ln_pstart[6];     // i2h_ln.w, i2h_ln.b, h2h_ln.w, h2h_ln.b, c_ln.w, c_ln.b
-    float sigma;
+    const float* ln_par;       // nullable (no affine): member LayerNorm parameters [n_members][4*5R + 2R]:
+                               // i2h_ln.w, i2h_ln.b, h2h_ln.w, h2h_ln.b [5R each], c_ln.w, c_ln.b [R each] (k_materialise_bias)
 };
-__device__ __forceinline__ float block_sum_128(float v, float* sh) {
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
-    __syncthreads();
-    return sh[0] + sh[1] + sh[2] + sh[3];
-}
-__device__ __forceinline__ float member_param(const LnParams& p, int which, int par, int64_t off, float sgn, int j, float dflt) {
-    if (!p.affine) return dflt;
-    const float t = p.theta32[(int64_t)par * p.D + p.ln_start[which] + j];
-    const float nz = __fmul_rn(p.sigma, __half2float(p.table[off + p.ln_pstart[which] + j]));
-    return sgn > 0.f ? __fadd_rn(t, nz) : __fsub_rn(t, nz);
-}
+__device__ __forceinline__ float warp_sum_f(float v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
 // LayerNorm variant of the cell (captioning/nets.py:102-104,126-127): LN over 5R of each addend, LN over R of c'.
+// One warp per (member, row); the normalised gate sums of the row live in shared memory.
 __global__ void __launch_bounds__(128) k_ln_gates(const LnParams p) {
-    __shared__ float sh[4];
-    extern __shared__ float s_sum[];                     // [5R] normalised sums, then [R] c'
-    const int64_t wid = blockIdx.x;
+    extern __shared__ float s_all[];                     // [4 warps][5R + R]
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + wq;
+    if (wid >= p.n_members * p.rows) return;
     const int64_t member = wid / p.rows;
     const int r = (int)(wid % p.rows);
     const int64_t grow = member * p.rows_pad + r;
     const int R = p.R, N = 5 * p.R;
-    const float sgn = p.sign[member];
-    const int64_t off = p.off[member];
-    const int par = p.parent ? p.parent[member] : 0;
+    float* s_sum = s_all + wq * (N + R);
+    float* s_c = s_sum + N;
+    const float* par = p.ln_par ? p.ln_par + member * (int64_t)(4 * N + 2 * R) : nullptr;
     const float* src[2] = {p.pre_i + grow * N, p.pre_h + grow * N};
-    for (int j = threadIdx.x; j < N; j += 128) s_sum[j] = 0.f;
     for (int a = 0; a < 2; ++a) {
         float s = 0.f;
-        for (int j = threadIdx.x; j < N; j += 128) s += src[a][j];
-        const float mean = block_sum_128(s, sh) / (float)N;
+        for (int j = lane; j < N; j += 32) s += src[a][j];
+        const float mean = warp_sum_f(s) / (float)N;
         float v = 0.f;
-        for (int j = threadIdx.x; j < N; j += 128) { const float d = src[a][j] - mean; v += d * d; }
-        const float rstd = 1.0f / sqrtf(block_sum_128(v, sh) / (float)N + 1e-5f);
-        for (int j = threadIdx.x; j < N; j += 128) {
-            const float w = member_param(p, 2 * a, par, off, sgn, j, 1.f), b = member_param(p, 2 * a + 1, par, off, sgn, j, 0.f);
-            s_sum[j] += (src[a][j] - mean) * rstd * w + b;
+        for (int j = lane; j < N; j += 32) { const float d = src[a][j] - mean; v += d * d; }
+        const float rstd = 1.0f / sqrtf(warp_sum_f(v) / (float)N + 1e-5f);
+        for (int j = lane; j < N; j += 32) {
+            const float w = par ? par[(2 * a) * N + j] : 1.f, b = par ? par[(2 * a + 1) * N + j] : 0.f;
+            const float y = (src[a][j] - mean) * rstd * w + b;
+            s_sum[j] = a == 0 ? y : s_sum[j] + y;
         }
     }
-    __syncthreads();
+    __syncwarp();
     float* cs = p.c_state + grow * R;
-    float* s_c = s_sum + N;
     float cs_sum = 0.f;
-    for (int j = threadIdx.x; j < R; j += 128) {
+    for (int j = lane; j < R; j += 32) {
         const float ig = sigmoid_f(s_sum[j]), fg = sigmoid_f(s_sum[R + j]);
         const float cand = fmaxf(s_sum[3 * R + j], s_sum[4 * R + j]);
         const float cn = __fadd_rn(__fmul_rn(fg, cs[j]), __fmul_rn(ig, cand));
         s_c[j] = cn; cs[j] = cn; cs_sum += cn;
     }
-    const float mean = block_sum_128(cs_sum, sh) / (float)R;
+    const float mean = warp_sum_f(cs_sum) / (float)R;
     float v = 0.f;
-    for (int j = threadIdx.x; j < R; j += 128) { const float d = s_c[j] - mean; v += d * d; }
-    const float rstd = 1.0f / sqrtf(block_sum_128(v, sh) / (float)R + 1e-5f);
-    for (int j = threadIdx.x; j < R; j += 128) {
-        const float w = member_param(p, 4, par, off, sgn, j, 1.f), b = member_param(p, 5, par, off, sgn, j, 0.f);
+    for (int j = lane; j < R; j += 32) { const float d = s_c[j] - mean; v += d * d; }
+    const float rstd = 1.0f / sqrtf(warp_sum_f(v) / (float)R + 1e-5f);
+    for (int j = lane; j < R; j += 32) {
+        const float w = par ? par[4 * N + j] : 1.f, b = par ? par[4 * N + R + j] : 0.f;
         const float og = sigmoid_f(s_sum[2 * R + j]);
         const float hn = og * tanhf((s_c[j] - mean) * rstd * w + b);
         __half a, l; split_half_dev(hn, kActScale, a, l);
@@ -328,6 +318,13 @@ int decode_create(Ctx* c, int wave_members, int rows) {
             if (dmalloc(&ws->wl_hi[0], rows_l * ws->E) || dmalloc(&ws->wl_lo[0], rows_l * ws->E) ||
                 dmalloc(&ws->wl_hi[1], rows_l * ws->R) || dmalloc(&ws->wl_lo[1], rows_l * ws->R) || dmalloc(&ws->wl_bias, rows_l)) return 1;
         }
+        ws->dense_ln = !factored && d.layer_n;
+        if (ws->dense_ln) {
+            const int64_t rows_n = (int64_t)ws->W * 5 * ws->R;
+            if (dmalloc(&ws->wn_hi[0], rows_n * ws->E) || dmalloc(&ws->wn_lo[0], rows_n * ws->E) || dmalloc(&ws->wn_hi[1], rows_n * ws->R) ||
+                dmalloc(&ws->wn_lo[1], rows_n * ws->R) || dmalloc(&ws->wn_bias[0], rows_n) || dmalloc(&ws->wn_bias[1], rows_n)) return 1;
+        }
+        if (d.layer_n && d.layer_n_affine && dmalloc(&ws->ln_par, (int64_t)ws->W * 22 * ws->R)) return 1;
         if (ws->dense_logit) {
             if (dmalloc(&ws->wv16, (int64_t)ws->W * ws->V1 * ws->R) || dmalloc(&ws->wv_bias, (int64_t)ws->W * ws->V1) ||
                 dmalloc(&ws->heads, 2 * WR) || dmalloc(&ws->entries, 2 * WR * kCandCap)) return 1;
@@ -352,7 +349,7 @@ void decode_destroy(Ctx* c) {
     DecodeWorkspace* ws = c->ws;
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
-                    ws->pre_i, ws->pre_h, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
+                    ws->pre_i, ws->pre_h, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
                     ws->d_lp, ws->d_forced};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
@@ -416,7 +413,7 @@ static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
 }
 
 // member weights of one wave, materialised once per rollout (dense.cuh)
-static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit, bool img) {
+static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit, bool img, bool ln, bool ln_par) {
     DecodeWorkspace* ws = c->ws;
     const Layout& L = c->lay;
     ProfScope prof(c, PROF_MATERIALISE);
@@ -428,8 +425,9 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         k_materialise<<<dim3((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(nm < 32768 ? nm : 32768)), 256, 0, c->stream>>>(q);
         c->launches++;
     };
-    auto matb = [&](int b0, int b1, int out_cols, int mode, int src_n, float* out) {
+    auto matb = [&](int b0, int b1, int out_cols, int mode, int src_n, float* out, int64_t out_stride = 0, int64_t out_off = 0) {
         MatBiasParams q{};
+        q.out_stride = out_stride; q.out_off = out_off;
         q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32;
         q.b_start[0] = L.t[b0].start; q.b_pstart[0] = L.t[b0].pstart; q.nb = 1;
         if (b1 >= 0) { q.b_start[1] = L.t[b1].start; q.b_pstart[1] = L.t[b1].pstart; q.nb = 2; }
@@ -442,6 +440,19 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         mat(T_I2H_W, ws->E, rows_l, 1, 5 * ws->R, ws->wl_hi[0], ws->wl_lo[0]);
         mat(T_H2H_W, ws->R, rows_l, 1, 5 * ws->R, ws->wl_hi[1], ws->wl_lo[1]);
         matb(T_I2H_B, T_H2H_B, rows_l, 1, 5 * ws->R, ws->wl_bias);
+    }
+    if (ln) {
+        const int N5 = 5 * ws->R;
+        mat(T_I2H_W, ws->E, N5, 0, N5, ws->wn_hi[0], ws->wn_lo[0]);
+        mat(T_H2H_W, ws->R, N5, 0, N5, ws->wn_hi[1], ws->wn_lo[1]);
+        matb(T_I2H_B, -1, N5, 0, N5, ws->wn_bias[0]);
+        matb(T_H2H_B, -1, N5, 0, N5, ws->wn_bias[1]);
+    }
+    if (ln_par) {        // member LayerNorm parameters (theta +- sigma eps of the six LN vectors) for k_ln_gates
+        const int N5 = 5 * ws->R;
+        const int64_t st = 22ll * ws->R;
+        for (int i = 0; i < 4; ++i) matb(T_I2H_LN_W + i, -1, N5, 0, N5, ws->ln_par, st, (int64_t)i * N5);
+        for (int i = 0; i < 2; ++i) matb(T_C_LN_W + i, -1, ws->R, 0, ws->R, ws->ln_par, st, 4ll * N5 + (int64_t)i * ws->R);
     }
     if (img) {
         mat(T_IMG_W, ws->Fd, ws->E, 0, ws->E, ws->wi_hi, ws->wi_lo);
@@ -507,6 +518,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     const bool hybrid = precision == NES_PREC_HYBRID && !logit_trace && ws->dense_logit;
     if (precision == NES_PREC_HYBRID) precision = NES_PREC_EXACT;
     const bool dense_lstm = ws->dense_lstm && precision == NES_PREC_EXACT;     // split-fp16 LSTM on materialised member weights
+    const bool dense_ln = ws->dense_ln && precision == NES_PREC_EXACT;         // LayerNorm cell on dense pre-activation GEMMs
     const bool scaled = c->scale32 != nullptr;                                 // safe-mutation scale: every member weight is materialised
     if (scaled) {
         NES_CHECK(hybrid && dense_lstm && !c->dims.layer_n, "a safe-mutation scale needs HYBRID precision on the dense kernels (no layer_n, no logit trace, R <= 512)");
@@ -559,7 +571,8 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
         NES_CUDA(cudaMemsetAsync(ws->h_hi[0], 0, sizeof(__half) * WR * R, c->stream));
         NES_CUDA(cudaMemsetAsync(ws->h_lo[0], 0, sizeof(__half) * WR * R, c->stream));
         NES_CUDA(cudaMemsetAsync(ws->unf_count, 0, sizeof(int32_t) * (T + 2) * ws->W, c->stream));
-        if ((dense_lstm || hybrid) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid, scaled)) return 1;
+        const bool ln_par = c->dims.layer_n && c->dims.layer_n_affine;
+        if ((dense_lstm || hybrid || dense_ln || ln_par) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid, scaled, dense_ln, ln_par)) return 1;
 
         GemmParams base{};
         base.rows = rows; base.rows_pad = rows_pad; base.m_tiles = m_tiles;
@@ -614,7 +627,21 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 p.c_state = ws->c_state; p.out_hi = ws->h_hi[hb ^ 1]; p.out_lo = ws->h_lo[hb ^ 1]; p.h_trace = ht;
                 if (launch_gemm_prec<EPI_LSTM>(c, p, nm, precision)) return 1;
             } else {
-                for (int s = 0; s < 2; ++s) {
+                for (int s = 0; s < 2 && dense_ln; ++s) {
+                    DenseParams p{};
+                    const int bk = DenseCfg<DEN_PLAIN>::BK;
+                    const int K = s == 0 ? E : R;
+                    const __half* ah = s == 0 ? ws->x_hi : ws->h_hi[hb]; const __half* al = s == 0 ? ws->x_lo : ws->h_lo[hb];
+                    if (get_map(ws, &p.a_hi[0], ah, a_rows_w, K, 128, bk) || get_map(ws, &p.a_lo[0], al, a_rows_w, K, 128, bk) ||
+                        get_map(ws, &p.b_hi[0], ws->wn_hi[s], (int64_t)ws->W * 5 * R, K, 256, bk) || get_map(ws, &p.b_lo[0], ws->wn_lo[s], (int64_t)ws->W * 5 * R, K, 256, bk)) return 1;
+                    p.a_hi[1] = p.a_hi[0]; p.a_lo[1] = p.a_lo[0]; p.b_hi[1] = p.b_hi[0]; p.b_lo[1] = p.b_lo[0];
+                    p.K[0] = K; p.K[1] = 0; p.nseg = 1; p.a_shared = 0;
+                    p.rows = rows; p.rows_pad = rows_pad; p.m_tiles = m_tiles; p.n_tiles = (5 * R + 255) / 256; p.N = 5 * R;
+                    p.b_rows = 5 * R; p.bias = ws->wn_bias[s]; p.bias_stride = 5 * R;
+                    p.out_f32 = s == 0 ? ws->pre_i : ws->pre_h; p.ld_out = 5 * R;
+                    if (launch_dense<DEN_PLAIN>(c, p, nm)) return 1;
+                }
+                for (int s = 0; s < 2 && !dense_ln; ++s) {
                     GemmParams p = base;
                     p.nseg = 1; p.N = 5 * R; p.chunk_stride = 0; p.n_tiles = (5 * R + 127) / 128;
                     if (s == 0) { if (fill_seg(c, p, 0, ws->x_hi, ws->x_lo, a_rows_w, E, 0, T_I2H_W, T_I2H_B, 128, precision)) return 1; }
@@ -625,11 +652,11 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 LnParams q{};
                 q.pre_i = ws->pre_i; q.pre_h = ws->pre_h; q.c_state = ws->c_state; q.h_hi = ws->h_hi[hb ^ 1]; q.h_lo = ws->h_lo[hb ^ 1];
                 q.h_trace = ht; q.rows = rows; q.rows_pad = rows_pad; q.R = R; q.n_members = nm;
-                q.off = base.off; q.sign = base.sign; q.parent = base.parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D;
-                q.affine = c->dims.layer_n_affine; q.sigma = sigma;
-                if (q.affine) for (int i = 0; i < 6; ++i) { q.ln_start[i] = L.t[T_I2H_LN_W + i].start; q.ln_pstart[i] = L.t[T_I2H_LN_W + i].pstart; }
+                q.ln_par = c->dims.layer_n_affine ? ws->ln_par : nullptr;
+                const size_t ln_smem = sizeof(float) * 4 * 6 * R;
+                if (ln_smem > 48 * 1024) { static size_t set_to = 0; if (set_to < ln_smem) { NES_CUDA(cudaFuncSetAttribute(k_ln_gates, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ln_smem)); set_to = ln_smem; } }
                 ProfScope prof(c, PROF_FINALIZE);
-                k_ln_gates<<<(unsigned)(nm * rows), 128, sizeof(float) * 6 * R, c->stream>>>(q);
+                k_ln_gates<<<(unsigned)((nm * rows + 3) / 4), 128, ln_smem, c->stream>>>(q);
                 c->launches++;
                 NES_CUDA(cudaGetLastError());
             }

@@ -37,7 +37,8 @@ struct alignas(64) DenseParams {
     int32_t b_rows;                         // weight rows per member in the materialised buffer
     int32_t a_shared;                       // 1: every member reads activation rows [0, rows_pad) (shared fc batch, PLAIN)
     const float* bias; int32_t bias_stride; // [W][bias_stride] member bias in accumulator-column order
-    float* c_state; __half* out_hi; __half* out_lo; float* h_trace;       // LSTM
+    float* c_state; __half* out_hi; __half* out_lo; float* h_trace;       // LSTM (PLAIN: out_hi / out_lo and / or out_f32)
+    float* out_f32; int32_t ld_out;                                       // PLAIN: [member*rows_pad + row, ld_out] float32 (nullable)
     CandHead* heads; CandEntry* entries; const float* margin;            // LOGITC
     int32_t debug;
 };
@@ -300,12 +301,20 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                         tc::tmem_ld32(trow + c0, y);
                         tc::tmem_ld_wait();
                         if (row_ok && n_base + c0 < p.N) {
+#pragma unroll
+                            for (int uu = 0; uu < 32; ++uu) y[uu] = fmaf(y[uu], sW, s_bias[c0 + uu]);
+                            if (p.out_f32) {
+#pragma unroll
+                                for (int v4 = 0; v4 < 8; ++v4)
+                                    if (n_base + c0 + v4 * 4 < p.N)
+                                        *reinterpret_cast<float4*>(p.out_f32 + grow * p.ld_out + n_base + c0 + v4 * 4) = *reinterpret_cast<float4*>(&y[v4 * 4]);
+                            }
                             __half hh[32], hl[32];
 #pragma unroll
-                            for (int uu = 0; uu < 32; ++uu) split_half_dev(fmaf(y[uu], sW, s_bias[c0 + uu]), kActScale, hh[uu], hl[uu]);
+                            for (int uu = 0; uu < 32; ++uu) split_half_dev(y[uu], kActScale, hh[uu], hl[uu]);
 #pragma unroll
                             for (int v4 = 0; v4 < 4; ++v4) {
-                                if (n_base + c0 + v4 * 8 < p.N) {
+                                if (p.out_hi && n_base + c0 + v4 * 8 < p.N) {
                                     *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + n_base + c0 + v4 * 8) = *reinterpret_cast<uint4*>(&hh[v4 * 8]);
                                     *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + n_base + c0 + v4 * 8) = *reinterpret_cast<uint4*>(&hl[v4 * 8]);
                                 }
@@ -449,6 +458,7 @@ struct MatBiasParams {
     int64_t b_start[2], b_pstart[2]; int32_t nb;
     int32_t out_cols, mode, R, src_n;
     float sigma; float* out; int64_t n_members;
+    int64_t out_stride, out_off;            // out[member * out_stride + out_off + col] (out_stride 0: = out_cols)
 };
 __global__ void __launch_bounds__(256) k_materialise_bias(const MatBiasParams p) {
     const int64_t total = p.n_members * p.out_cols;
@@ -472,7 +482,7 @@ __global__ void __launch_bounds__(256) k_materialise_bias(const MatBiasParams p)
                 b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
             }
         }
-        p.out[i] = b;
+        p.out[member * (p.out_stride ? p.out_stride : (int64_t)p.out_cols) + p.out_off + col] = b;
     }
 }
 
