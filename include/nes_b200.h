@@ -90,6 +90,12 @@ int nes_get_theta(nes_ctx* ctx, int parent, void* out, int as_f64);
 int nes_evolve(nes_ctx* ctx, int parent, int64_t offset, float sign, float sigma,
                float* member_out, float* noise_out, int dst_parent);
 
+/* n evolve calls with dst_parent set, as one launch (the survivors of a NIC-ES generation, nic_es_master.py:155-167 +
+ * nic_es_worker.py:188): parent dst[i] = theta(src[i]) + sigmas[i] * eps(offsets[i]) (sigma 0 copies an elite).  HOST arrays;
+ * the destination slots must be distinct and disjoint from the source slots. */
+int nes_evolve_batch(nes_ctx* ctx, int n, const int32_t* src_parent, const int64_t* offsets, const float* sigmas,
+                     const int32_t* dst_parent);
+
 /* Safe mutations (PolicyNet.evolve, algorithm/nets.py:104-111).  NES_MUT_PROPORTIONAL (the reference's "SM-PROPORTIONAL", shipped in
  * experiments/mscoco_es.json): noise = sigma * eps (.) |theta_p|, exact zeros of theta_p replaced by mean|theta_p|.  Applies to
  * nes_evolve and nes_rollout (HYBRID precision, no layer_n); K7 scales its result by the scale of parent 0. */

@@ -131,6 +131,13 @@ class NesContext:
                                        _lib.ptr(member), _lib.ptr(noise), int(dst_parent)))
         return member, noise
 
+    def evolve_batch(self, src_parents, offsets, sigmas, dst_parents):
+        """dst_parents[i] <- theta(src_parents[i]) + sigmas[i] * eps(offsets[i]) for all i in one launch (host arrays)"""
+        src = np.ascontiguousarray(src_parents, dtype=np.int32); dst = np.ascontiguousarray(dst_parents, dtype=np.int32)
+        off = np.ascontiguousarray(offsets, dtype=np.int64); sg = np.ascontiguousarray(sigmas, dtype=np.float32)
+        assert len(src) == len(dst) == len(off) == len(sg)
+        _lib.check(self.lib.nes_evolve_batch(self._h, len(src), _lib.ptr(src), _lib.ptr(off), _lib.ptr(sg), _lib.ptr(dst)))
+
     # ---- population rollout
     def rollout(self, offsets, signs, fc, sigma, parents=None, precision=PREC_EXACT, shared_batch=None,
                 out_device='cpu', forced_tokens=None, trace=False):

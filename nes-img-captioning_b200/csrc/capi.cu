@@ -241,6 +241,12 @@ int nes_evolve(nes_ctx* ctx, int parent, int64_t offset, float sign, float sigma
     return rc;
 }
 
+int nes_evolve_batch(nes_ctx* ctx, int n, const int32_t* src_parent, const int64_t* offsets, const float* sigmas, const int32_t* dst_parent) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    NES_CHECK(n == 0 || (src_parent && offsets && sigmas && dst_parent), "null argument");
+    return launch_evolve_batch(c, n, src_parent, offsets, sigmas, dst_parent);
+}
+
 int nes_rollout_trace(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,
                       const float* fc, int rows, int shared_batch, float sigma, int precision, const int64_t* forced,
                       int64_t* seq, float* logprobs, float* h_trace, float* logit_trace) {

@@ -137,6 +137,8 @@ int launch_prop_scale(Ctx* c, int parent);        // theta32 -> scale32 (SM-PROP
 int set_mutation(Ctx* c, int kind);
 int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64);
 int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, float* d_member, float* d_noise, int dst_parent);
+int launch_evolve_batch(Ctx* c, int n, const int32_t* src, const int64_t* offsets, const float* sigmas, const int32_t* dst);   // host arrays
+int launch_bound_norms_batch(Ctx* c, const int32_t* parents, int n);   // theta_rowmax of several parents in one launch (decode.cu)
 
 // master.cu
 int launch_ranks(Ctx* c, const double* d_x, int64_t n, int64_t* d_ranks);

@@ -750,6 +750,17 @@ int launch_bound_norms(Ctx* c, int parent) {
     return 0;
 }
 
+int launch_bound_norms_batch(Ctx* c, const int32_t* parents, int n) {
+    // c->d_ranks still holds the packed (src | dst << 32) items of launch_evolve_batch; the dst slots are the parents to refresh
+    if (!c->is_fc || n == 0) return 0;
+    const int R = c->dims.rnn_size, V1 = c->dims.vocab_size + 1;
+    for (int i = 0; i < n; ++i) NES_CUDA(cudaMemsetAsync(c->d_theta_rowmax + parents[i], 0, sizeof(float), c->stream));
+    k_rowmax_theta_batch<<<dim3(37, n), 256, 0, c->stream>>>(c->theta32, c->lay.D, c->lay.t[T_LOGIT_W].start, V1, R, c->d_ranks, c->d_theta_rowmax);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int decode_hybrid_stats(Ctx* c, int64_t* out4, int reset) {
     DecodeWorkspace* ws = c->ws;
     NES_CHECK(ws != nullptr, "context has no decode workspace");

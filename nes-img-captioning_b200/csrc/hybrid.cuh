@@ -32,6 +32,20 @@ __global__ void __launch_bounds__(256) k_rowmax_theta(const float* __restrict__ 
     }
     if (lane == 0) atomic_max_pos(out, sqrtf(best) * 1.0001f);
 }
+// the same for several parents at once: blockIdx.y = item, parents[item] = parent slot
+__global__ void __launch_bounds__(256) k_rowmax_theta_batch(const float* __restrict__ theta32, int64_t D, int64_t w_start, int64_t n_rows, int R,
+                                                            const int64_t* __restrict__ srcdst, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int par = (int)(srcdst[blockIdx.y] >> 32);
+    const float* w = theta32 + (int64_t)par * D + w_start;
+    float best = 0.f;
+    for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < n_rows; r += (int64_t)gridDim.x * 8) {
+        float s = 0.f;
+        for (int k = lane; k < R; k += 32) { const float v = w[r * R + k]; s = fmaf(v, v, s); }
+        best = fmaxf(best, warp_sum(s));
+    }
+    if (lane == 0) atomic_max_pos(out + par, sqrtf(best) * 1.0001f);
+}
 // max over the rows of the [L/R, R] view of the fp16 noise table of the row 2-norm
 __global__ void __launch_bounds__(256) k_rowmax_eps(const __half* __restrict__ table, int64_t n_rows, int R, float* __restrict__ out) {
     const int lane = threadIdx.x & 31;

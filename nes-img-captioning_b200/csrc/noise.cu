@@ -169,6 +169,65 @@ int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, f
     return 0;
 }
 
+// ---- NIC-ES survivor materialisation, all survivors in one launch: item i becomes parent dst[i] = theta32[src[i]] + sigma_i * eps(off_i)
+// (nic_es_worker.py:188 without the .pth file); writes the float64 master, the float32 copy and the padded split-fp16 shadow in one pass
+__global__ void __launch_bounds__(256) k_evolve_batch(float* theta32, double* __restrict__ theta64, __half* __restrict__ th_hi,
+                                                      __half* __restrict__ th_lo, const __half* __restrict__ table, const Layout* __restrict__ lay,
+                                                      const int64_t* __restrict__ offs, const float* __restrict__ sigmas, const int64_t* __restrict__ srcdst,
+                                                      const float* __restrict__ scale) {
+    const int k = blockIdx.y;
+    const int item = blockIdx.z;
+    const TensorDesc t = lay->t[k];
+    const int64_t D = lay->D, D_pad = lay->D_pad;
+    const int64_t pend = (k + 1 < lay->n) ? lay->t[k + 1].pstart : D_pad;
+    const int64_t span = pend - t.pstart;
+    const int src = (int)(srcdst[item] & 0xffffffffll), dst = (int)(srcdst[item] >> 32);
+    const float sigma = sigmas[item];
+    const float* th = theta32 + (int64_t)src * D;
+    const __half* row = table + offs[item];
+    const float* sc = scale ? scale + (int64_t)src * D : nullptr;
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < span; j += (int64_t)gridDim.x * blockDim.x) {
+        __half a = __float2half_rn(0.f), b = a;
+        if (j < t.count) {
+            const float m = __fadd_rn(th[t.start + j], mut_noise(sigma, __half2float(row[t.pstart + j]), sc, t.start + j));
+            theta32[(int64_t)dst * D + t.start + j] = m;       // dst slots are disjoint from src slots (checked by the host)
+            theta64[(int64_t)dst * D + t.start + j] = (double)m;
+            split_half(m, kThetaScale, a, b);
+        }
+        th_hi[(int64_t)dst * D_pad + t.pstart + j] = a;
+        th_lo[(int64_t)dst * D_pad + t.pstart + j] = b;
+    }
+}
+int launch_evolve_batch(Ctx* c, int n, const int32_t* src, const int64_t* offsets, const float* sigmas, const int32_t* dst) {
+    NES_CHECK(n >= 0 && n <= 65535, "too many items");
+    if (n == 0) return 0;
+    std::vector<uint8_t> is_src(c->n_parents, 0), is_dst(c->n_parents, 0);
+    std::vector<int64_t> packed(n);
+    for (int i = 0; i < n; ++i) {
+        NES_CHECK(src[i] >= 0 && src[i] < c->n_parents && dst[i] >= 0 && dst[i] < c->n_parents, "parent index out of range");
+        NES_CHECK(offsets[i] >= 0 && offsets[i] + c->lay.D_pad <= c->table_len && offsets[i] % c->lay.G == 0, "offset outside the noise table or not slot aligned");
+        NES_CHECK(!is_dst[dst[i]], "a destination slot appears twice");
+        is_src[src[i]] = 1; is_dst[dst[i]] = 1;
+        packed[i] = (int64_t)src[i] | ((int64_t)dst[i] << 32);
+    }
+    for (int p = 0; p < c->n_parents; ++p) NES_CHECK(!(is_src[p] && is_dst[p]), "destination slots must be disjoint from source slots");
+    if (ensure_small(c, n)) return 1;
+    NES_CUDA(cudaMemcpyAsync(c->d_offsets, offsets, sizeof(int64_t) * n, cudaMemcpyDefault, c->stream));
+    NES_CUDA(cudaMemcpyAsync(c->d_weights, sigmas, sizeof(float) * n, cudaMemcpyDefault, c->stream));
+    NES_CUDA(cudaMemcpyAsync(c->d_ranks, packed.data(), sizeof(int64_t) * n, cudaMemcpyDefault, c->stream));
+    NES_CUDA(cudaStreamSynchronize(c->stream));            // `packed` is a stack-lifetime host buffer
+    dim3 grid(148, c->lay.n, n);
+    k_evolve_batch<<<grid, 256, 0, c->stream>>>(c->theta32, c->theta64, c->theta_hi, c->theta_lo, c->table, c->d_lay, c->d_offsets, c->d_weights, c->d_ranks, c->scale32);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    for (int i = 0; i < n; ++i) {
+        c->theta_is_f32[dst[i]] = 1;
+        if (c->mut_kind == NES_MUT_PROPORTIONAL && launch_prop_scale(c, dst[i])) return 1;
+    }
+    if (c->is_fc) return launch_bound_norms_batch(c, dst, n);
+    return 0;
+}
+
 // ---- SM-PROPORTIONAL scale (algorithm/nets.py:107-111): params = theta.clone(); params[params == 0] = mean(|theta|); noise *= |params|
 // The mean is accumulated in float64 in a fixed order and rounded to float32 (torch's float32 pairwise mean agrees to ~1 ulp;
 // it only enters through parameters that are exactly zero, i.e. untrained biases).

@@ -185,10 +185,11 @@ def es_select_and_materialise(ctx: NesContext, fitness_all, offs, pars, mu, num_
     keep, _ = ESMaster.selection(fitness_all, mu, num_elites)
     sel = torch.stack([keep, offs[keep], pars[keep].to(torch.int64)], 1).cpu().numpy()      # the master's one sync point
     nxt = mu - base
-    for e in range(num_elites):
-        ctx.evolve(0, 0.0, 1.0, parent=base + e, dst_parent=nxt + e, want_member=False, want_noise=False)
-    for j, (_, off, par) in enumerate(sel):
-        ctx.evolve(int(off), sigma, 1.0, parent=base + int(par), dst_parent=nxt + num_elites + j, want_member=False, want_noise=False)
+    n = num_elites + len(sel)
+    src = np.concatenate([base + np.arange(num_elites), base + sel[:, 2]]).astype(np.int32)
+    off = np.concatenate([np.zeros(num_elites, dtype=np.int64), sel[:, 1]]).astype(np.int64)
+    sg = np.concatenate([np.zeros(num_elites), np.full(len(sel), sigma)]).astype(np.float32)      # sigma 0: the elite itself
+    ctx.evolve_batch(src, off, sg, nxt + np.arange(n))
     return nxt
 
 

@@ -299,6 +299,46 @@ def test_es_generation_against_oracle():
     ctx.close()
 
 
+def test_evolve_batch_equals_sequential_evolves():
+    """nes_evolve_batch == the same evolve(dst_parent=) calls one by one: float32 and float64 weights bit-identical, and a HYBRID
+    rollout from the batch-built parents (split-fp16 shadow, hybrid row bound) gives the tokens of the one-by-one parents"""
+    import nes_b200
+    V, E, R, Fd, B, sigma = 199, 64, 64, 128, 6, 0.05
+    dims = fc_caption.Dims(V, E, R, Fd)
+    G = noise.granularity(E, R, Fd)
+    play, D, D_pad = noise.padded_layout(dims.layout(), G)
+    L = D_pad + 255 * G
+    fc = torch.from_numpy(noise.table_slice(6, 0, B * Fd).astype(np.float32).reshape(B, Fd)).cuda()
+    src = np.array([0, 1, 2, 2, 0], dtype=np.int32); dst = np.array([3, 4, 5, 6, 7], dtype=np.int32)
+    offs = np.array([0, 0, 17 * G, 200 * G, 255 * G], dtype=np.int64)
+    sg = np.array([0.0, 0.0, sigma, sigma, 0.5 * sigma], dtype=np.float32)
+    out = []
+    for batch in (False, True):
+        ctx = nes_b200.NesContext(dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd), seed=21, table_len=L, n_parents=8, wave_members=8, rows=B)
+        for k in range(3):
+            ctx.set_theta(fc_caption.xavier_theta(dims, 90 + k), k)
+        if batch:
+            ctx.evolve_batch(src, offs, sg, dst)
+        else:
+            for i in range(5):
+                ctx.evolve(int(offs[i]), float(sg[i]), 1.0, parent=int(src[i]), dst_parent=int(dst[i]), want_member=False, want_noise=False)
+        th32 = [ctx.get_theta(int(d)).numpy() for d in dst]
+        th64 = [ctx.get_theta(int(d), dtype=torch.float64).numpy() for d in dst]
+        o = ctx.sample_offsets(3, 10, device=True)
+        par = torch.tensor([3, 4, 5, 6, 7, 3, 4, 5, 6, 7], dtype=torch.int32, device='cuda')
+        seq, lp = ctx.rollout(o, torch.ones(10, device='cuda'), fc, sigma, parents=par, precision=nes_b200.PREC_HYBRID)
+        out.append((th32, th64, seq.cpu().numpy(), lp.cpu().numpy()))
+        if batch:
+            with pytest.raises(Exception):
+                ctx.evolve_batch([0, 3], [0, 0], [0.0, 0.0], [3, 4])          # slot 3 both read and written
+            with pytest.raises(Exception):
+                ctx.evolve_batch([0, 1], [0, 0], [0.0, 0.0], [4, 4])          # destination twice
+        ctx.close()
+    for a, b in zip(out[0][0] + out[0][1], out[1][0] + out[1][1]):
+        assert np.array_equal(a, b)
+    assert np.array_equal(out[0][2], out[1][2]) and np.array_equal(out[0][3], out[1][3])
+
+
 def _prop_case():
     V, E, R, Fd, B = 299, 64, 128, 128, 6
     dims = fc_caption.Dims(V, E, R, Fd)
