@@ -111,6 +111,14 @@ int nes_set_mutation(nes_ctx* ctx, int kind);
 int nes_rollout(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs,
                 const int32_t* parents, const float* fc, int rows, int shared_batch, float sigma,
                 int precision, int64_t* seq, float* logprobs);
+/* FCModel._sample(fc_feats, greedy=False) (src/captioning/nets.py:210-231) for every member: the token of (member, row, step t) is
+ * numpy's legacy choice(p = exp(logprobs) / |.|_1) evaluated at the caller's uniform uniforms[member][row][t-1] in [0, 1) (float64,
+ * host or device) -- the reference draws them from the unseeded global generator, one per row per step.  logprobs holds the
+ * log-probability of the sampled token.  Runs on the accurate (split-fp16) logits; finished-row bookkeeping as nes_rollout. */
+int nes_rollout_sample(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,
+                       const float* fc, int rows, int shared_batch, float sigma, const double* uniforms, int64_t* seq,
+                       float* logprobs);
+
 /* test hook: teacher-forced decode of ONE wave with per-step dumps.  forced_tokens int64 [n_members, rows, T]
  * (NULL = greedy feedback); h_trace float32 [T+1, n_members, rows, R]; logit_trace float32 [T, n_members, rows, V+1]
  * (either may be NULL). */

@@ -140,8 +140,10 @@ class NesContext:
 
     # ---- population rollout
     def rollout(self, offsets, signs, fc, sigma, parents=None, precision=PREC_EXACT, shared_batch=None,
-                out_device='cpu', forced_tokens=None, trace=False):
+                out_device='cpu', forced_tokens=None, trace=False, uniforms=None):
         """offsets int64 [P], signs float32 [P], fc float32 [rows, Fd] (shared) or [P, rows, Fd].
+        uniforms float64 [P, rows, T] in [0, 1): sampled decode (FCModel._sample(greedy=False), captioning/nets.py:210-231),
+        token = numpy's legacy choice evaluated at that draw; None = greedy.
         Returns seq int64 [P, rows, T], logprobs float32 [P, rows, T] (+ h_trace, logit_trace when trace)."""
         offsets = torch.as_tensor(offsets, dtype=torch.int64).contiguous()
         signs = torch.as_tensor(signs, dtype=torch.float32).contiguous()
@@ -161,6 +163,15 @@ class NesContext:
         T, R, V1 = self.dims['seq_length'], self.dims['rnn_size'], self.dims['vocab_size'] + 1
         seq = torch.empty((P, rows, T), dtype=torch.int64, device=out_device)
         lp = torch.empty((P, rows, T), dtype=torch.float32, device=out_device)
+        if uniforms is not None:
+            assert not trace and forced_tokens is None
+            if isinstance(uniforms, np.ndarray):
+                uniforms = torch.from_numpy(np.ascontiguousarray(uniforms, dtype=np.float64))
+            uniforms = uniforms.to(torch.float64).contiguous()
+            assert tuple(uniforms.shape) == (P, rows, T)
+            _lib.check(self.lib.nes_rollout_sample(self._h, P, _lib.ptr(offsets), _lib.ptr(signs), _lib.ptr(parents), _lib.ptr(fc),
+                                                   int(rows), int(bool(shared_batch)), float(sigma), _lib.ptr(uniforms), _lib.ptr(seq), _lib.ptr(lp)))
+            return seq, lp
         if not trace and forced_tokens is None:
             _lib.check(self.lib.nes_rollout(self._h, P, _lib.ptr(offsets), _lib.ptr(signs), _lib.ptr(parents), _lib.ptr(fc),
                                             int(rows), int(bool(shared_batch)), float(sigma), int(precision),

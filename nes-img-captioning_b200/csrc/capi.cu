@@ -269,6 +269,19 @@ int nes_rollout_trace(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, c
     return 0;
 }
 
+int nes_rollout_sample(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents, const float* fc,
+                       int rows, int shared_batch, float sigma, const double* uniforms, int64_t* seq, float* logprobs) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    NES_CHECK(c->is_fc && c->ws, "not an fc_caption context with a decode workspace");
+    NES_CHECK(n_members >= 0, "negative member count");
+    if (n_members == 0) return 0;
+    NES_CHECK(offsets && signs && fc && uniforms, "null argument");
+    NES_CHECK(c->scale32 == nullptr, "sampled decode with a safe-mutation scale is not built");
+    if (decode_rollout(c, n_members, offsets, signs, parents, fc, rows, shared_batch, sigma, NES_PREC_EXACT, nullptr, seq, logprobs, nullptr, nullptr, uniforms)) return 1;
+    if (finish_output(c, seq) || finish_output(c, logprobs)) return 1;
+    return 0;
+}
+
 int nes_rollout(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents, const float* fc,
                 int rows, int shared_batch, float sigma, int precision, int64_t* seq, float* logprobs) {
     return nes_rollout_trace(ctx, n_members, offsets, signs, parents, fc, rows, shared_batch, sigma, precision, nullptr, seq, logprobs,

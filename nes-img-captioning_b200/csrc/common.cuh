@@ -151,7 +151,7 @@ int decode_create(Ctx* c, int wave_members, int rows);
 void decode_destroy(Ctx* c);
 int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,
                    const float* fc, int rows, int shared_batch, float sigma, int precision,
-                   const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace);
+                   const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace, const double* uniforms = nullptr);
 int decode_logprob_fitness(Ctx* c, int64_t n_members, int rows, double* out);
 int decode_hybrid_stats(Ctx* c, int64_t* out4, int reset);
 const int64_t* decode_resident_seq(Ctx* c, int64_t n_members, int rows, int* T);

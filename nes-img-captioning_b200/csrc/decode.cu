@@ -87,6 +87,8 @@ struct DecodeWorkspace {
     int64_t* d_off = nullptr; float* d_sign = nullptr; int32_t* d_parent = nullptr;
     int64_t* d_seq = nullptr; float* d_lp = nullptr; int64_t out_cap = 0;
     int64_t* d_forced = nullptr; int64_t forced_cap = 0;
+    double* d_uniforms = nullptr; int64_t uniforms_cap = 0;      // sampled decode: the caller's draws [n_members, rows, T]
+    float* samp_logits = nullptr;                                // sampled decode: all logits of one step of one wave [W * rows_cap, V1]
     std::map<std::tuple<const void*, int64_t, int64_t, int, int, int, int64_t>, CUtensorMap> maps;
     bool attrs_set = false;
 };
@@ -211,6 +213,64 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
         }
         *reinterpret_cast<uint4*>(p.x_hi + grow * p.E + e) = *reinterpret_cast<uint4*>(hh);
         *reinterpret_cast<uint4*>(p.x_lo + grow * p.E + e) = *reinterpret_cast<uint4*>(hl);
+    }
+}
+
+struct SampleParams {
+    const float* logits;                         // [n_members * rows, V1] of this step
+    const LogitPartial* partials; int n_tiles;
+    const double* u;                             // [n_members, rows, T]
+    int rows, rows_pad, T, t, V1; int64_t n_members;
+    int32_t* tok; float* lp;                     // [n_members * rows_pad]
+};
+// Sampled decode (captioning/nets.py:210-231): one CTA per (member, row).  prob = exp(log_softmax(logits)) in float32, divided by its
+// 1-norm, accumulated into a float64 cdf that is normalised by its last entry; the token is the first index whose cdf exceeds the
+// caller's uniform draw (numpy's legacy choice: cdf.searchsorted(u, side='right')).
+__global__ void __launch_bounds__(256) k_sample(const SampleParams p) {
+    extern __shared__ float s_p[];               // V1 probabilities
+    __shared__ float s_f[8];
+    __shared__ double s_d[8];
+    __shared__ int s_i[8];
+    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
+    const int64_t member = blockIdx.x / p.rows;
+    const int r = (int)(blockIdx.x % p.rows);
+    const int64_t grow = member * p.rows_pad + r;
+    const float* lg = p.logits + (member * p.rows + r) * (int64_t)p.V1;
+    float mx = -INFINITY;
+    for (int j = 0; j < p.n_tiles; ++j) mx = fmaxf(mx, p.partials[grow * p.n_tiles + j].mx);
+    float se = 0.f;
+    for (int j = 0; j < p.n_tiles; ++j) { const LogitPartial q = p.partials[grow * p.n_tiles + j]; se += q.sum * expf(q.mx - mx); }
+    const float lse = logf(se);
+    float acc = 0.f;
+    for (int j = tid; j < p.V1; j += 256) { const float e = expf(__fsub_rn(__fsub_rn(lg[j], mx), lse)); s_p[j] = e; acc += e; }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) s_f[wq] = acc;
+    __syncthreads();
+    float norm1 = 0.f;
+    for (int w = 0; w < 8; ++w) norm1 += s_f[w];
+    // float64 cdf over contiguous chunks
+    const int C = (p.V1 + 255) / 256, j0 = tid * C, j1 = min(p.V1, j0 + C);
+    double loc = 0.0;
+    for (int j = j0; j < j1; ++j) { const float nj = __fdiv_rn(s_p[j], norm1); s_p[j] = nj; loc += (double)nj; }
+    double inc = loc;                            // inclusive scan over the 256 chunk sums
+    for (int o = 1; o < 32; o <<= 1) { const double v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    if (lane == 31) s_d[wq] = inc;
+    __syncthreads();
+    double base = 0.0, total = 0.0;
+    for (int w = 0; w < 8; ++w) { if (w < wq) base += s_d[w]; total += s_d[w]; }
+    const double u = p.u[(member * p.rows + r) * p.T + (p.t - 1)];
+    double run = base + (inc - loc);
+    int first = 0x7fffffff;
+    for (int j = j0; j < j1; ++j) { run += (double)s_p[j]; if (first == 0x7fffffff && run / total > u) first = j; }
+    for (int o = 16; o > 0; o >>= 1) first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+    if (lane == 0) s_i[wq] = first;
+    __syncthreads();
+    if (tid == 0) {
+        int idx = 0x7fffffff;
+        for (int w = 0; w < 8; ++w) idx = min(idx, s_i[w]);
+        if (idx >= p.V1) idx = p.V1 - 1;         // u within rounding of 1: the last entry, as searchsorted would clamp through choice's own check
+        p.tok[grow] = idx;
+        p.lp[grow] = __fsub_rn(__fsub_rn(lg[idx], mx), lse);
     }
 }
 
@@ -350,7 +410,7 @@ void decode_destroy(Ctx* c) {
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
                     ws->pre_i, ws->pre_h, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
-                    ws->d_lp, ws->d_forced};
+                    ws->d_lp, ws->d_forced, ws->d_uniforms, ws->samp_logits};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
     c->ws = nullptr;
@@ -506,7 +566,7 @@ static int ensure_call_buffers(Ctx* c, int64_t n_members, int rows, bool forced)
 
 int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,
                    const float* fc, int rows, int shared_batch, float sigma, int precision,
-                   const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace) {
+                   const int64_t* forced, int64_t* seq, float* logp, float* h_trace, float* logit_trace, const double* uniforms) {
     DecodeWorkspace* ws = c->ws;
     NES_CHECK(ws != nullptr, "context has no decode workspace");
     NES_CHECK(rows >= 1 && rows <= ws->rows_cap, "rows exceeds the workspace capacity given to nes_ctx_create_fc");
@@ -515,7 +575,9 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     const bool tracing = h_trace || logit_trace || forced;
     // HYBRID = split-fp16 everywhere except the vocabulary projection, which runs on fp16 operands with an exact
     // fp32 re-evaluation of the arg-max candidates (hybrid.cuh); a logit trace needs the accurate logits themselves
-    const bool hybrid = precision == NES_PREC_HYBRID && !logit_trace && ws->dense_logit;
+    const bool sampling = uniforms != nullptr;      // tokens are drawn from the full distribution: every accurate logit is needed
+    NES_CHECK(!sampling || !logit_trace, "sampled decode and a logit trace exclude each other");
+    const bool hybrid = precision == NES_PREC_HYBRID && !logit_trace && !sampling && ws->dense_logit;
     if (precision == NES_PREC_HYBRID) precision = NES_PREC_EXACT;
     const bool dense_lstm = ws->dense_lstm && precision == NES_PREC_EXACT;     // split-fp16 LSTM on materialised member weights
     const bool dense_ln = ws->dense_ln && precision == NES_PREC_EXACT;         // LayerNorm cell on dense pre-activation GEMMs
@@ -538,6 +600,17 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     if (parents) NES_CUDA(cudaMemcpyAsync(ws->d_parent, parents, sizeof(int32_t) * n_members, cudaMemcpyDefault, c->stream));
     else NES_CUDA(cudaMemsetAsync(ws->d_parent, 0, sizeof(int32_t) * n_members, c->stream));
     if (forced) NES_CUDA(cudaMemcpyAsync(ws->d_forced, forced, sizeof(int64_t) * n_members * rows * T, cudaMemcpyDefault, c->stream));
+    if (sampling) {
+        NES_CHECK(precision != NES_PREC_FAST, "sampled decode runs on the accurate logits (EXACT / HYBRID)");
+        const int64_t un = n_members * rows * T;
+        if (un > ws->uniforms_cap) {
+            if (ws->d_uniforms) cudaFree(ws->d_uniforms);
+            if (dmalloc(&ws->d_uniforms, un)) return 1;
+            ws->uniforms_cap = un;
+        }
+        NES_CUDA(cudaMemcpyAsync(ws->d_uniforms, uniforms, sizeof(double) * un, cudaMemcpyDefault, c->stream));
+        if (!ws->samp_logits && dmalloc(&ws->samp_logits, (int64_t)ws->W * ws->rows_cap * V1)) return 1;
+    }
     NES_CUDA(cudaMemsetAsync(ws->d_seq, 0, sizeof(int64_t) * n_members * rows * T, c->stream));
     NES_CUDA(cudaMemsetAsync(ws->d_lp, 0, sizeof(float) * n_members * rows * T, c->stream));
 
@@ -708,7 +781,18 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 if (!(hybrid && scaled)) {
                 if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128, precision)) return 1;
                 p.logit_trace = logit_trace ? logit_trace + (int64_t)(t - 1) * n_members * rows * V1 : nullptr; p.ld_trace = V1;
+                if (sampling) p.logit_trace = ws->samp_logits;
                 if (launch_gemm_prec<EPI_LOGIT>(c, p, nm, precision)) return 1;
+                }
+                if (sampling) {
+                    SampleParams sp{};
+                    sp.logits = ws->samp_logits; sp.partials = ws->partials; sp.n_tiles = 2; sp.u = ws->d_uniforms + m0 * rows * T;
+                    sp.rows = rows; sp.rows_pad = rows_pad; sp.T = T; sp.t = t; sp.V1 = V1; sp.n_members = nm; sp.tok = ws->pre_tok; sp.lp = ws->pre_lp;
+                    const size_t smem = sizeof(float) * V1;
+                    if (smem > 48 * 1024) { static size_t set_to = 0; if (set_to < smem) { NES_CUDA(cudaFuncSetAttribute(k_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set_to = smem; } }
+                    ProfScope prof(c, PROF_FINALIZE);
+                    k_sample<<<(unsigned)(nm * rows), 256, smem, c->stream>>>(sp); c->launches++;
+                    NES_CUDA(cudaGetLastError());
                 }
             }
             if (t < T || t >= 1) {
@@ -720,6 +804,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;
                 f.forced = forced ? ws->d_forced + m0 * rows * T : nullptr;
                 f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0;
+                if (sampling && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = 1; }
                 if (hybrid && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = scaled ? 1 : 0; }
                 ProfScope prof(c, PROF_FINALIZE);
                 k_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(f);

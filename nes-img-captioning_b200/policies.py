@@ -142,7 +142,7 @@ class CaptPolicy(Policy):
         seq, _ = self.rollout_tokens(data)
         return float(self.scorer(seq.numpy(), data))
 
-    def rollout_population_fitness(self, offsets, signs, data, sigma, parents=None):
+    def rollout_population_fitness(self, offsets, signs, data, sigma, parents=None, uniforms=None):
         """CIDEr-D * 100 of every member (float64 numpy [P]): decode on the device, score the resident tokens on the device
         against data['gts'] (list over images of int arrays [n_refs, T]); only P x rows float64 scores travel to the host."""
         assert isinstance(self.scorer, CiderD), 'needs scorer = nes_b200.CiderD(ctx, ...)'
@@ -151,11 +151,42 @@ class CaptPolicy(Policy):
         P = len(offsets)
         self.ctx.rollout(offsets, signs, fc, sigma, parents=parents, precision=self.precision, out_device=self.ctx.dev)
         kind = self.options.fitness or 'greedy'
+        if kind in ('sample', 'self_critical', 'sc_loss'):
+            return self._sampled_population_fitness(kind, offsets, signs, data, sigma, parents, uniforms)
         if kind == 'greedy':
             return self.scorer.fitness(P, fc.shape[0])                      # float(cider * 100), policies.py:125
-        assert kind in self.ctx.FITNESS_KINDS and kind != 'sc_loss', 'fitness %r needs sampled decode, which is not on the B200 path' % kind
+        assert kind in self.ctx.FITNESS_KINDS, 'unknown fitness %r' % kind
         self.scorer.scores(None, P, fc.shape[0], device=self.ctx.dev)       # per-caption CIDEr-D stays on the device
         return self.ctx.shaped_fitness(kind, P, fc.shape[0]).numpy()        # crit(logprobs, seq, ciders), policies.py:119-123
+
+    def _sampled_population_fitness(self, kind, offsets, signs, data, sigma, parents, uniforms):
+        """the fitnesses that decode by sampling (Fitness.SAMPLE / SELF_CRITICAL / SC_LOSS, captioning/policies.py:27-30,113-125,164-186).
+        Replicated rows draw independently, so all batch_size * seq_per_img rows are decoded; the self-critical baseline is the
+        greedy caption of the image (unique rows, repeated).  uniforms float64 [P, rows, T] or None = torch.rand on the device
+        (the reference: the unseeded global numpy generator)."""
+        ctx, spi = self.ctx, self.seq_per_img
+        fc_all = torch.from_numpy(np.ascontiguousarray(np.asarray(data['fc_feats'], dtype=np.float32)))
+        P, rows, T = len(offsets), fc_all.shape[0], ctx.dims['seq_length']
+        sc = kind in ('self_critical', 'sc_loss')
+        # compute_ciders scores 2 * batch captions in self-critical mode, so every image is a corpus document 2 * seq_per_img times (:175-177)
+        self.scorer.set_refs(data['gts'], seq_per_img=(2 * spi if sc else spi), rows_per_img=1)
+        base = None
+        if sc:
+            fc_u = torch.from_numpy(np.ascontiguousarray(self._unique_rows(data['fc_feats'])))
+            ctx.rollout(offsets, signs, fc_u, sigma, parents=parents, precision=self.precision, out_device=ctx.dev)
+            base = self.scorer.scores(None, P, fc_u.shape[0], device=ctx.dev).repeat_interleave(spi, 1)
+        if uniforms is None:
+            uniforms = torch.rand((P, rows, T), dtype=torch.float64, device=ctx.dev)
+        ctx.rollout(offsets, signs, fc_all, sigma, parents=parents, out_device=ctx.dev, uniforms=uniforms)
+        self.scorer.rows_per_img = spi
+        scores = self.scorer.scores(None, P, rows, device=ctx.dev)
+        self.scorer.rows_per_img = 1
+        if sc:
+            scores = scores - base                                          # policies.py:183
+        if kind == 'sc_loss':
+            return ctx.shaped_fitness(kind, P, rows, scores=scores).numpy() # LogFitnessCriterion(sample_logprobs, gen_result, rewards)
+        s = scores.cpu().numpy()
+        return np.array([float(np.mean(s[m]) * 100) for m in range(P)], dtype=np.float64)
 
     def rollout_population(self, offsets, signs, data, sigma, parents=None, out_device='cpu'):
         """all members at once -> seq int64 [P, rows, T], logprobs float32 [P, rows, T] (unique rows)."""

@@ -129,3 +129,63 @@ def decode_greedy(dims, theta, fc_feats, trace=False):
         if trace:
             return seq.numpy(), lps.numpy(), tr
         return seq.numpy(), lps.numpy()
+
+
+def choice_from_probs(prob_row, u):
+    """what `np.random.choice(len(n_row), 1, p=n_row)` returns when the generator's next uniform is u
+    (src/captioning/nets.py:217-222 + numpy's legacy RandomState.choice: float64 cdf = p.cumsum(), cdf /= cdf[-1],
+    searchsorted(u, side='right')).  prob_row float32 = exp(log_softmax row).  -> (index, distance of u to the nearest
+    edge of the chosen cdf interval, a measure of how close the draw was to flipping)"""
+    row = np.asarray(prob_row, dtype=np.float32)
+    n_row = row / np.linalg.norm(row, ord=1)
+    cdf = n_row.astype(np.float64).cumsum()
+    cdf /= cdf[-1]
+    idx = int(cdf.searchsorted(u, side='right'))
+    lo = cdf[idx - 1] if idx > 0 else 0.0
+    return idx, min(u - lo, cdf[idx] - u)
+
+
+def decode_sample(dims, theta, fc_feats, uniforms, forced=None):
+    """FCModel._sample(fc, greedy=False) -- src/captioning/nets.py:183-245 -- with the uniforms the reference draws from the
+    global numpy generator made an explicit input: uniforms float64 [B, T], [b, t-1] = the draw of row b at step t
+    (the reference also draws B values at the image step t = 0 and throws the sampled tokens away, :197-198).
+    forced int64 [B, T] (optional): feed these tokens forward instead of the sampled ones (per-step comparison).
+    Returns seq int64 [B, T], seq_logprobs float32 [B, T], gap float64 [B, T] (see choice_from_probs; inf where no draw)."""
+    with torch.no_grad():
+        p = unflatten(dims, theta)
+        fc = torch.as_tensor(np.asarray(fc_feats, dtype=np.float32))
+        B, T, R = fc.shape[0], dims.seq_length, dims.rnn_size
+        h = torch.zeros(B, R)
+        c = torch.zeros(B, R)
+        seq = torch.zeros(B, T, dtype=torch.long)
+        lps = torch.zeros(B, T)
+        gap = np.full((B, T), np.inf)
+        unfinished = None
+        it = None
+        for t in range(T + 1):
+            if t == 0:
+                xt = F.linear(fc, p['img_embed.weight'], p['img_embed.bias'])
+            else:
+                if t == 1:
+                    it = torch.zeros(B, dtype=torch.long)
+                xt = F.embedding(it, p['embed.weight'])
+            h, c = lstm_core(dims, p, xt, h, c)
+            if t == 0:
+                continue
+            logprobs = F.log_softmax(F.linear(h, p['logit.weight'], p['logit.bias']), dim=1)
+            prob_prev = torch.exp(logprobs).numpy()
+            result = []
+            for b in range(B):
+                idx, g = choice_from_probs(prob_prev[b], float(uniforms[b, t - 1]))
+                result.append(idx); gap[b, t - 1] = g
+            it = torch.LongTensor(result)
+            lp = logprobs.gather(1, it.unsqueeze(1)).view(-1)
+            unfinished = (it > 0) if t == 1 else unfinished * (it > 0)
+            it = it * unfinished.type_as(it)
+            seq[:, t - 1] = it
+            lps[:, t - 1] = lp
+            if unfinished.sum() == 0:
+                break
+            if forced is not None:
+                it = torch.as_tensor(np.asarray(forced)[:, t - 1], dtype=torch.long)
+        return seq.numpy(), lps.numpy(), gap

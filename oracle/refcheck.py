@@ -41,6 +41,26 @@ def check_decode(ref, V, E, R, Fd, B, ln=False, affine=False, seed=0):
     return True
 
 
+def check_sample_decode(ref, V=199, E=64, R=64, Fd=128, B=7, seed=11):
+    """FCModel._sample(greedy=False) with the global numpy generator seeded == decode_sample fed the same generator's
+    uniforms (B draws per step starting with the image step, whose samples the reference discards)"""
+    opt = ref.ModelOptions(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd, layer_n=False, layer_n_affine=False)
+    torch.manual_seed(seed)
+    model = ref.FCModel(options=opt)
+    dims = fc_caption.Dims(V, E, R, Fd)
+    theta = model.parameter_vector().numpy().copy()
+    fc = torch.randn(B, Fd)
+    T = dims.seq_length
+    for s in range(3):
+        np.random.seed(100 + s)
+        seq_r, lp_r = model(fc, greedy=False)
+        draws = np.random.RandomState(100 + s).random_sample((T + 1, B))       # [t, b]; row 0 = the image step
+        seq_o, lp_o, gap = fc_caption.decode_sample(dims, theta, fc.numpy(), draws[1:].T.copy())
+        assert np.array_equal(seq_r.numpy(), seq_o), 'sampled seq differs'
+        assert np.array_equal(lp_r.numpy(), lp_o), 'sampled logprobs differ'
+    return True
+
+
 def check_master_math(ref, F=37, D=1000, seed=0):
     rs = np.random.RandomState(seed)
     m = object.__new__(ref.NESMaster)      # the math methods use no instance state
@@ -149,8 +169,8 @@ def main():
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)
     assert fc_caption.Dims(9487, 128, 128, 2048).num_params() == 2865808
     assert fc_caption.Dims(9487, 512, 512, 2048).num_params() == 13400848
-    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref)
-    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL OK' % n)
+    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref); check_sample_decode(ref)
+    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL, sampled decode OK' % n)
     return 0
 
 
