@@ -451,6 +451,17 @@ def extras(ctx, nes_b200, torch, dev, peaks):
     cpu_s = (time.perf_counter() - t0) / 3
     ex['cider_d'] = {'captions': n_m * 128, 'ms': ms_c, 'captions_per_s': n_m * 128 / (ms_c * 1e-3),
                      'cpu_port_captions_per_s_one_core': 128 / cpu_s, 'refs_per_image': 5}
+    # sampled decode (Fitness.SAMPLE / SELF_CRITICAL / SC_LOSS): the same 1000 members drawing their tokens from the full
+    # distribution (all accurate logits + k_sample) instead of the arg-max
+    u = torch.rand((n_m, 128, T), dtype=torch.float64, device=dev)
+    offs = ctx.sample_offsets(300, Fp, device=True).repeat_interleave(2)
+    ctx.rollout(offs, signs, fc, 0.01, out_device=dev, uniforms=u)
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(2):
+        ctx.rollout(offs, signs, fc, 0.01, out_device=dev, uniforms=u)
+    e1.record(); torch.cuda.synchronize()
+    ex['sampled_decode'] = {'rollouts': n_m, 'rows': 128, 'ms': e0.elapsed_time(e1) / 2, 'rollouts_per_s': n_m * 2 / (e0.elapsed_time(e1) * 1e-3)}
     return ex
 
 

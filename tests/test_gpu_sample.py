@@ -134,3 +134,29 @@ def test_sampling_fitnesses_through_capt_policy(kind):
     one = pol.rollout(None, data, None)
     assert np.isfinite(one)
     ctx.close()
+
+
+@pytest.mark.parametrize('name', ['g1', 'g2', 'g5'])
+def test_sampled_decode_against_reference_golden(name, golden_mod):
+    """the device sampler against what the REAL reference sampled with its numpy generator seeded (tests/golden/golden_sample_v1.npz)"""
+    import os
+    import nes_b200
+    import make_golden_sample as mgs
+    gs = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'golden_sample_v1.npz'))
+    c = golden_mod.CASES[name]
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    ln, aff = c.get('ln', False), c.get('affine', False)
+    ctx = nes_b200.NesContext(dict(vocab_size=c['V'], input_encoding_size=c['E'], rnn_size=c['R'], fc_feat_size=c['Fd'], layer_n=ln, layer_n_affine=aff),
+                              seed=golden_mod.TABLE_SEED, table_len=L, wave_members=4, rows=c['B'])
+    ctx.set_theta(theta)
+    eps = noise.noise_row(golden_mod.TABLE_SEED, offs[0], play, D)
+    diverged = 0
+    for k, seed in enumerate(mgs.SEEDS):
+        u = mgs.uniforms(seed, dims.seq_length, c['B'])
+        seq, lp = ctx.rollout(np.repeat(offs[:1], 2), np.array([1.0, -1.0], dtype=np.float32), fc, c['sigma'], uniforms=np.stack([u, u]))
+        for j, sign in enumerate((+1, -1)):
+            th, _ = noise.member_theta(theta, eps, c['sigma'], sign)
+            _, _, gap = fc_caption.decode_sample(dims, th, fc, u)
+            diverged += _compare_rows(seq[j].numpy(), lp[j].numpy(), gs[name + '_seq'][k, j].astype(np.int64), gs[name + '_logprobs'][k, j], gap)
+    assert diverged <= 1
+    ctx.close()

@@ -1,4 +1,5 @@
 """Oracle vs the golden vectors the REAL reference produced (CPU, no GPU)."""
+import os
 import numpy as np
 import pytest
 
@@ -74,3 +75,20 @@ def test_early_break_leaves_zeros():
     theta[s] = 5.0
     seq, lp = fc_caption.decode_greedy(dims, theta, np.ones((3, 8), dtype=np.float32))
     assert (seq == 0).all() and (lp[:, 1:] == 0).all() and (lp[:, 0] < 0).all()
+
+
+@pytest.mark.parametrize('name', ['g1', 'g2', 'g5'])
+def test_sampled_decode_matches_reference_golden(name, golden_mod):
+    """oracle decode_sample fed the uniforms of the seeded numpy generator == the reference's FCModel._sample(greedy=False)"""
+    import make_golden_sample as mgs
+    gs = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'golden_sample_v1.npz'))
+    c = golden_mod.CASES[name]
+    dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
+    eps = noise.noise_row(golden_mod.TABLE_SEED, offs[0], play, D)
+    for k, seed in enumerate(mgs.SEEDS):
+        u = mgs.uniforms(seed, dims.seq_length, c['B'])
+        for j, sign in enumerate((+1, -1)):
+            th, _ = noise.member_theta(theta, eps, c['sigma'], sign)
+            s, lp, _ = fc_caption.decode_sample(dims, th, fc, u)
+            assert np.array_equal(s, gs[name + '_seq'][k, j])
+            assert np.array_equal(lp, gs[name + '_logprobs'][k, j])
