@@ -139,6 +139,12 @@ int nes_compute_ranks(nes_ctx* ctx, const double* x, int64_t n, int64_t* ranks);
  * g = f32(sigma) * sum_i w_i eps_i / (2F) over table rows; weights NULL = the ctx weights of the last
  * nes_rank_weights.  g_out float32 [D] nullable (the gradient stays resident in the ctx). */
 int nes_gradient(nes_ctx* ctx, const int64_t* offsets, const float* weights, int64_t F, float sigma, float* g_out);
+
+/* K7 sharded over the parameter axis for one process per GPU: shard `shard` of `n_shards` sums ALL F rows for its contiguous slice
+ * of elements (same arithmetic as nes_gradient) and leaves zeros elsewhere, so an all-reduce(sum) of the n_shards vectors equals
+ * nes_gradient's result bit for bit on every rank (replaces the master-only np.dot of nic_nes_master.py:207-221). */
+int nes_gradient_shard(nes_ctx* ctx, const int64_t* offsets, const float* weights, int64_t F, float sigma, int shard, int n_shards,
+                       float* g_out);
 /* K8: G = -g + l2*theta; Optimizer.update (optimizers.py:15-22) with SGD (:44-47) or Adam (:78-83);
  * float64 state, float64 master theta, float32 + split-fp16 evaluation copies refreshed in the same pass.
  * grad NULL = the resident gradient.  ratio_out float64 (nullable) = |step| / |theta|. */

@@ -7,9 +7,9 @@ from .context import NesContext, PREC_EXACT, PREC_FAST, PREC_HYBRID, OPT_ADAM, O
 from .nets import FCModel, ModelOptions, Mutation, PolicyNet
 from .policies import CaptPolicy, Net, Policy, PolicyFactory, PolicyOptions, SuppDataset
 from .cider import CiderD
-from .master import (Adam, ESMaster, NESMaster, Optimizer, SGD, all_gather_fitness, es_generation, es_sample_generation,
+from .master import (Adam, ESMaster, NESMaster, Optimizer, SGD, all_gather_fitness, all_reduce_gradient, sharded_master_step, es_generation, es_sample_generation,
                      es_select_and_materialise, nes_iteration, shard_bounds)
 
 __all__ = ['NesContext', 'NesError', 'FCModel', 'ModelOptions', 'Mutation', 'PolicyNet', 'CaptPolicy', 'Net', 'Policy',
            'PolicyFactory', 'PolicyOptions', 'SuppDataset', 'Adam', 'SGD', 'Optimizer', 'NESMaster', 'nes_iteration',
-           'shard_bounds', 'all_gather_fitness', 'ESMaster', 'es_generation', 'es_sample_generation', 'es_select_and_materialise', 'CiderD', 'PREC_EXACT', 'PREC_FAST', 'PREC_HYBRID', 'OPT_ADAM', 'OPT_SGD', 'gemm_selftest']
+           'shard_bounds', 'all_gather_fitness', 'all_reduce_gradient', 'sharded_master_step', 'ESMaster', 'es_generation', 'es_sample_generation', 'es_select_and_materialise', 'CiderD', 'PREC_EXACT', 'PREC_FAST', 'PREC_HYBRID', 'OPT_ADAM', 'OPT_SGD', 'gemm_selftest']

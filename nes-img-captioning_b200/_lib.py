@@ -48,6 +48,7 @@ SIGNATURES = {
     'nes_rank_weights': (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     'nes_compute_ranks': (c_i32, [c_vp, c_vp, c_i64, c_vp]),
     'nes_gradient': (c_i32, [c_vp, c_vp, c_vp, c_i64, c_f32, c_vp]),
+    'nes_gradient_shard': (c_i32, [c_vp, c_vp, c_vp, c_i64, c_f32, c_i32, c_i32, c_vp]),
     'nes_opt_init': (c_i32, [c_vp, c_i32, c_f64, c_f64, c_f64, c_f64]),
     'nes_opt_set_stepsize': (c_i32, [c_vp, c_f64]),
     'nes_opt_update': (c_i32, [c_vp, c_vp, c_f64, ctypes.POINTER(c_f64)]),

@@ -213,24 +213,26 @@ class NesContext:
         _lib.check(self.lib.nes_compute_ranks(self._h, _lib.ptr(x), x.numel(), _lib.ptr(out)))
         return out
 
-    def rank_weights(self, fitness, want_centered=True):
+    def rank_weights(self, fitness, want_centered=True, want_weights=True):
         fit = fitness if torch.is_tensor(fitness) else torch.from_numpy(np.ascontiguousarray(fitness, dtype=np.float64))
         fit = fit.to(torch.float64).contiguous()
         F = fit.shape[0]
         assert fit.numel() == 2 * F
         cen = torch.empty((F, 2), dtype=torch.float64) if want_centered else None
-        w = torch.empty(F, dtype=torch.float32)
+        w = torch.empty(F, dtype=torch.float32) if want_weights else None      # None: the weights just stay on the device for K7
         _lib.check(self.lib.nes_rank_weights(self._h, _lib.ptr(fit), F, _lib.ptr(cen), _lib.ptr(w)))
         return cen, w
 
-    def gradient(self, offsets, weights, sigma, out_device='cpu', want=True):
+    def gradient(self, offsets, weights, sigma, out_device='cpu', want=True, shard=(0, 1)):
+        """K7.  weights None = the weights the last rank_weights call left on the device.  shard (r, n): only slice r of n of the
+        parameter axis is summed, the rest of the vector is zero (all-reduce over the n ranks gives the whole)."""
         offsets = torch.as_tensor(offsets, dtype=torch.int64).contiguous()
         F = offsets.numel()
         if weights is not None:
             weights = torch.as_tensor(weights, dtype=torch.float32).contiguous()
             assert weights.numel() == F
         g = torch.empty(self.D, dtype=torch.float32, device=out_device) if want else None
-        _lib.check(self.lib.nes_gradient(self._h, _lib.ptr(offsets), _lib.ptr(weights), F, float(sigma), _lib.ptr(g)))
+        _lib.check(self.lib.nes_gradient_shard(self._h, _lib.ptr(offsets), _lib.ptr(weights), F, float(sigma), int(shard[0]), int(shard[1]), _lib.ptr(g)))
         return g
 
     def opt_init(self, kind, stepsize, momentum_or_beta1=0.9, beta2=0.999, epsilon=1e-8):

@@ -344,6 +344,10 @@ int nes_rank_weights(nes_ctx* ctx, const double* fitness, int64_t F, double* cen
 }
 
 int nes_gradient(nes_ctx* ctx, const int64_t* offsets, const float* weights, int64_t F, float sigma, float* g_out) {
+    return nes_gradient_shard(ctx, offsets, weights, F, sigma, 0, 1, g_out);
+}
+
+int nes_gradient_shard(nes_ctx* ctx, const int64_t* offsets, const float* weights, int64_t F, float sigma, int shard, int n_shards, float* g_out) {
     NEED_CTX(ctx); Ctx* c = CTX(ctx);
     NES_CHECK(F >= 0, "negative F");
     if (ensure_small(c, F)) return 1;
@@ -351,7 +355,7 @@ int nes_gradient(nes_ctx* ctx, const int64_t* offsets, const float* weights, int
         if (offsets) NES_CUDA(cudaMemcpyAsync(c->d_offsets, offsets, sizeof(int64_t) * F, cudaMemcpyDefault, c->stream));
         if (weights) NES_CUDA(cudaMemcpyAsync(c->d_weights, weights, sizeof(float) * F, cudaMemcpyDefault, c->stream));
     }
-    if (launch_gradient(c, c->d_offsets, c->d_weights, F, sigma, c->grad)) return 1;
+    if (launch_gradient(c, c->d_offsets, c->d_weights, F, sigma, c->grad, shard, n_shards)) return 1;
     if (g_out) { NES_CUDA(cudaMemcpyAsync(g_out, c->grad, sizeof(float) * c->lay.D, cudaMemcpyDefault, c->stream)); return finish_output(c, g_out); }
     return 0;
 }

@@ -143,7 +143,7 @@ int launch_bound_norms_batch(Ctx* c, const int32_t* parents, int n);   // theta_
 // master.cu
 int launch_ranks(Ctx* c, const double* d_x, int64_t n, int64_t* d_ranks);
 int launch_rank_weights(Ctx* c, const double* d_fit, int64_t F, double* d_centered, float* d_w);
-int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g);
+int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g, int shard = 0, int n_shards = 1);
 int launch_opt_update(Ctx* c, const float* d_g, const double* d_G64, int direct, double l2, double* ratio_host_or_null);
 
 // decode.cu

@@ -81,11 +81,11 @@ constexpr int kGradChunk = 512;
 template <int UNROLL>
 __global__ void __launch_bounds__(256) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
                                                   const float* __restrict__ w, int64_t F, GradPlan plan,
-                                                  const Layout* __restrict__ lay, float sigma, float* __restrict__ g) {
+                                                  const Layout* __restrict__ lay, float sigma, float* __restrict__ g, int64_t v_lo, int64_t v_hi) {
     __shared__ int64_t s_off[kGradChunk];
     __shared__ float s_w[kGradChunk];
-    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool active = v < plan.vec_prefix[plan.n];
+    const int64_t v = v_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // [v_lo, v_hi): this rank's slice of the parameter axis
+    const bool active = v < v_hi;
     int k = 0;
     if (active) { while (v >= plan.vec_prefix[k + 1]) ++k; }
     const TensorDesc t = lay->t[k];
@@ -125,14 +125,20 @@ __global__ void __launch_bounds__(256) k_gradient(const __half* __restrict__ tab
 __global__ void __launch_bounds__(256) k_scale_vec(float* __restrict__ g, const float* __restrict__ s, int64_t D) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += (int64_t)gridDim.x * blockDim.x) g[i] = __fmul_rn(g[i], s[i]);
 }
-int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g) {
+int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g, int shard, int n_shards) {
     GradPlan plan; plan.n = c->lay.n; plan.vec_prefix[0] = 0;
     for (int k = 0; k < c->lay.n; ++k) plan.vec_prefix[k + 1] = plan.vec_prefix[k] + (c->lay.t[k].count + 7) / 8;
     const int64_t total = plan.vec_prefix[plan.n];
     if (F == 0) { NES_CUDA(cudaMemsetAsync(d_g, 0, sizeof(float) * c->lay.D, c->stream)); return 0; }
-    unsigned grid = (unsigned)((total + 255) / 256);
+    // multi-GPU: the parameter axis is cut into n_shards runs of whole CTAs; every element is summed over all F rows by one rank in the
+    // single-GPU order, the other ranks hold zeros, so the all-reduce that follows reproduces the single-GPU vector bit for bit
+    NES_CHECK(n_shards >= 1 && shard >= 0 && shard < n_shards, "bad gradient shard");
+    const int64_t blocks = (total + 255) / 256, per = (blocks + n_shards - 1) / n_shards;
+    const int64_t v_lo = std::min(total, (int64_t)shard * per * 256), v_hi = std::min(total, v_lo + per * 256);
+    if (n_shards > 1) NES_CUDA(cudaMemsetAsync(d_g, 0, sizeof(float) * c->lay.D, c->stream));
+    unsigned grid = (unsigned)((v_hi - v_lo + 255) / 256);
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_a, c->stream));
-    k_gradient<8><<<grid, 256, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g);
+    if (grid) k_gradient<8><<<grid, 256, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
     if (c->scale32) { k_scale_vec<<<148 * 8, 256, 0, c->stream>>>(d_g, c->scale32, c->lay.D); c->launches++; }
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_b, c->stream));
     c->launches++;

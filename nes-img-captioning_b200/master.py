@@ -136,6 +136,26 @@ def all_gather_fitness(local_fit, F, world_size, rank, group=None):
     return torch.cat([o[:hi - lo] for o, (lo, hi) in zip(out, sizes)], 0)
 
 
+def all_reduce_gradient(g, world_size, group=None):
+    """sum of the ranks' parameter-axis slices of K7 (nes_gradient_shard: zeros outside a rank's own slice, so the sum is exact and
+    every rank ends with the single-GPU vector).  The second and last exchange step of an iteration: 4 * D bytes."""
+    if world_size > 1:
+        import torch.distributed as dist
+        dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group)
+    return g
+
+
+def sharded_master_step(ctx: NesContext, fit, offsets, sigma, l2coeff, world_size=1, rank=0, group=None, want_ratio=True):
+    """NESMaster's half of an iteration (nic_nes_master.py:120-137) on every rank: centred-rank weights from the gathered
+    fitnesses, K7 over this rank's slice of the parameter axis, all-reduce, then the identical optimizer update everywhere."""
+    if world_size == 1:
+        return ctx.master_step(fit, offsets, sigma, l2coeff, want_ratio=want_ratio)
+    ctx.rank_weights(fit, want_centered=False, want_weights=False)
+    g = ctx.gradient(offsets, None, sigma, out_device=ctx.dev, shard=(rank, world_size))
+    all_reduce_gradient(g, world_size, group)
+    return ctx.opt_update(g, l2coeff, want_ratio=want_ratio)
+
+
 def nes_iteration(ctx: NesContext, optimizer: Optimizer, iteration, F, fc, sigma, l2coeff, fitness_fn,
                   world_size=1, rank=0, precision=PREC_EXACT, group=None):
     """One NIC-NES iteration.  fitness_fn(seq [P,rows,T], logprobs [P,rows,T]) -> float64 [P] scores the
@@ -149,7 +169,7 @@ def nes_iteration(ctx: NesContext, optimizer: Optimizer, iteration, F, fc, sigma
     seq, lp = ctx.rollout(offs2, signs, fc, sigma, precision=precision, out_device=ctx.dev)
     fit = torch.as_tensor(fitness_fn(seq, lp), dtype=torch.float64).reshape(n, 2)
     fit = all_gather_fitness(fit.to(ctx.dev), F, world_size, rank, group)
-    ratio = ctx.master_step(fit, offsets, sigma, l2coeff)
+    ratio = sharded_master_step(ctx, fit, offsets, sigma, l2coeff, world_size, rank, group)
     optimizer.t += 1
     return ratio, fit
 

@@ -188,3 +188,37 @@ def test_gradient_with_proportional_scale():
     got = nes_b200.NESMaster(ctx).gradient_estimate(fit, offs, 0.1)
     assert np.allclose(got, want, rtol=1e-5, atol=1e-9)
     ctx.close()
+
+
+@pytest.mark.parametrize('n_shards', [2, 3, 8])
+def test_gradient_shards_are_disjoint_and_sum_to_the_whole(g1, n_shards):
+    """multi-GPU K7 (nes_gradient_shard): every element is produced by exactly one shard with the single-GPU arithmetic, zeros
+    elsewhere, so the all-reduce over ranks equals nes_gradient bit for bit; sharded_master_step at world size 1 is master_step"""
+    import nes_b200
+    ctx, dims, play, D, theta = g1
+    F = 97
+    rs = np.random.RandomState(3)
+    w = rs.randn(F).astype(np.float32)
+    offs = ctx.sample_offsets(9, F)
+    whole = ctx.gradient(offs, w, 0.01, out_device='cuda')
+    parts = [ctx.gradient(offs, w, 0.01, out_device='cuda', shard=(r, n_shards)) for r in range(n_shards)]
+    owners = sum((p != 0).to(torch.int32) for p in parts)
+    assert int(owners.max()) <= 1
+    assert torch.equal(sum(parts), whole)
+    nz = [torch.nonzero(p).flatten() for p in parts]
+    for a, b in zip(nz[:-1], nz[1:]):                           # contiguous slices in rank order
+        if len(a) and len(b):
+            assert int(a.max()) < int(b.min())
+    fit = rs.randn(F, 2)
+    nes_b200.Adam(ctx, theta.copy(), stepsize=0.001)
+    r_a = ctx.master_step(fit, offs, 0.01, 1e-7)
+    th_a = ctx.get_theta(dtype=torch.float64).numpy()
+    nes_b200.Adam(ctx, theta.copy(), stepsize=0.001)
+    r_b = nes_b200.sharded_master_step(ctx, torch.from_numpy(fit).cuda(), offs, 0.01, 1e-7, world_size=1)
+    assert r_a == r_b and np.array_equal(th_a, ctx.get_theta(dtype=torch.float64).numpy())
+    # the multi-rank code path on one GPU: weights left on the device, slice by slice, summed, then the update
+    nes_b200.Adam(ctx, theta.copy(), stepsize=0.001)
+    ctx.rank_weights(fit, want_centered=False, want_weights=False)
+    g = sum(ctx.gradient(offs, None, 0.01, out_device='cuda', shard=(r, n_shards)) for r in range(n_shards))
+    r_c = ctx.opt_update(g, 1e-7)
+    assert r_a == r_c and np.array_equal(th_a, ctx.get_theta(dtype=torch.float64).numpy())

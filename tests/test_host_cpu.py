@@ -94,6 +94,14 @@ w = torch.from_numpy(nes_math.rank_weights(got.numpy()))
 ws = [torch.empty_like(w) for _ in range(world)]
 dist.all_gather(ws, w)
 assert all(torch.equal(ws[0], x) for x in ws)
+# the second exchange: each rank holds its slice of the gradient and zeros elsewhere; the all-reduce gives every rank the whole, exactly
+D = 1001
+g_full = torch.from_numpy(np.random.RandomState(1).randn(D).astype(np.float32))
+per = (D + world - 1) // world
+mine = torch.zeros(D, dtype=torch.float32)
+mine[rank * per:(rank + 1) * per] = g_full[rank * per:(rank + 1) * per]
+got_g = nes_b200.all_reduce_gradient(mine, world)
+assert torch.equal(got_g, g_full)
 dist.destroy_process_group()
 print('rank', rank, 'ok')
 '''
