@@ -482,7 +482,9 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32;
         q.w_start = L.t[wt].start; q.w_pstart = L.t[wt].pstart; q.K = K; q.out_rows = out_rows; q.mode = mode; q.R = ws->R; q.src_rows = src_rows;
         q.sigma = sigma; q.hi = hi; q.lo = lo; q.n_members = nm;
-        k_materialise<<<dim3((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(nm < 32768 ? nm : 32768)), 256, 0, c->stream>>>(q);
+        const dim3 grid((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(nm < 32768 ? nm : 32768));
+        if (q.scale) { if (lo) k_materialise<true, true><<<grid, 256, 0, c->stream>>>(q); else k_materialise<true, false><<<grid, 256, 0, c->stream>>>(q); }
+        else         { if (lo) k_materialise<false, true><<<grid, 256, 0, c->stream>>>(q); else k_materialise<false, false><<<grid, 256, 0, c->stream>>>(q); }
         c->launches++;
     };
     auto matb = [&](int b0, int b1, int out_cols, int mode, int src_n, float* out, int64_t out_stride = 0, int64_t out_off = 0) {

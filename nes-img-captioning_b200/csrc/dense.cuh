@@ -396,9 +396,21 @@ struct MatParams {
     __half* hi; __half* lo;
     int64_t n_members;
 };
-constexpr int kMatRowsPerBlock = 32;
-// grid = (ceil(out_rows / 32), members): one block writes 32 output rows of one member; a row is covered by K/8 threads
-// (16 bytes of eps each), so all index arithmetic is 32-bit and per row, not per element
+constexpr int kMatRowsPerBlock = 64;
+constexpr int kMatBatch = 4;                 // rows in flight per thread: all loads of a batch are issued before the first store
+__device__ __forceinline__ void st_stream_128(void* p, const uint4& v) {
+    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_nc_128(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// grid = (ceil(out_rows / 64), members): one block writes 64 output rows of one member; a row is covered by K/8 threads
+// (16 bytes of eps each), so all index arithmetic is 32-bit and per row, not per element.  HBM-stream bound: a thread keeps
+// kMatBatch rows (one 16-byte table load and two 16-byte theta loads each) in flight, the operand tiles leave through streaming
+// stores (they are next read a whole rollout phase later; theta stays in L2)
+template <bool SCALED, bool HAS_LO>
 __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
     const int kv = p.K / 8;
     const int tpr = kv < 256 ? kv : 256;                 // threads per row
@@ -407,46 +419,74 @@ __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
     if (lr >= rpi) return;
     const int r_end = min(p.out_rows, ((int)blockIdx.x + 1) * kMatRowsPerBlock);
     for (int64_t member = blockIdx.y; member < p.n_members; member += gridDim.y) {
-        const float sgn = p.sign[member];
+        // W * 2^8 = fma(theta, 2^8, +-fl(2^8 sigma * eps)): scaling by a power of two commutes with every rounding, so this is
+        // 2^8 * fl(theta +- fl(sigma * eps)) -- the reference's member weight -- with one FFMA instead of FADD + FMUL
+        const float ssig = __fmul_rn(p.sign[member] > 0.f ? p.sigma : -p.sigma, kThetaScale);
         const int64_t pbase = (int64_t)(p.parent ? p.parent[member] : 0) * p.D + p.w_start;
-        const float* tbase = p.theta32 + pbase;
-        const float* sbase = p.scale ? p.scale + pbase : nullptr;
-        const __half* ebase = p.table + p.off[member] + p.w_pstart;
-        for (int r = blockIdx.x * kMatRowsPerBlock + lr; r < r_end; r += rpi) {
-            int src = r;
-            if (p.mode == 1) {
-                const int tile = r / kLstmTileCols, rr = r - tile * kLstmTileCols;
-                const int c = rr / kLstmTileUnits, u = rr - c * kLstmTileUnits;
-                const int unit = tile * kLstmTileUnits + u;
-                src = unit < p.R ? c * p.R + unit : -1;
-            } else if (r >= p.src_rows) src = -1;
-            for (int k = kvi * 8; k < p.K; k += tpr * 8) {
-                __half hh[8], hl[8];
-                if (src >= 0) {
-                    const float* tw = tbase + (int64_t)src * p.K + k;
-                    const uint4 ev = *reinterpret_cast<const uint4*>(ebase + (int64_t)src * p.K + k);
-                    const __half* eh = reinterpret_cast<const __half*>(&ev);
-                    float tv[8];
-                    if ((reinterpret_cast<uintptr_t>(tw) & 15) == 0) {
-                        *reinterpret_cast<float4*>(&tv[0]) = reinterpret_cast<const float4*>(tw)[0];
-                        *reinterpret_cast<float4*>(&tv[4]) = reinterpret_cast<const float4*>(tw)[1];
+        const float* __restrict__ tbase = p.theta32 + pbase;
+        const float* __restrict__ sbase = p.scale ? p.scale + pbase : nullptr;
+        const __half* __restrict__ ebase = p.table + p.off[member] + p.w_pstart;
+        const bool aligned = (reinterpret_cast<uintptr_t>(tbase) & 15) == 0;          // K is a multiple of 64, so every row start is too
+        for (int k = kvi * 8; k < p.K; k += tpr * 8) {
+            for (int r0 = blockIdx.x * kMatRowsPerBlock + lr; r0 < r_end; r0 += rpi * kMatBatch) {
+                int src[kMatBatch];
+                uint4 ev[kMatBatch];
+                float tv[kMatBatch][8];
+#pragma unroll
+                for (int b = 0; b < kMatBatch; ++b) {
+                    const int r = r0 + b * rpi;
+                    src[b] = -2;                                     // past the block: nothing to write
+                    if (r < r_end) {
+                        src[b] = r;
+                        if (p.mode == 1) {
+                            const int tile = r / kLstmTileCols, rr = r - tile * kLstmTileCols;
+                            const int c = rr / kLstmTileUnits, u = rr - c * kLstmTileUnits;
+                            const int unit = tile * kLstmTileUnits + u;
+                            src[b] = unit < p.R ? c * p.R + unit : -1;
+                        } else if (r >= p.src_rows) src[b] = -1;
+                    }
+                }
+#pragma unroll
+                for (int b = 0; b < kMatBatch; ++b) {
+                    if (src[b] < 0) continue;
+                    const float* tw = tbase + (int64_t)src[b] * p.K + k;
+                    ev[b] = ld_nc_128(ebase + (int64_t)src[b] * p.K + k);
+                    if (aligned) {
+                        *reinterpret_cast<float4*>(&tv[b][0]) = __ldg(reinterpret_cast<const float4*>(tw));
+                        *reinterpret_cast<float4*>(&tv[b][4]) = __ldg(reinterpret_cast<const float4*>(tw) + 1);
                     } else {
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) tv[e] = tw[e];
+                        for (int e = 0; e < 8; ++e) tv[b][e] = __ldg(tw + e);
                     }
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const float nz = mut_noise(p.sigma, __half2float(eh[e]), sbase, (int64_t)src * p.K + k + e);
-                        const float w = sgn > 0.f ? __fadd_rn(tv[e], nz) : __fsub_rn(tv[e], nz);
-                        split_half_dev(w, kThetaScale, hh[e], hl[e]);
-                    }
-                } else {
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) { hh[e] = __float2half_rn(0.f); hl[e] = hh[e]; }
                 }
-                const int64_t o = (member * p.out_rows + r) * (int64_t)p.K + k;
-                *reinterpret_cast<uint4*>(p.hi + o) = *reinterpret_cast<uint4*>(hh);
-                if (p.lo) *reinterpret_cast<uint4*>(p.lo + o) = *reinterpret_cast<uint4*>(hl);
+#pragma unroll
+                for (int b = 0; b < kMatBatch; ++b) {
+                    if (src[b] == -2) continue;
+                    __align__(16) __half2 hh[4];
+                    __align__(16) __half2 hl[4];
+                    if (src[b] >= 0) {
+                        const __half2* eh = reinterpret_cast<const __half2*>(&ev[b]);
+                        const float* sc = SCALED ? sbase + (int64_t)src[b] * p.K + k : nullptr;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float2 ef = __half22float2(eh[e]);
+                            float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
+                            if (SCALED) { n0 = __fmul_rn(n0, __ldg(sc + 2 * e)); n1 = __fmul_rn(n1, __ldg(sc + 2 * e + 1)); }
+                            const float x0 = __fmaf_rn(tv[b][2 * e], kThetaScale, n0), x1 = __fmaf_rn(tv[b][2 * e + 1], kThetaScale, n1);
+                            hh[e] = __floats2half2_rn(x0, x1);
+                            if (HAS_LO) {
+                                const float2 hf = __half22float2(hh[e]);
+                                hl[e] = __floats2half2_rn(__fsub_rn(x0, hf.x), __fsub_rn(x1, hf.y));
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) { hh[e] = __floats2half2_rn(0.f, 0.f); hl[e] = hh[e]; }
+                    }
+                    const int64_t o = (member * p.out_rows + (r0 + b * rpi)) * (int64_t)p.K + k;
+                    st_stream_128(p.hi + o, *reinterpret_cast<uint4*>(hh));
+                    if (HAS_LO) st_stream_128(p.lo + o, *reinterpret_cast<uint4*>(hl));
+                }
             }
         }
     }

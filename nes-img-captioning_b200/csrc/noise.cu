@@ -183,19 +183,49 @@ __global__ void __launch_bounds__(256) k_evolve_batch(float* theta32, double* __
     const int64_t span = pend - t.pstart;
     const int src = (int)(srcdst[item] & 0xffffffffll), dst = (int)(srcdst[item] >> 32);
     const float sigma = sigmas[item];
-    const float* th = theta32 + (int64_t)src * D;
-    const __half* row = table + offs[item];
+    const float* th = theta32 + (int64_t)src * D + t.start;
+    const __half* row = table + offs[item] + t.pstart;
     const float* sc = scale ? scale + (int64_t)src * D : nullptr;
-    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < span; j += (int64_t)gridDim.x * blockDim.x) {
+    float* d32 = theta32 + (int64_t)dst * D + t.start;           // dst slots are disjoint from src slots (checked by the host)
+    double* d64 = theta64 + (int64_t)dst * D + t.start;
+    __half* dhi = th_hi + (int64_t)dst * D_pad + t.pstart;
+    __half* dlo = th_lo + (int64_t)dst * D_pad + t.pstart;
+    // 8 elements per thread through 16-byte accesses where the tensor starts on a 16-byte boundary in every array
+    const bool vec = ((reinterpret_cast<uintptr_t>(th) | reinterpret_cast<uintptr_t>(d32) | reinterpret_cast<uintptr_t>(d64) |
+                       reinterpret_cast<uintptr_t>(row) | reinterpret_cast<uintptr_t>(dhi)) & 15) == 0;
+    const int64_t n8 = vec ? t.count / 8 : 0;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t v = tid; v < n8; v += nth) {
+        const int64_t j = v * 8;
+        const uint4 ev = __ldg(reinterpret_cast<const uint4*>(row + j));
+        const float4 a = __ldg(reinterpret_cast<const float4*>(th + j)), b = __ldg(reinterpret_cast<const float4*>(th + j) + 1);
+        const float tv[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        const __half* eh = reinterpret_cast<const __half*>(&ev);
+        __align__(16) float m[8];
+        __align__(16) __half hh[8];
+        __align__(16) __half hl[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            m[e] = __fadd_rn(tv[e], mut_noise(sigma, __half2float(eh[e]), sc, t.start + j + e));
+            split_half(m[e], kThetaScale, hh[e], hl[e]);
+        }
+        reinterpret_cast<float4*>(d32 + j)[0] = *reinterpret_cast<float4*>(&m[0]);
+        reinterpret_cast<float4*>(d32 + j)[1] = *reinterpret_cast<float4*>(&m[4]);
+#pragma unroll
+        for (int e = 0; e < 8; e += 2) *reinterpret_cast<double2*>(d64 + j + e) = make_double2((double)m[e], (double)m[e + 1]);
+        *reinterpret_cast<uint4*>(dhi + j) = *reinterpret_cast<uint4*>(hh);
+        *reinterpret_cast<uint4*>(dlo + j) = *reinterpret_cast<uint4*>(hl);
+    }
+    for (int64_t j = n8 * 8 + tid; j < span; j += nth) {          // ragged tail, unaligned tensors, zero padding of the shadow
         __half a = __float2half_rn(0.f), b = a;
         if (j < t.count) {
-            const float m = __fadd_rn(th[t.start + j], mut_noise(sigma, __half2float(row[t.pstart + j]), sc, t.start + j));
-            theta32[(int64_t)dst * D + t.start + j] = m;       // dst slots are disjoint from src slots (checked by the host)
-            theta64[(int64_t)dst * D + t.start + j] = (double)m;
+            const float m = __fadd_rn(th[j], mut_noise(sigma, __half2float(row[j]), sc, t.start + j));
+            d32[j] = m;
+            d64[j] = (double)m;
             split_half(m, kThetaScale, a, b);
         }
-        th_hi[(int64_t)dst * D_pad + t.pstart + j] = a;
-        th_lo[(int64_t)dst * D_pad + t.pstart + j] = b;
+        dhi[j] = a;
+        dlo[j] = b;
     }
 }
 int launch_evolve_batch(Ctx* c, int n, const int32_t* src, const int64_t* offsets, const float* sigmas, const int32_t* dst) {
