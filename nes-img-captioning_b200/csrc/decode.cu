@@ -201,15 +201,32 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
     const int par = p.parent ? p.parent[member] : 0;
     const float* te = p.theta32 + (int64_t)par * p.D + p.emb_start + tok * p.E;
     const __half* ee = p.table + p.off[member] + p.emb_pstart + tok * p.E;
+    const float* se = p.scale ? p.scale + (int64_t)par * p.D + p.emb_start + tok * p.E : nullptr;
+    // x * 2^5 = fma(theta, 2^5, +-fl(2^5 sigma eps)) = 2^5 fl(theta +- fl(sigma eps)): powers of two commute with the roundings
+    const float ssig = __fmul_rn(sgn > 0.f ? p.sigma : -p.sigma, kActScale);
+    const bool aligned = (reinterpret_cast<uintptr_t>(te) & 15) == 0;
     for (int e = lane * 8; e < p.E; e += 256) {
         const uint4 ev = *reinterpret_cast<const uint4*>(ee + e);
-        const __half* eh = reinterpret_cast<const __half*>(&ev);
-        __half hh[8], hl[8];
+        const __half2* eh = reinterpret_cast<const __half2*>(&ev);
+        float tv[8];
+        if (aligned) {
+            *reinterpret_cast<float4*>(&tv[0]) = __ldg(reinterpret_cast<const float4*>(te + e));
+            *reinterpret_cast<float4*>(&tv[4]) = __ldg(reinterpret_cast<const float4*>(te + e) + 1);
+        } else {
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const float nz = mut_noise(p.sigma, __half2float(eh[u]), p.scale, (int64_t)par * p.D + p.emb_start + tok * p.E + e + u);
-            const float x = sgn > 0.f ? __fadd_rn(te[e + u], nz) : __fsub_rn(te[e + u], nz);
-            split_half_dev(x, kActScale, hh[u], hl[u]);
+            for (int u = 0; u < 8; ++u) tv[u] = te[e + u];
+        }
+        __align__(16) __half2 hh[4];
+        __align__(16) __half2 hl[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float2 ef = __half22float2(eh[u]);
+            float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
+            if (se) { n0 = __fmul_rn(n0, se[e + 2 * u]); n1 = __fmul_rn(n1, se[e + 2 * u + 1]); }
+            const float x0 = __fmaf_rn(tv[2 * u], kActScale, n0), x1 = __fmaf_rn(tv[2 * u + 1], kActScale, n1);
+            hh[u] = __floats2half2_rn(x0, x1);
+            const float2 hf = __half22float2(hh[u]);
+            hl[u] = __floats2half2_rn(__fsub_rn(x0, hf.x), __fsub_rn(x1, hf.y));
         }
         *reinterpret_cast<uint4*>(p.x_hi + grow * p.E + e) = *reinterpret_cast<uint4*>(hh);
         *reinterpret_cast<uint4*>(p.x_lo + grow * p.E + e) = *reinterpret_cast<uint4*>(hl);

@@ -149,34 +149,63 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
     __syncwarp();
     const float S = h0.sum * expf(h0.mx - M) + h1.sum * expf(h1.mx - M);
     const int my_idx = lane < count ? s_idx[wq][lane] : -1;
-    const float sgn = p.sign[member];
+    const float ssig = p.sign[member] > 0.f ? p.sigma : -p.sigma;      // theta - fl(sigma eps) == theta + fl(-sigma eps), bit for bit
     const int64_t off = p.off[member];
     const int par = p.parent ? p.parent[member] : 0;
+    // this lane's slice of the row's hidden state (R <= 512: two chunks of 8), rebuilt from the split halves once
+    float xs[2][8];
+#pragma unroll
+    for (int c2 = 0; c2 < 2; ++c2) {
+        const int k = c2 * 256 + lane * 8;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) xs[c2][e] = 0.f;
+        if (k < p.R) {
+            const uint4 a = *reinterpret_cast<const uint4*>(p.h_hi + grow * p.R + k), b = *reinterpret_cast<const uint4*>(p.h_lo + grow * p.R + k);
+            const __half2 *ha = reinterpret_cast<const __half2*>(&a), *hb = reinterpret_cast<const __half2*>(&b);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 fa = __half22float2(ha[e]), fb = __half22float2(hb[e]);
+                xs[c2][2 * e] = (fa.x + fb.x) * (1.0f / kActScale); xs[c2][2 * e + 1] = (fa.y + fb.y) * (1.0f / kActScale);
+            }
+        }
+    }
+    const float* wbase = p.theta32 + (int64_t)par * p.D + p.w_start;
+    const bool aligned = (reinterpret_cast<uintptr_t>(wbase) & 15) == 0;     // R is a multiple of 64: every row start shares it
     float my_val = -INFINITY;
     for (int c = 0; c < count; ++c) {
         const int j = __shfl_sync(0xffffffffu, my_idx, c);
-        const float* tw = p.theta32 + (int64_t)par * p.D + p.w_start + (int64_t)j * p.R;
+        const float* tw = wbase + (int64_t)j * p.R;
         const __half* ew = p.table + off + p.w_pstart + (int64_t)j * p.R;
+        const float* sw = p.scale ? p.scale + (int64_t)par * p.D + p.w_start + (int64_t)j * p.R : nullptr;
         float acc = 0.f;
-        for (int k = lane * 8; k < p.R; k += 256) {
-            const uint4 a = *reinterpret_cast<const uint4*>(p.h_hi + grow * p.R + k), b = *reinterpret_cast<const uint4*>(p.h_lo + grow * p.R + k);
-            const uint4 ev = *reinterpret_cast<const uint4*>(ew + k);
-            const __half *ha = reinterpret_cast<const __half*>(&a), *hb = reinterpret_cast<const __half*>(&b), *he = reinterpret_cast<const __half*>(&ev);
-            float tv[8];                                           // scalar loads: parent*D need not be 16-byte aligned
 #pragma unroll
-            for (int e = 0; e < 8; ++e) tv[e] = tw[k + e];
+        for (int c2 = 0; c2 < 2; ++c2) {
+            const int k = c2 * 256 + lane * 8;
+            if (k < p.R) {
+                const uint4 ev = *reinterpret_cast<const uint4*>(ew + k);
+                const __half2* he = reinterpret_cast<const __half2*>(&ev);
+                float tv[8];
+                if (aligned) {
+                    *reinterpret_cast<float4*>(&tv[0]) = __ldg(reinterpret_cast<const float4*>(tw + k));
+                    *reinterpret_cast<float4*>(&tv[4]) = __ldg(reinterpret_cast<const float4*>(tw + k) + 1);
+                } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const float x = (__half2float(ha[e]) + __half2float(hb[e])) * (1.0f / kActScale);
-                const float nz = mut_noise(p.sigma, __half2float(he[e]), p.scale, (int64_t)par * p.D + p.w_start + (int64_t)j * p.R + k + e);
-                const float w = sgn > 0.f ? __fadd_rn(tv[e], nz) : __fsub_rn(tv[e], nz);
-                acc = fmaf(x, w, acc);
+                    for (int e = 0; e < 8; ++e) tv[e] = tw[k + e];
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 ef = __half22float2(he[e]);
+                    float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
+                    if (sw) { n0 = __fmul_rn(n0, sw[k + 2 * e]); n1 = __fmul_rn(n1, sw[k + 2 * e + 1]); }
+                    acc = fmaf(xs[c2][2 * e], __fadd_rn(tv[2 * e], n0), acc);
+                    acc = fmaf(xs[c2][2 * e + 1], __fadd_rn(tv[2 * e + 1], n1), acc);
+                }
             }
         }
         acc = warp_sum(acc);
         const float tb = p.theta32[(int64_t)par * p.D + p.b_start + j];
-        const float nzb = mut_noise(p.sigma, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j);
-        const float v = acc + (sgn > 0.f ? __fadd_rn(tb, nzb) : __fsub_rn(tb, nzb));
+        const float nzb = mut_noise(ssig, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j);
+        const float v = acc + __fadd_rn(tb, nzb);
         if (lane == c) my_val = v;
     }
     const float vmax = warp_max(my_val);
