@@ -36,7 +36,8 @@ class PolicyNet:
 
     def __init__(self, ctx: NesContext, parent=0, options=None, vbn=False):
         self.ctx, self.parent = ctx, int(parent)
-        self.mutations = Mutation((options and options.safe_mutations) or '')
+        sm = options.get('safe_mutations') if isinstance(options, dict) else getattr(options, 'safe_mutations', None)
+        self.mutations = Mutation(sm or '')
         if self.mutations not in (Mutation.DEFAULT, Mutation.SAFE_PROPORTIONAL):
             raise NotImplementedError('gradient / vector safe mutations are not on the B200 path (SURVEY 8f-3)')
         ctx.set_mutation(self.mutations.value)        # context-wide: every parent slot mutates the same way
