@@ -37,8 +37,9 @@ typedef struct nes_fc_dims {
     int32_t rnn_size;              /* R */
     int32_t fc_feat_size;          /* Fd */
     int32_t seq_length;            /* T = 16 (captioning/nets.py:147) */
-    int32_t layer_n;               /* LayerNorm on i2h / h2h / c (captioning/nets.py:93-96) */
-    int32_t layer_n_affine;
+    int32_t layer_n;               /* 1: LayerNorm on i2h / h2h / c (captioning/nets.py:93-96); 2: the reference's "virtual batch norm",
+                                      BatchNorm1d over the rows of the batch without running statistics (captioning/nets.py:87-91) */
+    int32_t layer_n_affine;        /* elementwise affine parameters of either (layer_n_affine / vbn_affine) */
 } nes_fc_dims;
 
 /* precision of the population GEMMs */

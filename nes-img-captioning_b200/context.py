@@ -28,6 +28,9 @@ class NesContext:
                              rnn_size=int(mo['rnn_size']), fc_feat_size=int(mo['fc_feat_size']),
                              seq_length=int(mo.get('seq_length') or 16), layer_n=int(bool(mo.get('layer_n'))),
                              layer_n_affine=int(bool(mo.get('layer_n_affine'))))
+            if mo.get('vbn'):                      # LSTMCore: `if self.vbn ... elif self.layer_n` (captioning/nets.py:87-96)
+                assert not mo.get('vbn_e'), 'vbn_e (batch norm on the embeddings) is not on the B200 path'
+                self.dims.update(layer_n=2, layer_n_affine=int(bool(mo.get('vbn_affine'))))
             d = _lib.FcDims(**self.dims)
             self.G = granule(self.dims['input_encoding_size'], self.dims['rnn_size'], self.dims['fc_feat_size'])
             self.tensors, self.D, self.D_pad = build_layout(

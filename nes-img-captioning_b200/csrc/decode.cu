@@ -349,6 +349,82 @@ __global__ void __launch_bounds__(128) k_ln_gates(const LnParams p) {
     }
 }
 
+// Batch-norm variant of the cell -- the reference's "virtual batch norm" (captioning/nets.py:87-91,99-101,124-125):
+// nn.BatchNorm1d(track_running_stats=False), i.e. every feature is normalised with the mean / biased variance over the ROWS of the
+// batch at hand, in eval mode too.  grid (ceil(R/32), members): a block owns 32 units of one member (lane = unit, warp = row subset),
+// which closes over everything the unit needs: its 5 gate columns of both addends and its cell value, over all rows.
+__global__ void __launch_bounds__(256) k_bn_gates(const LnParams p) {
+    __shared__ float s_red[8][11][32];
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    const int64_t member = blockIdx.y;
+    const int R = p.R, N = 5 * p.R;
+    const int j = blockIdx.x * 32 + lane;
+    const bool live = j < R;
+    const float* par = p.ln_par ? p.ln_par + member * (int64_t)(4 * N + 2 * R) : nullptr;
+    const float* pi = p.pre_i + member * (int64_t)p.rows_pad * N;
+    const float* ph = p.pre_h + member * (int64_t)p.rows_pad * N;
+    float* cs = p.c_state + member * (int64_t)p.rows_pad * R;
+    const float inv_n = 1.0f / (float)p.rows;
+    // block-wide column reduction of `v[q]` (q < nq) over the warps; result in s_mean / s_rstd via the callback
+    auto reduce = [&](const float (&v)[11], int nq, float (&out)[11]) {
+        __syncthreads();
+        for (int q = 0; q < nq; ++q) s_red[wq][q][lane] = v[q];
+        __syncthreads();
+        for (int q = 0; q < nq; ++q) { float a = 0.f; for (int w = 0; w < 8; ++w) a += s_red[w][q][lane]; out[q] = a; }
+    };
+    float acc[11], tot[11], mean[11], rstd[11];
+    // ---- statistics of the 10 pre-activation columns (gate g of addend a: q = 2 g + a)
+    for (int q = 0; q < 11; ++q) acc[q] = 0.f;
+    if (live) for (int r = wq; r < p.rows; r += 8)
+        for (int g = 0; g < 5; ++g) { acc[2 * g] += pi[(int64_t)r * N + g * R + j]; acc[2 * g + 1] += ph[(int64_t)r * N + g * R + j]; }
+    reduce(acc, 10, tot);
+    for (int q = 0; q < 10; ++q) { mean[q] = tot[q] * inv_n; acc[q] = 0.f; }
+    if (live) for (int r = wq; r < p.rows; r += 8)
+        for (int g = 0; g < 5; ++g) {
+            const float a = pi[(int64_t)r * N + g * R + j] - mean[2 * g], b = ph[(int64_t)r * N + g * R + j] - mean[2 * g + 1];
+            acc[2 * g] = fmaf(a, a, acc[2 * g]); acc[2 * g + 1] = fmaf(b, b, acc[2 * g + 1]);
+        }
+    reduce(acc, 10, tot);
+    for (int q = 0; q < 10; ++q) rstd[q] = 1.0f / sqrtf(tot[q] * inv_n + 1e-5f);
+    float wgt[10], bia[10];
+    for (int g = 0; g < 5; ++g)
+        for (int a = 0; a < 2; ++a) {
+            wgt[2 * g + a] = (par && live) ? par[(2 * a) * N + g * R + j] : 1.f;
+            bia[2 * g + a] = (par && live) ? par[(2 * a + 1) * N + g * R + j] : 0.f;
+        }
+    auto gate = [&](int r, int g) {
+        const float a = (pi[(int64_t)r * N + g * R + j] - mean[2 * g]) * rstd[2 * g] * wgt[2 * g] + bia[2 * g];
+        const float b = (ph[(int64_t)r * N + g * R + j] - mean[2 * g + 1]) * rstd[2 * g + 1] * wgt[2 * g + 1] + bia[2 * g + 1];
+        return a + b;
+    };
+    // ---- c' = f c + i max(g3, g4), its statistics over the rows
+    acc[10] = 0.f;
+    if (live) for (int r = wq; r < p.rows; r += 8) {
+        const float ig = sigmoid_f(gate(r, 0)), fg = sigmoid_f(gate(r, 1));
+        const float cand = fmaxf(gate(r, 3), gate(r, 4));
+        const float cn = __fadd_rn(__fmul_rn(fg, cs[(int64_t)r * R + j]), __fmul_rn(ig, cand));
+        cs[(int64_t)r * R + j] = cn;
+        acc[10] += cn;
+    }
+    {
+        float v[11], o[11]; v[0] = acc[10];
+        reduce(v, 1, o); mean[10] = o[0] * inv_n;
+        float d2 = 0.f;
+        if (live) for (int r = wq; r < p.rows; r += 8) { const float d = cs[(int64_t)r * R + j] - mean[10]; d2 = fmaf(d, d, d2); }
+        v[0] = d2; reduce(v, 1, o); rstd[10] = 1.0f / sqrtf(o[0] * inv_n + 1e-5f);
+    }
+    const float cw = (par && live) ? par[4 * N + j] : 1.f, cb = (par && live) ? par[4 * N + R + j] : 0.f;
+    // ---- h = o tanh(bn(c'))
+    if (live) for (int r = wq; r < p.rows; r += 8) {
+        const float og = sigmoid_f(gate(r, 2));
+        const float hn = og * tanhf((cs[(int64_t)r * R + j] - mean[10]) * rstd[10] * cw + cb);
+        const int64_t grow = member * p.rows_pad + r;
+        __half a, l; split_half_dev(hn, kActScale, a, l);
+        p.h_hi[grow * R + j] = a; p.h_lo[grow * R + j] = l;
+        if (p.h_trace) p.h_trace[(member * p.rows + r) * (int64_t)R + j] = hn;
+    }
+}
+
 __global__ void __launch_bounds__(256) k_logprob_fitness(const float* __restrict__ lp, int64_t per_member, double* __restrict__ out) {
     __shared__ double sh[8];
     const float* src = lp + blockIdx.x * per_member;
@@ -748,7 +824,8 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 const size_t ln_smem = sizeof(float) * 4 * 6 * R;
                 if (ln_smem > 48 * 1024) { static size_t set_to = 0; if (set_to < ln_smem) { NES_CUDA(cudaFuncSetAttribute(k_ln_gates, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ln_smem)); set_to = ln_smem; } }
                 ProfScope prof(c, PROF_FINALIZE);
-                k_ln_gates<<<(unsigned)((nm * rows + 3) / 4), 128, ln_smem, c->stream>>>(q);
+                if (c->dims.layer_n == 2) k_bn_gates<<<dim3((unsigned)((R + 31) / 32), (unsigned)nm), 256, 0, c->stream>>>(q);
+                else k_ln_gates<<<(unsigned)((nm * rows + 3) / 4), 128, ln_smem, c->stream>>>(q);
                 c->launches++;
                 NES_CUDA(cudaGetLastError());
             }

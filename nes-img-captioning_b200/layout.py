@@ -12,15 +12,17 @@ TensorSpec = namedtuple('TensorSpec', ['name', 'shape', 'start', 'count', 'pstar
 
 
 def fc_tensors(vocab_size, input_encoding_size, rnn_size, fc_feat_size, layer_n=False, layer_n_affine=False):
+    """layer_n: 0 none, 1 LayerNorm (core.*_ln), 2 batch norm over the rows = the reference's vbn (core.*_bn)"""
     V1, E, R, Fd = vocab_size + 1, input_encoding_size, rnn_size, fc_feat_size
     t = [('img_embed.weight', (E, Fd)), ('img_embed.bias', (E,)), ('embed.weight', (V1, E)),
          ('logit.weight', (V1, R)), ('logit.bias', (V1,)),
          ('core.i2h.weight', (5 * R, E)), ('core.i2h.bias', (5 * R,)),
          ('core.h2h.weight', (5 * R, R)), ('core.h2h.bias', (5 * R,))]
     if layer_n and layer_n_affine:
-        t += [('core.i2h_ln.weight', (5 * R,)), ('core.i2h_ln.bias', (5 * R,)),
-              ('core.h2h_ln.weight', (5 * R,)), ('core.h2h_ln.bias', (5 * R,)),
-              ('core.c_ln.weight', (R,)), ('core.c_ln.bias', (R,))]
+        k = 'bn' if int(layer_n) == 2 else 'ln'
+        t += [('core.i2h_%s.weight' % k, (5 * R,)), ('core.i2h_%s.bias' % k, (5 * R,)),
+              ('core.h2h_%s.weight' % k, (5 * R,)), ('core.h2h_%s.bias' % k, (5 * R,)),
+              ('core.c_%s.weight' % k, (R,)), ('core.c_%s.bias' % k, (R,))]
     return t
 
 

@@ -41,8 +41,8 @@ class PolicyNet:
         if self.mutations not in (Mutation.DEFAULT, Mutation.SAFE_PROPORTIONAL):
             raise NotImplementedError('gradient / vector safe mutations are not on the B200 path (SURVEY 8f-3)')
         ctx.set_mutation(self.mutations.value)        # context-wide: every parent slot mutates the same way
-        if vbn:
-            raise NotImplementedError('virtual batch norm is not on the B200 path (SURVEY 8f-3)')
+        if vbn and ctx.dims is not None and ctx.dims['layer_n'] != 2:
+            raise AssertionError('vbn=True needs a context created with model_options.vbn')
         self.nb_learnable_params = ctx.D
         self.nb_params = ctx.D
         self._theta_dtype = torch.float32
@@ -123,7 +123,7 @@ class FCModel(PolicyNet):
         gen.manual_seed(int(rng_state) if rng_state is not None else torch.seed() % (1 << 31))
         flat = torch.zeros(self.ctx.D, dtype=torch.float32)
         for t in self.ctx.tensors:
-            if 'ln' in t.name:
+            if 'ln' in t.name or 'bn' in t.name:
                 if t.name.endswith('weight'):
                     flat[t.start:t.start + t.count] = 1.0
             elif t.name.endswith('weight'):

@@ -19,18 +19,20 @@ from .noise import flat_layout
 
 class Dims:
     def __init__(self, vocab_size, input_encoding_size, rnn_size, fc_feat_size,
-                 seq_length=16, layer_n=False, layer_n_affine=False):
+                 seq_length=16, layer_n=False, layer_n_affine=False, vbn=False, vbn_affine=False):
         self.vocab_size = vocab_size
         self.input_encoding_size = input_encoding_size
         self.rnn_size = rnn_size
         self.fc_feat_size = fc_feat_size
         self.seq_length = seq_length
-        self.layer_n = bool(layer_n)
+        self.vbn = bool(vbn)                       # batch norm over the rows of the batch, no running statistics (captioning/nets.py:87-91)
+        self.vbn_affine = bool(vbn_affine)
+        self.layer_n = bool(layer_n) and not self.vbn
         self.layer_n_affine = bool(layer_n_affine)
 
     def layout(self):
         return flat_layout(self.vocab_size, self.input_encoding_size, self.rnn_size,
-                           self.fc_feat_size, self.layer_n, self.layer_n_affine)
+                           self.fc_feat_size, self.layer_n, self.layer_n_affine, self.vbn, self.vbn_affine)
 
     def num_params(self):
         lay = self.layout()
@@ -53,7 +55,7 @@ def xavier_theta(dims, seed):
     from .noise import table_slice
     theta = np.zeros(dims.num_params(), dtype=np.float32)
     for name, shape, start, cnt in dims.layout():
-        if 'ln' in name:
+        if 'ln' in name or 'bn' in name:
             if name.endswith('weight'):
                 theta[start:start + cnt] = 1.0
         elif name.endswith('weight'):
@@ -67,12 +69,20 @@ def _ln(x, n, w, b):
     return F.layer_norm(x, (n,), w, b, 1e-5)
 
 
+def _bn(x, w, b):
+    """nn.BatchNorm1d(track_running_stats=False): the statistics of the batch at hand, in train and eval mode alike"""
+    return F.batch_norm(x, None, None, w, b, True, 0.1, 1e-5)
+
+
 def lstm_core(dims, p, xt, h, c):
     """src/captioning/nets.py:98-134."""
     R = dims.rnn_size
     a_i = F.linear(xt, p['core.i2h.weight'], p['core.i2h.bias'])
     a_h = F.linear(h, p['core.h2h.weight'], p['core.h2h.bias'])
-    if dims.layer_n:
+    if dims.vbn:
+        a_i = _bn(a_i, p.get('core.i2h_bn.weight'), p.get('core.i2h_bn.bias'))
+        a_h = _bn(a_h, p.get('core.h2h_bn.weight'), p.get('core.h2h_bn.bias'))
+    elif dims.layer_n:
         a_i = _ln(a_i, 5 * R, p.get('core.i2h_ln.weight'), p.get('core.i2h_ln.bias'))
         a_h = _ln(a_h, 5 * R, p.get('core.h2h_ln.weight'), p.get('core.h2h_ln.bias'))
     sums = a_i + a_h
@@ -80,7 +90,10 @@ def lstm_core(dims, p, xt, h, c):
     in_gate, forget_gate, out_gate = sig[:, :R], sig[:, R:2 * R], sig[:, 2 * R:3 * R]
     in_transform = torch.max(sums[:, 3 * R:4 * R], sums[:, 4 * R:5 * R])
     next_c = forget_gate * c + in_gate * in_transform
-    act_c = _ln(next_c, R, p.get('core.c_ln.weight'), p.get('core.c_ln.bias')) if dims.layer_n else next_c
+    if dims.vbn:
+        act_c = _bn(next_c, p.get('core.c_bn.weight'), p.get('core.c_bn.bias'))
+    else:
+        act_c = _ln(next_c, R, p.get('core.c_ln.weight'), p.get('core.c_ln.bias')) if dims.layer_n else next_c
     next_h = out_gate * torch.tanh(act_c)
     return next_h, next_c
 

@@ -107,7 +107,7 @@ def lcm(*xs):
 
 
 def flat_layout(vocab_size, input_encoding_size, rnn_size, fc_feat_size,
-                layer_n=False, layer_n_affine=False):
+                layer_n=False, layer_n_affine=False, vbn=False, vbn_affine=False):
     """[(name, shape, start, count)] in `named_parameters()` order of the
     reference FCModel (src/captioning/nets.py:150-153, LSTMCore :81-96)."""
     V1, E, R, Fd = vocab_size + 1, input_encoding_size, rnn_size, fc_feat_size
@@ -118,6 +118,14 @@ def flat_layout(vocab_size, input_encoding_size, rnn_size, fc_feat_size,
         ('core.i2h.weight', (5 * R, E)), ('core.i2h.bias', (5 * R,)),
         ('core.h2h.weight', (5 * R, R)), ('core.h2h.bias', (5 * R,)),
     ]
+    if vbn:                                      # LSTMCore: `if self.vbn ... elif self.layer_n` (captioning/nets.py:87-96)
+        layer_n = False
+        if vbn_affine:
+            tensors += [
+                ('core.i2h_bn.weight', (5 * R,)), ('core.i2h_bn.bias', (5 * R,)),
+                ('core.h2h_bn.weight', (5 * R,)), ('core.h2h_bn.bias', (5 * R,)),
+                ('core.c_bn.weight', (R,)), ('core.c_bn.bias', (R,)),
+            ]
     if layer_n and layer_n_affine:
         tensors += [
             ('core.i2h_ln.weight', (5 * R,)), ('core.i2h_ln.bias', (5 * R,)),

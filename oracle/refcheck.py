@@ -11,12 +11,16 @@ import torch
 from . import _refimport, fc_caption, nes_math, noise
 
 
-def check_decode(ref, V, E, R, Fd, B, ln=False, affine=False, seed=0):
+def check_decode(ref, V, E, R, Fd, B, ln=False, affine=False, seed=0, vbn=False):
     opt = ref.ModelOptions(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd,
-                           layer_n=ln, layer_n_affine=affine)
+                           layer_n=ln, layer_n_affine=affine, vbn=vbn, vbn_e=False, vbn_affine=affine and vbn)
     torch.manual_seed(seed)
-    model = ref.FCModel(options=opt)
-    dims = fc_caption.Dims(V, E, R, Fd, layer_n=ln, layer_n_affine=affine)
+    model = ref.FCModel(options=opt, vbn=vbn)
+    if vbn and affine:                       # the reference leaves BN at 1 / 0: give the affine parameters something to do
+        for n, p_ in model.named_parameters():
+            if 'bn' in n:
+                p_.data.add_(torch.randn(p_.shape) * 0.1)
+    dims = fc_caption.Dims(V, E, R, Fd, layer_n=ln, layer_n_affine=affine, vbn=vbn, vbn_affine=affine and vbn)
     # layout: names, shapes and order must match named_parameters()
     got = [(n, tuple(p.shape)) for n, p in model.named_parameters()]
     want = [(n, tuple(s)) for n, s, _, _ in dims.layout()]
@@ -164,6 +168,7 @@ def main():
     for cfg in [dict(V=199, E=64, R=64, Fd=128, B=8), dict(V=999, E=64, R=128, Fd=256, B=5),
                 dict(V=300, E=128, R=128, Fd=512, B=12, ln=True),
                 dict(V=300, E=128, R=128, Fd=512, B=12, ln=True, affine=True),
+                dict(V=300, E=128, R=128, Fd=512, B=12, vbn=True), dict(V=300, E=128, R=128, Fd=512, B=12, vbn=True, affine=True),
                 dict(V=9487, E=128, R=128, Fd=2048, B=4)]:
         check_decode(ref, **cfg); n += 1
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)

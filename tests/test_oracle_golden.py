@@ -92,3 +92,17 @@ def test_sampled_decode_matches_reference_golden(name, golden_mod):
             s, lp, _ = fc_caption.decode_sample(dims, th, fc, u)
             assert np.array_equal(s, gs[name + '_seq'][k, j])
             assert np.array_equal(lp, gs[name + '_logprobs'][k, j])
+
+
+@pytest.mark.parametrize('name', ['v1', 'v2', 'v3'])
+def test_vbn_decode_matches_reference_golden(name):
+    """the batch-norm ("vbn") cell of the oracle against the real reference's outputs"""
+    import make_golden_vbn as mv
+    gv = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'golden_vbn_v1.npz'))
+    c = mv.CASES[name]
+    dims, G, play, D, D_pad, L, theta, fc, offs = mv.case_inputs(c)
+    eps = noise.noise_row(mv.TABLE_SEED, offs[0], play, D)
+    for j, sign in enumerate((+1, -1)):
+        th, _ = noise.member_theta(theta, eps, c['sigma'], sign)
+        s, lp = fc_caption.decode_greedy(dims, th, fc)
+        assert np.array_equal(s, gv[name + '_seq'][j]) and np.array_equal(lp, gv[name + '_logprobs'][j])
