@@ -278,7 +278,9 @@ __global__ void __launch_bounds__(256) k_sample(const SampleParams p) {
     const double u = p.u[(member * p.rows + r) * p.T + (p.t - 1)];
     double run = base + (inc - loc);
     int first = 0x7fffffff;
-    for (int j = j0; j < j1; ++j) { run += (double)s_p[j]; if (first == 0x7fffffff && run / total > u) first = j; }
+    // cdf_j / cdf_last > u, with the float64 division done only where the cheap product test says it can be true
+    const double pre = u * total * (1.0 - 1e-15);
+    for (int j = j0; j < j1; ++j) { run += (double)s_p[j]; if (first == 0x7fffffff && run >= pre && run / total > u) first = j; }
     for (int o = 16; o > 0; o >>= 1) first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
     if (lane == 0) s_i[wq] = first;
     __syncthreads();
@@ -935,7 +937,8 @@ int launch_bound_norms_batch(Ctx* c, const int32_t* parents, int n) {
     // c->d_ranks still holds the packed (src | dst << 32) items of launch_evolve_batch; the dst slots are the parents to refresh
     if (!c->is_fc || n == 0) return 0;
     const int R = c->dims.rnn_size, V1 = c->dims.vocab_size + 1;
-    for (int i = 0; i < n; ++i) NES_CUDA(cudaMemsetAsync(c->d_theta_rowmax + parents[i], 0, sizeof(float), c->stream));
+    (void)parents;
+    k_zero_slots<<<(n + 255) / 256, 256, 0, c->stream>>>(c->d_ranks, n, c->d_theta_rowmax);
     k_rowmax_theta_batch<<<dim3(37, n), 256, 0, c->stream>>>(c->theta32, c->lay.D, c->lay.t[T_LOGIT_W].start, V1, R, c->d_ranks, c->d_theta_rowmax);
     c->launches++;
     NES_CUDA(cudaGetLastError());

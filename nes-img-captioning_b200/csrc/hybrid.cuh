@@ -32,6 +32,10 @@ __global__ void __launch_bounds__(256) k_rowmax_theta(const float* __restrict__ 
     }
     if (lane == 0) atomic_max_pos(out, sqrtf(best) * 1.0001f);
 }
+__global__ void k_zero_slots(const int64_t* __restrict__ srcdst, int n, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[(int)(srcdst[i] >> 32)] = 0.f;
+}
 // the same for several parents at once: blockIdx.y = item, parents[item] = parent slot
 __global__ void __launch_bounds__(256) k_rowmax_theta_batch(const float* __restrict__ theta32, int64_t D, int64_t w_start, int64_t n_rows, int R,
                                                             const int64_t* __restrict__ srcdst, float* __restrict__ out) {

@@ -11,7 +11,8 @@ timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/$
 if [ "${2:-ncu}" = "ncu" ]; then
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/${tag}_launches.csv python bench.py --steps 1 --warmup 1 --no-extras > gpurun_out/${tag}_ncu_launch.log 2>&1; echo "ncu launches rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_member_dense" -s 10 -c 4 -o gpurun_out/${tag}_full_dense -f python bench.py --steps 1 --warmup 1 --no-extras > gpurun_out/${tag}_ncu_full_dense.log 2>&1; echo "ncu full dense rc=$?"
-timeout 900 ncu --set full --clock-control none -k regex:"k_materialise|k_refine|k_finalize|k_member_gemm|k_row_margin" -s 9 -c 10 -o gpurun_out/${tag}_full_aux -f python bench.py --steps 1 --warmup 1 --no-extras > gpurun_out/${tag}_ncu_full_aux.log 2>&1; echo "ncu full aux rc=$?"
+timeout 900 ncu --set full --clock-control none -k regex:"k_materialise|k_refine|k_finalize|k_member_gemm|k_row_margin" -c 16 -o gpurun_out/${tag}_full_aux -f python bench.py --steps 1 --warmup 1 --no-extras > gpurun_out/${tag}_ncu_full_aux.log 2>&1; echo "ncu full aux rc=$?"
+timeout 900 ncu --set full --clock-control none -k regex:"k_evolve_batch|k_rowmax_theta_batch" -c 2 -o gpurun_out/${tag}_full_evolve -f python bench.py --steps 1 --warmup 1 --no-extras > gpurun_out/${tag}_ncu_full_evolve.log 2>&1; echo "ncu full evolve rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_gradient|k_opt_update" -s 3 -c 3 -o gpurun_out/${tag}_full_master -f python bench.py --steps 1 --warmup 1 --population 148 --cpu-seconds 1 > gpurun_out/${tag}_ncu_full_master.log 2>&1; echo "ncu full master rc=$?"
 fi
 for m in hybrid exact fast; do python tools/show_bench.py gpurun_out/${tag}_bench_$m.json $m; done
