@@ -99,9 +99,15 @@ int nes_evolve_batch(nes_ctx* ctx, int n, const int32_t* src_parent, const int64
 
 /* Safe mutations (PolicyNet.evolve, algorithm/nets.py:104-111).  NES_MUT_PROPORTIONAL (the reference's "SM-PROPORTIONAL", shipped in
  * experiments/mscoco_es.json): noise = sigma * eps (.) |theta_p|, exact zeros of theta_p replaced by mean|theta_p|.  Applies to
- * nes_evolve and nes_rollout (HYBRID precision, no layer_n); K7 scales its result by the scale of parent 0. */
-enum { NES_MUT_DEFAULT = 0, NES_MUT_PROPORTIONAL = 1 };
+ * nes_evolve and nes_rollout (HYBRID precision, no layer_n); K7 scales its result by the scale of parent 0.
+ * NES_MUT_SENSITIVITY ("SM-VECTOR", and "SM-G-SUM" / "SM-G-ABS" with sensitivities computed by the caller's autograd,
+ * algorithm/nets.py:104-105, safe_mutations.py:27-32): noise = sigma * eps / sens_p, a true float32 division like the reference's;
+ * sens_p is 1 until nes_set_sensitivity supplies it. */
+enum { NES_MUT_DEFAULT = 0, NES_MUT_PROPORTIONAL = 1, NES_MUT_SENSITIVITY = 2 };
 int nes_set_mutation(nes_ctx* ctx, int kind);
+/* sens: D positive float32 divisors, host or device, as Sensitivity.set_sensitivity leaves them (clamped below at the underflow value,
+ * divided by their minimum); parent < 0 sets every parent slot. */
+int nes_set_sensitivity(nes_ctx* ctx, int parent, const float* sens);
 
 /* ---- population rollout (NESWorker.fitness nic_nes_worker.py:131-154 / ESWorker.fitness
  *      nic_es_worker.py:142-175 -> CaptPolicy.rollout captioning/policies.py:86-116 ->

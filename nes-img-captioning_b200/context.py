@@ -101,15 +101,27 @@ class NesContext:
         return out
 
     # ---- safe mutations (src/algorithm/nets.py:104-111)
-    MUTATIONS = {'': 0, 'SM-PROPORTIONAL': 1}
+    MUTATIONS = {'': 0, 'SM-PROPORTIONAL': 1, 'SM-VECTOR': 2, 'SM-G-SUM': 2, 'SM-G-ABS': 2}
 
     def set_mutation(self, kind):
-        """'' (default) or 'SM-PROPORTIONAL' (noise scaled by |theta_p|, zeros by mean|theta_p|); the gradient-based safe
-        mutations (SM-G-SUM / SM-G-ABS) need autograd and are not on the B200 path"""
+        """'' (default), 'SM-PROPORTIONAL' (noise scaled by |theta_p|, zeros by mean|theta_p|), or one of the sensitivity mutations
+        'SM-VECTOR' / 'SM-G-SUM' / 'SM-G-ABS' (noise divided by a sensitivity vector given through set_sensitivity; computing
+        the gradient-based ones needs autograd and stays with the caller)"""
         if kind not in self.MUTATIONS:
             raise NotImplementedError('mutation %r is not on the B200 path (SURVEY 8f-3)' % (kind,))
         _lib.check(self.lib.nes_set_mutation(self._h, self.MUTATIONS[kind]))
         self.mutation = kind
+
+    def set_sensitivity(self, sens, parent=None, underflow=None):
+        """sens float32 [D] (numpy / torch, host or device): noise /= sens for members of `parent` (None: every parent slot).
+        underflow given: first clamp and normalise like Sensitivity.set_sensitivity (safe_mutations.py:27-32):
+        sens[sens < underflow] = underflow; sens /= sens.min()"""
+        sens = torch.as_tensor(sens).to(torch.float32).clone().contiguous()
+        assert sens.numel() == self.D
+        if underflow is not None:
+            sens[sens < underflow] = underflow
+            sens /= sens.min()
+        _lib.check(self.lib.nes_set_sensitivity(self._h, -1 if parent is None else int(parent), _lib.ptr(sens)))
 
     # ---- theta
     def set_theta(self, vector, parent=0):

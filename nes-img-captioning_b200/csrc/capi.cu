@@ -313,6 +313,11 @@ int nes_set_mutation(nes_ctx* ctx, int kind) {
     return set_mutation(CTX(ctx), kind);
 }
 
+int nes_set_sensitivity(nes_ctx* ctx, int parent, const float* sens) {
+    NEED_CTX(ctx);
+    return set_sensitivity(CTX(ctx), parent, sens);
+}
+
 int nes_shaped_fitness(nes_ctx* ctx, int kind, int64_t n_members, int rows, const double* scores, double* out) {
     NEED_CTX(ctx); Ctx* c = CTX(ctx);
     if (cider_shaped_fitness(c, kind, n_members, rows, scores, out)) return 1;

@@ -41,9 +41,12 @@ enum { T_IMG_W = 0, T_IMG_B, T_EMB_W, T_LOGIT_W, T_LOGIT_B, T_I2H_W, T_I2H_B, T_
 
 constexpr int kAbsBlocks = 296;
 // the perturbation of one parameter: f32(sigma) * eps, times the safe-mutation scale when one is set (algorithm/nets.py:101-111)
-__device__ __forceinline__ float mut_noise(float sigma, float eps, const float* __restrict__ scale, int64_t idx) {
+// the perturbation of one parameter: sigma*eps, times the safe-mutation scale (SM-PROPORTIONAL, algorithm/nets.py:107-111) or divided by
+// the sensitivity (SM-VECTOR / SM-G-*, :104-105: noise /= sensitivity) -- a true division, as the reference's
+__device__ __forceinline__ float apply_scale(float nz, float s, int div) { return div ? __fdiv_rn(nz, s) : __fmul_rn(nz, s); }
+__device__ __forceinline__ float mut_noise(float sigma, float eps, const float* __restrict__ scale, int64_t idx, int div) {
     const float nz = __fmul_rn(sigma, eps);
-    return scale ? __fmul_rn(nz, scale[idx]) : nz;
+    return scale ? apply_scale(nz, scale[idx], div) : nz;
 }
 
 // theta / activation scaling of the split-fp16 operands (exact powers of two)
@@ -80,6 +83,7 @@ struct Ctx {
     // replaced by mean|theta_p|; s_p is refreshed whenever parent p changes (launch_theta_shadow)
     int mut_kind = 0;
     float* scale32 = nullptr;         // [n_parents, D] (nullptr: default mutation)
+    int scale_div = 0;                // 1: scale32 holds sensitivities, the noise is divided by them (NES_MUT_SENSITIVITY)
     float* d_scale_max = nullptr;     // [n_parents] max of s_p (HYBRID error bound)
     double* d_abs_partials = nullptr; // [kAbsBlocks]
 
@@ -134,6 +138,7 @@ int launch_sample_parents(Ctx* c, uint64_t iteration, int64_t F, int32_t n_paren
 int launch_bound_norms(Ctx* c, int parent);       // parent >= 0: theta_rowmax[parent]; parent < 0: eps_rowmax (decode.cu)
 int launch_theta_shadow(Ctx* c, int parent);      // theta32 -> theta_hi/lo (padded)
 int launch_prop_scale(Ctx* c, int parent);        // theta32 -> scale32 (SM-PROPORTIONAL)
+int set_sensitivity(Ctx* c, int parent, const float* sens);   // host or device vector of D divisors (parent < 0: all parents)
 int set_mutation(Ctx* c, int kind);
 int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64);
 int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, float* d_member, float* d_noise, int dst_parent);

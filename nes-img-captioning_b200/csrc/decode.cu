@@ -130,7 +130,7 @@ struct FinalizeParams {
     int rows, rows_pad, T, E, t;                 // t in 1..T (0: <bos> gather only)
     int64_t n_members;
     const int64_t* off; const float* sign; const int32_t* parent;
-    const float* theta32; const __half* table; int64_t D; const float* scale;
+    const float* theta32; const __half* table; int64_t D; const float* scale; int scale_div;
     int64_t emb_start, emb_pstart;
     float sigma;
     uint8_t* unfinished; int32_t* unf_count;     // [T+1, W]
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
         for (int u = 0; u < 4; ++u) {
             const float2 ef = __half22float2(eh[u]);
             float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
-            if (se) { n0 = __fmul_rn(n0, se[e + 2 * u]); n1 = __fmul_rn(n1, se[e + 2 * u + 1]); }
+            if (se) { n0 = apply_scale(n0, se[e + 2 * u], p.scale_div); n1 = apply_scale(n1, se[e + 2 * u + 1], p.scale_div); }
             const float x0 = __fmaf_rn(tv[2 * u], kActScale, n0), x1 = __fmaf_rn(tv[2 * u + 1], kActScale, n1);
             hh[u] = __floats2half2_rn(x0, x1);
             const float2 hf = __half22float2(hh[u]);
@@ -574,7 +574,7 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
     ProfScope prof(c, PROF_MATERIALISE);
     auto mat = [&](int wt, int K, int out_rows, int mode, int src_rows, __half* hi, __half* lo) {
         MatParams q{};
-        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32;
+        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32; q.scale_div = c->scale_div;
         q.w_start = L.t[wt].start; q.w_pstart = L.t[wt].pstart; q.K = K; q.out_rows = out_rows; q.mode = mode; q.R = ws->R; q.src_rows = src_rows;
         q.sigma = sigma; q.hi = hi; q.lo = lo; q.n_members = nm;
         const dim3 grid((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(nm < 32768 ? nm : 32768));
@@ -585,7 +585,7 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
     auto matb = [&](int b0, int b1, int out_cols, int mode, int src_n, float* out, int64_t out_stride = 0, int64_t out_off = 0) {
         MatBiasParams q{};
         q.out_stride = out_stride; q.out_off = out_off;
-        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32;
+        q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32; q.scale_div = c->scale_div;
         q.b_start[0] = L.t[b0].start; q.b_pstart[0] = L.t[b0].pstart; q.nb = 1;
         if (b1 >= 0) { q.b_start[1] = L.t[b1].start; q.b_pstart[1] = L.t[b1].pstart; q.nb = 2; }
         q.out_cols = out_cols; q.mode = mode; q.R = ws->R; q.src_n = src_n; q.sigma = sigma; q.out = out; q.n_members = nm;
@@ -862,7 +862,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     RefineParams rf{};
                     rf.heads = ws->heads; rf.entries = ws->entries; rf.margin = ws->margin; rf.h_hi = ws->h_hi[hb]; rf.h_lo = ws->h_lo[hb]; rf.R = R; rf.V1 = V1;
                     rf.rows = rows; rf.rows_pad = rows_pad; rf.m_tiles = m_tiles; rf.n_members = nm;
-                    rf.off = base.off; rf.sign = base.sign; rf.parent = base.parent; rf.theta32 = c->theta32; rf.table = c->table; rf.D = L.D; rf.scale = c->scale32;
+                    rf.off = base.off; rf.sign = base.sign; rf.parent = base.parent; rf.theta32 = c->theta32; rf.table = c->table; rf.D = L.D; rf.scale = c->scale32; rf.scale_div = c->scale_div;
                     rf.w_start = L.t[T_LOGIT_W].start; rf.w_pstart = L.t[T_LOGIT_W].pstart; rf.b_start = L.t[T_LOGIT_B].start; rf.b_pstart = L.t[T_LOGIT_B].pstart;
                     rf.sigma = sigma; rf.tok = ws->pre_tok; rf.lp = ws->pre_lp; rf.unit_flag = ws->unit_flag; rf.stats = c->profiling ? ws->stats : nullptr;
                     rf.force_overflow = (env_debug() & 64) ? 1 : 0;
@@ -896,7 +896,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             if (t < T || t >= 1) {
                 FinalizeParams f{};
                 f.partials = ws->partials; f.n_tiles = 2; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
-                f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table; f.scale = c->scale32;
+                f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table; f.scale = c->scale32; f.scale_div = c->scale_div;
                 f.D = L.D; f.emb_start = L.t[T_EMB_W].start; f.emb_pstart = L.t[T_EMB_W].pstart; f.sigma = sigma;
                 f.unfinished = ws->unfinished; f.unf_count = ws->unf_count; f.W = ws->W;
                 f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;

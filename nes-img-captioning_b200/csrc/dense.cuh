@@ -389,7 +389,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
 struct MatParams {
     const int64_t* off; const float* sign; const int32_t* parent;
     const float* theta32; const __half* table; int64_t D;
-    const float* scale;                     // nullable: safe-mutation scale [n_parents, D]
+    const float* scale; int scale_div;      // nullable: safe-mutation scale [n_parents, D] (scale_div: divide by it)
     int64_t w_start, w_pstart;
     int32_t K, out_rows, mode, R, src_rows;
     float sigma;
@@ -471,7 +471,7 @@ __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
                         for (int e = 0; e < 4; ++e) {
                             const float2 ef = __half22float2(eh[e]);
                             float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
-                            if (SCALED) { n0 = __fmul_rn(n0, __ldg(sc + 2 * e)); n1 = __fmul_rn(n1, __ldg(sc + 2 * e + 1)); }
+                            if (SCALED) { n0 = apply_scale(n0, __ldg(sc + 2 * e), p.scale_div); n1 = apply_scale(n1, __ldg(sc + 2 * e + 1), p.scale_div); }
                             const float x0 = __fmaf_rn(tv[b][2 * e], kThetaScale, n0), x1 = __fmaf_rn(tv[b][2 * e + 1], kThetaScale, n1);
                             hh[e] = __floats2half2_rn(x0, x1);
                             if (HAS_LO) {
@@ -494,7 +494,7 @@ __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
 // member biases in accumulator-column order: LSTM (mode 1) = (b_i2h +- sigma eps) + (b_h2h +- sigma eps); logit (mode 0)
 struct MatBiasParams {
     const int64_t* off; const float* sign; const int32_t* parent;
-    const float* theta32; const __half* table; int64_t D; const float* scale;
+    const float* theta32; const __half* table; int64_t D; const float* scale; int scale_div;
     int64_t b_start[2], b_pstart[2]; int32_t nb;
     int32_t out_cols, mode, R, src_n;
     float sigma; float* out; int64_t n_members;
@@ -518,7 +518,7 @@ __global__ void __launch_bounds__(256) k_materialise_bias(const MatBiasParams p)
             const int64_t off = p.off[member];
             for (int s = 0; s < p.nb; ++s) {
                 const float tb = p.theta32[par * p.D + p.b_start[s] + n];
-                const float nz = mut_noise(p.sigma, __half2float(p.table[off + p.b_pstart[s] + n]), p.scale, par * p.D + p.b_start[s] + n);
+                const float nz = mut_noise(p.sigma, __half2float(p.table[off + p.b_pstart[s] + n]), p.scale, par * p.D + p.b_start[s] + n, p.scale_div);
                 b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
             }
         }

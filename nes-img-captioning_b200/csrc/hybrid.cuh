@@ -105,7 +105,7 @@ struct RefineParams {
     const CandHead* heads; const CandEntry* entries; const float* margin;
     const __half *h_hi, *h_lo; int R, V1; int rows, rows_pad, m_tiles; int64_t n_members;
     const int64_t* off; const float* sign; const int32_t* parent;
-    const float* theta32; const __half* table; int64_t D; const float* scale;
+    const float* theta32; const __half* table; int64_t D; const float* scale; int scale_div;
     int64_t w_start, w_pstart, b_start, b_pstart;     // logit.weight / logit.bias: flat and padded starts
     float sigma;
     int32_t* tok; float* lp;                          // [member*rows_pad + row]: arg-max column and its log-prob
@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
                 for (int e = 0; e < 4; ++e) {
                     const float2 ef = __half22float2(he[e]);
                     float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
-                    if (sw) { n0 = __fmul_rn(n0, sw[k + 2 * e]); n1 = __fmul_rn(n1, sw[k + 2 * e + 1]); }
+                    if (sw) { n0 = apply_scale(n0, sw[k + 2 * e], p.scale_div); n1 = apply_scale(n1, sw[k + 2 * e + 1], p.scale_div); }
                     acc = fmaf(xs[c2][2 * e], __fadd_rn(tv[2 * e], n0), acc);
                     acc = fmaf(xs[c2][2 * e + 1], __fadd_rn(tv[2 * e + 1], n1), acc);
                 }
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
         }
         acc = warp_sum(acc);
         const float tb = p.theta32[(int64_t)par * p.D + p.b_start + j];
-        const float nzb = mut_noise(ssig, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j);
+        const float nzb = mut_noise(ssig, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j, p.scale_div);
         const float v = acc + __fadd_rn(tb, nzb);
         if (lane == c) my_val = v;
     }
@@ -247,13 +247,13 @@ __global__ void __launch_bounds__(256) k_exact_rows(const RefineParams p) {
         float acc = 0.f;
         for (int k = lane; k < p.R; k += 32) {
             const float x = (__half2float(p.h_hi[grow * p.R + k]) + __half2float(p.h_lo[grow * p.R + k])) * (1.0f / kActScale);
-            const float nz = mut_noise(p.sigma, __half2float(ew[k]), p.scale, (int64_t)par * p.D + p.w_start + (int64_t)j * p.R + k);
+            const float nz = mut_noise(p.sigma, __half2float(ew[k]), p.scale, (int64_t)par * p.D + p.w_start + (int64_t)j * p.R + k, p.scale_div);
             acc = fmaf(x, sgn > 0.f ? __fadd_rn(tw[k], nz) : __fsub_rn(tw[k], nz), acc);
         }
         acc = warp_sum(acc);
         if (lane == 0) {
             const float tb = p.theta32[(int64_t)par * p.D + p.b_start + j];
-            const float nzb = mut_noise(p.sigma, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j);
+            const float nzb = mut_noise(p.sigma, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j, p.scale_div);
             s_logit[j] = acc + (sgn > 0.f ? __fadd_rn(tb, nzb) : __fsub_rn(tb, nzb));
         }
     }

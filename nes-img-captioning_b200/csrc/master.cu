@@ -122,8 +122,8 @@ __global__ void __launch_bounds__(256) k_gradient(const __half* __restrict__ tab
 
 // with a safe-mutation scale the reference sums w_i * (sigma eps_i (.) s); the scale is common to all rows, so it is applied
 // once to the sum (agrees to float32 round-off, within the 1e-5 the update is held to)
-__global__ void __launch_bounds__(256) k_scale_vec(float* __restrict__ g, const float* __restrict__ s, int64_t D) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += (int64_t)gridDim.x * blockDim.x) g[i] = __fmul_rn(g[i], s[i]);
+__global__ void __launch_bounds__(256) k_scale_vec(float* __restrict__ g, const float* __restrict__ s, int64_t D, int div) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += (int64_t)gridDim.x * blockDim.x) g[i] = apply_scale(g[i], s[i], div);
 }
 int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g, int shard, int n_shards) {
     GradPlan plan; plan.n = c->lay.n; plan.vec_prefix[0] = 0;
@@ -139,7 +139,7 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
     unsigned grid = (unsigned)((v_hi - v_lo + 255) / 256);
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_a, c->stream));
     if (grid) k_gradient<8><<<grid, 256, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
-    if (c->scale32) { k_scale_vec<<<148 * 8, 256, 0, c->stream>>>(d_g, c->scale32, c->lay.D); c->launches++; }
+    if (c->scale32) { k_scale_vec<<<148 * 8, 256, 0, c->stream>>>(d_g, c->scale32, c->lay.D, c->scale_div); c->launches++; }
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_b, c->stream));
     c->launches++;
     NES_CUDA(cudaGetLastError());

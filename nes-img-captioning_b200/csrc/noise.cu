@@ -143,10 +143,10 @@ int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64) {
 // noise = f32(sigma) * f32(eps) ; member = theta + noise  (sign<0: theta - noise, nic_nes_worker.py:151)
 __global__ void __launch_bounds__(256) k_evolve(const float* __restrict__ th, const __half* __restrict__ row, const Layout* __restrict__ lay,
                                                 float sign, float sigma, float* __restrict__ member, float* __restrict__ noise,
-                                                double* __restrict__ dst64, float* __restrict__ dst32, const float* __restrict__ scale) {
+                                                double* __restrict__ dst64, float* __restrict__ dst32, const float* __restrict__ scale, int scale_div) {
     const TensorDesc t = lay->t[blockIdx.y];
     for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < t.count; j += (int64_t)gridDim.x * blockDim.x) {
-        float nz = mut_noise(sigma, __half2float(row[t.pstart + j]), scale, t.start + j);
+        float nz = mut_noise(sigma, __half2float(row[t.pstart + j]), scale, t.start + j, scale_div);
         float th0 = th[t.start + j];
         float m = sign > 0.f ? __fadd_rn(th0, nz) : __fsub_rn(th0, nz);
         if (noise)  noise[t.start + j] = nz;
@@ -162,7 +162,7 @@ int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, f
     k_evolve<<<grid, 256, 0, c->stream>>>(c->theta32 + parent * D, c->table + offset, c->d_lay, sign, sigma, d_member, d_noise,
                                           dst_parent >= 0 ? c->theta64 + dst_parent * D : nullptr,
                                           dst_parent >= 0 ? c->theta32 + dst_parent * D : nullptr,
-                                          c->scale32 ? c->scale32 + parent * D : nullptr);
+                                          c->scale32 ? c->scale32 + parent * D : nullptr, c->scale_div);
     c->launches++;
     NES_CUDA(cudaGetLastError());
     if (dst_parent >= 0) { c->theta_is_f32[dst_parent] = 1; return launch_theta_shadow(c, dst_parent); }
@@ -174,7 +174,7 @@ int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, f
 __global__ void __launch_bounds__(256) k_evolve_batch(float* theta32, double* __restrict__ theta64, __half* __restrict__ th_hi,
                                                       __half* __restrict__ th_lo, const __half* __restrict__ table, const Layout* __restrict__ lay,
                                                       const int64_t* __restrict__ offs, const float* __restrict__ sigmas, const int64_t* __restrict__ srcdst,
-                                                      const float* __restrict__ scale) {
+                                                      const float* __restrict__ scale, int scale_div) {
     const int k = blockIdx.y;
     const int item = blockIdx.z;
     const TensorDesc t = lay->t[k];
@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(256) k_evolve_batch(float* theta32, double* __
         __align__(16) __half hl[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-            m[e] = __fadd_rn(tv[e], mut_noise(sigma, __half2float(eh[e]), sc, t.start + j + e));
+            m[e] = __fadd_rn(tv[e], mut_noise(sigma, __half2float(eh[e]), sc, t.start + j + e, scale_div));
             split_half(m[e], kThetaScale, hh[e], hl[e]);
         }
         reinterpret_cast<float4*>(d32 + j)[0] = *reinterpret_cast<float4*>(&m[0]);
@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(256) k_evolve_batch(float* theta32, double* __
     for (int64_t j = n8 * 8 + tid; j < span; j += nth) {          // ragged tail, unaligned tensors, zero padding of the shadow
         __half a = __float2half_rn(0.f), b = a;
         if (j < t.count) {
-            const float m = __fadd_rn(th[j], mut_noise(sigma, __half2float(row[j]), sc, t.start + j));
+            const float m = __fadd_rn(th[j], mut_noise(sigma, __half2float(row[j]), sc, t.start + j, scale_div));
             d32[j] = m;
             d64[j] = (double)m;
             split_half(m, kThetaScale, a, b);
@@ -247,7 +247,7 @@ int launch_evolve_batch(Ctx* c, int n, const int32_t* src, const int64_t* offset
     NES_CUDA(cudaMemcpyAsync(c->d_ranks, packed.data(), sizeof(int64_t) * n, cudaMemcpyDefault, c->stream));
     NES_CUDA(cudaStreamSynchronize(c->stream));            // `packed` is a stack-lifetime host buffer
     dim3 grid(148, c->lay.n, n);
-    k_evolve_batch<<<grid, 256, 0, c->stream>>>(c->theta32, c->theta64, c->theta_hi, c->theta_lo, c->table, c->d_lay, c->d_offsets, c->d_weights, c->d_ranks, c->scale32);
+    k_evolve_batch<<<grid, 256, 0, c->stream>>>(c->theta32, c->theta64, c->theta_hi, c->theta_lo, c->table, c->d_lay, c->d_offsets, c->d_weights, c->d_ranks, c->scale32, c->scale_div);
     c->launches++;
     NES_CUDA(cudaGetLastError());
     for (int i = 0; i < n; ++i) {
@@ -256,6 +256,10 @@ int launch_evolve_batch(Ctx* c, int n, const int32_t* src, const int64_t* offset
     }
     if (c->is_fc) return launch_bound_norms_batch(c, dst, n);
     return 0;
+}
+
+__global__ void __launch_bounds__(256) k_fill_f32(float* __restrict__ p, int64_t n, float v) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
 
 // ---- SM-PROPORTIONAL scale (algorithm/nets.py:107-111): params = theta.clone(); params[params == 0] = mean(|theta|); noise *= |params|
@@ -296,21 +300,51 @@ int launch_prop_scale(Ctx* c, int parent) {
     return 0;
 }
 int set_mutation(Ctx* c, int kind) {
-    NES_CHECK(kind == NES_MUT_DEFAULT || kind == NES_MUT_PROPORTIONAL, "only the default and SM-PROPORTIONAL mutations run on the device");
-    NES_CHECK(!(kind == NES_MUT_PROPORTIONAL && c->is_fc && c->dims.layer_n), "SM-PROPORTIONAL with layer_n is not supported");
+    NES_CHECK(kind == NES_MUT_DEFAULT || kind == NES_MUT_PROPORTIONAL || kind == NES_MUT_SENSITIVITY, "unknown mutation kind");
+    NES_CHECK(!(kind != NES_MUT_DEFAULT && c->is_fc && c->dims.layer_n), "safe mutations with layer_n / vbn are not supported");
     if (kind == c->mut_kind) return 0;
     NES_CUDA(cudaStreamSynchronize(c->stream));
-    if (kind == NES_MUT_PROPORTIONAL) {
-        NES_CUDA(cudaMalloc((void**)&c->scale32, sizeof(float) * (size_t)c->n_parents * c->lay.D));
-        NES_CUDA(cudaMalloc((void**)&c->d_scale_max, sizeof(float) * c->n_parents));
-        NES_CUDA(cudaMalloc((void**)&c->d_abs_partials, sizeof(double) * kAbsBlocks));
-        c->mut_kind = kind;
-        for (int p = 0; p < c->n_parents; ++p) if (launch_prop_scale(c, p)) return 1;
-    } else {
+    if (c->scale32) {
         cudaFree(c->scale32); cudaFree(c->d_scale_max); cudaFree(c->d_abs_partials);
         c->scale32 = nullptr; c->d_scale_max = nullptr; c->d_abs_partials = nullptr;
-        c->mut_kind = kind;
     }
+    c->mut_kind = kind;
+    c->scale_div = kind == NES_MUT_SENSITIVITY ? 1 : 0;
+    if (kind == NES_MUT_DEFAULT) return 0;
+    NES_CUDA(cudaMalloc((void**)&c->scale32, sizeof(float) * (size_t)c->n_parents * c->lay.D));
+    NES_CUDA(cudaMalloc((void**)&c->d_scale_max, sizeof(float) * c->n_parents));
+    NES_CUDA(cudaMalloc((void**)&c->d_abs_partials, sizeof(double) * kAbsBlocks));
+    if (kind == NES_MUT_PROPORTIONAL) {
+        for (int p = 0; p < c->n_parents; ++p) if (launch_prop_scale(c, p)) return 1;
+    } else {                                   // sensitivities of 1 until nes_set_sensitivity supplies them
+        k_fill_f32<<<148 * 8, 256, 0, c->stream>>>(c->scale32, (int64_t)c->n_parents * c->lay.D, 1.0f);
+        k_fill_f32<<<1, 256, 0, c->stream>>>(c->d_scale_max, c->n_parents, 1.0f);
+        c->launches += 2;
+        NES_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
+
+// sensitivities of one parent (parent < 0: of every parent): noise /= sens.  scale_max = max 1/sens bounds the multiplier for the
+// HYBRID error margin.
+__global__ void __launch_bounds__(256) k_inv_max(const float* __restrict__ s, int64_t D, float* __restrict__ out) {
+    float mx = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += (int64_t)gridDim.x * blockDim.x) mx = fmaxf(mx, fabsf(__fdiv_rn(1.0f, s[i])));
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<int*>(out), __float_as_int(mx));
+}
+int set_sensitivity(Ctx* c, int parent, const float* sens) {
+    NES_CHECK(c->mut_kind == NES_MUT_SENSITIVITY && c->scale32, "call nes_set_mutation(NES_MUT_SENSITIVITY) first");
+    NES_CHECK(sens != nullptr && parent < c->n_parents, "bad sensitivity argument");
+    const int64_t D = c->lay.D;
+    for (int p = (parent < 0 ? 0 : parent); p < (parent < 0 ? c->n_parents : parent + 1); ++p) {
+        NES_CUDA(cudaMemcpyAsync(c->scale32 + (int64_t)p * D, sens, sizeof(float) * D, cudaMemcpyDefault, c->stream));
+        NES_CUDA(cudaMemsetAsync(c->d_scale_max + p, 0, sizeof(float), c->stream));
+        k_inv_max<<<kAbsBlocks, 256, 0, c->stream>>>(c->scale32 + (int64_t)p * D, D, c->d_scale_max + p);
+        c->launches++;
+    }
+    NES_CUDA(cudaGetLastError());
+    NES_CUDA(cudaStreamSynchronize(c->stream));          // sens may be a pageable host buffer
     return 0;
 }
 

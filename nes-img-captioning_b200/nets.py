@@ -38,9 +38,12 @@ class PolicyNet:
         self.ctx, self.parent = ctx, int(parent)
         sm = options.get('safe_mutations') if isinstance(options, dict) else getattr(options, 'safe_mutations', None)
         self.mutations = Mutation(sm or '')
-        if self.mutations not in (Mutation.DEFAULT, Mutation.SAFE_PROPORTIONAL):
-            raise NotImplementedError('gradient / vector safe mutations are not on the B200 path (SURVEY 8f-3)')
         ctx.set_mutation(self.mutations.value)        # context-wide: every parent slot mutates the same way
+        self._underflow = (options.get('safe_mutation_underflow') if isinstance(options, dict) else getattr(options, 'safe_mutation_underflow', None)) or 0.01
+        if self.mutations == Mutation.SAFE_VECTOR:     # algorithm/nets.py:49-50
+            vec = options.get('safe_mutation_vector') if isinstance(options, dict) else getattr(options, 'safe_mutation_vector', None)
+            if vec is not None and not (isinstance(vec, (int, float)) and not vec):
+                self.set_sensitivity_vector(vec)
         if vbn and ctx.dims is not None and ctx.dims['layer_n'] != 2:
             raise AssertionError('vbn=True needs a context created with model_options.vbn')
         self.nb_learnable_params = ctx.D
@@ -99,7 +102,24 @@ class PolicyNet:
         self.load_state_dict(torch.load(serialized, map_location='cpu'))
 
     def calc_sensitivity(self, *a, **k):
-        return None     # no-op for Mutation.DEFAULT, like the reference (nets.py:121-123)
+        """no-op unless the mutation is gradient based, like the reference (nets.py:121-123); the Jacobian of SM-G-SUM / SM-G-ABS
+        (safe_mutations.py:34-117) needs autograd: compute it with PyTorch and hand the vector to set_sensitivity_vector"""
+        if self.mutations in (Mutation.SAFE_GRAD_SUM, Mutation.SAFE_GRAD_ABS):
+            raise NotImplementedError('compute the output-gradient sensitivity with autograd and pass it to set_sensitivity_vector')
+        return None
+
+    def set_sensitivity_vector(self, vector):
+        """algorithm/nets.py:125-126 -> Sensitivity.set_sensitivity (safe_mutations.py:27-32): a path to a torch-saved vector, or
+        the vector itself; clamped below at safe_mutation_underflow and divided by its minimum, then noise /= sensitivity"""
+        if isinstance(vector, str):
+            vector = torch.load(vector, map_location='cpu')
+        self._sensitivity = torch.as_tensor(vector).to(torch.float32).clone()
+        self._sensitivity[self._sensitivity < self._underflow] = self._underflow
+        self._sensitivity /= self._sensitivity.min()
+        self.ctx.set_sensitivity(self._sensitivity, parent=self.parent if self.mutations != Mutation.SAFE_VECTOR else None)
+
+    def get_sensitivity_vector(self):
+        return getattr(self, '_sensitivity', None)
 
 
 class FCModel(PolicyNet):

@@ -182,12 +182,23 @@ def proportional_scale(theta):
     return np.where(theta == 0, np.abs(mean), np.abs(theta)).astype(np.float32)
 
 
-def member_theta(theta, eps, sigma, sign, scale=None):
+def sensitivity_vector(raw, underflow):
+    """Sensitivity.set_sensitivity (src/algorithm/safe_mutations.py:27-32): clamp below at the underflow value, divide by the minimum"""
+    s = np.asarray(raw, dtype=np.float32).copy()
+    s[s < np.float32(underflow)] = np.float32(underflow)
+    s /= s.min()
+    return s
+
+
+def member_theta(theta, eps, sigma, sign, scale=None, sens=None):
     """theta +/- float32(sigma)*eps in float32 (src/algorithm/nets.py:113,
-    src/algorithm/nic_nes/nic_nes_worker.py:151); with a safe-mutation scale the noise is multiplied by it first (:104-111)."""
+    src/algorithm/nic_nes/nic_nes_worker.py:151); with a safe-mutation scale the noise is multiplied by it first (:107-111),
+    with a sensitivity vector divided by it (:104-105)."""
     noise = np.float32(sigma) * eps.astype(np.float32)
     if scale is not None:
         noise = noise * scale.astype(np.float32)
+    if sens is not None:
+        noise = noise / sens.astype(np.float32)
     return (theta + noise) if sign > 0 else (theta - noise), noise
 
 

@@ -159,6 +159,34 @@ def check_proportional(ref, seed=3):
     return True
 
 
+def check_sensitivity(ref, seed=5):
+    """SM-VECTOR: oracle sensitivity_vector + division against the reference's PolicyNet.evolve with a sensitivity file
+    (algorithm/nets.py:49-50,104-105, safe_mutations.py:27-32): bit-exact"""
+    import tempfile, os
+    from algorithm.nets import Mutation
+    rs = np.random.RandomState(seed)
+    D = fc_caption.Dims(199, 64, 64, 128).num_params()
+    raw_sens = np.abs(rs.randn(D)).astype(np.float32) * 0.05          # many entries below the 0.01 underflow
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, 'sens.pt')
+        torch.save(torch.from_numpy(raw_sens.copy()), path)
+        opt = ref.ModelOptions(vocab_size=199, input_encoding_size=64, rnn_size=64, fc_feat_size=128, safe_mutations='SM-VECTOR',
+                               safe_mutation_vector=path, safe_mutation_underflow=0.01)
+        torch.manual_seed(seed)
+        model = ref.FCModel(options=opt)
+    assert model.mutations == Mutation.SAFE_VECTOR
+    theta = model.parameter_vector().numpy().copy()
+    sens = noise.sensitivity_vector(raw_sens, 0.01)
+    assert np.array_equal(model.get_sensitivity_vector().numpy(), sens)
+    torch.manual_seed(seed + 1)
+    raw = torch.empty(theta.size).normal_(mean=0.0, std=0.25).numpy().copy()
+    torch.manual_seed(seed + 1)
+    got = model.evolve(0.25)
+    assert np.array_equal(got, raw / sens)
+    assert np.array_equal(model.parameter_vector().numpy(), theta + raw / sens)
+    return True
+
+
 def main():
     if not _refimport.available():
         print('reference not present; nothing checked'); return 1
@@ -174,8 +202,8 @@ def main():
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)
     assert fc_caption.Dims(9487, 128, 128, 2048).num_params() == 2865808
     assert fc_caption.Dims(9487, 512, 512, 2048).num_params() == 13400848
-    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref); check_sample_decode(ref)
-    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL, sampled decode OK' % n)
+    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref); check_sample_decode(ref); check_sensitivity(ref)
+    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL, SM-VECTOR, sampled decode OK' % n)
     return 0
 
 

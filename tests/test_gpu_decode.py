@@ -417,3 +417,57 @@ def test_rollout_rejects_bad_arguments():
     seq, lp = ctx.rollout(np.zeros(0, dtype=np.int64), np.zeros(0, dtype=np.float32), np.zeros((4, 64), dtype=np.float32), 0.0)
     assert tuple(seq.shape) == (0, 4, 16)
     ctx.close()
+
+
+def test_sensitivity_mutation_evolve_rollout_and_policy(monkeypatch, tmp_path):
+    """SM-VECTOR / externally computed SM-G-* sensitivities (algorithm/nets.py:104-105, safe_mutations.py:27-32): noise /= sens, a true
+    float32 division.  nes_evolve bit-exact, HYBRID rollout (incl. the forced fallback) and the survivor path against the oracle,
+    per-parent sensitivities, and PolicyNet(safe_mutations='SM-VECTOR', safe_mutation_vector=file)."""
+    import nes_b200
+    V, E, R, Fd, B, dims, G, play, D, D_pad = _prop_case()
+    ctx = nes_b200.NesContext(dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd), seed=31, table_len=D_pad + 63 * G, n_parents=3, wave_members=4, rows=B)
+    thetas = [fc_caption.xavier_theta(dims, 60), fc_caption.xavier_theta(dims, 61)]
+    ctx.set_theta(thetas[0], 0); ctx.set_theta(thetas[1], 1)
+    rs = np.random.RandomState(4)
+    raw = [np.abs(rs.randn(D)).astype(np.float32) * 0.05, np.abs(rs.randn(D)).astype(np.float32) * 0.2]
+    sens = [noise.sensitivity_vector(r, 0.01) for r in raw]
+    ctx.set_mutation('SM-G-SUM')
+    offs = ctx.sample_offsets(4, 5).numpy()
+    sigma = 0.05
+    m0, _ = ctx.evolve(int(offs[0]), sigma, 1.0, parent=0)                        # sensitivities default to 1: the plain mutation
+    assert np.array_equal(m0.numpy(), noise.member_theta(thetas[0], noise.noise_row(31, offs[0], play, D), sigma, +1)[0])
+    ctx.set_sensitivity(raw[0], parent=0, underflow=0.01)
+    ctx.set_sensitivity(sens[1], parent=1)
+    member, nz = ctx.evolve(int(offs[0]), sigma, -1.0, parent=1)
+    want_m, want_nz = noise.member_theta(thetas[1], noise.noise_row(31, offs[0], play, D), sigma, -1, sens=sens[1])
+    assert np.array_equal(nz.numpy(), want_nz) and np.array_equal(member.numpy(), want_m)
+    fc = noise.table_slice(14, 0, B * Fd).astype(np.float32).reshape(B, Fd)
+    parents = np.array([0, 1, 1, 0, 1], dtype=np.int32)
+    signs = np.array([1, -1, 1, 1, -1], dtype=np.float32)
+    for dbg in ('0', '64'):
+        monkeypatch.setenv('NES_DEBUG', dbg)
+        seq, lp = ctx.rollout(offs, signs, fc, sigma, parents=parents, precision=nes_b200.PREC_HYBRID)
+        for i in range(5):
+            th, _ = noise.member_theta(thetas[parents[i]], noise.noise_row(31, offs[i], play, D), sigma, int(signs[i]), sens=sens[parents[i]])
+            s_, l_ = fc_caption.decode_greedy(dims, th, fc)
+            assert np.array_equal(seq[i].numpy(), s_), (dbg, i, (seq[i].numpy() != s_).sum())
+            assert np.allclose(lp[i].numpy(), l_, rtol=1e-4, atol=1e-5)
+    monkeypatch.setenv('NES_DEBUG', '0')
+    # survivors: one by one and batched, from parent 1 into slot 2
+    ctx.evolve(int(offs[1]), sigma, 1.0, parent=1, dst_parent=2, want_member=False, want_noise=False)
+    new2, _ = noise.member_theta(thetas[1], noise.noise_row(31, offs[1], play, D), sigma, +1, sens=sens[1])
+    assert np.array_equal(ctx.get_theta(2).numpy(), new2)
+    ctx.evolve_batch([1], [int(offs[2])], [sigma], [2])
+    assert np.array_equal(ctx.get_theta(2).numpy(), noise.member_theta(thetas[1], noise.noise_row(31, offs[2], play, D), sigma, +1, sens=sens[1])[0])
+    ctx.close()
+    # the reference's way in: a torch-saved vector named by model_options.safe_mutation_vector
+    path = str(tmp_path / 'sens.pt')
+    torch.save(torch.from_numpy(raw[0].copy()), path)
+    model = nes_b200.FCModel(options=dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd, safe_mutations='SM-VECTOR',
+                                          safe_mutation_vector=path, safe_mutation_underflow=0.01), rng_state=3, seed=31, table_len=D_pad + 63 * G, wave_members=2, rows=B)
+    assert np.array_equal(model.get_sensitivity_vector().numpy(), sens[0])
+    th0 = model.parameter_vector().numpy().copy()
+    got_nz = model.evolve(sigma, offset=int(offs[3]))
+    want_m, want_nz = noise.member_theta(th0, noise.noise_row(31, offs[3], play, D), sigma, +1, sens=sens[0])
+    assert np.array_equal(got_nz, want_nz) and np.array_equal(model.parameter_vector().numpy(), want_m)
+    model.ctx.close()

@@ -222,3 +222,25 @@ def test_gradient_shards_are_disjoint_and_sum_to_the_whole(g1, n_shards):
     g = sum(ctx.gradient(offs, None, 0.01, out_device='cuda', shard=(r, n_shards)) for r in range(n_shards))
     r_c = ctx.opt_update(g, 1e-7)
     assert r_a == r_c and np.array_equal(th_a, ctx.get_theta(dtype=torch.float64).numpy())
+
+
+def test_gradient_with_sensitivity_divisor():
+    """K7 under the sensitivity mutations: g = sum_i w_i (sigma eps_i / sens) / (2F); the common divisor is applied to the sum"""
+    import nes_b200
+    from oracle import nes_math, noise
+    D = 5000
+    ctx = nes_b200.NesContext(counts=[D], seed=11, table_len=1 << 20)
+    theta = (np.random.RandomState(0).randn(D) * 0.05).astype(np.float32)
+    ctx.set_theta(theta)
+    ctx.set_mutation('SM-VECTOR')
+    sens = noise.sensitivity_vector(np.abs(np.random.RandomState(2).randn(D)).astype(np.float32), 0.01)
+    ctx.set_sensitivity(sens)
+    F = 37
+    offs = ctx.sample_offsets(2, F).numpy()
+    fit = np.random.RandomState(1).randn(F, 2)
+    play, D_, D_pad = noise.padded_layout([('t0', (D,), 0, D)], 64)
+    nz = np.stack([noise.member_theta(theta, noise.noise_row(11, o, play, D), 0.1, +1, sens=sens)[1] for o in offs])
+    want = nes_math.gradient_estimate(fit, nz)
+    got = nes_b200.NESMaster(ctx).gradient_estimate(fit, offs, 0.1)
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-9)
+    ctx.close()
