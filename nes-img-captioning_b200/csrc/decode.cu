@@ -528,7 +528,6 @@ static int launch_gemm(Ctx* c, GemmParams& p, int64_t n_members) {
     const int64_t units = n_members * p.m_tiles;
     NES_CHECK(units >= 1 && units < (1ll << 31), "bad unit count");
     p.n_units = (int32_t)units;
-    p.debug = env_debug();
     // persistent: one CTA per SM, CTA b owns units b, b + grid, ... and sweeps every weight tile of each
     const int sms = sm_count(c);
     const unsigned grid = (unsigned)(units < sms ? units : sms);
@@ -543,7 +542,7 @@ static int launch_gemm_prec(Ctx* c, GemmParams& p, int64_t n_members, int prec) 
     return prec == NES_PREC_EXACT ? launch_gemm<EPI, NES_PREC_EXACT>(c, p, n_members) : launch_gemm<EPI, NES_PREC_FAST>(c, p, n_members);
 }
 
-static int env_debug() { const char* e = getenv("NES_DEBUG"); return e ? atoi(e) : 0; }     // experiments / tests only
+static int env_debug() { const char* e = getenv("NES_DEBUG"); return e ? atoi(e) : 0; }     // tests: bit 6 (64) sends every row through the HYBRID fallback
 template <int EPI>
 static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
     using C = DenseCfg<EPI>;
@@ -555,7 +554,6 @@ static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
     const int64_t units = n_members * p.m_tiles;
     NES_CHECK(units >= 1 && units < (1ll << 31), "bad unit count");
     p.n_units = (int32_t)units;
-    p.debug = env_debug();
     const int sms = sm_count(c);
     const int64_t items = EPI != DEN_LOGITC ? units * p.n_tiles : units;   // see k_member_dense: LSTM / PLAIN work items are (unit, tile) pairs
     NES_CHECK(items < (1ll << 31), "too many work items");

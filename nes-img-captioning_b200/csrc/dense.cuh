@@ -40,7 +40,6 @@ struct alignas(64) DenseParams {
     float* c_state; __half* out_hi; __half* out_lo; float* h_trace;       // LSTM (PLAIN: out_hi / out_lo and / or out_f32)
     float* out_f32; int32_t ld_out;                                       // PLAIN: [member*rows_pad + row, ld_out] float32 (nullable)
     CandHead* heads; CandEntry* entries; const float* margin;            // LOGITC
-    int32_t debug;
 };
 
 template <int EPI> struct DenseCfg {
@@ -255,7 +254,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                 tc::mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
                 tc::tc_fence_after();
                 const uint32_t trow = tmem_base + buf * C::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
-                if (!(p.debug & 1)) {
+                {
                 if (C::LSTM) {
 #pragma unroll
                     for (int sb = 0; sb < 3; ++sb) {
@@ -365,7 +364,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                         }
                     }
                 }
-                }   // !debug
+                }
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&tempty_bar[buf]);

@@ -64,7 +64,6 @@ struct GemmParams {
     float* logit_trace; int64_t ld_trace;    // nullable, [member*rows + row, ld_trace]
     float tie_delta;                         // one float32 ulp of log(V+1)
     const uint8_t* unit_mask;                // nullable: only units with a non-zero flag are computed (HYBRID fallback)
-    int32_t debug;                           // experiments: bit 0 = skip the epilogue work (timing only, wrong results)
 };
 
 template <int EPI, int PREC> struct GemmCfg {
@@ -153,12 +152,9 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                             if (((q++) & 1) != pid) { if (++stage == C::STAGES) { stage = 0; phase ^= 1; } continue; }
                             tc::mbar_wait(&empty_bar[stage], phase ^ 1);
                             uint8_t* st = smem + stage * C::STAGE_BYTES;
-                            const bool skip_a = (p.debug & 2) && nt > 0;      // experiment: emulate a smem-resident A operand (wrong results)
-                            tc::mbar_expect_tx(&full_bar[stage], skip_a ? C::NB * C::B_BYTES : C::STAGE_BYTES);
-                            if (!skip_a) {
+                            tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
                             tc::tma_load_2d(st, &mp.a_hi, &full_bar[stage], kb * C::BK, a_row);
                             if (PREC == NES_PREC_EXACT) tc::tma_load_2d(st + C::A_BYTES, &mp.a_lo, &full_bar[stage], kb * C::BK, a_row);
-                            }
                             uint8_t* sb = st + C::NA * C::A_BYTES;      // [theta_hi | eps | theta_lo]
                             if (C::NCH > 1) {       // the gate blocks of this tile in one 3-D request per operand
                                 tc::tma_load_3d(sb, &mp.w_hi, &full_bar[stage], kb * C::BK, w_row0, 0);
@@ -278,7 +274,7 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                 tc::mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
                 tc::tc_fence_after();
                 const uint32_t trow = tmem_base + buf * C::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
-                if (!(p.debug & 1)) {
+                {
                 if (EPI == EPI_LSTM) {
                     // columns: chunk c (0 in, 1 forget, 2 out, 3/4 maxout candidates) x 16 hidden units; this warp owns 8 of them
                     const int j0 = nt * 16 + hf * 8;
@@ -385,14 +381,13 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                         }
                     }
                 }
-                }   // !debug
+                }
                 // this accumulator buffer may be overwritten by the MMAs of tile it+2
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&tempty_bar[buf]);
             }
             if (EPI == EPI_LOGIT && row_ok) {
-                if (p.debug & 1) { run_max = 0.f; run_sum = 1.f + 1e-3f * (float)(grow % 977); run_idx = 1; lo_val = 0.f; lo_idx = 1; }
                 LogitPartial lp; lp.mx = run_max; lp.idx = run_idx; lp.sum = run_sum; lp.lo_val = lo_val; lp.lo_idx = lo_idx;
                 lp.pad[0] = lp.pad[1] = lp.pad[2] = 0;
                 float4* dst = reinterpret_cast<float4*>(&p.partials[grow * 2 + hf]);
