@@ -64,6 +64,14 @@ class Policy:
     def serialized(self, path=''):
         return self.policy_net.serialize(path=path)
 
+    def save(self, path, filename):
+        """src/algorithm/policies.py:93-97"""
+        import os
+        assert self.policy_net is not None, 'set model first!'
+        os.makedirs(path, exist_ok=True)
+        assert not os.path.exists(os.path.join(path, filename))
+        torch.save(self.policy_net.state_dict(), os.path.join(path, filename))
+
     def init_model(self, model=None):
         assert self.policy_net is None
         assert isinstance(model, PolicyNet), '{}'.format(type(model))
@@ -116,6 +124,7 @@ class CaptPolicy(Policy):
         super().__init__(dataset, options, ctx, **ctx_kwargs)
         self.scorer, self.seq_per_img = scorer, int(seq_per_img)
         self.precision = PREC_EXACT
+        self.language_eval = None        # callable(predictions, directory, split) -> {'CIDEr': ...}: the COCO evaluator of accuracy_on
 
     @property
     def ctx(self):
@@ -124,6 +133,16 @@ class CaptPolicy(Policy):
     def _unique_rows(self, fc):
         fc = np.asarray(fc, dtype=np.float32)
         return fc[::self.seq_per_img] if self.seq_per_img > 1 else fc
+
+    def accuracy_on(self, dataloader, config, directory) -> float:
+        """validation score (captioning/policies.py:130-143): greedy captions of the split through eval_split, scored by the injected
+        COCO evaluator (self.language_eval; the reference's needs Java)"""
+        from .eval_utils import eval_split
+        assert directory is not None
+        if self.language_eval is None:
+            raise NotImplementedError('set policy.language_eval = callable(predictions, directory, split) -> {"CIDEr": score}')
+        lang_stats, _ = eval_split(self.policy_net, dataloader.loader, directory, num=config.num_val_items, language_eval=self.language_eval)
+        return float(lang_stats['CIDEr'])
 
     def rollout_tokens(self, data):
         seq, lp = self.policy_net(torch.from_numpy(np.ascontiguousarray(self._unique_rows(data['fc_feats']))), greedy=True)
