@@ -21,7 +21,13 @@
 namespace nes {
 
 enum { DEN_LSTM = 0, DEN_LOGITC = 1, DEN_PLAIN = 2 };
-constexpr int kLstmTileUnits = 48;          // hidden units per LSTM tile; accumulator column = gate * 48 + unit
+#ifndef NES_LSTM_TILE_UNITS
+#define NES_LSTM_TILE_UNITS 48
+#endif
+constexpr int kLstmTileUnits = NES_LSTM_TILE_UNITS;   // hidden units per LSTM tile (multiple of 16); accumulator column = gate * units + unit
+constexpr int kLstmHalfUnits = kLstmTileUnits / 2;    // per epilogue warp of a TMEM lane quarter
+constexpr int kLstmSubBatches = kLstmHalfUnits / 8;
+static_assert(kLstmTileUnits % 16 == 0 && 5 * kLstmTileUnits <= 256, "LSTM tile shape");
 constexpr int kLstmTileCols = 5 * kLstmTileUnits;
 constexpr int kCandCap = 64;                // candidate entries per half row (append-only; overflow -> split-fp16 fallback)
 
@@ -236,11 +242,11 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                     b_cur = (nt + 1 < nt1) ? bias_val(u, nt + 1)
                           : (C::SPLIT ? bias_val(nx / p.n_tiles, nx % p.n_tiles) : bias_val(nx, 0));
                 }
-                float cprev[24];
+                float cprev[kLstmHalfUnits];
                 if (C::LSTM) {
 #pragma unroll
-                    for (int sb = 0; sb < 3; ++sb) {
-                        const int j0 = nt * kLstmTileUnits + hf * 24 + sb * 8;
+                    for (int sb = 0; sb < kLstmSubBatches; ++sb) {
+                        const int j0 = nt * kLstmTileUnits + hf * kLstmHalfUnits + sb * 8;
                         if (row_ok && j0 < p.N) {
                             const float4* cp4 = reinterpret_cast<const float4*>(p.c_state + grow * p.N + j0);
                             *reinterpret_cast<float4*>(&cprev[sb * 8]) = cp4[0];
@@ -257,8 +263,8 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                 {
                 if (C::LSTM) {
 #pragma unroll
-                    for (int sb = 0; sb < 3; ++sb) {
-                        const int cu = hf * 24 + sb * 8;                 // first unit of this sub-batch inside the tile
+                    for (int sb = 0; sb < kLstmSubBatches; ++sb) {
+                        const int cu = hf * kLstmHalfUnits + sb * 8;                 // first unit of this sub-batch inside the tile
                         const int j0 = nt * kLstmTileUnits + cu;        // hidden unit index
                         float pre[5][8];
 #pragma unroll

@@ -1,0 +1,10 @@
+#!/bin/bash
+# experiment: A/B two builds of the library on one box (A = the in-tree build, B = nes-img-captioning_b200/libnes_b200_$1.so), A B A B
+d=nes-img-captioning_b200
+cp $d/libnes_b200.so /tmp/libA.so
+for leg in A B A B; do
+  if [ $leg = A ]; then cp /tmp/libA.so $d/libnes_b200.so; else cp $d/libnes_b200_$1.so $d/libnes_b200.so; fi
+  echo "== $leg"; python tools/phase_trace.py 10 prof 2>&1 | tail -2
+done
+cp /tmp/libA.so $d/libnes_b200.so
+cp $d/libnes_b200_$1.so $d/libnes_b200.so; timeout 600 python -m pytest tests/test_gpu_decode.py -m gpu -q -x --timeout 300 2>&1 | tail -2; cp /tmp/libA.so $d/libnes_b200.so
