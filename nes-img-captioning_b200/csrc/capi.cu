@@ -87,6 +87,8 @@ static int ctx_common_init(Ctx* c, int device, uint64_t seed, int64_t table_len,
     NES_CUDA(cudaMemset(c->opt_v, 0, sizeof(double) * D));
     c->theta_is_f32 = new uint8_t[n_parents];
     for (int i = 0; i < n_parents; ++i) c->theta_is_f32[i] = 1;
+    c->theta64_stale = new uint8_t[n_parents];
+    for (int i = 0; i < n_parents; ++i) c->theta64_stale[i] = 0;
     NES_CUDA(cudaEventCreate(&c->ev_a)); NES_CUDA(cudaEventCreate(&c->ev_b));
     NES_CUDA(cudaEventCreate(&c->ev_c)); NES_CUDA(cudaEventCreate(&c->ev_d));
     return ensure_small(c, 1024);
@@ -152,6 +154,7 @@ int nes_ctx_destroy(nes_ctx* ctx) {
     for (auto& r : c->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto& r : c->prof_pool) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     delete[] c->theta_is_f32;
+    delete[] c->theta64_stale;
     delete c;
     return 0;
 }
@@ -218,6 +221,7 @@ int nes_get_theta(nes_ctx* ctx, int parent, void* out, int as_f64) {
     NES_CHECK(out, "null output");
     NES_CHECK(parent >= 0 && parent < c->n_parents, "parent index out of range");
     const int64_t D = c->lay.D;
+    if (as_f64 && refresh_theta64(c, parent)) return 1;
     if (as_f64) NES_CUDA(cudaMemcpyAsync(out, c->theta64 + parent * D, sizeof(double) * D, cudaMemcpyDefault, c->stream));
     else        NES_CUDA(cudaMemcpyAsync(out, c->theta32 + parent * D, sizeof(float) * D, cudaMemcpyDefault, c->stream));
     return finish_output(c, out);

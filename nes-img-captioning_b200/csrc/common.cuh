@@ -74,6 +74,7 @@ struct Ctx {
     __half* theta_hi = nullptr;       // [n_parents, D_pad] padded layout, theta*2^8 split hi/lo
     __half* theta_lo = nullptr;
     uint8_t* theta_is_f32 = nullptr;  // host flags [n_parents]: master theta still has float32 provenance
+    uint8_t* theta64_stale = nullptr; // host flags [n_parents]: theta64 not yet refreshed from theta32 (NIC-ES survivors never read it)
     Layout* d_lay = nullptr;          // device copy of lay
     float* d_theta_rowmax = nullptr;  // [n_parents] max row 2-norm of logit.weight (HYBRID error bound)
     float* d_eps_rowmax = nullptr;    // [1] max 2-norm over the rows of the [L/R, R] view of the noise table
@@ -142,6 +143,7 @@ int set_sensitivity(Ctx* c, int parent, const float* sens);   // host or device 
 int set_mutation(Ctx* c, int kind);
 int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64);
 int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, float* d_member, float* d_noise, int dst_parent);
+int refresh_theta64(Ctx* c, int parent);          // theta64 <- (double)theta32 if the slot is stale
 int launch_evolve_batch(Ctx* c, int n, const int32_t* src, const int64_t* offsets, const float* sigmas, const int32_t* dst);   // host arrays
 int launch_bound_norms_batch(Ctx* c, const int32_t* parents, int n);   // theta_rowmax of several parents in one launch (decode.cu)
 

@@ -230,6 +230,7 @@ static void opt_dispatch(Ctx* c, int gmode, const float* d_g, const double* d_G6
 // direct: 0 = fused from the gradient estimate g (nic_nes_master.py:123-133), 1 = d_g IS globalg (float32), 2 = d_G64 is globalg (float64)
 int launch_opt_update(Ctx* c, const float* d_g, const double* d_G64, int direct, double l2, double* ratio_out) {
     NES_CHECK(c->opt_kind == NES_OPT_ADAM || c->opt_kind == NES_OPT_SGD, "nes_opt_init has not been called");
+    if (refresh_theta64(c, 0)) return 1;
     c->opt_t += 1;
     const int gmode = direct == 0 ? (c->theta_is_f32[0] ? 1 : 0) : (direct == 1 ? 2 : 3);
     if (c->opt_kind == NES_OPT_ADAM) {

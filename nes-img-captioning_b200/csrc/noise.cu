@@ -136,6 +136,7 @@ int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64) {
     c->launches++;
     NES_CUDA(cudaGetLastError());
     c->theta_is_f32[parent] = is_f64 ? 0 : 1;
+    c->theta64_stale[parent] = 0;
     return launch_theta_shadow(c, parent);
 }
 
@@ -165,13 +166,27 @@ int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, f
                                           c->scale32 ? c->scale32 + parent * D : nullptr, c->scale_div);
     c->launches++;
     NES_CUDA(cudaGetLastError());
-    if (dst_parent >= 0) { c->theta_is_f32[dst_parent] = 1; return launch_theta_shadow(c, dst_parent); }
+    if (dst_parent >= 0) { c->theta_is_f32[dst_parent] = 1; c->theta64_stale[dst_parent] = 0; return launch_theta_shadow(c, dst_parent); }
     return 0;
 }
 
 // ---- NIC-ES survivor materialisation, all survivors in one launch: item i becomes parent dst[i] = theta32[src[i]] + sigma_i * eps(off_i)
-// (nic_es_worker.py:188 without the .pth file); writes the float64 master, the float32 copy and the padded split-fp16 shadow in one pass
-__global__ void __launch_bounds__(256) k_evolve_batch(float* theta32, double* __restrict__ theta64, __half* __restrict__ th_hi,
+// (nic_es_worker.py:188 without the .pth file); writes the float32 copy and the padded split-fp16 shadow in one pass (the float64 master
+// copy is marked stale and rebuilt only if somebody asks for it)
+__global__ void __launch_bounds__(256) k_widen(const float* __restrict__ src, double* __restrict__ dst, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) dst[i] = (double)src[i];
+}
+int refresh_theta64(Ctx* c, int parent) {
+    if (!c->theta64_stale[parent]) return 0;
+    const int64_t D = c->lay.D;
+    k_widen<<<148 * 8, 256, 0, c->stream>>>(c->theta32 + (int64_t)parent * D, c->theta64 + (int64_t)parent * D, D);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    c->theta64_stale[parent] = 0;
+    return 0;
+}
+
+__global__ void __launch_bounds__(256) k_evolve_batch(float* theta32, __half* __restrict__ th_hi,
                                                       __half* __restrict__ th_lo, const __half* __restrict__ table, const Layout* __restrict__ lay,
                                                       const int64_t* __restrict__ offs, const float* __restrict__ sigmas, const int64_t* __restrict__ srcdst,
                                                       const float* __restrict__ scale, int scale_div) {
@@ -187,41 +202,49 @@ __global__ void __launch_bounds__(256) k_evolve_batch(float* theta32, double* __
     const __half* row = table + offs[item] + t.pstart;
     const float* sc = scale ? scale + (int64_t)src * D : nullptr;
     float* d32 = theta32 + (int64_t)dst * D + t.start;           // dst slots are disjoint from src slots (checked by the host)
-    double* d64 = theta64 + (int64_t)dst * D + t.start;
     __half* dhi = th_hi + (int64_t)dst * D_pad + t.pstart;
     __half* dlo = th_lo + (int64_t)dst * D_pad + t.pstart;
     // 8 elements per thread through 16-byte accesses where the tensor starts on a 16-byte boundary in every array
-    const bool vec = ((reinterpret_cast<uintptr_t>(th) | reinterpret_cast<uintptr_t>(d32) | reinterpret_cast<uintptr_t>(d64) |
+    const bool vec = ((reinterpret_cast<uintptr_t>(th) | reinterpret_cast<uintptr_t>(d32) |
                        reinterpret_cast<uintptr_t>(row) | reinterpret_cast<uintptr_t>(dhi)) & 15) == 0;
     const int64_t n8 = vec ? t.count / 8 : 0;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t v = tid; v < n8; v += nth) {
-        const int64_t j = v * 8;
-        const uint4 ev = __ldg(reinterpret_cast<const uint4*>(row + j));
-        const float4 a = __ldg(reinterpret_cast<const float4*>(th + j)), b = __ldg(reinterpret_cast<const float4*>(th + j) + 1);
-        const float tv[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-        const __half* eh = reinterpret_cast<const __half*>(&ev);
-        __align__(16) float m[8];
-        __align__(16) __half hh[8];
-        __align__(16) __half hl[8];
+    constexpr int U = 4;                                          // vectors in flight per thread: all loads of a batch before the first store
+    for (int64_t v0 = tid; v0 < n8; v0 += U * nth) {
+        uint4 ev[U]; float4 ta[U], tb[U];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            m[e] = __fadd_rn(tv[e], mut_noise(sigma, __half2float(eh[e]), sc, t.start + j + e, scale_div));
-            split_half(m[e], kThetaScale, hh[e], hl[e]);
+        for (int u = 0; u < U; ++u) {
+            const int64_t j = (v0 + u * nth) * 8;
+            if (v0 + u * nth < n8) {
+                ev[u] = __ldg(reinterpret_cast<const uint4*>(row + j));
+                ta[u] = __ldg(reinterpret_cast<const float4*>(th + j)); tb[u] = __ldg(reinterpret_cast<const float4*>(th + j) + 1);
+            }
         }
-        reinterpret_cast<float4*>(d32 + j)[0] = *reinterpret_cast<float4*>(&m[0]);
-        reinterpret_cast<float4*>(d32 + j)[1] = *reinterpret_cast<float4*>(&m[4]);
 #pragma unroll
-        for (int e = 0; e < 8; e += 2) *reinterpret_cast<double2*>(d64 + j + e) = make_double2((double)m[e], (double)m[e + 1]);
-        *reinterpret_cast<uint4*>(dhi + j) = *reinterpret_cast<uint4*>(hh);
-        *reinterpret_cast<uint4*>(dlo + j) = *reinterpret_cast<uint4*>(hl);
+        for (int u = 0; u < U; ++u) {
+            const int64_t j = (v0 + u * nth) * 8;
+            if (v0 + u * nth >= n8) break;
+            const float tv[8] = {ta[u].x, ta[u].y, ta[u].z, ta[u].w, tb[u].x, tb[u].y, tb[u].z, tb[u].w};
+            const __half* eh = reinterpret_cast<const __half*>(&ev[u]);
+            __align__(16) float m[8];
+            __align__(16) __half hh[8];
+            __align__(16) __half hl[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                m[e] = __fadd_rn(tv[e], mut_noise(sigma, __half2float(eh[e]), sc, t.start + j + e, scale_div));
+                split_half(m[e], kThetaScale, hh[e], hl[e]);
+            }
+            __stcs(reinterpret_cast<float4*>(d32 + j), *reinterpret_cast<float4*>(&m[0]));
+            __stcs(reinterpret_cast<float4*>(d32 + j) + 1, *reinterpret_cast<float4*>(&m[4]));
+            __stcs(reinterpret_cast<uint4*>(dhi + j), *reinterpret_cast<uint4*>(hh));
+            __stcs(reinterpret_cast<uint4*>(dlo + j), *reinterpret_cast<uint4*>(hl));
+        }
     }
     for (int64_t j = n8 * 8 + tid; j < span; j += nth) {          // ragged tail, unaligned tensors, zero padding of the shadow
         __half a = __float2half_rn(0.f), b = a;
         if (j < t.count) {
             const float m = __fadd_rn(th[j], mut_noise(sigma, __half2float(row[j]), sc, t.start + j, scale_div));
             d32[j] = m;
-            d64[j] = (double)m;
             split_half(m, kThetaScale, a, b);
         }
         dhi[j] = a;
@@ -247,11 +270,12 @@ int launch_evolve_batch(Ctx* c, int n, const int32_t* src, const int64_t* offset
     NES_CUDA(cudaMemcpyAsync(c->d_ranks, packed.data(), sizeof(int64_t) * n, cudaMemcpyDefault, c->stream));
     NES_CUDA(cudaStreamSynchronize(c->stream));            // `packed` is a stack-lifetime host buffer
     dim3 grid(148, c->lay.n, n);
-    k_evolve_batch<<<grid, 256, 0, c->stream>>>(c->theta32, c->theta64, c->theta_hi, c->theta_lo, c->table, c->d_lay, c->d_offsets, c->d_weights, c->d_ranks, c->scale32, c->scale_div);
+    k_evolve_batch<<<grid, 256, 0, c->stream>>>(c->theta32, c->theta_hi, c->theta_lo, c->table, c->d_lay, c->d_offsets, c->d_weights, c->d_ranks, c->scale32, c->scale_div);
     c->launches++;
     NES_CUDA(cudaGetLastError());
     for (int i = 0; i < n; ++i) {
         c->theta_is_f32[dst[i]] = 1;
+        c->theta64_stale[dst[i]] = 1;          // the float64 master copy is rebuilt on demand (refresh_theta64): NIC-ES never reads it
         if (c->mut_kind == NES_MUT_PROPORTIONAL && launch_prop_scale(c, dst[i])) return 1;
     }
     if (c->is_fc) return launch_bound_norms_batch(c, dst, n);
