@@ -105,9 +105,10 @@ class CiderD:
         self.n_img, self.rows_per_img, self.seq_per_img = len(cooked), int(rows_per_img), int(seq_per_img)
         return self
 
-    def scores(self, seq=None, n_members=None, rows=None, device='cpu'):
+    def scores(self, seq=None, n_members=None, rows=None, device='cpu', rows_per_img=None):
         """per-caption scores float64 [n_members, rows]; seq int64 [n_members, rows, T] (torch / numpy, host or device) or
-        None = the tokens of the last rollout, still resident on the device"""
+        None = the tokens of the last rollout, still resident on the device.  rows_per_img overrides set_refs' value for this call
+        (sampled decode scores all batch_size * seq_per_img rows, greedy decode the unique ones)."""
         if seq is not None:
             seq = torch.as_tensor(seq).to(torch.int64).contiguous()
             if seq.dim() == 2:
@@ -116,7 +117,7 @@ class CiderD:
         else:
             T = self.ctx.dims['seq_length']
         out = torch.empty((int(n_members), int(rows)), dtype=torch.float64, device=device)
-        _lib.check(self.ctx.lib.nes_cider_scores(self.ctx._h, _lib.ptr(seq), int(n_members), int(rows), int(T), self.rows_per_img, _lib.ptr(out)))
+        _lib.check(self.ctx.lib.nes_cider_scores(self.ctx._h, _lib.ptr(seq), int(n_members), int(rows), int(T), int(rows_per_img or self.rows_per_img), _lib.ptr(out)))
         return out
 
     def compute_score(self, gts, res):

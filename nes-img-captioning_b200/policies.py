@@ -197,9 +197,7 @@ class CaptPolicy(Policy):
         if uniforms is None:
             uniforms = torch.rand((P, rows, T), dtype=torch.float64, device=ctx.dev)
         ctx.rollout(offsets, signs, fc_all, sigma, parents=parents, out_device=ctx.dev, uniforms=uniforms)
-        self.scorer.rows_per_img = spi
-        scores = self.scorer.scores(None, P, rows, device=ctx.dev)
-        self.scorer.rows_per_img = 1
+        scores = self.scorer.scores(None, P, rows, device=ctx.dev, rows_per_img=spi)
         if sc:
             scores = scores - base                                          # policies.py:183
         if kind == 'sc_loss':
