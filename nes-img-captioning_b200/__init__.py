@@ -8,6 +8,7 @@ from .nets import FCModel, ModelOptions, Mutation, PolicyNet
 from .policies import CaptPolicy, Net, Policy, PolicyFactory, PolicyOptions, SuppDataset
 from .cider import CiderD
 from .eval_utils import decode_sequence, eval_split
+from . import schedule
 from .master import (Adam, ESMaster, NESMaster, Optimizer, SGD, all_gather_fitness, all_reduce_gradient, sharded_master_step, es_generation, es_sample_generation,
                      es_select_and_materialise, nes_iteration, shard_bounds)
 
