@@ -5,8 +5,8 @@ Differences that follow from the design (documented in DESIGN.md):
   * evolve() draws its noise from the shared noise table (a fresh offset per call) instead of an
     unseeded torch.normal_ -- the returned vector is still float32 sigma*eps of length D;
   * set_from_vector() copies (the reference aliases the caller's memory, nets.py:163-165);
-  * Mutation.DEFAULT and Mutation.SAFE_PROPORTIONAL run on the CUDA path; the gradient / vector safe mutations raise
-    (SURVEY section 8f-3).
+  * every Mutation runs on the CUDA path; for SM-G-SUM / SM-G-ABS the sensitivity vector itself comes from autograd
+    (safe_mutations.py here) and the kernels divide the noise by it.
 """
 from collections import OrderedDict, namedtuple
 from enum import Enum
@@ -15,6 +15,7 @@ import numpy as np
 import torch
 
 from .context import NesContext, PREC_EXACT
+from .safe_mutations import Sensitivity
 
 _model_opt_fields = ['vocab_size', 'input_encoding_size', 'rnn_type', 'rnn_size', 'num_layers',
                      'drop_prob_lm', 'seq_length', 'fc_feat_size', 'vbn', 'vbn_e', 'vbn_affine', 'layer_n',
@@ -40,6 +41,8 @@ class PolicyNet:
         self.mutations = Mutation(sm or '')
         ctx.set_mutation(self.mutations.value)        # context-wide: every parent slot mutates the same way
         self._underflow = (options.get('safe_mutation_underflow') if isinstance(options, dict) else getattr(options, 'safe_mutation_underflow', None)) or 0.01
+        if self.mutations in (Mutation.SAFE_GRAD_SUM, Mutation.SAFE_GRAD_ABS):     # algorithm/nets.py:46-48
+            self.sensitivity_wrapper = Sensitivity(self, self._underflow, self.mutations)
         if self.mutations == Mutation.SAFE_VECTOR:     # algorithm/nets.py:49-50
             vec = options.get('safe_mutation_vector') if isinstance(options, dict) else getattr(options, 'safe_mutation_vector', None)
             if vec is not None and not (isinstance(vec, (int, float)) and not vec):
@@ -101,11 +104,14 @@ class PolicyNet:
     def from_serialized(self, serialized):
         self.load_state_dict(torch.load(serialized, map_location='cpu'))
 
-    def calc_sensitivity(self, *a, **k):
-        """no-op unless the mutation is gradient based, like the reference (nets.py:121-123); the Jacobian of SM-G-SUM / SM-G-ABS
-        (safe_mutations.py:34-117) needs autograd: compute it with PyTorch and hand the vector to set_sensitivity_vector"""
+    def calc_sensitivity(self, task_id, parent_id, experiences, batch_size, directory):
+        """algorithm/nets.py:121-123: a no-op unless the mutation is gradient based.  SM-G-SUM / SM-G-ABS: the output-gradient
+        sensitivity of this parent (safe_mutations.py:34-147; autograd on the device, cached per (task_id, parent_id) in memory and
+        in sens_t*_p*_*.pt under `directory` like the reference) and handed to the device, where noise /= sensitivity"""
         if self.mutations in (Mutation.SAFE_GRAD_SUM, Mutation.SAFE_GRAD_ABS):
-            raise NotImplementedError('compute the output-gradient sensitivity with autograd and pass it to set_sensitivity_vector')
+            if self.sensitivity_wrapper.calc_sensitivity(task_id, parent_id, experiences, batch_size, directory):
+                self._sensitivity = self.sensitivity_wrapper.get_sensitivity().to(torch.float32)
+                self.ctx.set_sensitivity(self._sensitivity, parent=self.parent)
         return None
 
     def set_sensitivity_vector(self, vector):

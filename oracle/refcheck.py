@@ -187,6 +187,39 @@ def check_sensitivity(ref, seed=5):
     return True
 
 
+def check_grad_sensitivity(ref):
+    """SM-G-SUM: the package's autograd restatement (nes-img-captioning_b200/safe_mutations.py, torch on the CPU here) against the
+    reference's Sensitivity.calc_sensitivity over FCModel.forward_for_sensitivity (safe_mutations.py:34-115, captioning/nets.py:22-69),
+    plain / LayerNorm / batch-norm cells: bit-exact on this torch build.  This is the one check that exercises product code: the
+    function is device-agnostic torch and has no separate oracle restatement."""
+    import importlib, tempfile
+    pkg_sm = importlib.import_module('nes-img-captioning_b200.safe_mutations')
+    lay = importlib.import_module('nes-img-captioning_b200.layout')
+    for cfg in [dict(V=199, E=64, R=64, Fd=128, ln=0, aff=0, vbn=0, uf=1e-4), dict(V=299, E=32, R=64, Fd=128, ln=1, aff=1, vbn=0, uf=0.01),
+                dict(V=230, E=32, R=32, Fd=64, ln=0, aff=1, vbn=1, uf=0.01), dict(V=230, E=32, R=32, Fd=64, ln=1, aff=0, vbn=0, uf=0.01)]:
+        opt = ref.ModelOptions(vocab_size=cfg['V'], input_encoding_size=cfg['E'], rnn_size=cfg['R'], fc_feat_size=cfg['Fd'],
+                               safe_mutations='SM-G-SUM', safe_mutation_underflow=cfg['uf'], layer_n=bool(cfg['ln']),
+                               layer_n_affine=bool(cfg['aff'] and cfg['ln']), vbn=bool(cfg['vbn']), vbn_affine=bool(cfg['aff'] and cfg['vbn']))
+        torch.manual_seed(3)
+        model = ref.FCModel(options=opt, vbn=bool(cfg['vbn']))
+        theta = model.parameter_vector().detach().clone()
+        fc = np.repeat(np.random.RandomState(1).randn(6, cfg['Fd']).astype(np.float32), 5, axis=0)
+        with tempfile.TemporaryDirectory() as d:
+            model.calc_sensitivity(0, 0, {'fc_feats': fc}, 4, d)
+            want = model.get_sensitivity_vector().numpy().copy()
+        torch.set_grad_enabled(False)                    # the reference leaves it off (safe_mutations.py:67)
+        layer_n = 2 if cfg['vbn'] else cfg['ln']
+        dims = dict(vocab_size=cfg['V'], input_encoding_size=cfg['E'], rnn_size=cfg['R'], fc_feat_size=cfg['Fd'], layer_n=layer_n, layer_n_affine=cfg['aff'])
+        tensors, D, _ = lay.build_layout(lay.fc_tensors(cfg['V'], cfg['E'], cfg['R'], cfg['Fd'], layer_n, cfg['aff']), 64)
+        assert D == theta.numel()
+        got = pkg_sm.sum_sensitivity(theta, tensors, dims, fc, 4)
+        got[got < cfg['uf']] = cfg['uf']
+        got /= cfg['uf']
+        assert np.array_equal(got.numpy(), want), np.max(np.abs(got.numpy() - want) / want)
+        assert 0.1 < (want == 1).mean() < 0.9
+    return True
+
+
 def main():
     if not _refimport.available():
         print('reference not present; nothing checked'); return 1
@@ -202,8 +235,8 @@ def main():
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)
     assert fc_caption.Dims(9487, 128, 128, 2048).num_params() == 2865808
     assert fc_caption.Dims(9487, 512, 512, 2048).num_params() == 13400848
-    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref); check_sample_decode(ref); check_sensitivity(ref)
-    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL, SM-VECTOR, sampled decode OK' % n)
+    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref); check_sample_decode(ref); check_sensitivity(ref); check_grad_sensitivity(ref)
+    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL, SM-VECTOR, SM-G-SUM sensitivity, sampled decode OK' % n)
     return 0
 
 

@@ -471,3 +471,38 @@ def test_sensitivity_mutation_evolve_rollout_and_policy(monkeypatch, tmp_path):
     want_m, want_nz = noise.member_theta(th0, noise.noise_row(31, offs[3], play, D), sigma, +1, sens=sens[0])
     assert np.array_equal(got_nz, want_nz) and np.array_equal(model.parameter_vector().numpy(), want_m)
     model.ctx.close()
+
+
+@pytest.mark.parametrize('name', ['s1', 's2'])
+def test_gradient_sensitivity_on_device_against_reference_golden(name, tmp_path):
+    """SM-G-SUM end to end (safe_mutations.py:34-115; nic_es_worker.py:173-175): FCModel.calc_sensitivity computes the output-gradient
+    sensitivity with autograd on the device holding theta, writes the reference's sens_t*_p*_*.pt file and hands the vector to the
+    library; evolve then divides the table noise by it (bit-exact against the oracle with the device's own vector).  The vector itself
+    against the REAL reference's golden (cuBLAS float32 instead of MKL: 1e-3)."""
+    import os, sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden'))
+    import make_golden_sens as ms
+    import nes_b200
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'golden_sens_v1.npz'))
+    c = ms.CASES[name]
+    dims, theta, fc5 = ms.case_inputs(c)
+    G = noise.granularity(c['E'], c['R'], c['Fd'])
+    play, D, D_pad = noise.padded_layout(dims.layout(), G)
+    model = nes_b200.FCModel(options=ms.model_options(c), rng_state=1, seed=31, table_len=D_pad + 63 * G, wave_members=2, rows=8)
+    model.set_from_vector(theta)
+    assert model.get_sensitivity_vector() is None
+    model.calc_sensitivity(3, 1, {'fc_feats': fc5}, c['bs'], str(tmp_path))
+    sens = model.get_sensitivity_vector().numpy()
+    want = gold[name + '_sens']
+    assert os.listdir(tmp_path) == ['sens_t3_p1_%d.pt' % os.getpid()]
+    assert np.array_equal(torch.load(tmp_path / os.listdir(tmp_path)[0]).numpy(), sens)
+    assert np.allclose(sens, want, rtol=1e-3, atol=1e-3), np.max(np.abs(sens - want) / want)
+    assert sens.min() == 1.0 and 0.2 < (sens == 1).mean() < 0.8
+    off = int(model.ctx.sample_offsets(9, 1)[0])
+    got_nz = model.evolve(0.05, offset=off)
+    want_m, want_nz = noise.member_theta(theta, noise.noise_row(31, off, play, D), 0.05, +1, sens=sens)
+    assert np.array_equal(got_nz, want_nz) and np.array_equal(model.parameter_vector().numpy(), want_m)
+    # same (task, parent): cached, nothing recomputed or rewritten
+    model.calc_sensitivity(3, 1, {'fc_feats': fc5}, c['bs'], str(tmp_path))
+    assert len(os.listdir(tmp_path)) == 1
+    model.ctx.close()
