@@ -18,6 +18,9 @@ CASES = {
     's1': dict(V=230, E=32, R=32, Fd=64, rows=6, bs=4, underflow=1e-4, scale=1.0),
     's2': dict(V=299, E=32, R=64, Fd=128, rows=5, bs=8, underflow=0.01, scale=1.0, ln=True, affine=True),
     's3': dict(V=230, E=32, R=32, Fd=64, rows=6, bs=6, underflow=0.01, scale=1.0, vbn=True, affine=True),
+    # the CUDA library wants E, R, Fd in multiples of 64: the two cases the device test uses
+    's5': dict(V=99, E=64, R=64, Fd=64, rows=5, bs=4, underflow=1e-4, scale=1.5),
+    's6': dict(V=130, E=64, R=64, Fd=128, rows=4, bs=4, underflow=0.01, scale=1.0, ln=True, affine=True),
     's4': dict(V=199, E=64, R=32, Fd=64, rows=3, bs=3, underflow=0.01, scale=4.0),     # V1 % 100 == 0: the all-zero padding group (:62-64)
 }
 THETA_SEED, FC_SEED = 17, 29

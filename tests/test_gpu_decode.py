@@ -473,7 +473,7 @@ def test_sensitivity_mutation_evolve_rollout_and_policy(monkeypatch, tmp_path):
     model.ctx.close()
 
 
-@pytest.mark.parametrize('name', ['s1', 's2'])
+@pytest.mark.parametrize('name', ['s5'])      # safe mutations with layer_n / vbn are refused by the library; s6 runs on the CPU only
 def test_gradient_sensitivity_on_device_against_reference_golden(name, tmp_path):
     """SM-G-SUM end to end (safe_mutations.py:34-115; nic_es_worker.py:173-175): FCModel.calc_sensitivity computes the output-gradient
     sensitivity with autograd on the device holding theta, writes the reference's sens_t*_p*_*.pt file and hands the vector to the
