@@ -109,6 +109,19 @@ int nes_set_mutation(nes_ctx* ctx, int kind);
  * divided by their minimum); parent < 0 sets every parent slot. */
 int nes_set_sensitivity(nes_ctx* ctx, int parent, const float* sens);
 
+/* ---- MNIST classifier population rollout (BASELINE configs[0], experiments/mnist_es.json): replaces, for n_members perturbed
+ *      members at once, ESWorker.fitness nic_es_worker.py:142-192 -> ClfPolicy.rollout classification/policies.py:16-48 ->
+ *      MnistNet.forward classification/nets.py:25-37 (and ClfPolicy.accuracy_on :50-86 through `correct`) ------------------------
+ * The context is a flat one (nes_ctx_create_flat) with MnistNet's six tensors in parameter_vector order: conv1.weight 250,
+ * conv1.bias 10, conv2.weight 5000, conv2.bias 20, fc1.weight 3200, fc1.bias 10.  member m = theta[parents[m]] +
+ * signs[m]*sigma*eps(offsets[m]) under the mutation set by nes_set_mutation; parents may be NULL (all 0); sigma = 0 evaluates theta.
+ * images: float32 [rows, 1, 28, 28] if shared_batch else [n_members, rows, 1, 28, 28]; labels: int64 [rows] / [n_members, rows].
+ * fitness: float64 [n_members] = -CrossEntropyLoss (mean over rows); correct (nullable): int32 [n_members] rows whose arg-max equals
+ * the label; logits (nullable): float32 [n_members, rows, 10].  Host or device pointers. */
+int nes_mnist_rollout(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,
+                      const float* images, const int64_t* labels, int rows, int shared_batch, float sigma,
+                      double* fitness, int32_t* correct, float* logits);
+
 /* ---- population rollout (NESWorker.fitness nic_nes_worker.py:131-154 / ESWorker.fitness
  *      nic_es_worker.py:142-175 -> CaptPolicy.rollout captioning/policies.py:86-116 ->
  *      FCModel._sample(greedy) captioning/nets.py:183-245), CIDEr scoring excluded --------------- */

@@ -26,6 +26,7 @@ SIGNATURES = {
     'nes_shaped_fitness': (c_i32, [c_vp, c_i32, c_i64, c_i32, c_vp, c_vp]),
     'nes_rollout_sample': (c_i32, [c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_f32, c_vp, c_vp, c_vp]),
     'nes_set_sensitivity': (c_i32, [c_vp, c_i32, c_vp]),
+    'nes_mnist_rollout': (c_i32, [c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_f32, c_vp, c_vp, c_vp]),
     'nes_evolve_batch': (c_i32, [c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
     'nes_set_mutation': (c_i32, [c_vp, c_i32]),
     'nes_cider_scores': (c_i32, [c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp]),

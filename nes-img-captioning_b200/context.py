@@ -13,11 +13,12 @@ OPT_SGD, OPT_ADAM = 0, 1
 
 
 class NesContext:
-    def __init__(self, model_options=None, *, counts=None, flat_granule=64, seed=1234, table_len=1 << 28,
+    def __init__(self, model_options=None, *, counts=None, tensors=None, flat_granule=64, seed=1234, table_len=1 << 28,
                  n_parents=1, wave_members=256, rows=128, device=0, fill=True):
         """model_options: dict / namedtuple with the fc_caption ModelOptions fields (vocab_size,
         input_encoding_size, rnn_size, fc_feat_size, layer_n, layer_n_affine[, seq_length]); or
-        counts=[...] for a generic flat parameter vector (master math only)."""
+        counts=[...] for a generic flat parameter vector (master math only), or tensors=[(name, shape), ...] for a flat vector
+        with named tensors (the MNIST net, layout.mnist_tensors())."""
         self.lib = _lib.load()
         self.device = int(device)
         self._h = ctypes.c_void_p()
@@ -40,10 +41,12 @@ class NesContext:
                                                   self.table_len, self.n_parents, int(wave_members), int(rows)))
             self.wave_members, self.rows_cap = int(wave_members), int(rows)
         else:
-            assert counts is not None, 'give model_options or counts'
+            assert counts is not None or tensors is not None, 'give model_options, counts or tensors'
             self.dims = None
             self.G = int(flat_granule)
-            self.tensors, self.D, self.D_pad = build_layout([('t%d' % i, (int(c),)) for i, c in enumerate(counts)], self.G)
+            named = [(n, tuple(sh)) for n, sh in tensors] if tensors is not None else [('t%d' % i, (int(c),)) for i, c in enumerate(counts)]
+            counts = [int(np.prod(sh)) for _, sh in named]
+            self.tensors, self.D, self.D_pad = build_layout(named, self.G)
             arr = (ctypes.c_int64 * len(counts))(*[int(c) for c in counts])
             _lib.check(self.lib.nes_ctx_create_flat(ctypes.byref(self._h), self.device, arr, len(counts), self.G,
                                                     self.seed, self.table_len, self.n_parents))
@@ -152,6 +155,34 @@ class NesContext:
         off = np.ascontiguousarray(offsets, dtype=np.int64); sg = np.ascontiguousarray(sigmas, dtype=np.float32)
         assert len(src) == len(dst) == len(off) == len(sg)
         _lib.check(self.lib.nes_evolve_batch(self._h, len(src), _lib.ptr(src), _lib.ptr(off), _lib.ptr(sg), _lib.ptr(dst)))
+
+    # ---- MNIST classifier (BASELINE configs[0]; classification/nets.py:25-37, classification/policies.py:16-86)
+    def mnist_rollout(self, offsets, signs, images, labels, sigma, parents=None, shared_batch=None, out_device='cpu', want_logits=False):
+        """offsets int64 [P], signs float32 [P]; images float32 [rows, 1, 28, 28] (shared) or [P, rows, 1, 28, 28]; labels int64 to match.
+        Returns fitness float64 [P] (= -CrossEntropyLoss), correct int32 [P] (+ logits float32 [P, rows, 10] when want_logits)."""
+        offsets = torch.as_tensor(offsets, dtype=torch.int64).contiguous()
+        signs = torch.as_tensor(signs, dtype=torch.float32).contiguous()
+        images = torch.as_tensor(images).to(torch.float32).contiguous()
+        labels = torch.as_tensor(labels).to(torch.int64).contiguous()
+        P = offsets.numel()
+        assert signs.numel() == P
+        if images.dim() in (2, 3) and images.shape[-1] == 28:          # [rows, 28, 28]
+            images = images.unsqueeze(-3)
+        if shared_batch is None:
+            shared_batch = images.dim() == 4
+        rows = images.shape[-4]
+        assert tuple(images.shape[-3:]) == (1, 28, 28) and (shared_batch or images.shape[0] == P)
+        assert labels.numel() == (1 if shared_batch else P) * rows
+        assert images.device == labels.device
+        if parents is not None:
+            parents = torch.as_tensor(parents, dtype=torch.int32).contiguous()
+            assert parents.numel() == P
+        fit = torch.empty(P, dtype=torch.float64, device=out_device)
+        cor = torch.empty(P, dtype=torch.int32, device=out_device)
+        lg = torch.empty((P, rows, 10), dtype=torch.float32, device=out_device) if want_logits else None
+        _lib.check(self.lib.nes_mnist_rollout(self._h, P, _lib.ptr(offsets), _lib.ptr(signs), _lib.ptr(parents), _lib.ptr(images), _lib.ptr(labels),
+                                              int(rows), int(bool(shared_batch)), float(sigma), _lib.ptr(fit), _lib.ptr(cor), _lib.ptr(lg)))
+        return (fit, cor, lg) if want_logits else (fit, cor)
 
     # ---- population rollout
     def rollout(self, offsets, signs, fc, sigma, parents=None, precision=PREC_EXACT, shared_batch=None,

@@ -312,6 +312,56 @@ int nes_cider_scores(nes_ctx* ctx, const int64_t* seq, int64_t n_members, int ro
     return finish_output(c, scores);
 }
 
+// ---- MNIST classifier population rollout (mnist.cu)
+int nes_mnist_rollout(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,
+                      const float* images, const int64_t* labels, int rows, int shared_batch, float sigma,
+                      double* fitness, int32_t* correct, float* logits) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    NES_CHECK(n_members >= 0 && rows >= 1, "bad geometry");
+    if (n_members == 0) return 0;
+    NES_CHECK(offsets && signs && images && labels && fitness, "null argument");
+    std::vector<void*> temps;
+    auto release = [&]() { for (void* t : temps) cudaFreeAsync(t, c->stream); };
+    auto dev_in = [&](const void* src, size_t bytes, const void** out) -> int {
+        if (!src || is_device_ptr(src)) { *out = src; return 0; }
+        void* d = nullptr;
+        NES_CUDA(cudaMallocAsync(&d, bytes, c->stream));
+        temps.push_back(d);
+        NES_CUDA(cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, c->stream));
+        *out = d; return 0;
+    };
+    auto dev_out = [&](void* dst, size_t bytes, void** out) -> int {
+        if (dst && is_device_ptr(dst)) { *out = dst; return 0; }
+        void* d = nullptr;
+        NES_CUDA(cudaMallocAsync(&d, bytes, c->stream));
+        temps.push_back(d);
+        *out = d; return 0;
+    };
+    if (!is_device_ptr(offsets))
+        for (int64_t i = 0; i < n_members; ++i) {
+            NES_CHECK(offsets[i] >= 0 && offsets[i] + c->lay.D_pad <= c->table_len && offsets[i] % c->lay.G == 0, "offset outside the noise table or not slot aligned");
+            NES_CHECK(!parents || is_device_ptr(parents) || (parents[i] >= 0 && parents[i] < c->n_parents), "parent index out of range");
+            NES_CHECK(is_device_ptr(signs) || signs[i] == 1.0f || signs[i] == -1.0f, "sign must be +1 or -1");
+        }
+    const int64_t n_img = (shared_batch ? 1 : n_members) * (int64_t)rows, n_out = n_members * (int64_t)rows;
+    const void *d_off, *d_sign, *d_par, *d_img, *d_lab;
+    void *d_loss, *d_pred, *d_fit, *d_cor, *d_log = nullptr;
+    int rc = dev_in(offsets, sizeof(int64_t) * n_members, &d_off) || dev_in(signs, sizeof(float) * n_members, &d_sign) ||
+             dev_in(parents, sizeof(int32_t) * n_members, &d_par) || dev_in(images, sizeof(float) * n_img * 784, &d_img) ||
+             dev_in(labels, sizeof(int64_t) * n_img, &d_lab) || dev_out(nullptr, sizeof(float) * n_out, &d_loss) ||
+             dev_out(nullptr, sizeof(int32_t) * n_out, &d_pred) || dev_out(fitness, sizeof(double) * n_members, &d_fit) ||
+             dev_out(correct, sizeof(int32_t) * n_members, &d_cor) || (logits ? dev_out(logits, sizeof(float) * n_out * 10, &d_log) : 0);
+    if (!rc) rc = mnist_rollout(c, n_members, (const int64_t*)d_off, (const float*)d_sign, (const int32_t*)d_par, (const float*)d_img, (const int64_t*)d_lab,
+                                rows, shared_batch, sigma, (float*)d_loss, (int32_t*)d_pred, (double*)d_fit, (int32_t*)d_cor, (float*)d_log);
+    if (!rc && d_fit != fitness) rc = cudaMemcpyAsync(fitness, d_fit, sizeof(double) * n_members, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess;
+    if (!rc && correct && d_cor != correct) rc = cudaMemcpyAsync(correct, d_cor, sizeof(int32_t) * n_members, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess;
+    if (!rc && logits && d_log != logits) rc = cudaMemcpyAsync(logits, d_log, sizeof(float) * n_out * 10, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess;
+    release();
+    if (!rc && (!is_device_ptr(fitness) || (correct && !is_device_ptr(correct)) || (logits && !is_device_ptr(logits)))) NES_CUDA(cudaStreamSynchronize(c->stream));
+    if (rc && g_err.empty()) set_error("nes_mnist_rollout: CUDA copy failed");
+    return rc ? 1 : 0;
+}
+
 int nes_set_mutation(nes_ctx* ctx, int kind) {
     NEED_CTX(ctx);
     return set_mutation(CTX(ctx), kind);

@@ -164,6 +164,11 @@ int decode_hybrid_stats(Ctx* c, int64_t* out4, int reset);
 const int64_t* decode_resident_seq(Ctx* c, int64_t n_members, int rows, int* T);
 const float* decode_resident_logprobs(Ctx* c, int64_t n_members, int rows);   // device seq of the last rollout (nullptr if not resident)
 
+// mnist.cu
+int mnist_rollout(Ctx* c, int64_t n_members, const int64_t* d_off, const float* d_sign, const int32_t* d_parent, const float* d_images,
+                  const int64_t* d_labels, int rows, int shared_batch, float sigma, float* d_loss, int32_t* d_pred,
+                  double* d_fitness, int32_t* d_correct, float* d_logits);
+
 // cider.cu
 int cider_set_tables(Ctx* c, const uint64_t* idf_keys, const double* idf_vals, int64_t n_idf, double idf_default,
                      const int32_t* img_ref_ptr, int32_t n_img, const int32_t* ref_ent_ptr, int32_t n_refs,

@@ -26,6 +26,12 @@ def fc_tensors(vocab_size, input_encoding_size, rnn_size, fc_feat_size, layer_n=
     return t
 
 
+def mnist_tensors():
+    """MnistNet.named_parameters() (src/classification/nets.py:13-15): D = 8490"""
+    return [('conv1.weight', (10, 1, 5, 5)), ('conv1.bias', (10,)), ('conv2.weight', (20, 10, 5, 5)), ('conv2.bias', (20,)),
+            ('fc1.weight', (10, 320)), ('fc1.bias', (10,))]
+
+
 def granule(input_encoding_size, rnn_size, fc_feat_size):
     g = 1
     for x in (fc_feat_size, input_encoding_size, rnn_size):

@@ -15,6 +15,8 @@ import numpy as np
 import torch
 
 from .context import NesContext, PREC_EXACT
+from . import safe_mutations as _sm
+from .layout import mnist_tensors
 from .safe_mutations import Sensitivity
 
 _model_opt_fields = ['vocab_size', 'input_encoding_size', 'rnn_type', 'rnn_size', 'num_layers',
@@ -158,6 +160,11 @@ class FCModel(PolicyNet):
                 flat[t.start:t.start + t.count] = torch.randn(t.count, generator=gen) * std
         self.set_from_vector(flat)
 
+    def sensitivity_forward(self, experiences, orig_bs):
+        """(theta, i) -> FCModel.forward_for_sensitivity(data, orig_bs, i) (captioning/nets.py:22-69) as a function of the flat theta"""
+        tensors, dims, fc = self.ctx.tensors, self.ctx.dims, experiences['fc_feats']
+        return lambda theta, i: _sm.forward_for_sensitivity(theta, tensors, dims, fc, orig_bs, i=i)
+
     def forward(self, fc_feats, greedy=True):
         """-> seq int64 [B, T], seq_logprobs float32 [B, T]  (FCModel._sample, nets.py:183-245)"""
         if not greedy:
@@ -167,5 +174,58 @@ class FCModel(PolicyNet):
         par = torch.tensor([self.parent], dtype=torch.int32)
         seq, lp = self.ctx.rollout(off, sg, fc_feats, 0.0, parents=par, precision=self.precision, shared_batch=True)
         return seq[0], lp[0]
+
+    __call__ = forward
+
+
+class MnistNet(PolicyNet):
+    """The reference's MNIST classifier (src/classification/nets.py:8-37; BASELINE configs[0], experiments/mnist_es.json): conv 1->10 5x5,
+    relu, maxpool, conv 10->20 5x5, relu, maxpool, fc 320->10; D = 8490.  Backed by a flat NesContext with the six named tensors; the
+    forward pass runs in k_mnist_rollout (csrc/mnist.cu).  vbn (BatchNorm2d over the batch) is not on the CUDA path."""
+
+    def __init__(self, ctx: NesContext = None, parent=0, options=None, rng_state=None, from_param_file=None, vbn=False, **ctx_kwargs):
+        assert not vbn, 'MnistNet with vbn is not on the B200 path'
+        if ctx is None:
+            ctx_kwargs.setdefault('table_len', 1 << 22)
+            ctx = NesContext(tensors=mnist_tensors(), **ctx_kwargs)
+        assert [t.name for t in ctx.tensors] == [n for n, _ in mnist_tensors()] and ctx.D == 8490
+        super().__init__(ctx, parent, options, vbn)
+        if from_param_file:
+            self.from_serialized(from_param_file)
+        else:
+            self.initialize_params(rng_state)
+
+    def initialize_params(self, rng_state=None):
+        """src/algorithm/nets.py:55-69: Xavier-normal weights / zero biases, EXCEPT parameters whose name contains '1' (conv1, fc1), which
+        keep torch's default nn.Conv2d / nn.Linear init: U(-1/sqrt(fan_in), 1/sqrt(fan_in)) for weight and bias"""
+        gen = torch.Generator()
+        gen.manual_seed(int(rng_state) if rng_state is not None else torch.seed() % (1 << 31))
+        flat = torch.zeros(self.ctx.D, dtype=torch.float32)
+        for t in self.ctx.tensors:
+            layer = t.name.split('.')[0]
+            w_shape = dict(mnist_tensors())[layer + '.weight']
+            fan_in = int(np.prod(w_shape[1:]))
+            fan_out = w_shape[0] * int(np.prod(w_shape[2:]))
+            if '1' in t.name:
+                bound = 1.0 / fan_in ** 0.5
+                flat[t.start:t.start + t.count] = (torch.rand(t.count, generator=gen) * 2 - 1) * bound
+            elif t.name.endswith('weight'):
+                flat[t.start:t.start + t.count] = torch.randn(t.count, generator=gen) * (2.0 / (fan_in + fan_out)) ** 0.5
+        self.set_from_vector(flat)
+
+    def sensitivity_forward(self, experiences, orig_bs):
+        """MnistNet.forward_for_sensitivity (classification/nets.py:39-49): the logits of the whole batch, or of sample i"""
+        images = torch.as_tensor(experiences[0])
+        tensors = self.ctx.tensors
+        return lambda theta, i: _sm.mnist_forward(theta, tensors, images if i < 0 else images[i:i + 1])
+
+    def forward(self, x):
+        """logits float32 [B, 10] of this individual"""
+        x = torch.as_tensor(x).to(torch.float32)
+        labels = torch.zeros(x.shape[0], dtype=torch.int64, device=x.device)
+        off = torch.zeros(1, dtype=torch.int64)
+        _, _, lg = self.ctx.mnist_rollout(off, torch.ones(1), x, labels, 0.0, parents=torch.tensor([self.parent], dtype=torch.int32),
+                                          shared_batch=True, out_device=x.device if x.is_cuda else 'cpu', want_logits=True)
+        return lg[0]
 
     __call__ = forward

@@ -11,7 +11,7 @@ import torch
 
 from .cider import CiderD
 from .context import NesContext, PREC_EXACT
-from .nets import FCModel, ModelOptions, PolicyNet
+from .nets import FCModel, MnistNet, ModelOptions, PolicyNet
 
 
 class SuppDataset(Enum):
@@ -34,8 +34,6 @@ class Policy:
         assert isinstance(dataset, SuppDataset)
         self.dataset, self.options = dataset, options
         self.net = Net(options.net)
-        if self.net != Net.FC_CAPTION:
-            raise NotImplementedError('only the fc_caption net is on the B200 path (config 1, MNIST, stays on the CPU reference)')
         self.vbn = bool(options.vbn)
         self.ref_batch = None
         mo = dict(options.model_options)
@@ -88,8 +86,9 @@ class Policy:
             self.policy_net.from_serialized(model)
 
     def generate_model(self, from_param_file=None, start_rng=None):
-        model = FCModel(self._ctx, 0, self.model_options, rng_state=start_rng, from_param_file=from_param_file,
-                        vbn=self.vbn, **self._ctx_kwargs)
+        cls = MnistNet if self.net == Net.MNIST else FCModel              # src/algorithm/policies.py:71-74
+        model = cls(self._ctx, 0, self.model_options, rng_state=start_rng, from_param_file=from_param_file,
+                    vbn=self.vbn, **self._ctx_kwargs)
         self._ctx = model.ctx
         return model
 
@@ -211,10 +210,48 @@ class CaptPolicy(Policy):
         return self.ctx.rollout(offsets, signs, fc, sigma, parents=parents, precision=self.precision, out_device=out_device)
 
 
+class ClfPolicy(Policy):
+    """src/classification/policies.py:14-86 for the MNIST net: fitness = -CrossEntropyLoss on a batch, accuracy over a loader"""
+
+    @property
+    def ctx(self):
+        return self.policy_net.ctx
+
+    def rollout(self, placeholder, data, config):
+        """:16-48 -- `placeholder` is the reference's reusable input tensor; unused here (the batch goes to the device as it is)"""
+        assert self.policy_net is not None, 'Set model first!'
+        assert isinstance(self.policy_net, PolicyNet), '{}'.format(type(self.policy_net))
+        inputs, labels = data
+        fit, _ = self.ctx.mnist_rollout(torch.zeros(1, dtype=torch.int64), torch.ones(1), inputs, labels, 0.0,
+                                        parents=torch.tensor([self.policy_net.parent], dtype=torch.int32), shared_batch=True)
+        return float(np.float32(fit[0].item()))
+
+    def rollout_population(self, offsets, signs, data, sigma, parents=None, out_device='cpu'):
+        """batched form of ESWorker.fitness's evolve_model + rollout (nic_es_worker.py:142-192): fitness float64 [P], correct int32 [P]"""
+        inputs, labels = data
+        return self.ctx.mnist_rollout(offsets, signs, inputs, labels, sigma, parents=parents, out_device=out_device)
+
+    def accuracy_on(self, dataloader, config, directory) -> float:
+        """:50-86 -- the mean of the per-batch accuracies (the reference's own caveat about a smaller last batch applies)"""
+        assert self.policy_net is not None, 'Set model first!'
+        accuracies = []
+        end = config.num_val_batches if getattr(config, 'num_val_batches', None) else len(dataloader)
+        for i, (inputs, labels) in enumerate(dataloader):
+            if i >= end:
+                break
+            _, cor = self.ctx.mnist_rollout(torch.zeros(1, dtype=torch.int64), torch.ones(1), inputs, labels, 0.0,
+                                            parents=torch.tensor([self.policy_net.parent], dtype=torch.int32), shared_batch=True)
+            accuracies.append(float(cor[0].item()) / torch.as_tensor(labels).numel())
+        return np.mean(accuracies).item()
+
+
 class PolicyFactory:
     @staticmethod
     def create(dataset, exp, **kw):
+        """src/algorithm/policies.py:175-186"""
         options = PolicyOptions(**exp['policy_options'])
+        if dataset == SuppDataset.MNIST:
+            return ClfPolicy(dataset, options, **kw)
         if dataset == SuppDataset.MSCOCO:
             return CaptPolicy(dataset, options, **kw)
-        raise NotImplementedError('only MSCOCO / fc_caption is on the B200 path')
+        raise NotImplementedError

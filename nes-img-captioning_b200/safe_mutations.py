@@ -78,12 +78,21 @@ def forward_for_sensitivity(theta, tensors, dims, fc_feats, orig_bs=0, i=-1, spl
     return ((torch.stack(extended.split(split, dim=1)) ** 2).sum(2) ** (1 / 2)).permute(1, 0)
 
 
-def sum_sensitivity(theta, tensors, dims, fc_feats, orig_bs=0):
+def mnist_forward(theta, tensors, images):
+    """MnistNet.forward (src/classification/nets.py:25-37) over views of one flat theta; images [B, 1, 28, 28] -> logits [B, 10]"""
+    p = _views(theta, tensors)
+    x = torch.as_tensor(images).to(device=theta.device, dtype=theta.dtype)
+    x = F.max_pool2d(F.relu(F.conv2d(x, p['conv1.weight'], p['conv1.bias'])), 2, 2)
+    x = F.max_pool2d(F.relu(F.conv2d(x, p['conv2.weight'], p['conv2.bias'])), 2, 2)
+    return F.linear(x.reshape(-1, 4 * 4 * 20), p['fc1.weight'], p['fc1.bias'])
+
+
+def sum_sensitivity_of(theta, fwd):
     """Sensitivity._calc_sum_sensitivity (safe_mutations.py:93-115): row k of the Jacobian is d(sum over the batch of output k)/dtheta,
-    sensitivity = sqrt(sum_k J_k^2) / batch.  One backward pass per output group (95 at V1 = 9488)."""
+    sensitivity = sqrt(sum_k J_k^2) / batch.  fwd(theta, i) -> [rows, K] (i = -1: the whole batch); one backward pass per output."""
     theta = theta.detach().clone().requires_grad_(True)
-    with torch.enable_grad():
-        out = forward_for_sensitivity(theta, tensors, dims, fc_feats, orig_bs)
+    with torch.enable_grad(), torch.backends.cudnn.flags(allow_tf32=False):       # float32 convolutions like the reference's CPU run
+        out = fwd(theta, -1)
         K, B = out.size(1), out.size(0)
         jac = torch.zeros(K, theta.numel(), dtype=theta.dtype, device=theta.device)
         grad_output = torch.zeros_like(out)
@@ -96,23 +105,33 @@ def sum_sensitivity(theta, tensors, dims, fc_feats, orig_bs=0):
     return sens.detach()
 
 
-def abs_sensitivity(theta, tensors, dims, fc_feats, orig_bs=0):
+def abs_sensitivity_of(theta, fwd):
     """Sensitivity._calc_abs_sensitivity (safe_mutations.py:119-147) as it is evidently meant: per-sample Jacobians, |.| averaged over
     the batch, then the same root of squares.  UNPINNED: the reference's own method raises AttributeError (`self.nb_params` at :125
-    does not exist on Sensitivity), so there is nothing to compare against; one forward + backward per (output group, sample)."""
+    does not exist on Sensitivity), so there is nothing to compare against; one forward + backward per (output, sample)."""
     theta = theta.detach().clone().requires_grad_(True)
-    with torch.enable_grad():
-        full = forward_for_sensitivity(theta, tensors, dims, fc_feats, orig_bs)
+    with torch.enable_grad(), torch.backends.cudnn.flags(allow_tf32=False):
+        full = fwd(theta, -1)
         K, B = full.size(1), full.size(0)
         acc = torch.zeros(K, theta.numel(), dtype=theta.dtype, device=theta.device)
         for i in range(B):
-            out_i = forward_for_sensitivity(theta, tensors, dims, fc_feats, orig_bs, i=i)
+            out_i = fwd(theta, i)
             grad_output = torch.zeros_like(out_i)
             for k in range(K):
                 grad_output.zero_()
                 grad_output[0, k] = 1.0
                 acc[k] += torch.autograd.grad(out_i, theta, grad_outputs=grad_output, retain_graph=True)[0].abs()
     return torch.sqrt(((acc / B) ** 2).sum(0)).detach()
+
+
+def sum_sensitivity(theta, tensors, dims, fc_feats, orig_bs=0):
+    """SM-G-SUM for fc_caption: sum_sensitivity_of over forward_for_sensitivity"""
+    return sum_sensitivity_of(theta, lambda th, i: forward_for_sensitivity(th, tensors, dims, fc_feats, orig_bs, i=i))
+
+
+def abs_sensitivity(theta, tensors, dims, fc_feats, orig_bs=0):
+    """SM-G-ABS for fc_caption (unpinned, see abs_sensitivity_of)"""
+    return abs_sensitivity_of(theta, lambda th, i: forward_for_sensitivity(th, tensors, dims, fc_feats, orig_bs, i=i))
 
 
 class Sensitivity(object):
@@ -173,5 +192,5 @@ class Sensitivity(object):
     def _calc_sensitivity(self, experiences):
         net = self.net
         theta = net.parameter_vector().to(device=net.ctx.dev, dtype=torch.float32)
-        fn = sum_sensitivity if self._type.value == 'SM-G-SUM' else abs_sensitivity
-        return fn(theta, net.ctx.tensors, net.ctx.dims, experiences['fc_feats'], self._orig_batch_size)
+        fwd = net.sensitivity_forward(experiences, self._orig_batch_size)
+        return (sum_sensitivity_of if self._type.value == 'SM-G-SUM' else abs_sensitivity_of)(theta, fwd)

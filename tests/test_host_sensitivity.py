@@ -73,6 +73,9 @@ class _FakeNet:
     def parameter_vector(self):
         return torch.from_numpy(self.theta.copy())
 
+    def sensitivity_forward(self, experiences, orig_bs):                  # as FCModel.sensitivity_forward
+        return lambda th, i: sm.forward_for_sensitivity(th, self.ctx.tensors, self.ctx.dims, experiences['fc_feats'], orig_bs, i=i)
+
 
 def test_sensitivity_file_protocol(tmp_path):
     """first call computes and writes sens_t{task}_p{parent}_{pid}.pt; the same (task, parent) again is a no-op; another worker loads the
