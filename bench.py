@@ -462,7 +462,63 @@ def extras(ctx, nes_b200, torch, dev, peaks):
         ctx.rollout(offs, signs, fc, 0.01, out_device=dev, uniforms=u)
     e1.record(); torch.cuda.synchronize()
     ex['sampled_decode'] = {'rollouts': n_m, 'rows': 128, 'ms': e0.elapsed_time(e1) / 2, 'rollouts_per_s': n_m * 2 / (e0.elapsed_time(e1) * 1e-3)}
+    ex['mnist_es'] = mnist_extras(nes_b200, torch, dev)
     return ex
+
+
+def mnist_extras(nes_b200, torch, dev):
+    """BASELINE configs[0] (experiments/mnist_es.json: nb_offspring 50, population_size 10, num_elites 3, batch 64, sigma 0.05): one
+    NIC-ES generation on the device (k_mnist_rollout + selection + survivors), the rollout alone at population 5000, and the oracle port
+    of evolve + ClfPolicy.rollout on ONE host core -- the reference runs this config with a single CPU worker"""
+    import numpy as np
+    from oracle import mnist as omnist
+    mu, el, P, sigma, rows = 10, 3, 50, 0.05, 64
+    mctx = nes_b200.NesContext(tensors=nes_b200.layout.mnist_tensors(), seed=4321, table_len=1 << 24, n_parents=2 * mu)
+    for k in range(mu):
+        mctx.set_theta(omnist.seeded_theta(k), k)
+    g = torch.Generator().manual_seed(2)
+    images = torch.randn(rows, 1, 28, 28, generator=g).to(dev)
+    labels = torch.randint(0, 10, (rows,), generator=g).to(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    base = 0
+    for it in range(3):
+        base = nes_b200.es_generation_mnist(mctx, it, P, mu, el, images, labels, sigma, base=base)[0]
+    torch.cuda.synchronize()
+    e0.record()
+    for it in range(3, 13):
+        base = nes_b200.es_generation_mnist(mctx, it, P, mu, el, images, labels, sigma, base=base)[0]
+    e1.record(); torch.cuda.synchronize()
+    gen_ms = e0.elapsed_time(e1) / 10
+    big = 5000
+    offs = mctx.sample_offsets(77, big, device=True)
+    ones = torch.ones(big, device=dev)
+    pars = mctx.sample_parents(77, big, mu, device=True)
+    mctx.mnist_rollout(offs, ones, images, labels, sigma, parents=pars, out_device=dev)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(5):
+        mctx.mnist_rollout(offs, ones, images, labels, sigma, parents=pars, out_device=dev)
+    e1.record(); torch.cuda.synchronize()
+    roll_ms = e0.elapsed_time(e1) / 5
+    # host: the oracle port, one core (torch threads pinned to 1 like src/main.py:8-11)
+    nt = torch.get_num_threads()
+    torch.set_num_threads(1)
+    th = omnist.seeded_theta(0)
+    im, lb = images.cpu().numpy(), labels.cpu().numpy()
+    rs = np.random.RandomState(0)
+    t0 = time.perf_counter()
+    n_cpu = 200
+    for _ in range(n_cpu):
+        member = th + np.float32(sigma) * rs.randn(omnist.D).astype(np.float32)          # PolicyNet.evolve
+        omnist.rollout(member, im, lb)
+    cpu_s = (time.perf_counter() - t0) / n_cpu
+    torch.set_num_threads(nt)
+    mctx.close()
+    return {'workload': 'configs[0]: MnistNet NIC-ES, nb_offspring 50, population_size 10, num_elites 3, 64 images / rollout, sigma 0.05',
+            'generation_ms': gen_ms, 'generation_evals_per_s': P / (gen_ms * 1e-3),
+            'rollout_5000_members_ms': roll_ms, 'rollout_evals_per_s': big / (roll_ms * 1e-3),
+            'rollout_gflops': big * rows * 2 * (1440 * 100 + 320 * 1000 + 3200) / (roll_ms * 1e-3) / 1e9,
+            'cpu_port_evals_per_s_one_core': 1.0 / cpu_s, 'cpu_sample': '%d evolve + rollout pairs, 1 thread' % n_cpu}
 
 
 if __name__ == '__main__':

@@ -214,18 +214,22 @@ def es_select_and_materialise(ctx: NesContext, fitness_all, offs, pars, mu, num_
 
 
 def es_generation(ctx: NesContext, iteration, n_local, mu, num_elites, fc, sigma, base=0, fitness_fn=None,
-                  world_size=1, rank=0, precision=PREC_EXACT, group=None):
+                  world_size=1, rank=0, precision=PREC_EXACT, group=None, evaluate=None):
     """One NIC-ES generation on a context created with n_parents = 2*mu (current parents in slots [base, base+mu)).
     Every rank evaluates n_local offspring of the n_local*world_size sampled; fitness_fn(seq, logprobs) -> float64 [n_local]
-    (None: sum of greedy log-probs, computed on the device).  Returns (new base, all fitnesses, offsets, parents)."""
+    (None: sum of greedy log-probs, computed on the device).  evaluate(offsets, signs, parent_slots, sigma) -> float64 [n_local] replaces
+    the fc_caption rollout altogether (the MNIST net: es_generation_mnist).  Returns (new base, all fitnesses, offsets, parents)."""
     assert ctx.n_parents >= 2 * mu and base in (0, mu)
     n_all = n_local * world_size
     offs, pars = es_sample_generation(ctx, iteration, n_all, mu)
     lo = rank * n_local
     ones = torch.ones(n_local, dtype=torch.float32, device=ctx.dev)
-    seq, lp = ctx.rollout(offs[lo:lo + n_local], ones, fc, sigma, parents=pars[lo:lo + n_local] + base, precision=precision, out_device=ctx.dev)
-    rows = seq.shape[1]
-    fit = ctx.logprob_fitness(n_local, rows, device=ctx.dev) if fitness_fn is None else torch.as_tensor(fitness_fn(seq, lp), dtype=torch.float64).to(ctx.dev)
+    if evaluate is not None:
+        fit = torch.as_tensor(evaluate(offs[lo:lo + n_local], ones, pars[lo:lo + n_local] + base, sigma), dtype=torch.float64).to(ctx.dev)
+    else:
+        seq, lp = ctx.rollout(offs[lo:lo + n_local], ones, fc, sigma, parents=pars[lo:lo + n_local] + base, precision=precision, out_device=ctx.dev)
+        rows = seq.shape[1]
+        fit = ctx.logprob_fitness(n_local, rows, device=ctx.dev) if fitness_fn is None else torch.as_tensor(fitness_fn(seq, lp), dtype=torch.float64).to(ctx.dev)
     if world_size > 1:
         import torch.distributed as dist
         out = torch.empty(n_all, dtype=torch.float64, device=ctx.dev)
@@ -233,3 +237,13 @@ def es_generation(ctx: NesContext, iteration, n_local, mu, num_elites, fc, sigma
         fit = out
     new_base = es_select_and_materialise(ctx, fit, offs, pars, mu, num_elites, base, sigma)
     return new_base, fit, offs, pars
+
+
+def es_generation_mnist(ctx: NesContext, iteration, n_local, mu, num_elites, images, labels, sigma, base=0, **kw):
+    """One NIC-ES generation of the MNIST classifier as experiments/mnist_es.json runs it (nb_offspring 50, population_size 10,
+    num_elites 3, batch 64; nic_es_worker.py:142-192 + ClfPolicy.rollout + nic_es_master.py:155-167): every offspring's
+    fitness = -CrossEntropyLoss on the batch from one k_mnist_rollout launch, selection and survivors as es_generation"""
+    images = torch.as_tensor(images).to(ctx.dev)
+    labels = torch.as_tensor(labels).to(ctx.dev)
+    return es_generation(ctx, iteration, n_local, mu, num_elites, None, sigma, base=base,
+                         evaluate=lambda o, s, p, sg: ctx.mnist_rollout(o, s, images, labels, sg, parents=p, out_device=ctx.dev)[0], **kw)

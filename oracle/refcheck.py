@@ -220,6 +220,31 @@ def check_grad_sensitivity(ref):
     return True
 
 
+def check_mnist(ref):
+    """oracle/mnist.py against the imported MnistNet / ClfPolicy.rollout (classification/nets.py:25-37, policies.py:16-48): logits bit-exact,
+    fitness to float32 round-off, the parameter order and count (8490)"""
+    from classification.nets import MnistNet
+    from classification.policies import ClfPolicy
+    from oracle import mnist
+    net = MnistNet(options=None)
+    assert [n for n, _ in net.named_parameters()] == [n for n, _, _, _ in mnist.layout()] and net.nb_learnable_params == mnist.D
+    policy = object.__new__(ClfPolicy)
+    policy.policy_net, policy.vbn = net, False
+    cfg = type('Cfg', (), {'cuda': False})()
+    rs = np.random.RandomState(2)
+    for k in range(3):
+        theta = mnist.seeded_theta(k, scale=1.0 + k)
+        images = rs.randn(33, 1, 28, 28).astype(np.float32)
+        labels = rs.randint(0, 10, 33).astype(np.int64)
+        net.set_from_vector(torch.from_numpy(theta.copy()))
+        want = net(torch.from_numpy(images)).numpy()
+        assert np.array_equal(mnist.forward(theta, images), want)
+        fit = policy.rollout(torch.empty(images.shape), (torch.from_numpy(images), torch.from_numpy(labels)), cfg)
+        got, cor = mnist.rollout(theta, images, labels)
+        assert got == fit and cor == int((want.argmax(1) == labels).sum())
+    return True
+
+
 def main():
     if not _refimport.available():
         print('reference not present; nothing checked'); return 1
@@ -235,8 +260,8 @@ def main():
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)
     assert fc_caption.Dims(9487, 128, 128, 2048).num_params() == 2865808
     assert fc_caption.Dims(9487, 512, 512, 2048).num_params() == 13400848
-    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref); check_sample_decode(ref); check_sensitivity(ref); check_grad_sensitivity(ref)
-    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL, SM-VECTOR, SM-G-SUM sensitivity, sampled decode OK' % n)
+    check_master_math(ref); check_optimizers(ref); check_cider(); check_shaped_fitness(); check_proportional(ref); check_sample_decode(ref); check_sensitivity(ref); check_grad_sensitivity(ref); check_mnist(ref)
+    print('oracle pinned against the imported reference: %d decode configs, master math, optimizers, CIDEr-D, shaped fitnesses, SM-PROPORTIONAL, SM-VECTOR, SM-G-SUM sensitivity, sampled decode, MNIST net OK' % n)
     return 0
 
 
