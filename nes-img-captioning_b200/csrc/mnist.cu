@@ -4,32 +4,83 @@
 //   ClfPolicy.accuracy_on (:50-86): prediction = argmax(outputs, 1), first index on ties
 // for members theta_p + s*sigma*eps(offset) [safe-mutation scaled] that are never written to HBM: a CTA rebuilds its member's 8490
 // parameters in shared memory straight from theta32 and the noise-table row (the arithmetic of k_evolve, so they equal nes_evolve's
-// bit for bit) and runs kImagesPerBlock images through the net with every intermediate in shared memory.  FP32 CUDA-core work: the
+// bit for bit) and runs kImagesPerBlock images through the net stage by stage with every intermediate in shared memory; the
+// convolutions are register tiled (5 output channels x the 2x2 pooling window per thread) so that the FMA pipe, not the
+// shared-memory pipe, is the limit.  FP32 CUDA-core work: the
 // whole net is 0.47 MFLOP-pairs per image, and a member's parameters (34 KB) are read once per CTA -- nothing here is GEMM shaped.
 #include "common.cuh"
 
 namespace nes {
 
 namespace {
-constexpr int kW1 = 0, kB1 = 250, kW2 = 260, kB2 = 5260, kW3 = 5280, kB3 = 8480, kParams = 8490;   // flat starts (parameter_vector order)
 constexpr int kImagesPerBlock = 8;
 constexpr int kThreads = 256;
+// shared-memory parameter layout: every 5x5 filter padded to 28 floats so that its taps load as 7 broadcast LDS.128
+constexpr int kFilt = 28;
+constexpr int sW1 = 0, sW2 = sW1 + 10 * kFilt, sW3 = sW2 + 200 * kFilt, sB1 = sW3 + 3200, sB2 = sB1 + 12, sB3 = sB2 + 20, sParams = sB3 + 12;
 
 struct MnistSmem {
-    float w[kParams + 6];          // member parameters
-    float img[28 * 28];
-    float p1[10 * 12 * 12];        // after conv1 + relu + pool
-    float p2[320];                 // after conv2 + relu + pool, flattened like x.view(-1, 4*4*20): [c][y][x]
-    float logits[10];
+    float w[sParams];                               // member parameters (36.5 KB)
+    float img[kImagesPerBlock][28 * 28];            // 25 KB; dead after conv1, p2 lives on top of it
+    float p1[kImagesPerBlock][10 * 12 * 12];        // after conv1 + relu + pool (46 KB)
+    float logits[kImagesPerBlock][10];
 };
+static_assert(sizeof(MnistSmem) <= 112 * 1024, "two CTAs per SM");
+static_assert(sW2 % 4 == 0 && sW3 % 4 == 0 && kFilt % 4 == 0, "filters must be 16-byte aligned");
 
-__global__ void __launch_bounds__(kThreads) k_mnist_rollout(const float* __restrict__ theta32, const __half* __restrict__ table, const Layout* __restrict__ lay,
-                                                            const int64_t* __restrict__ offs, const float* __restrict__ signs, const int32_t* __restrict__ parents,
-                                                            float sigma, const float* __restrict__ scale, int scale_div,
-                                                            const float* __restrict__ images, const int64_t* __restrict__ labels, int rows, int shared_batch,
-                                                            float* __restrict__ loss, int32_t* __restrict__ pred, float* __restrict__ logits_out) {
-    extern __shared__ uint8_t smem_raw[];
+// flat parameter index of tensor k, element j -> position in MnistSmem::w
+__device__ __forceinline__ int smem_pos(int k, int j) {
+    switch (k) {
+        case 0: return sW1 + (j / 25) * kFilt + j % 25;
+        case 1: return sB1 + j;
+        case 2: return sW2 + (j / 25) * kFilt + j % 25;
+        case 3: return sB2 + j;
+        case 4: return sW3 + j;
+        default: return sB3 + j;
+    }
+}
+
+// CO output channels of one pooled position: acc[c][0..3] = the four conv outputs under the 2x2 pooling window, accumulated over one
+// input plane.  in: the plane's 6x6 patch origin (row stride LD, 8-byte aligned); wf: CO filters, stride WS floats (16-byte aligned).
+// Loads per plane: 18 LDS.64 of inputs (conflict free) + 7*CO broadcast LDS.128 of taps for 100*CO FMAs -- the first version of this
+// kernel issued 0.85 shared-memory wavefronts per FMA and sat at 97 % of the LSU pipe (profiles/r1_full_v17_mnist_summary.txt)
+template <int CO, int LD, int WS>
+__device__ __forceinline__ void conv_plane(const float* __restrict__ in, const float* __restrict__ wf, float (&acc)[CO][4]) {
+    float x[6][6];
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const float2 v = *reinterpret_cast<const float2*>(in + r * LD + 2 * q);
+            x[r][2 * q] = v.x; x[r][2 * q + 1] = v.y;
+        }
+#pragma unroll
+    for (int c = 0; c < CO; ++c) {
+        float w[28];
+#pragma unroll
+        for (int q = 0; q < 7; ++q) {
+            const float4 v = *reinterpret_cast<const float4*>(wf + c * WS + 4 * q);
+            w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+        }
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx) {
+                const float wv = w[ky * 5 + kx];
+                acc[c][0] = fmaf(wv, x[ky][kx], acc[c][0]);     acc[c][1] = fmaf(wv, x[ky][kx + 1], acc[c][1]);
+                acc[c][2] = fmaf(wv, x[ky + 1][kx], acc[c][2]); acc[c][3] = fmaf(wv, x[ky + 1][kx + 1], acc[c][3]);
+            }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) k_mnist_rollout(const float* __restrict__ theta32, const __half* __restrict__ table, const Layout* __restrict__ lay,
+                                                               const int64_t* __restrict__ offs, const float* __restrict__ signs, const int32_t* __restrict__ parents,
+                                                               float sigma, const float* __restrict__ scale, int scale_div,
+                                                               const float* __restrict__ images, const int64_t* __restrict__ labels, int rows, int shared_batch,
+                                                               float* __restrict__ loss, int32_t* __restrict__ pred, float* __restrict__ logits_out) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
     MnistSmem& s = *reinterpret_cast<MnistSmem*>(smem_raw);
+    float (*p2)[320] = reinterpret_cast<float (*)[320]>(&s.img[0][0]);      // after conv2 + relu + pool, [c][y][x] like x.view(-1, 320)
     const int m = blockIdx.y, tid = threadIdx.x;
     const int par = parents ? parents[m] : 0;
     const int64_t D = lay->D;
@@ -46,82 +97,65 @@ __global__ void __launch_bounds__(kThreads) k_mnist_rollout(const float* __restr
                 const float nz = mut_noise(sigma, __half2float(row[t.pstart + j]), sc, t.start + j, scale_div);
                 v = sign > 0.f ? __fadd_rn(th0, nz) : __fsub_rn(th0, nz);
             }
-            s.w[t.start + j] = v;
+            s.w[smem_pos(k, j)] = v;
         }
     }
     const float* img_base = images + (shared_batch ? 0 : (int64_t)m * rows * 784);
     const int r0 = blockIdx.x * kImagesPerBlock;
-    for (int r = r0; r < min(r0 + kImagesPerBlock, rows); ++r) {
-        __syncthreads();                                   // parameters ready / previous image done
-        for (int j = tid; j < 784; j += kThreads) s.img[j] = img_base[(int64_t)r * 784 + j];
-        __syncthreads();
-        // conv1 + bias + relu + maxpool: one pooled output per item, its 6x6 input patch in registers
-        for (int o = tid; o < 1440; o += kThreads) {
-            const int c = o / 144, py = (o % 144) / 12, px = o % 12;
-            const float* w = s.w + kW1 + c * 25;
-            float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
+    const int n_img = min(kImagesPerBlock, rows - r0);
+    for (int j = tid; j < n_img * 784; j += kThreads) (&s.img[0][0])[j] = img_base[(int64_t)r0 * 784 + j];
+    __syncthreads();
+    // conv1 + bias + relu + maxpool: item = (image, half of the channels, pooled position), 5 channels per item
+    for (int o = tid; o < n_img * 2 * 144; o += kThreads) {
+        const int im = o / 288, cg = (o % 288) / 144, pos = o % 144, py = pos / 12, px = pos % 12;
+        float acc[5][4] = {};
+        conv_plane<5, 28, kFilt>(&s.img[im][(2 * py) * 28 + 2 * px], s.w + sW1 + cg * 5 * kFilt, acc);
 #pragma unroll
-            for (int ky = 0; ky < 5; ++ky) {
-                const float* i0 = s.img + (2 * py + ky) * 28 + 2 * px;
-                const float* i1 = i0 + 28;
-#pragma unroll
-                for (int kx = 0; kx < 5; ++kx) {
-                    const float wv = w[ky * 5 + kx];
-                    a00 = fmaf(wv, i0[kx], a00); a01 = fmaf(wv, i0[kx + 1], a01);
-                    a10 = fmaf(wv, i1[kx], a10); a11 = fmaf(wv, i1[kx + 1], a11);
-                }
-            }
-            const float mx = fmaxf(fmaxf(a00, a01), fmaxf(a10, a11)) + s.w[kB1 + c];
-            s.p1[o] = fmaxf(mx, 0.f);
+        for (int c = 0; c < 5; ++c) {
+            const float mx = fmaxf(fmaxf(acc[c][0], acc[c][1]), fmaxf(acc[c][2], acc[c][3])) + s.w[sB1 + cg * 5 + c];
+            s.p1[im][(cg * 5 + c) * 144 + pos] = fmaxf(mx, 0.f);
         }
-        __syncthreads();
-        // conv2 + bias + relu + maxpool
-        for (int o = tid; o < 320; o += kThreads) {
-            const int c = o / 16, py = (o % 16) / 4, px = o % 4;
-            float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
-            for (int ci = 0; ci < 10; ++ci) {
-                const float* w = s.w + kW2 + (c * 10 + ci) * 25;
-                const float* pin = s.p1 + ci * 144;
-#pragma unroll
-                for (int ky = 0; ky < 5; ++ky) {
-                    const float* i0 = pin + (2 * py + ky) * 12 + 2 * px;
-                    const float* i1 = i0 + 12;
-#pragma unroll
-                    for (int kx = 0; kx < 5; ++kx) {
-                        const float wv = w[ky * 5 + kx];
-                        a00 = fmaf(wv, i0[kx], a00); a01 = fmaf(wv, i0[kx + 1], a01);
-                        a10 = fmaf(wv, i1[kx], a10); a11 = fmaf(wv, i1[kx + 1], a11);
-                    }
-                }
-            }
-            const float mx = fmaxf(fmaxf(a00, a01), fmaxf(a10, a11)) + s.w[kB2 + c];
-            s.p2[o] = fmaxf(mx, 0.f);
-        }
-        __syncthreads();
-        // fc1: warp w computes outputs w and w + 8
-        const int warp = tid >> 5, lane = tid & 31;
-        for (int o = warp; o < 10; o += kThreads / 32) {
-            const float* w = s.w + kW3 + o * 320;
-            float a = 0.f;
-            for (int j = lane; j < 320; j += 32) a = fmaf(w[j], s.p2[j], a);
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
-            if (lane == 0) s.logits[o] = a + s.w[kB3 + o];
-        }
-        __syncthreads();
-        if (tid == 0) {
-            // CrossEntropyLoss = log_softmax + nll (policies.py:39-40); argmax with the first index on ties (:72)
-            float mx = s.logits[0]; int am = 0;
-            for (int o = 1; o < 10; ++o) if (s.logits[o] > mx) { mx = s.logits[o]; am = o; }
-            float se = 0.f;
-            for (int o = 0; o < 10; ++o) se += expf(s.logits[o] - mx);
-            const int64_t lab = labels[(shared_batch ? 0 : (int64_t)m * rows) + r];
-            const float lp = (s.logits[lab] - mx) - logf(se);
-            loss[(int64_t)m * rows + r] = -lp;
-            pred[(int64_t)m * rows + r] = am;
-        }
-        if (logits_out && tid < 10) logits_out[((int64_t)m * rows + r) * 10 + tid] = s.logits[tid];
     }
+    __syncthreads();
+    // conv2 + bias + relu + maxpool: item = (image, group of 5 output channels, pooled position): 8 x 4 x 16 = 512 items = two full rounds
+    for (int o = tid; o < n_img * 4 * 16; o += kThreads) {
+        const int im = o / 64, cg = (o % 64) / 16, pos = o % 16, py = pos / 4, px = pos % 4;
+        float acc[5][4] = {};
+        for (int ci = 0; ci < 10; ++ci)
+            conv_plane<5, 12, 10 * kFilt>(&s.p1[im][ci * 144 + (2 * py) * 12 + 2 * px], s.w + sW2 + (cg * 5 * 10 + ci) * kFilt, acc);
+#pragma unroll
+        for (int c = 0; c < 5; ++c) {
+            const float mx = fmaxf(fmaxf(acc[c][0], acc[c][1]), fmaxf(acc[c][2], acc[c][3])) + s.w[sB2 + cg * 5 + c];
+            p2[im][(cg * 5 + c) * 16 + pos] = fmaxf(mx, 0.f);
+        }
+    }
+    __syncthreads();
+    // fc1: one warp per (image, output)
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int o = warp; o < n_img * 10; o += kThreads / 32) {
+        const int im = o / 10, k = o % 10;
+        const float* w = s.w + sW3 + k * 320;
+        float a = 0.f;
+        for (int j = lane; j < 320; j += 32) a = fmaf(w[j], p2[im][j], a);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
+        if (lane == 0) s.logits[im][k] = a + s.w[sB3 + k];
+    }
+    __syncthreads();
+    if (tid < n_img) {
+        // CrossEntropyLoss = log_softmax + nll (policies.py:39-40); argmax with the first index on ties (:72)
+        const float* lg = s.logits[tid];
+        const int r = r0 + tid;
+        float mx = lg[0]; int am = 0;
+        for (int o = 1; o < 10; ++o) if (lg[o] > mx) { mx = lg[o]; am = o; }
+        float se = 0.f;
+        for (int o = 0; o < 10; ++o) se += expf(lg[o] - mx);
+        const int64_t lab = labels[(shared_batch ? 0 : (int64_t)m * rows) + r];
+        const float lp = (lg[lab] - mx) - logf(se);
+        loss[(int64_t)m * rows + r] = -lp;
+        pred[(int64_t)m * rows + r] = am;
+    }
+    if (logits_out && tid < n_img * 10) logits_out[((int64_t)m * rows + r0) * 10 + tid] = (&s.logits[0][0])[tid];
 }
 
 // fitness = -mean loss (float64 accumulation in row order), correct = number of rows whose prediction equals the label
