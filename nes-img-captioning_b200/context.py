@@ -109,7 +109,7 @@ class NesContext:
     def set_mutation(self, kind):
         """'' (default), 'SM-PROPORTIONAL' (noise scaled by |theta_p|, zeros by mean|theta_p|), or one of the sensitivity mutations
         'SM-VECTOR' / 'SM-G-SUM' / 'SM-G-ABS' (noise divided by a sensitivity vector given through set_sensitivity; the
-        gradient-based ones come from autograd, safe_mutations.py / PolicyNet.calc_sensitivity)"""
+        gradient-based ones come from autograd, sensitivity.py / PolicyNet.calc_sensitivity)"""
         if kind not in self.MUTATIONS:
             raise NotImplementedError('mutation %r is not on the B200 path (SURVEY 8f-3)' % (kind,))
         _lib.check(self.lib.nes_set_mutation(self._h, self.MUTATIONS[kind]))

@@ -6,7 +6,7 @@ Differences that follow from the design (documented in DESIGN.md):
     unseeded torch.normal_ -- the returned vector is still float32 sigma*eps of length D;
   * set_from_vector() copies (the reference aliases the caller's memory, nets.py:163-165);
   * every Mutation runs on the CUDA path; for SM-G-SUM / SM-G-ABS the sensitivity vector itself comes from autograd
-    (safe_mutations.py here) and the kernels divide the noise by it.
+    (sensitivity.py here) and the kernels divide the noise by it.
 """
 from collections import OrderedDict, namedtuple
 from enum import Enum
@@ -15,9 +15,9 @@ import numpy as np
 import torch
 
 from .context import NesContext, PREC_EXACT
-from . import safe_mutations as _sm
+from . import sensitivity as _sm
 from .layout import mnist_tensors
-from .safe_mutations import Sensitivity
+from .sensitivity import Sensitivity
 
 _model_opt_fields = ['vocab_size', 'input_encoding_size', 'rnn_type', 'rnn_size', 'num_layers',
                      'drop_prob_lm', 'seq_length', 'fc_feat_size', 'vbn', 'vbn_e', 'vbn_affine', 'layer_n',

@@ -134,59 +134,54 @@ def abs_sensitivity(theta, tensors, dims, fc_feats, orig_bs=0):
     return abs_sensitivity_of(theta, lambda th, i: forward_for_sensitivity(th, tensors, dims, fc_feats, orig_bs, i=i))
 
 
-class Sensitivity(object):
-    """src/algorithm/safe_mutations.py:14-91: caches the vector per (task_id, parent_id) in memory and in
-    `sens_t{task}_p{parent}_{pid}.pt` under `directory`, so the first worker to need a parent's sensitivity computes it and the
-    others load the file.  `net` supplies parameter_vector(), ctx.tensors / ctx.dims and the device."""
+class Sensitivity:
+    """Per-parent sensitivity vector with the reference's sharing protocol (src/algorithm/safe_mutations.py:14-91): a vector is valid
+    for one (task_id, parent_id); the first worker that needs it computes it and leaves `sens_t{task}_p{parent}_{pid}.pt` in
+    `directory`, everybody else loads that file.  `net` supplies parameter_vector(), sensitivity_forward() and ctx.dev."""
+
+    FILE = 'sens_t{t}_p{p}_{i}.pt'
 
     def __init__(self, net, underflow, method):
-        self._sensitivity = None
-        self._sens_iteration = -1
-        self._parent_id = -1
-        self.net = net
-        self._orig_batch_size = 0
-        self._underflow = underflow
-        self._type = method
+        self.net, self._underflow, self._type = net, underflow, method
+        self._vector = None
+        self._valid_for = None              # (task_id, parent_id) the vector belongs to
+        self._orig_batch_size = 0           # batch size of the first call; later calls keep using it (:57-58)
 
     def get_sensitivity(self):
-        return self._sensitivity
+        return self._vector
 
     def set_sensitivity(self, path):
-        """:27-32 -- a precomputed vector (SM-VECTOR): clamp at the underflow value, divide by the minimum"""
-        sensitivity = torch.load(path, map_location='cpu') if isinstance(path, str) else torch.as_tensor(path).clone()
-        sensitivity = sensitivity.to(torch.float32)
-        sensitivity[sensitivity < self._underflow] = self._underflow
-        sensitivity /= sensitivity.min()
-        self._sensitivity = sensitivity
+        """:27-32 -- a precomputed vector (SM-VECTOR), from a torch-saved file or in memory: floor at the underflow value, then
+        scale so that the smallest entry is 1"""
+        vec = torch.load(path, map_location='cpu') if isinstance(path, str) else torch.as_tensor(path).clone()
+        vec = vec.to(torch.float32).clamp_(min=self._underflow)
+        self._vector = vec / vec.min()
 
     def calc_sensitivity(self, task_id, parent_id, experiences, batch_size, directory):
         """:34-91.  Returns True when the vector changed (the caller then hands it to the device)."""
-        pattern = 'sens_t{t}_p{p}_[0-9]*?.pt'.format(t=task_id, p=parent_id)
-        if self._sensitivity is not None and self._sens_iteration == task_id and self._parent_id == parent_id:
+        key = (task_id, parent_id)
+        if self._vector is not None and self._valid_for == key:
             return False
-        filename = find_file_with_pattern(pattern, directory)
-        if filename:
+        pattern = self.FILE.format(t=task_id, p=parent_id, i='[0-9]*?')
+        while True:
+            found = find_file_with_pattern(pattern, directory)
+            if not found:
+                break
             try:
-                self._sensitivity = torch.load(os.path.join(directory, filename), map_location='cpu')
-                self._sens_iteration, self._parent_id = task_id, parent_id
+                self._vector, self._valid_for = torch.load(os.path.join(directory, found), map_location='cpu'), key
                 logging.info('took sensitivity from file')
                 return True
-            except (RuntimeError, EOFError):            # another worker is still writing it
+            except (RuntimeError, EOFError):            # another worker is still writing it: wait and look again (:50-52)
                 time.sleep(2)
-                return self.calc_sensitivity(task_id, parent_id, experiences, batch_size, directory)
-        start_time = time.time()
-        if self._orig_batch_size == 0:
-            self._orig_batch_size = batch_size
-        sensitivity = self._calc_sensitivity(experiences).cpu()
-        sensitivity[sensitivity < self._underflow] = self._underflow
-        sensitivity /= self._underflow                   # :65 -- by the underflow value here, not by the minimum
-        logging.info('Safe mutation sensitivity computed in {:.2f}s on {} samples'.format(time.time() - start_time, batch_size))
+        t0 = time.time()
+        self._orig_batch_size = self._orig_batch_size or batch_size
+        vec = self._calc_sensitivity(experiences).cpu().clamp_(min=self._underflow)
+        vec /= self._underflow                           # :65 -- by the underflow value here, not by the minimum as in set_sensitivity
+        logging.info('Safe mutation sensitivity computed in {:.2f}s on {} samples'.format(time.time() - t0, batch_size))
         if not find_file_with_pattern(pattern, directory):
-            torch.save(sensitivity.clone(), os.path.join(directory, 'sens_t{t}_p{p}_{i}.pt'.format(t=task_id, p=parent_id, i=os.getpid())))
-        self._sensitivity = sensitivity
-        self._sens_iteration, self._parent_id = task_id, parent_id
-        logging.info('Sensitivity parent {}: min {:.2f}, mean {:.2f}, max {:.2f}'.format(
-            parent_id, sensitivity.min().item(), sensitivity.mean().item(), sensitivity.max().item()))
+            torch.save(vec.clone(), os.path.join(directory, self.FILE.format(t=task_id, p=parent_id, i=os.getpid())))
+        self._vector, self._valid_for = vec, key
+        logging.info('Sensitivity parent {}: min {:.2f}, mean {:.2f}, max {:.2f}'.format(parent_id, vec.min().item(), vec.mean().item(), vec.max().item()))
         return True
 
     def _calc_sensitivity(self, experiences):

@@ -188,12 +188,12 @@ def check_sensitivity(ref, seed=5):
 
 
 def check_grad_sensitivity(ref):
-    """SM-G-SUM: the package's autograd restatement (nes-img-captioning_b200/safe_mutations.py, torch on the CPU here) against the
+    """SM-G-SUM: the package's autograd restatement (nes-img-captioning_b200/sensitivity.py, torch on the CPU here) against the
     reference's Sensitivity.calc_sensitivity over FCModel.forward_for_sensitivity (safe_mutations.py:34-115, captioning/nets.py:22-69),
     plain / LayerNorm / batch-norm cells: bit-exact on this torch build.  This is the one check that exercises product code: the
     function is device-agnostic torch and has no separate oracle restatement."""
     import importlib, tempfile
-    pkg_sm = importlib.import_module('nes-img-captioning_b200.safe_mutations')
+    pkg_sm = importlib.import_module('nes-img-captioning_b200.sensitivity')
     lay = importlib.import_module('nes-img-captioning_b200.layout')
     for cfg in [dict(V=199, E=64, R=64, Fd=128, ln=0, aff=0, vbn=0, uf=1e-4), dict(V=299, E=32, R=64, Fd=128, ln=1, aff=1, vbn=0, uf=0.01),
                 dict(V=230, E=32, R=32, Fd=64, ln=0, aff=1, vbn=1, uf=0.01), dict(V=230, E=32, R=32, Fd=64, ln=1, aff=0, vbn=0, uf=0.01)]:

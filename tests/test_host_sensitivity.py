@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, 'golden'))
 import make_golden_sens as ms  # noqa: E402
 
-sm = importlib.import_module('nes-img-captioning_b200.safe_mutations')
+sm = importlib.import_module('nes-img-captioning_b200.sensitivity')
 lay = importlib.import_module('nes-img-captioning_b200.layout')
 GOLD = np.load(os.path.join(HERE, 'golden', 'golden_sens_v1.npz'))
 

@@ -45,7 +45,7 @@ def test_oracle_matches_reference_golden():
 
 def test_package_sum_sensitivity_matches_reference_golden():
     """SM-G-SUM as mnist_es.json configures it (underflow 0.2): the package's autograd path on the CPU against the reference's vector"""
-    sm = importlib.import_module('nes-img-captioning_b200.safe_mutations')
+    sm = importlib.import_module('nes-img-captioning_b200.sensitivity')
     lay = importlib.import_module('nes-img-captioning_b200.layout')
     play, D, D_pad, L, theta, images, labels, offs = mg.case_inputs()
     tensors, _, _ = lay.build_layout(lay.mnist_tensors(), 64)
