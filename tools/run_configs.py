@@ -1,5 +1,6 @@
 #!/usr/bin/env python
 """Measure the BASELINE.json configs that are not bench.py's headline line, on one GPU (or one rank of N under torchrun):
+  --config 1 : experiments/mnist_es.json -- MnistNet NIC-ES generation (50 offspring, mu 10, 3 elites, 64 images) + the rollout at population 5000
   --config 3 : NIC-NES, Adam, antithetic, population 5000 pairs (10 000 rollouts) per iteration, E = R = 512
   --config 4 : bu_xent shapes E = R = 128, LayerNorm + affine, 512 rows, population `--pairs`
   --config 5 : K7 aggregation + K8 update sweep, D in 1M..50M x F in 1k..20k, GB/s against the HBM roofline
@@ -102,7 +103,11 @@ if __name__ == '__main__':
     ap.add_argument('--wave', type=int, default=1024)
     ap.add_argument('--steps', type=int, default=2)
     a = ap.parse_args()
-    if a.config == 3:
+    if a.config == 1:
+        sys.path.insert(0, ROOT)
+        import bench
+        print(json.dumps({'config': '1: mnist_es.json', **bench.mnist_extras(nes_b200, torch, torch.device('cuda', 0))}))
+    elif a.config == 3:
         nes_config(a, 512, 512, 128, False, a.pairs or 5000, 0.01, '3: fc_caption NIC-NES Adam antithetic, population 5000')
     elif a.config == 4:
         nes_config(a, 128, 128, 512, True, a.pairs or 1250, 0.01, '4: bu_xent shapes, LayerNorm + affine, 512 rows')
