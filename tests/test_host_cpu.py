@@ -137,3 +137,45 @@ def test_decode_sequence_matches_the_reference_rule():
     seq = np.array([[3, 1, 0, 5], [0, 2, 2, 2], [7, 8, 9, 1]])
     assert nes_b200.decode_sequence(vocab, seq) == ['w3 w1', '', 'w7 w8 w9 w1']
     assert nes_b200.decode_sequence(vocab, torch.from_numpy(seq)) == ['w3 w1', '', 'w7 w8 w9 w1']
+
+
+def test_mnist_net_init_rule_on_a_stub_context():
+    """MnistNet.initialize_params (src/algorithm/nets.py:55-69): parameters whose name contains '1' (conv1, fc1) keep torch's default
+    uniform init, conv2 is Xavier-normal with a zero bias; layout = MnistNet.named_parameters(), D = 8490.  Host logic only: the
+    context is a stub that records what set_theta receives."""
+    import importlib
+    import numpy as np
+    nets = importlib.import_module('nes-img-captioning_b200.nets')
+    lay = importlib.import_module('nes-img-captioning_b200.layout')
+
+    class StubCtx:
+        dims = None
+        dev = 'cpu'
+
+        def __init__(self):
+            self.tensors, self.D, self.D_pad = lay.build_layout(lay.mnist_tensors(), 64)
+            self.theta = None
+
+        def set_mutation(self, kind):
+            self.mutation = kind
+
+        def set_theta(self, vector, parent=0):
+            self.theta = vector.clone()
+
+        def get_theta(self, parent=0, dtype=None):
+            return self.theta.clone()
+
+    ctx = StubCtx()
+    net = nets.MnistNet(ctx, rng_state=5, options={'safe_mutations': '', 'safe_mutation_underflow': 0.2})
+    assert ctx.D == 8490 and net.get_nb_learnable_params() == 8490 and ctx.mutation == ''
+    th = ctx.theta.numpy()
+    seg = {t.name: th[t.start:t.start + t.count] for t in ctx.tensors}
+    assert np.abs(seg['conv1.weight']).max() <= 1 / 5 and np.abs(seg['conv1.bias']).max() <= 1 / 5 and np.abs(seg['conv1.bias']).max() > 0
+    assert np.abs(seg['fc1.weight']).max() <= 1 / np.sqrt(320) + 1e-7 and np.abs(seg['fc1.bias']).max() > 0
+    assert np.all(seg['conv2.bias'] == 0)
+    assert abs(seg['conv2.weight'].std() - np.sqrt(2.0 / (250 + 500))) < 0.003           # Xavier-normal, fan_in 250, fan_out 500
+    sd = net.state_dict()
+    assert list(sd) == ['conv1.weight', 'conv1.bias', 'conv2.weight', 'conv2.bias', 'fc1.weight', 'fc1.bias']
+    assert tuple(sd['conv1.weight'].shape) == (10, 1, 5, 5) and tuple(sd['fc1.weight'].shape) == (10, 320)
+    same = nets.MnistNet(StubCtx(), rng_state=5, options={})
+    assert np.array_equal(same.parameter_vector().numpy(), th)                               # seeded init is reproducible
