@@ -179,3 +179,58 @@ def test_mnist_net_init_rule_on_a_stub_context():
     assert tuple(sd['conv1.weight'].shape) == (10, 1, 5, 5) and tuple(sd['fc1.weight'].shape) == (10, 320)
     same = nets.MnistNet(StubCtx(), rng_state=5, options={})
     assert np.array_equal(same.parameter_vector().numpy(), th)                               # seeded init is reproducible
+
+
+def test_clf_policy_host_logic_on_a_stub_context():
+    """ClfPolicy.rollout / accuracy_on / set_model (src/classification/policies.py:16-86, src/algorithm/policies.py:76-111) with the device
+    call replaced by the oracle: the float the reference returns, the mean of per-batch accuracies, state_dict hand-over"""
+    import importlib
+    import numpy as np
+    import torch
+    from oracle import mnist
+    pkg = importlib.import_module('nes-img-captioning_b200')
+    lay = pkg.layout
+
+    class StubCtx:
+        dims, dev = None, 'cpu'
+
+        def __init__(self):
+            self.tensors, self.D, self.D_pad = lay.build_layout(lay.mnist_tensors(), 64)
+            self.theta = {}
+
+        def set_mutation(self, kind):
+            pass
+
+        def set_theta(self, vector, parent=0):
+            self.theta[parent] = vector.clone()
+
+        def get_theta(self, parent=0, dtype=None):
+            return self.theta[parent].clone()
+
+        def mnist_rollout(self, offsets, signs, images, labels, sigma, parents=None, shared_batch=None, out_device='cpu', want_logits=False):
+            assert sigma == 0.0 and len(offsets) == 1
+            f, c = mnist.rollout(self.theta[int(parents[0])].numpy(), np.asarray(images), np.asarray(labels))
+            return torch.tensor([f], dtype=torch.float64), torch.tensor([c], dtype=torch.int32)
+
+    exp = {'policy_options': {'net': 'mnist', 'vbn': False, 'model_options': {'safe_mutations': ''}}}
+    policy = pkg.PolicyFactory.create(pkg.SuppDataset.MNIST, exp, ctx=StubCtx())
+    assert isinstance(policy, pkg.ClfPolicy) and policy.net == pkg.Net.MNIST and policy.nb_learnable_params() == 8490
+    theta = mnist.seeded_theta(3, scale=2.0)
+    policy.set_from_parameter_vector(theta)
+    rs = np.random.RandomState(0)
+    batches = [(torch.from_numpy(rs.randn(n, 1, 28, 28).astype(np.float32)), torch.from_numpy(rs.randint(0, 10, n))) for n in (16, 16, 5)]
+    fit = policy.rollout(None, batches[0], None)
+    want, _ = mnist.rollout(theta, batches[0][0].numpy(), batches[0][1].numpy())
+    assert isinstance(fit, float) and fit == float(np.float32(want))
+    cfg = type('Cfg', (), {'num_val_batches': 2})()
+    accs = [mnist.rollout(theta, b[0].numpy(), b[1].numpy())[1] / len(b[1]) for b in batches]
+    assert abs(policy.accuracy_on(batches, cfg, None) - np.mean(accs[:2])) < 1e-12           # num_val_batches caps the loop (:57-60)
+    cfg.num_val_batches = 0
+    assert abs(policy.accuracy_on(batches, cfg, None) - np.mean(accs)) < 1e-12              # unweighted mean, the reference's own caveat
+    # set_model with a state_dict (src/algorithm/policies.py:80-88)
+    sd = policy.get_model().state_dict()
+    sd['fc1.bias'] = sd['fc1.bias'] + 1.0
+    policy.set_model(sd)
+    assert np.array_equal(policy.parameter_vector().numpy()[-10:], theta[-10:] + 1.0)
+    with pytest.raises(AssertionError):
+        policy.set_from_parameter_vector(np.zeros(10, dtype=np.float32))
