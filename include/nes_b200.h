@@ -81,6 +81,11 @@ int nes_fill_table(nes_ctx* ctx);                                     /* K1: Phi
 int nes_table_slice(nes_ctx* ctx, int64_t start, int64_t count, void* out_f16);
 int nes_sample_offsets(nes_ctx* ctx, uint64_t iteration, int64_t F, int64_t* out);
 int nes_sample_parents(nes_ctx* ctx, uint64_t iteration, int64_t F, int32_t n_parents, int32_t* out);
+/* ESWorker.fitness with selection == 'tournament' (algorithm/nic_es/nic_es_worker.py:150-158): per offspring, tournament_size distinct
+ * parent indices drawn without replacement, the lowest one (parents are sorted best first) wins.  The reference draws from an unseeded
+ * numpy RandomState; here a uniformly random subset by Floyd's algorithm on the context's Philox stream (spec: oracle/noise.py).
+ * 1 <= n_parents <= 4096; tournament_size is clipped to n_parents; iteration < 2^48. */
+int nes_sample_parents_tournament(nes_ctx* ctx, uint64_t iteration, int64_t F, int32_t n_parents, int32_t tournament_size, int32_t* out);
 
 /* ---- theta (Policy.set_from_parameter_vector / parameter_vector, algorithm/policies.py:102-111) */
 int nes_set_theta(nes_ctx* ctx, int parent, const void* theta, int is_f64);
@@ -97,16 +102,35 @@ int nes_evolve(nes_ctx* ctx, int parent, int64_t offset, float sign, float sigma
 int nes_evolve_batch(nes_ctx* ctx, int n, const int32_t* src_parent, const int64_t* offsets, const float* sigmas,
                      const int32_t* dst_parent);
 
+/* ESMaster.selection (algorithm/nic_es/nic_es_master.py:155-167) + the parent files ESIteration.record_parents keeps
+ * (algorithm/nic_es/iteration.py:83-99, written by the workers at nic_es_worker.py:188), without a host round trip: the n fitnesses
+ * are ranked like Python's stable `sort(key=fitness, reverse=True)` (equal fitnesses keep their submission order; NaN ranks last) and
+ * the n_keep best offspring are re-derived into parent slots dst_base + r <- theta[parents[i_r]] + sigma * eps(offsets[i_r]), r = rank.
+ * fitness float64 [n], offsets int64 [n], parents int32 [n] (absolute slot indices; NULL = slot 0): host or device; order_out
+ * (nullable) int64 [n_keep] = i_r.  The destination slots must not be read by any member (a wild or overlapping index falls back to a
+ * slot outside the destination range instead of faulting). */
+int nes_es_select_evolve(nes_ctx* ctx, const double* fitness, const int64_t* offsets, const int32_t* parents, int64_t n, int n_keep,
+                         float sigma, int dst_base, int64_t* order_out);
+/* parent slot dst <- parent slot src in stream order, with every derived copy (an elite entering the podium is a file copy in the
+ * reference: algorithm/tools/podium.py:43-62; so is ESIteration.set_next_elites_to_evaluate, nic_es/iteration.py:113-129) */
+int nes_copy_parent(nes_ctx* ctx, int src_parent, int dst_parent);
+
 /* Safe mutations (PolicyNet.evolve, algorithm/nets.py:104-111).  NES_MUT_PROPORTIONAL (the reference's "SM-PROPORTIONAL", shipped in
  * experiments/mscoco_es.json): noise = sigma * eps (.) |theta_p|, exact zeros of theta_p replaced by mean|theta_p|.  Applies to
- * nes_evolve and nes_rollout (HYBRID precision, no layer_n); K7 scales its result by the scale of parent 0.
+ * nes_evolve and nes_rollout (HYBRID precision); K7 scales its result by the scale of parent 0.
  * NES_MUT_SENSITIVITY ("SM-VECTOR", and "SM-G-SUM" / "SM-G-ABS" with sensitivities computed by the caller's autograd,
  * algorithm/nets.py:104-105, safe_mutations.py:27-32): noise = sigma * eps / sens_p, a true float32 division like the reference's;
- * sens_p is 1 until nes_set_sensitivity supplies it. */
-enum { NES_MUT_DEFAULT = 0, NES_MUT_PROPORTIONAL = 1, NES_MUT_SENSITIVITY = 2 };
+ * sens_p is 1 until nes_set_sensitivity supplies it.
+ * NES_MUT_SCALE: noise = sigma * eps (.) s_p with a caller-supplied multiplier s_p (nes_set_sensitivity supplies it; 1 until then).
+ * With theta_p = 0 (LayerNorm weights 1), s_p = the Xavier std of each weight (0 for biases) and sigma = 1 a member is a freshly
+ * initialised model (PolicyNet.initialize_params, algorithm/nets.py:52-81): the `parent is None` first generation of NIC-ES
+ * (nic_es_worker.py:166-169) as noise-table rows.
+ * A NES_MUT_SENSITIVITY slot that nes_evolve_batch / nes_es_select_evolve overwrite has its divisors set to NaN until
+ * nes_set_sensitivity supplies the new parent's (the reference recomputes them per (task, parent), nic_es_worker.py:172-173). */
+enum { NES_MUT_DEFAULT = 0, NES_MUT_PROPORTIONAL = 1, NES_MUT_SENSITIVITY = 2, NES_MUT_SCALE = 3 };
 int nes_set_mutation(nes_ctx* ctx, int kind);
 /* sens: D positive float32 divisors, host or device, as Sensitivity.set_sensitivity leaves them (clamped below at the underflow value,
- * divided by their minimum); parent < 0 sets every parent slot. */
+ * divided by their minimum); parent < 0 sets every parent slot.  Under NES_MUT_SCALE the vector holds the multipliers instead. */
 int nes_set_sensitivity(nes_ctx* ctx, int parent, const float* sens);
 
 /* ---- MNIST classifier population rollout (BASELINE configs[0], experiments/mnist_es.json): replaces, for n_members perturbed

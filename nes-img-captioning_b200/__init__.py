@@ -7,11 +7,10 @@ from .context import NesContext, PREC_EXACT, PREC_FAST, PREC_HYBRID, OPT_ADAM, O
 from .nets import FCModel, MnistNet, ModelOptions, Mutation, PolicyNet
 from .policies import CaptPolicy, ClfPolicy, Net, Policy, PolicyFactory, PolicyOptions, SuppDataset
 from .cider import CiderD
-from .eval_utils import decode_sequence, eval_split
 from . import schedule
-from .master import (Adam, ESMaster, NESMaster, Optimizer, SGD, all_gather_fitness, all_reduce_gradient, sharded_master_step, es_generation, es_generation_mnist, es_sample_generation,
-                     es_select_and_materialise, nes_iteration, shard_bounds)
+from .master import (Adam, ESMaster, NESMaster, Optimizer, SGD, all_gather_fitness, all_reduce_gradient, sharded_master_step, ESPopulation, es_generation, es_generation_mnist,
+                     nes_iteration, shard_bounds)
 
 __all__ = ['NesContext', 'NesError', 'FCModel', 'MnistNet', 'ClfPolicy', 'ModelOptions', 'Mutation', 'PolicyNet', 'CaptPolicy', 'Net', 'Policy',
            'PolicyFactory', 'PolicyOptions', 'SuppDataset', 'Adam', 'SGD', 'Optimizer', 'NESMaster', 'nes_iteration',
-           'shard_bounds', 'all_gather_fitness', 'all_reduce_gradient', 'sharded_master_step', 'ESMaster', 'es_generation', 'es_generation_mnist', 'es_sample_generation', 'es_select_and_materialise', 'CiderD', 'PREC_EXACT', 'PREC_FAST', 'PREC_HYBRID', 'OPT_ADAM', 'OPT_SGD', 'gemm_selftest']
+           'shard_bounds', 'all_gather_fitness', 'all_reduce_gradient', 'sharded_master_step', 'ESMaster', 'ESPopulation', 'es_generation', 'es_generation_mnist', 'CiderD', 'PREC_EXACT', 'PREC_FAST', 'PREC_HYBRID', 'OPT_ADAM', 'OPT_SGD', 'gemm_selftest']

@@ -41,6 +41,9 @@ SIGNATURES = {
     'nes_table_slice': (c_i32, [c_vp, c_i64, c_i64, c_vp]),
     'nes_sample_offsets': (c_i32, [c_vp, c_u64, c_i64, c_vp]),
     'nes_sample_parents': (c_i32, [c_vp, c_u64, c_i64, c_i32, c_vp]),
+    'nes_sample_parents_tournament': (c_i32, [c_vp, c_u64, c_i64, c_i32, c_i32, c_vp]),
+    'nes_es_select_evolve': (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_f32, c_i32, c_vp]),
+    'nes_copy_parent': (c_i32, [c_vp, c_i32, c_i32]),
     'nes_set_theta': (c_i32, [c_vp, c_i32, c_vp, c_i32]),
     'nes_get_theta': (c_i32, [c_vp, c_i32, c_vp, c_i32]),
     'nes_evolve': (c_i32, [c_vp, c_i32, c_i64, c_f32, c_f32, c_vp, c_vp, c_i32]),

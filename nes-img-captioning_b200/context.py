@@ -103,8 +103,15 @@ class NesContext:
         _lib.check(self.lib.nes_sample_parents(self._h, int(iteration), int(F), int(n_parents), _lib.ptr(out)))
         return out
 
+    def sample_parents_tournament(self, iteration, F, n_parents, tournament_size, device=False):
+        """parent index of every offspring under selection == 'tournament' (nic_es_worker.py:150-158): the lowest of
+        min(n_parents, tournament_size) distinct indices"""
+        out = torch.empty(int(F), dtype=torch.int32, device=self.dev if device else 'cpu')
+        _lib.check(self.lib.nes_sample_parents_tournament(self._h, int(iteration), int(F), int(n_parents), int(tournament_size), _lib.ptr(out)))
+        return out
+
     # ---- safe mutations (src/algorithm/nets.py:104-111)
-    MUTATIONS = {'': 0, 'SM-PROPORTIONAL': 1, 'SM-VECTOR': 2, 'SM-G-SUM': 2, 'SM-G-ABS': 2}
+    MUTATIONS = {'': 0, 'SM-PROPORTIONAL': 1, 'SM-VECTOR': 2, 'SM-G-SUM': 2, 'SM-G-ABS': 2, 'SCALE': 3}
 
     def set_mutation(self, kind):
         """'' (default), 'SM-PROPORTIONAL' (noise scaled by |theta_p|, zeros by mean|theta_p|), or one of the sensitivity mutations
@@ -155,6 +162,23 @@ class NesContext:
         off = np.ascontiguousarray(offsets, dtype=np.int64); sg = np.ascontiguousarray(sigmas, dtype=np.float32)
         assert len(src) == len(dst) == len(off) == len(sg)
         _lib.check(self.lib.nes_evolve_batch(self._h, len(src), _lib.ptr(src), _lib.ptr(off), _lib.ptr(sg), _lib.ptr(dst)))
+
+    def es_select_evolve(self, fitness, offsets, parents, n_keep, sigma, dst_base, want_order=True):
+        """ESMaster.selection + the survivors written as parent slots dst_base .. dst_base + n_keep - 1, on the device
+        (nes_es_select_evolve).  fitness float64 [n], offsets int64 [n], parents int32 [n] absolute slots (torch, any device).
+        Returns the device tensor order int64 [n_keep] (offspring index at each rank) or None."""
+        fitness = torch.as_tensor(fitness, dtype=torch.float64).contiguous()
+        offsets = torch.as_tensor(offsets, dtype=torch.int64).contiguous()
+        parents = None if parents is None else torch.as_tensor(parents, dtype=torch.int32).contiguous()
+        n = fitness.numel()
+        assert offsets.numel() == n and (parents is None or parents.numel() == n)
+        order = torch.empty(int(n_keep), dtype=torch.int64, device=self.dev) if want_order else None
+        _lib.check(self.lib.nes_es_select_evolve(self._h, _lib.ptr(fitness), _lib.ptr(offsets), _lib.ptr(parents), n, int(n_keep),
+                                                 float(sigma), int(dst_base), _lib.ptr(order)))
+        return order
+
+    def copy_parent(self, src, dst):
+        _lib.check(self.lib.nes_copy_parent(self._h, int(src), int(dst)))
 
     # ---- MNIST classifier (BASELINE configs[0]; classification/nets.py:25-37, classification/policies.py:16-86)
     def mnist_rollout(self, offsets, signs, images, labels, sigma, parents=None, shared_batch=None, out_device='cpu', want_logits=False):

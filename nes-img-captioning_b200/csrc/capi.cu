@@ -89,6 +89,8 @@ static int ctx_common_init(Ctx* c, int device, uint64_t seed, int64_t table_len,
     for (int i = 0; i < n_parents; ++i) c->theta_is_f32[i] = 1;
     c->theta64_stale = new uint8_t[n_parents];
     for (int i = 0; i < n_parents; ++i) c->theta64_stale[i] = 0;
+    c->scale_stale = new uint8_t[n_parents];
+    for (int i = 0; i < n_parents; ++i) c->scale_stale[i] = 0;
     NES_CUDA(cudaEventCreate(&c->ev_a)); NES_CUDA(cudaEventCreate(&c->ev_b));
     NES_CUDA(cudaEventCreate(&c->ev_c)); NES_CUDA(cudaEventCreate(&c->ev_d));
     return ensure_small(c, 1024);
@@ -155,6 +157,7 @@ int nes_ctx_destroy(nes_ctx* ctx) {
     for (auto& r : c->prof_pool) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     delete[] c->theta_is_f32;
     delete[] c->theta64_stale;
+    delete[] c->scale_stale;
     delete c;
     return 0;
 }
@@ -194,6 +197,17 @@ int nes_sample_parents(nes_ctx* ctx, uint64_t iteration, int64_t F, int32_t n_pa
     if (ensure_small(c, F)) return 1;
     int32_t* tmp = reinterpret_cast<int32_t*>(c->d_ranks);
     if (launch_sample_parents(c, iteration, F, n_parents, tmp)) return 1;
+    NES_CUDA(cudaMemcpyAsync(out, tmp, sizeof(int32_t) * F, cudaMemcpyDefault, c->stream));
+    return finish_output(c, out);
+}
+
+int nes_sample_parents_tournament(nes_ctx* ctx, uint64_t iteration, int64_t F, int32_t n_parents, int32_t tournament_size, int32_t* out) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    NES_CHECK(F >= 0 && out, "bad arguments");
+    if (F == 0) return 0;
+    if (ensure_small(c, F)) return 1;
+    int32_t* tmp = reinterpret_cast<int32_t*>(c->d_ranks);
+    if (launch_sample_parents_tournament(c, iteration, F, n_parents, tournament_size, tmp)) return 1;
     NES_CUDA(cudaMemcpyAsync(out, tmp, sizeof(int32_t) * F, cudaMemcpyDefault, c->stream));
     return finish_output(c, out);
 }
@@ -249,6 +263,41 @@ int nes_evolve_batch(nes_ctx* ctx, int n, const int32_t* src_parent, const int64
     NEED_CTX(ctx); Ctx* c = CTX(ctx);
     NES_CHECK(n == 0 || (src_parent && offsets && sigmas && dst_parent), "null argument");
     return launch_evolve_batch(c, n, src_parent, offsets, sigmas, dst_parent);
+}
+
+int nes_es_select_evolve(nes_ctx* ctx, const double* fitness, const int64_t* offsets, const int32_t* parents, int64_t n, int n_keep,
+                         float sigma, int dst_base, int64_t* order_out) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    NES_CHECK(n >= 1 && fitness && offsets, "bad arguments");
+    // inputs that live on the host are staged in stream order; device inputs are used where they are (no host round trip)
+    std::vector<void*> temps;
+    auto stage = [&](const void* src, size_t bytes, const void** out) -> int {
+        if (!src || is_device_ptr(src)) { *out = src; return 0; }
+        void* d = nullptr;
+        NES_CUDA(cudaMallocAsync(&d, bytes, c->stream));
+        temps.push_back(d);
+        NES_CUDA(cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, c->stream));
+        *out = d; return 0;
+    };
+    const void *d_fit, *d_off, *d_par;
+    int64_t* d_order = nullptr;
+    int rc = stage(fitness, sizeof(double) * n, &d_fit) || stage(offsets, sizeof(int64_t) * n, &d_off) || stage(parents, sizeof(int32_t) * n, &d_par);
+    if (!rc) {
+        if (order_out && is_device_ptr(order_out)) d_order = order_out;
+        else { rc = cudaMallocAsync((void**)&d_order, sizeof(int64_t) * (n_keep > 0 ? n_keep : 1), c->stream) != cudaSuccess; if (!rc) temps.push_back(d_order); }
+    }
+    if (!rc) rc = launch_es_select_evolve(c, (const double*)d_fit, (const int64_t*)d_off, (const int32_t*)d_par, n, n_keep, sigma, dst_base, d_order);
+    if (!rc && order_out && d_order != order_out && n_keep > 0) rc = cudaMemcpyAsync(order_out, d_order, sizeof(int64_t) * n_keep, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess;
+    const bool host_io = !temps.empty();
+    for (void* t : temps) cudaFreeAsync(t, c->stream);
+    if (!rc && host_io) NES_CUDA(cudaStreamSynchronize(c->stream));          // pageable host inputs / a host output must be complete on return
+    if (rc && g_err.empty()) set_error("nes_es_select_evolve: CUDA call failed");
+    return rc ? 1 : 0;
+}
+
+int nes_copy_parent(nes_ctx* ctx, int src_parent, int dst_parent) {
+    NEED_CTX(ctx);
+    return copy_parent(CTX(ctx), src_parent, dst_parent);
 }
 
 int nes_rollout_trace(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, const float* signs, const int32_t* parents,

@@ -86,6 +86,7 @@ struct Ctx {
     float* scale32 = nullptr;         // [n_parents, D] (nullptr: default mutation)
     int scale_div = 0;                // 1: scale32 holds sensitivities, the noise is divided by them (NES_MUT_SENSITIVITY)
     float* d_scale_max = nullptr;     // [n_parents] max of s_p (HYBRID error bound)
+    uint8_t* scale_stale = nullptr;   // host flags [n_parents]: NES_MUT_SENSITIVITY divisors of this slot predate its current parent
     double* d_abs_partials = nullptr; // [kAbsBlocks]
 
     // master math
@@ -136,6 +137,7 @@ int ensure_small(Ctx* c, int64_t n);   // (re)allocate the small per-iteration s
 int launch_fill_table(Ctx* c);
 int launch_sample_offsets(Ctx* c, uint64_t iteration, int64_t F, int64_t* d_out);
 int launch_sample_parents(Ctx* c, uint64_t iteration, int64_t F, int32_t n_parents, int32_t* d_out);
+int launch_sample_parents_tournament(Ctx* c, uint64_t iteration, int64_t F, int32_t n_parents, int32_t tournament_size, int32_t* d_out);
 int launch_bound_norms(Ctx* c, int parent);       // parent >= 0: theta_rowmax[parent]; parent < 0: eps_rowmax (decode.cu)
 int launch_theta_shadow(Ctx* c, int parent);      // theta32 -> theta_hi/lo (padded)
 int launch_prop_scale(Ctx* c, int parent);        // theta32 -> scale32 (SM-PROPORTIONAL)
@@ -145,6 +147,9 @@ int launch_set_theta(Ctx* c, int parent, const void* d_src, bool is_f64);
 int launch_evolve(Ctx* c, int parent, int64_t offset, float sign, float sigma, float* d_member, float* d_noise, int dst_parent);
 int refresh_theta64(Ctx* c, int parent);          // theta64 <- (double)theta32 if the slot is stale
 int launch_evolve_batch(Ctx* c, int n, const int32_t* src, const int64_t* offsets, const float* sigmas, const int32_t* dst);   // host arrays
+int launch_es_select_evolve(Ctx* c, const double* d_fit, const int64_t* d_off, const int32_t* d_par, int64_t n, int n_keep, float sigma,
+                            int dst_base, int64_t* d_order);   // device arrays; d_order [n_keep] device
+int copy_parent(Ctx* c, int src, int dst);
 int launch_bound_norms_batch(Ctx* c, const int32_t* parents, int n);   // theta_rowmax of several parents in one launch (decode.cu)
 
 // master.cu
@@ -199,4 +204,5 @@ __host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
 }
 constexpr uint32_t kOffsetDomain = 0x4F464653u;  // "OFFS"
 constexpr uint32_t kParentDomain = 0x50415245u;  // "PARE"
+constexpr uint32_t kTournDomain  = 0x544F5552u;  // "TOUR"
 }  // namespace nes

@@ -678,7 +678,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     const bool dense_ln = ws->dense_ln && precision == NES_PREC_EXACT;         // LayerNorm cell on dense pre-activation GEMMs
     const bool scaled = c->scale32 != nullptr;                                 // safe-mutation scale: every member weight is materialised
     if (scaled) {
-        NES_CHECK(hybrid && dense_lstm && !c->dims.layer_n, "a safe-mutation scale needs HYBRID precision on the dense kernels (no layer_n, no logit trace, R <= 512)");
+        NES_CHECK(hybrid && (dense_lstm || dense_ln), "a safe-mutation scale needs HYBRID precision on the dense kernels (no logit trace, R <= 512)");
         if (!ws->wi_hi) {
             if (dmalloc(&ws->wi_hi, (int64_t)ws->W * ws->E * ws->Fd) || dmalloc(&ws->wi_lo, (int64_t)ws->W * ws->E * ws->Fd) || dmalloc(&ws->wi_bias, (int64_t)ws->W * ws->E)) return 1;
         }

@@ -48,3 +48,24 @@ def build_layout(tensors, G):
         pos += cnt
         p = -(-(p + cnt) // G) * G
     return out, pos, p
+
+
+def fresh_model_vectors(tensors):
+    """(blank theta, per-parameter std) such that blank + std * N(0, 1) is a freshly initialised model as
+    PolicyNet.initialize_params leaves it (src/algorithm/nets.py:62-69): Xavier-normal on every '*weight*', zero on every '*bias*',
+    parameters whose name contains 'bn', 'ln' or '1' skipped -- for the fc_caption tensors that is the LayerNorm / batch-norm
+    affine pair, which stays at torch's default weight 1 / bias 0.  A tensor that keeps torch's default Kaiming-uniform init
+    (MnistNet's conv1 / fc1) is not a Gaussian and raises."""
+    D = tensors[-1].start + tensors[-1].count
+    blank, std = np.zeros(D, dtype=np.float32), np.zeros(D, dtype=np.float32)
+    for t in tensors:
+        sl = slice(t.start, t.start + t.count)
+        if 'bn' in t.name or 'ln' in t.name:
+            if t.name.endswith('weight'):
+                blank[sl] = 1.0
+        elif '1' in t.name:
+            raise NotImplementedError('%s keeps torch default init (not Gaussian): supply fresh models yourself' % t.name)
+        elif 'weight' in t.name:
+            fan_out, fan_in = t.shape[0], int(np.prod(t.shape[1:]))          # nn.init.xavier_normal_: std = sqrt(2 / (fan_in + fan_out))
+            std[sl] = np.float32((2.0 / (fan_in + fan_out)) ** 0.5)
+    return blank, std

@@ -5,10 +5,12 @@ SGD / Adam optimizers (src/algorithm/nic_nes/optimizers.py) and one whole NIC-NE
 sharded step: every rank evaluates its slice of antithetic pairs, fitness scalars are all-gathered
 (NCCL on GPUs; gloo in the CPU tests of the sharding logic), and every rank applies the identical update.
 """
+from collections import namedtuple
+
 import numpy as np
 import torch
 
-from .context import NesContext, OPT_ADAM, OPT_SGD, PREC_EXACT
+from .context import NesContext, OPT_ADAM, OPT_SGD, PREC_EXACT, PREC_HYBRID
 
 
 class NESMaster:
@@ -189,61 +191,245 @@ class ESMaster:
         return order[:max(0, int(pop_size) - int(num_elites))], fit[order]
 
 
-def es_sample_generation(ctx: NesContext, iteration, n_offspring, mu):
-    """(offset, parent) of every offspring of a generation, identical on every rank (shared seed), grouped by parent: members
-    of one parent are adjacent so that their CTAs hit the same theta tiles in L2 (offspring order carries no meaning in ES)."""
-    offs = ctx.sample_offsets(iteration, n_offspring, device=True)
-    pars = ctx.sample_parents(iteration, n_offspring, mu, device=True)
-    pars, perm = torch.sort(pars, stable=True)
-    return offs[perm].contiguous(), pars.contiguous()
+EvalES = namedtuple('EvalES', ['evaluated_cand_id', 'evaluated_cand', 'score'])       # the fields of ESResult that record_eval_result reads
 
 
-def es_select_and_materialise(ctx: NesContext, fitness_all, offs, pars, mu, num_elites, base, sigma):
-    """truncation selection on the gathered fitnesses, then the next generation's parents are written into the other half of
-    the context's 2*mu parent slots: the first num_elites parents carried over unchanged, then the selected offspring
-    re-derived from (parent, offset) -- no weights ever leave the device.  Returns the new base slot."""
-    keep, _ = ESMaster.selection(fitness_all, mu, num_elites)
-    sel = torch.stack([keep, offs[keep], pars[keep].to(torch.int64)], 1).cpu().numpy()      # the master's one sync point
-    nxt = mu - base
-    n = num_elites + len(sel)
-    src = np.concatenate([base + np.arange(num_elites), base + sel[:, 2]]).astype(np.int32)
-    off = np.concatenate([np.zeros(num_elites, dtype=np.int64), sel[:, 1]]).astype(np.int64)
-    sg = np.concatenate([np.zeros(num_elites), np.full(len(sel), sigma)]).astype(np.float32)      # sigma 0: the elite itself
-    ctx.evolve_batch(src, off, sg, nxt + np.arange(n))
-    return nxt
+class ESPopulation:
+    """One NIC-ES run on a device: the reference master's bookkeeping (ESIteration + Podium + ESMaster.selection in the order of
+    ESMaster.run_master, nic_es_master.py:66-125) driving models that are parent slots of a NesContext instead of `.pth` files.
+
+    What the reference does per generation and where it happens here:
+      workers pick a parent (uniform or tournament, nic_es_worker.py:150-162), mutate it and evaluate      sample() + the caller's rollout
+      `parent is None` (first generation after init_from_zero): a fresh random model per offspring (:166-169)   sample(): blank slot, sigma 1,
+                                                                                           per-parameter Xavier std as the noise scale
+      workers evaluate the elite candidates on validation data (:114-141)                                    the caller's elite_scores
+      process_evaluated_elites -> Podium.record_elites (tools/iteration.py:117-148, tools/podium.py:43-62)  end_generation(), SlotStore copies
+      ESMaster.selection, set_next_elites_to_evaluate, record_parents (nic_es_master.py:119-125)            end_generation(): nes_es_select_evolve
+                                                                                           + the same ESIteration calls
+    The parents of the next generation are the podium's elites followed by the population_size - num_elites best offspring, best first.
+
+    Slots: [0, mu) and [mu, 2 mu) take the survivors of alternate generations; slot 2 mu is the blank model of a fresh initialisation,
+    the num_elites + num_elite_cands slots behind it hold the podium and the elite candidates.  `ESPopulation.slots_needed(exp)` is the n_parents the context must have."""
+
+    def __init__(self, ctx, exp, config=None, sensitivity_fn=None, root='/nes_es'):
+        from .schedule import Config, ESIteration, SlotStore
+        self.ctx, self.exp = ctx, dict(exp)
+        self.mu = int(exp.get('population_size', exp['nb_offspring']))
+        self.E, self.C = int(exp['num_elites']), int(exp['num_elite_cands'])
+        self.selection = exp.get('selection', 'uniform')
+        self.tournament_size = int(exp.get('tournament_size') or 0)
+        assert ctx.n_parents >= self.slots_needed(exp), 'the context needs n_parents >= %d' % self.slots_needed(exp)
+        assert self.mu > self.E >= 0 and self.C <= self.mu - self.E
+        config = config if config is not None else Config(**exp.get('config', {}))
+        self.store = SlotStore(ctx, free_slots=range(2 * self.mu + 1, 2 * self.mu + 1 + self.E + self.C))
+        self.blank = 2 * self.mu
+        self.it = ESIteration(config, dict(exp, log_dir=root), store=self.store)
+        self.block = 0                      # the half that receives the next survivors
+        self.sensitivity_fn = sensitivity_fn
+        self.mutation = getattr(ctx, 'mutation', '')
+        self._fresh_mode = False
+        self.last = {}
+
+    @staticmethod
+    def slots_needed(exp):
+        mu = int(exp.get('population_size', exp['nb_offspring']))
+        return 2 * mu + 1 + int(exp['num_elites']) + int(exp['num_elite_cands'])
+
+    # ---- ESIteration.init_from_zero / init_from_singles (nic_es/iteration.py:50-81)
+    def _enter_fresh_mode(self):
+        if not self._fresh_mode:
+            from .layout import fresh_model_vectors
+            blank, std = fresh_model_vectors(self.ctx.tensors)
+            self.ctx.set_mutation('SCALE')
+            self.ctx.set_theta(blank, self.blank)
+            self.ctx.set_sensitivity(std, parent=self.blank)
+            self._fresh_mode = True
+
+    def _leave_fresh_mode(self):
+        if self._fresh_mode:
+            self.ctx.set_mutation(self.mutation)
+            self._fresh_mode = False
+
+    def init_from_zero(self, seed_iteration=(1 << 41)):
+        """parents = population_size x None, num_elite_cands freshly initialised elite candidates"""
+        pop = self
+        self._enter_fresh_mode()
+        offsets = self.ctx.sample_offsets(int(seed_iteration), self.C)
+
+        class _Fresh:
+            def __init__(self, j): self.j = j
+
+            def serialize(self, path=''):
+                slot = pop.store.free.pop(0)
+                pop.store.adopt(path, slot, tag='init_elite:%d' % self.j)
+                pop.ctx.evolve(int(offsets[self.j]), 1.0, 1.0, parent=pop.blank, want_member=False, want_noise=False, dst_parent=slot)
+                return path
+
+        class _Policy:
+            n = 0
+
+            def generate_model(self, from_param_file=None, start_rng=None):
+                _Policy.n += 1
+                return _Fresh(_Policy.n - 1)
+
+        self.it.init_from_zero(self.exp, _Policy())
+
+    def init_from_thetas(self, thetas):
+        """init_from_singles with the models given as flat vectors: every one becomes a parent, the first num_elite_cands also elite
+        candidates"""
+        pop = self
+
+        class _Given:
+            def __init__(self, k): self.k = k
+
+            def serialize(self, path=''):
+                if path.startswith(pop.it.offspring_dir()):      # a parent: the half that the first survivors do NOT go to
+                    slot = pop.mu + self.k
+                else:
+                    slot = pop.store.free.pop(0)
+                pop.store.adopt(path, slot, tag='single:%d' % self.k)
+                pop.ctx.set_theta(thetas[self.k], slot)
+                return path
+
+        class _Policy:
+            def generate_model(self, from_param_file=None, start_rng=None):
+                return _Given(int(from_param_file))
+
+        assert len(thetas) <= self.mu
+        self.it.init_from_singles(list(range(len(thetas))), self.exp, _Policy())
+
+    # ---- readers
+    def parent_slots(self):
+        """slot of every parent in the reference's order (best first), or None while the parents are still `None`"""
+        ps = self.it.parents()
+        return None if ps and ps[0][1] is None else [self.store.slot(p) for _, p in ps]
+
+    def elite_candidate_slots(self):
+        return [self.store.slot(p) for _, p in self.it.elites_to_evaluate()]
+
+    def podium(self):
+        return [(self.store.slot(p), sc) for p, sc in self.it.best_elites()]
+
+    @property
+    def sigma(self):
+        """the noise_stdev a rollout of the current generation uses (1 while the offspring are fresh random models)"""
+        return 1.0 if self.parent_slots() is None else float(self.it.noise_stdev())
+
+    def tags(self):
+        """{parents, elites_to_evaluate, podium: where each model came from}; resolves the device-side selection order on demand"""
+        def tag(path):
+            t = self.store.tags.get(path)
+            if isinstance(t, tuple):
+                gen, rank, order = t
+                t = 'g%d:o%d' % (gen, int(order[rank]))
+            return t
+        return {'parents': [tag(p) for _, p in self.it.parents()], 'elites_to_evaluate': [tag(p) for _, p in self.it.elites_to_evaluate()],
+                'podium': [[tag(p), sc] for p, sc in self.it.best_elites()]}
+
+    # ---- one generation
+    def begin_generation(self):
+        self.it.incr_iteration()
+        slots = self.parent_slots()
+        if slots is None:
+            self._enter_fresh_mode()
+        elif self.ctx.MUTATIONS.get(self.mutation) == 2:
+            # the reference recomputes / reloads the sensitivity for every (task, parent) (nic_es_worker.py:172-173)
+            assert self.sensitivity_fn is not None, 'a sensitivity mutation needs sensitivity_fn(slot) for the new parents'
+            for s in sorted(set(slots)):
+                self.sensitivity_fn(s)
+
+    def sample(self, n_offspring=None):
+        """(offsets int64 [n], parent slots int32 [n]) on the device, identical on every rank (shared seed); members of one parent are
+        adjacent so that their CTAs share the parent's theta through L2 (the order of the offspring carries no meaning)"""
+        n = int(n_offspring or self.exp['nb_offspring'])
+        gen = self.it.iteration()
+        offs = self.ctx.sample_offsets(gen, n, device=True)
+        slots = self.parent_slots()
+        if slots is None:
+            return offs, torch.full((n,), self.blank, dtype=torch.int32, device=self.ctx.dev)
+        if self.selection == 'tournament':
+            idx = self.ctx.sample_parents_tournament(gen, n, len(slots), self.tournament_size, device=True)
+        else:
+            idx = self.ctx.sample_parents(gen, n, len(slots), device=True)
+        idx, perm = torch.sort(idx, stable=True)
+        table = torch.tensor(slots, dtype=torch.int32).to(self.ctx.dev, non_blocking=True)
+        return offs[perm].contiguous(), table[idx.long()].contiguous()
+
+    def end_generation(self, fitness_all, offs, slots, elite_scores):
+        """fitness_all float64 [n] (all ranks' offspring, any device), offs / slots as sample() returned them, elite_scores: one
+        validation score per elite candidate (ESWorker.accuracy).  Order of operations = nic_es_master.py:116-125."""
+        it = self.it
+        cands = it.elites_to_evaluate()
+        assert len(elite_scores) == len(cands)
+        for (cid, cpath), score in zip(cands, elite_scores):
+            it.record_eval_result(EvalES(cid, cpath, float(score)))
+        best_sc, best_ind = it.process_evaluated_elites()
+        n_keep = min(self.mu - self.E, int(fitness_all.numel()))
+        base = self.block * self.mu
+        order = self.ctx.es_select_evolve(fitness_all, offs, slots, n_keep, self.sigma, base)
+        self._leave_fresh_mode()
+        gen = it.iteration()
+        paths = []
+        for r in range(n_keep):
+            path = '%s/r%d_%d_offspring_params.pth' % (it.offspring_dir(), r, gen)
+            self.store.adopt(path, base + r, tag=(gen - 1, r, order))
+            paths.append(path)
+        it.set_next_elites_to_evaluate(paths[:self.C])
+        it.record_parents(paths)
+        self.block ^= 1
+        self.last = {'best_evaluated_score': best_sc, 'best_evaluated_slot': None if best_ind is None else self.store.slot_of.get(best_ind),
+                     'order': order, 'patience_reached': it.patience_reached(), 'schedule_reached': it.schedule_reached()}
+        return self.last
 
 
-def es_generation(ctx: NesContext, iteration, n_local, mu, num_elites, fc, sigma, base=0, fitness_fn=None,
-                  world_size=1, rank=0, precision=PREC_EXACT, group=None, evaluate=None):
-    """One NIC-ES generation on a context created with n_parents = 2*mu (current parents in slots [base, base+mu)).
-    Every rank evaluates n_local offspring of the n_local*world_size sampled; fitness_fn(seq, logprobs) -> float64 [n_local]
-    (None: sum of greedy log-probs, computed on the device).  evaluate(offsets, signs, parent_slots, sigma) -> float64 [n_local] replaces
-    the fc_caption rollout altogether (the MNIST net: es_generation_mnist).  Returns (new base, all fitnesses, offsets, parents)."""
-    assert ctx.n_parents >= 2 * mu and base in (0, mu)
+def es_generation(pop: ESPopulation, fc, fitness_fn=None, elite_score_fn=None, n_local=None, world_size=1, rank=0, precision=PREC_HYBRID,
+                  group=None, evaluate=None):
+    """One NIC-ES generation of `pop` (ESWorker.fitness nic_es_worker.py:142-192 for every offspring + the master's half).  Every rank
+    evaluates n_local offspring of the n_local * world_size sampled; fitness_fn(seq, logprobs) -> float64 [n_local] (None: the sum of greedy
+    log-probs, on the device); evaluate(offsets, signs, slots, sigma) -> float64 [n] replaces the fc_caption rollout (the MNIST net);
+    elite_score_fn(slots) -> one score per elite candidate (the reference's validation run, ESWorker.accuracy; None: the fitness of the
+    unperturbed candidate on the same batch).  Returns (all fitnesses, offsets, parent slots)."""
+    ctx = pop.ctx
+    pop.begin_generation()
+    n_local = int(n_local or pop.exp['nb_offspring'])
     n_all = n_local * world_size
-    offs, pars = es_sample_generation(ctx, iteration, n_all, mu)
+    offs, slots = pop.sample(n_all)
     lo = rank * n_local
     ones = torch.ones(n_local, dtype=torch.float32, device=ctx.dev)
-    if evaluate is not None:
-        fit = torch.as_tensor(evaluate(offs[lo:lo + n_local], ones, pars[lo:lo + n_local] + base, sigma), dtype=torch.float64).to(ctx.dev)
+
+    def run(o, sg, sl, sigma):
+        if evaluate is not None:
+            return torch.as_tensor(evaluate(o, sg, sl, sigma), dtype=torch.float64).to(ctx.dev)
+        seq, lp = ctx.rollout(o, sg, fc, sigma, parents=sl, precision=precision, out_device=ctx.dev)
+        if fitness_fn is None:
+            return ctx.logprob_fitness(o.numel(), seq.shape[1], device=ctx.dev)
+        return torch.as_tensor(fitness_fn(seq, lp), dtype=torch.float64).to(ctx.dev)
+
+    # the elite candidates first: their scores are only needed by the host after the offspring are done
+    cand = pop.elite_candidate_slots()
+    if elite_score_fn is not None:
+        elite = elite_score_fn(cand)
+    elif cand:
+        cs = torch.tensor(cand, dtype=torch.int32, device=ctx.dev)
+        elite = run(torch.zeros(len(cand), dtype=torch.int64, device=ctx.dev), torch.ones(len(cand), dtype=torch.float32, device=ctx.dev), cs, 0.0)
     else:
-        seq, lp = ctx.rollout(offs[lo:lo + n_local], ones, fc, sigma, parents=pars[lo:lo + n_local] + base, precision=precision, out_device=ctx.dev)
-        rows = seq.shape[1]
-        fit = ctx.logprob_fitness(n_local, rows, device=ctx.dev) if fitness_fn is None else torch.as_tensor(fitness_fn(seq, lp), dtype=torch.float64).to(ctx.dev)
+        elite = []
+    fit = run(offs[lo:lo + n_local], ones, slots[lo:lo + n_local], pop.sigma)
     if world_size > 1:
         import torch.distributed as dist
         out = torch.empty(n_all, dtype=torch.float64, device=ctx.dev)
         dist.all_gather_into_tensor(out, fit.contiguous(), group=group)
         fit = out
-    new_base = es_select_and_materialise(ctx, fit, offs, pars, mu, num_elites, base, sigma)
-    return new_base, fit, offs, pars
+    elite = elite.cpu().tolist() if torch.is_tensor(elite) else list(elite)            # the master's one sync point of a generation
+    pop.end_generation(fit, offs, slots, elite)
+    return fit, offs, slots
 
 
-def es_generation_mnist(ctx: NesContext, iteration, n_local, mu, num_elites, images, labels, sigma, base=0, **kw):
+def es_generation_mnist(pop: ESPopulation, images, labels, **kw):
     """One NIC-ES generation of the MNIST classifier as experiments/mnist_es.json runs it (nb_offspring 50, population_size 10,
-    num_elites 3, batch 64; nic_es_worker.py:142-192 + ClfPolicy.rollout + nic_es_master.py:155-167): every offspring's
-    fitness = -CrossEntropyLoss on the batch from one k_mnist_rollout launch, selection and survivors as es_generation"""
+    num_elites 3, batch 64; nic_es_worker.py:142-192 + ClfPolicy.rollout + nic_es_master.py:116-125): every offspring's
+    fitness = -CrossEntropyLoss on the batch from one k_mnist_rollout launch"""
+    ctx = pop.ctx
     images = torch.as_tensor(images).to(ctx.dev)
     labels = torch.as_tensor(labels).to(ctx.dev)
-    return es_generation(ctx, iteration, n_local, mu, num_elites, None, sigma, base=base,
-                         evaluate=lambda o, s, p, sg: ctx.mnist_rollout(o, s, images, labels, sg, parents=p, out_device=ctx.dev)[0], **kw)
+    return es_generation(pop, None, evaluate=lambda o, s, p, sg: ctx.mnist_rollout(o, s, images, labels, sg, parents=p, out_device=ctx.dev)[0], **kw)

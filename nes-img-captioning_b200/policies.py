@@ -123,7 +123,7 @@ class CaptPolicy(Policy):
         super().__init__(dataset, options, ctx, **ctx_kwargs)
         self.scorer, self.seq_per_img = scorer, int(seq_per_img)
         self.precision = PREC_EXACT
-        self.language_eval = None        # callable(predictions, directory, split) -> {'CIDEr': ...}: the COCO evaluator of accuracy_on
+        self.validation_fn = None        # callable(policy_net, dataloader, config, directory) -> float: the validation run of accuracy_on
 
     @property
     def ctx(self):
@@ -134,14 +134,12 @@ class CaptPolicy(Policy):
         return fc[::self.seq_per_img] if self.seq_per_img > 1 else fc
 
     def accuracy_on(self, dataloader, config, directory) -> float:
-        """validation score (captioning/policies.py:130-143): greedy captions of the split through eval_split, scored by the injected
-        COCO evaluator (self.language_eval; the reference's needs Java)"""
-        from .eval_utils import eval_split
+        """validation score (captioning/policies.py:130-143).  The reference decodes the validation split and scores it with the COCO
+        caption evaluators (Java); that run is outside the hot path, so it is whatever the caller plugs in."""
         assert directory is not None
-        if self.language_eval is None:
-            raise NotImplementedError('set policy.language_eval = callable(predictions, directory, split) -> {"CIDEr": score}')
-        lang_stats, _ = eval_split(self.policy_net, dataloader.loader, directory, num=config.num_val_items, language_eval=self.language_eval)
-        return float(lang_stats['CIDEr'])
+        if self.validation_fn is None:
+            raise NotImplementedError('validation is outside the hot path: set policy.validation_fn = callable(policy_net, dataloader, config, directory) -> float')
+        return float(self.validation_fn(self.policy_net, dataloader, config, directory))
 
     def rollout_tokens(self, data):
         seq, lp = self.policy_net(torch.from_numpy(np.ascontiguousarray(self._unique_rows(data['fc_feats']))), greedy=True)

@@ -34,22 +34,88 @@ Config = namedtuple('Config', CONFIG_FIELDS, defaults=(None,) * len(CONFIG_FIELD
 INFOS_PATTERN = r'z_info_e[0-9]*?_i[0-9]*?-[0-9]*?.json'
 
 
-def _only_keep(directory, keep):
-    for name in os.listdir(directory):
-        path = os.path.join(directory, name)
-        if os.path.isfile(path) and path not in keep:
-            os.remove(path)
+class FileStore:
+    """Where the models that the bookkeeping moves around live.  The reference keeps every model as a `.pth` file and copies / renames /
+    removes those (tools/utils.py:108-141); this is that behaviour.  `SlotStore` below keeps them as parent slots of a NesContext instead,
+    so that the same bookkeeping (pinned against the reference's classes) drives a population that never leaves the device."""
+
+    def makedirs(self, directory): os.makedirs(directory, exist_ok=True)
+    def isfile(self, path): return os.path.isfile(path)
+    def copy(self, src, dst): shutil.copy(src, dst)
+
+    def rename(self, src, dst):
+        if os.path.exists(dst):
+            os.remove(dst)
+        os.rename(src, dst)
+
+    def only_keep(self, directory, keep):
+        for name in os.listdir(directory):
+            path = os.path.join(directory, name)
+            if os.path.isfile(path) and path not in keep:
+                os.remove(path)
+
+
+class SlotStore:
+    """Models as parent slots of a NesContext: a path is a name for a slot, copy = nes_copy_parent in stream order (so the podium's
+    sequential copies alias exactly as the reference's file copies do), rename = the name moves to the other slot, remove = the slot
+    returns to the free pool.  `tags[path]` says where the slot's content came from (tests compare it with the content of the
+    reference's files).  Slots handed in through `adopt` (the survivors nes_es_select_evolve wrote) belong to the store from then on."""
+
+    def __init__(self, ctx, free_slots):
+        self.ctx, self.free = ctx, list(free_slots)
+        self.pool = set(self.free)          # only these return to the free list; adopted slots belong to whoever handed them in
+        self.slot_of, self.tags = {}, {}
+
+    def makedirs(self, directory): pass
+    def isfile(self, path): return path in self.slot_of
+    def slot(self, path): return self.slot_of[path]
+
+    def adopt(self, path, slot, tag=None):
+        assert path not in self.slot_of and slot not in self.slot_of.values()
+        if slot in self.free:
+            self.free.remove(slot)
+        self.slot_of[path], self.tags[path] = slot, tag
+
+    def _release(self, path):
+        slot = self.slot_of.pop(path)
+        if slot in self.pool:
+            self.free.append(slot)
+        self.tags.pop(path, None)
+
+    def copy(self, src, dst):
+        if src == dst:
+            return
+        if dst not in self.slot_of:
+            if not self.free:
+                raise OSError('no free parent slot for %s' % dst)
+            self.slot_of[dst] = self.free.pop(0)
+        self.ctx.copy_parent(self.slot_of[src], self.slot_of[dst])
+        self.tags[dst] = self.tags.get(src)
+
+    def rename(self, src, dst):
+        if dst in self.slot_of:
+            self._release(dst)
+        self.slot_of[dst], self.tags[dst] = self.slot_of.pop(src), self.tags.pop(src, None)
+
+    def only_keep(self, directory, keep):
+        prefix = directory.rstrip(os.sep) + os.sep
+        for path in [p for p in self.slot_of if p.startswith(prefix) and os.sep not in p[len(prefix):] and p not in keep]:
+            self._release(path)
+
+
+_FILES = FileStore()
 
 
 class Podium:
     """The `num_elites` best (file, score) pairs seen so far, files copied to <directory>/best_elite/0_<rank>_elite.pth.  A
     generation is good when at least one file moved onto (or within) the podium; reading the flag resets it."""
 
-    def __init__(self, patience, directory, num_elites):
+    def __init__(self, patience, directory, num_elites, store=_FILES):
         self._n = num_elites
         self._patience = patience
+        self._store = store
         self._dir = os.path.join(directory, 'best_elite')
-        os.makedirs(self._dir, exist_ok=True)
+        store.makedirs(self._dir)
         self._slots = [('', float('-inf'))] * num_elites
         self._bad = True
 
@@ -59,7 +125,7 @@ class Podium:
     def init_from_infos(self, infos):
         slots = []
         for rank, (path, score) in enumerate(infos['best_elites']):
-            shutil.copy(path, self._slot_path(rank))
+            self._store.copy(path, self._slot_path(rank))
             slots.append((self._slot_path(rank), score))
         self._slots = slots
 
@@ -74,12 +140,12 @@ class Podium:
             slots.append((dst, score))
             if path != dst:
                 try:
-                    shutil.copy(path, dst)
+                    self._store.copy(path, dst)
                     self._bad = False
                 except OSError:
                     logging.error('[Podium]: tried to copy non existing elite')
         self._slots = slots
-        _only_keep(self._dir, [p for p, _ in slots])
+        self._store.only_keep(self._dir, [p for p, _ in slots])
 
     def is_bad_generation(self):
         bad, self._bad = self._bad, True
@@ -98,7 +164,8 @@ class Iteration:
                   ('noise_stdev', '_noise_stdev', 0), ('batch_size', '_batch_size', 0), ('times_orig_bs', '_times_orig_bs', 0),
                   ('nb_samples_used', '_nb_samples_used', 0))
 
-    def __init__(self, config, exp):
+    def __init__(self, config, exp, store=_FILES):
+        self._store = store
         self._noise_stdev, self._batch_size = config.noise_stdev, config.batch_size
         self._times_orig_bs, self._nb_samples_used = 1, 0
         self._bad_generations, self._epoch, self._iteration = 0, 0, 0
@@ -112,7 +179,7 @@ class Iteration:
         self._waiting_for_eval_run = False
         self._log_dir = exp['log_dir']
         self._models_dir = os.path.join(self._log_dir, 'models')
-        self._podium = Podium(config.patience, os.path.join(self._models_dir, 'best'), num_elites=exp['num_elites'])
+        self._podium = Podium(config.patience, os.path.join(self._models_dir, 'best'), num_elites=exp['num_elites'], store=store)
 
     # ---- snapshot
     def to_dict(self):
@@ -153,7 +220,7 @@ class Iteration:
     def process_evaluated_elites(self):
         """Hand this iteration's evaluated elite candidates (those whose file exists) to the podium; count a bad generation when
         patience is on and nothing new reached the podium.  Returns the best (score, file) of the candidates."""
-        cands = [(ind, sc) for ind, sc in self._eval_results.values() if os.path.isfile(ind)]
+        cands = [(ind, sc) for ind, sc in self._eval_results.values() if self._store.isfile(ind)]
         best_sc, best_ind = float('-inf'), None
         for ind, sc in cands:
             if sc > best_sc:
@@ -234,8 +301,8 @@ class ESIteration(Iteration):
     """NIC-ES: parents live beside the offspring in models/offspring (0_<i>_parent_params.pth), elite candidates in models/elite
     (0_<i>_elite_params.pth)."""
 
-    def __init__(self, config, exp):
-        super().__init__(config, exp)
+    def __init__(self, config, exp, store=_FILES):
+        super().__init__(config, exp, store)
         self._offspring_dir = os.path.join(self._models_dir, 'offspring')
         self._elite_dir = os.path.join(self._models_dir, 'elite')
         self._pop_size = exp.get('population_size', self._nb_offspring)
@@ -252,22 +319,22 @@ class ESIteration(Iteration):
         super().init_from_infos(infos)
         # files are placed under the id stored with them, the lists are renumbered by position (nic_es/iteration.py:41-48)
         for kind, key in ((self._elite_path, 'elites_to_evaluate'), (self._parent_path, 'parents')):
-            os.makedirs(os.path.dirname(kind(0)), exist_ok=True)
+            self._store.makedirs(os.path.dirname(kind(0)))
             for i, path in infos[key]:
-                shutil.copy(path, kind(i))
+                self._store.copy(path, kind(i))
         self._elites_to_evaluate = [(n, self._elite_path(n)) for n in range(len(infos['elites_to_evaluate']))]
         self._parents = [(n, self._parent_path(n)) for n in range(len(infos['parents']))]
 
     def init_from_zero(self, exp, policy):
         # parent None = "draw a fresh random model": the first generation is pop_size random individuals
         self._parents = [(i, None) for i in range(self._pop_size)]
-        os.makedirs(self._elite_dir, exist_ok=True)
+        self._store.makedirs(self._elite_dir)
         self._elites_to_evaluate = [(i, policy.generate_model().serialize(path=self._elite_path(i))) for i in range(self._num_elite_cands)]
 
     def init_from_singles(self, param_file_names, exp, policy):
         names = [param_file_names] if isinstance(param_file_names, str) else list(param_file_names)
-        os.makedirs(self._elite_dir, exist_ok=True)
-        os.makedirs(self._offspring_dir, exist_ok=True)
+        self._store.makedirs(self._elite_dir)
+        self._store.makedirs(self._offspring_dir)
         self._parents, self._elites_to_evaluate = [], []
         for i, name in enumerate(names):
             self._parents.append((i, policy.generate_model(from_param_file=name).serialize(path=self._parent_path(i))))
@@ -280,20 +347,18 @@ class ESIteration(Iteration):
         renamed = []
         for i, src in enumerate(parents):
             dst = self._parent_path(i)
-            if os.path.exists(dst):
-                os.remove(dst)
-            os.rename(src, dst)
+            self._store.rename(src, dst)
             renamed.append(dst)
         self._parents = list(enumerate([e for e, _ in self.best_elites()] + renamed))
-        _only_keep(self._offspring_dir, [p for _, p in self._parents])
+        self._store.only_keep(self._offspring_dir, [p for _, p in self._parents])
 
     def set_next_elites_to_evaluate(self, best_individuals):
-        os.makedirs(self._elite_dir, exist_ok=True)
+        self._store.makedirs(self._elite_dir)
         cands = []
         for i, src in enumerate(best_individuals):
-            shutil.copy(src, self._elite_path(i))
+            self._store.copy(src, self._elite_path(i))
             cands.append((i, self._elite_path(i)))
-        _only_keep(self._elite_dir, [p for _, p in cands])
+        self._store.only_keep(self._elite_dir, [p for _, p in cands])
         self._elites_to_evaluate = cands
 
     def record_eval_result(self, eval_return):
@@ -334,7 +399,7 @@ class NESIteration(Iteration):
         self._model = policy.generate_model(from_param_file=param_file_name).serialize(path=self._current_path)
 
     def set_model(self, model):
-        _only_keep(self._current_dir, [])
+        _FILES.only_keep(self._current_dir, [])
         self._model = model.serialize(path=self._current_path)
 
     def record_eval_result(self, result):

@@ -47,6 +47,7 @@ W1 = 0xBB67AE85
 MASK = np.uint64(0xFFFFFFFF)
 OFFSET_DOMAIN = 0x4F464653  # "OFFS"
 PARENT_DOMAIN = 0x50415245  # "PARE"
+TOURN_DOMAIN = 0x544F5552   # "TOUR"
 
 
 def philox4x32_10(c0, c1, c2, c3, k0, k1):
@@ -210,3 +211,30 @@ def sample_parents(seed, iteration, F, n_parents):
     it = int(iteration) & 0xFFFFFFFFFFFFFFFF
     r0, _, _, _ = philox4x32_10(i, it & 0xFFFFFFFF, it >> 32, PARENT_DOMAIN, k0, k1)
     return ((r0.astype(np.uint64) * np.uint64(n_parents)) >> np.uint64(32)).astype(np.int32)
+
+
+def sample_parents_tournament(seed, iteration, F, n_parents, tournament_size):
+    """NIC-ES parent pick with selection == 'tournament' (nic_es_worker.py:150-158:
+    `rs.choice(len(parents), min(len(parents), tournament_size), replace=False).min()` from an unseeded RandomState;
+    parents are sorted best first).  This build's rule: a uniformly random t-subset by Floyd's algorithm,
+        for d in 0..t-1: j = n - t + d;  r = (u_d * (j + 1)) >> 32;  pick = j if r is already in the set else r
+    with u_d = word d % 4 of philox(counter = (i, lo32(it), hi32(it) + ((d // 4) << 16), TOURN_DOMAIN), key(seed));
+    the parent is the lowest pick."""
+    k0, k1 = _key(seed)
+    n, t = int(n_parents), min(int(n_parents), int(tournament_size))
+    assert 1 <= t and n <= 4096
+    it = int(iteration) & 0xFFFFFFFFFFFFFFFF
+    assert it >> 48 == 0
+    i = np.arange(F, dtype=np.uint64)
+    chosen = np.zeros((F, n), dtype=bool)
+    best = np.full(F, n, dtype=np.int64)
+    words = None
+    for d in range(t):
+        if d % 4 == 0:
+            words = philox4x32_10(i, it & 0xFFFFFFFF, (it >> 32) + ((d // 4) << 16), TOURN_DOMAIN, k0, k1)
+        j = n - t + d
+        r = ((words[d % 4].astype(np.uint64) * np.uint64(j + 1)) >> np.uint64(32)).astype(np.int64)
+        pick = np.where(chosen[np.arange(F), r], j, r)
+        chosen[np.arange(F), pick] = True
+        best = np.minimum(best, pick)
+    return best.astype(np.int32)

@@ -267,38 +267,6 @@ def test_full_size_population_hybrid_equals_exact(rows):
     ctx.close()
 
 
-def test_es_generation_against_oracle():
-    """two NIC-ES generations (nic_es_worker.py:142-192 + nic_es_master.py:155-167) through es_generation against a plain
-    numpy restatement: same offspring, same survivors, the next parents' float32 weights bit-identical"""
-    import nes_b200
-    V, E, R, Fd, B, mu, el, P, sigma = 199, 64, 64, 128, 6, 4, 1, 14, 0.05
-    dims = fc_caption.Dims(V, E, R, Fd)
-    G = noise.granularity(E, R, Fd)
-    play, D, D_pad = noise.padded_layout(dims.layout(), G)
-    L = D_pad + 255 * G
-    ctx = nes_b200.NesContext(dict(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd), seed=21, table_len=L, n_parents=2 * mu, wave_members=8, rows=B)
-    parents = [fc_caption.xavier_theta(dims, 70 + k) for k in range(mu)]
-    for k in range(mu):
-        ctx.set_theta(parents[k], k)
-    fc = noise.table_slice(6, 0, B * Fd).astype(np.float32).reshape(B, Fd)
-    base = 0
-    for it in range(2):
-        base, fit, offs, pars = nes_b200.es_generation(ctx, it, P, mu, el, torch.from_numpy(fc).cuda(), sigma, base=base, precision=nes_b200.PREC_HYBRID)
-        offs, pars, fit = offs.cpu().numpy(), pars.cpu().numpy(), fit.cpu().numpy()
-        members, want_fit = [], []
-        for i in range(P):
-            th, _ = noise.member_theta(parents[pars[i]], noise.noise_row(21, offs[i], play, D), sigma, +1)
-            _, lp = fc_caption.decode_greedy(dims, th, fc)
-            members.append(th); want_fit.append(lp.astype(np.float64).sum())
-        assert np.allclose(fit, want_fit, rtol=1e-5)
-        order = sorted(range(P), key=lambda i: want_fit[i], reverse=True)[:mu - el]
-        parents = parents[:el] + [members[i] for i in order]
-        for k in range(mu):
-            got = ctx.get_theta(base + k).numpy()
-            assert np.array_equal(got, parents[k]), (it, k, np.abs(got - parents[k]).max())
-    ctx.close()
-
-
 def test_evolve_batch_equals_sequential_evolves():
     """nes_evolve_batch == the same evolve(dst_parent=) calls one by one: float32 and float64 weights bit-identical, and a HYBRID
     rollout from the batch-built parents (split-fp16 shadow, hybrid row bound) gives the tokens of the one-by-one parents"""
@@ -473,7 +441,7 @@ def test_sensitivity_mutation_evolve_rollout_and_policy(monkeypatch, tmp_path):
     model.ctx.close()
 
 
-@pytest.mark.parametrize('name', ['s5'])      # safe mutations with layer_n / vbn are refused by the library; s6 runs on the CPU only
+@pytest.mark.parametrize('name', ['s5', 's6'])
 def test_gradient_sensitivity_on_device_against_reference_golden(name, tmp_path):
     """SM-G-SUM end to end (safe_mutations.py:34-115; nic_es_worker.py:173-175): FCModel.calc_sensitivity computes the output-gradient
     sensitivity with autograd on the device holding theta, writes the reference's sens_t*_p*_*.pt file and hands the vector to the

@@ -130,15 +130,6 @@ def test_es_selection_is_the_references_stable_descending_sort():
     assert keep.numel() == 0
 
 
-def test_decode_sequence_matches_the_reference_rule():
-    """eval_utils.decode_sequence (src/captioning/eval_utils.py:13-27): words up to the first 0, joined by single spaces"""
-    import nes_b200
-    vocab = {str(i): 'w%d' % i for i in range(1, 10)}
-    seq = np.array([[3, 1, 0, 5], [0, 2, 2, 2], [7, 8, 9, 1]])
-    assert nes_b200.decode_sequence(vocab, seq) == ['w3 w1', '', 'w7 w8 w9 w1']
-    assert nes_b200.decode_sequence(vocab, torch.from_numpy(seq)) == ['w3 w1', '', 'w7 w8 w9 w1']
-
-
 def test_mnist_net_init_rule_on_a_stub_context():
     """MnistNet.initialize_params (src/algorithm/nets.py:55-69): parameters whose name contains '1' (conv1, fc1) keep torch's default
     uniform init, conv2 is Xavier-normal with a zero bias; layout = MnistNet.named_parameters(), D = 8490.  Host logic only: the

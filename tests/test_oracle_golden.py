@@ -106,3 +106,23 @@ def test_vbn_decode_matches_reference_golden(name):
         th, _ = noise.member_theta(theta, eps, c['sigma'], sign)
         s, lp = fc_caption.decode_greedy(dims, th, fc)
         assert np.array_equal(s, gv[name + '_seq'][j]) and np.array_equal(lp, gv[name + '_logprobs'][j])
+
+
+@pytest.mark.parametrize('name,members', [('t5a', [0, 1, 2, 3]), ('t5b', [0, 1]), ('t4', [1]), ('t2', [6])])
+def test_oracle_matches_reference_at_the_timed_shapes(name, members):
+    """the restatement against the goldens at the shapes the benchmarks time (tests/golden/make_golden_timed.py): LayerNorm with 150 / 200 /
+    512 rows, and one E = R = 512 / V = 9487 member of a parent other than parent 0 with a negative sign"""
+    import os
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, 'golden'))
+    import make_golden_timed as mt
+    from oracle import fc_caption, noise
+    gold = np.load(os.path.join(here, 'golden', 'golden_timed_v1.npz'))
+    c = mt.CASES[name]
+    dims, G, play, D, D_pad, L, thetas, fc, offs = mt.case_inputs(c)
+    for i in members:
+        th, _ = noise.member_theta(thetas[c['parents'][i]], noise.noise_row(mt.TABLE_SEED, offs[i], play, D), c['sigma'], c['signs'][i])
+        s, lp = fc_caption.decode_greedy(dims, th, fc)
+        assert np.array_equal(s, gold[name + '_seq'][i].astype(np.int64))
+        assert np.allclose(lp, gold[name + '_logprobs'][i], rtol=2e-6, atol=2e-6)     # MKL's summation order follows the thread count

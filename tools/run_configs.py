@@ -39,7 +39,7 @@ def nes_config(a, E, R, rows, ln, pairs, sigma, label):
         import torch.distributed as dist
         dist.init_process_group('nccl', device_id=dev)
     mo = dict(vocab_size=9487, input_encoding_size=E, rnn_size=R, fc_feat_size=2048, layer_n=ln, layer_n_affine=ln)
-    ctx = nes_b200.NesContext(mo, seed=1234, table_len=1 << 28, n_parents=1, wave_members=a.wave, rows=rows, device=local)
+    ctx = nes_b200.NesContext(mo, seed=1234, table_len=1 << a.table_log2, n_parents=1, wave_members=a.wave, rows=rows, device=local)
     nes_b200.FCModel(ctx, parent=0, rng_state=0)
     opt = nes_b200.Adam(ctx, None, stepsize=0.001)
     fc = torch.randn(rows, 2048, generator=torch.Generator().manual_seed(0)).to(dev)
@@ -74,26 +74,45 @@ def sweep(a):
     except Exception:
         pass
     hbm = peaks.get('hbm_gbs', 6650.0)
-    dev = torch.device('cuda', 0)
+    rank, world = int(os.environ.get('RANK', '0')), int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=dev)
     for D in (1_000_000, 2_000_000, 5_000_000, 13_400_848, 25_000_000, 50_000_000):
-        ctx = nes_b200.NesContext(counts=[D], seed=1234, table_len=1 << 28, device=0)
+        ctx = nes_b200.NesContext(counts=[D], seed=1234, table_len=1 << a.table_log2, device=local)
         ctx.set_theta(torch.randn(D) * 0.02)
         nes_b200.Adam(ctx, None, stepsize=0.001)
         for F in (1000, 2000, 5000, 10000, 20000):
             offs = ctx.sample_offsets(F, F, device=True)
             w = torch.randn(F, device=dev)
-            ctx.last_gradient_ms()
-            t = []
-            for i in range(4):
-                ctx.gradient(offs, w, 0.01, want=False)
-                if i:
-                    t.append(ctx.last_gradient_ms())
-            ms = sum(t) / len(t)
+            if world > 1:
+                # N GPUs: every rank sums all F rows for its slice of the parameter axis, then one all-reduce gives every rank the whole
+                # vector (master.sharded_master_step); timed on the device as the max over ranks, the all-reduce included
+                def k7():
+                    g = ctx.gradient(offs, w, 0.01, out_device=dev, shard=(rank, world))
+                    dist.all_reduce(g)
+                tt = torch.tensor([time_ms(k7, 3)], dtype=torch.float64, device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                ms = tt.item()
+            else:
+                ctx.last_gradient_ms()
+                t = []
+                for i in range(4):
+                    ctx.gradient(offs, w, 0.01, want=False)
+                    if i:
+                        t.append(ctx.last_gradient_ms())
+                ms = sum(t) / len(t)
             gb = (F * D * 2 + D * 4) / 1e9
             ms8 = time_ms(lambda: ctx.opt_update(None, 1e-7, want_ratio=False), 3)
-            print(json.dumps({'config': '5: K7 + K8 sweep', 'D': D, 'F': F, 'k7_ms': ms, 'k7_GBps': gb / (ms * 1e-3), 'k7_frac_of_measured_peak': gb / (ms * 1e-3) / hbm,
+            if rank == 0:
+              print(json.dumps({'config': '5: K7 + K8 sweep', 'n_gpus': world, 'table_log2': a.table_log2, 'D': D, 'F': F, 'k7_ms': ms, 'k7_GBps': gb / (ms * 1e-3), 'k7_frac_of_measured_peak': gb / (ms * 1e-3) / hbm,
                               'k7_frac_of_8TBps': gb / (ms * 1e-3) / 8000.0, 'k8_adam_ms': ms8, 'k8_GBps_approx_56B_per_param': 56.0 * D / 1e9 / (ms8 * 1e-3)}))
         ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == '__main__':
@@ -102,6 +121,7 @@ if __name__ == '__main__':
     ap.add_argument('--pairs', type=int, default=0)
     ap.add_argument('--wave', type=int, default=1024)
     ap.add_argument('--steps', type=int, default=2)
+    ap.add_argument('--table-log2', type=int, default=32)
     a = ap.parse_args()
     if a.config == 1:
         sys.path.insert(0, ROOT)

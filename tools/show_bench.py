@@ -9,8 +9,14 @@ try:
     r = d['roofline']; sh = r['kernel_time_share']; ms = d['ms_per_step']
     ks = {r['kernel'].split(' ')[0]: r}
     ks.update({v['kernel'].split(' ')[0]: v for v in r.get('other_kernels', {}).values()})
-    kk = ' '.join('%s %.2fms %.0f%s(%.2f)' % (n.replace('k_member_', ''), v['avg_launch_ms'], v['achieved'], v['unit'], v['frac']) for n, v in ks.items())
+    kk = ' '.join('%s %.2fms %.0f%s(%.2f)' % (n.replace('k_member_', ''), v.get('avg_launch_ms', v.get('ms_per_wave', 0)), v['achieved'], v['unit'], v['frac']) for n, v in ks.items())
     print('%s evals/s %.0f ms %.1f e2e %.0f clk %s | %s | shares %s | hyb %s' % (tag, d['value'], ms, d['e2e']['value'], d['clocks']['sm_mhz'], kk,
           {k: round(v * ms, 1) for k, v in sh.items()}, d.get('hybrid_stats', {}).get('rows_overflowed')))
+    if 'nes_config3' in d:
+        n3 = d['nes_config3']
+        print('   config3: %d GPUs %.1f ms / iteration, %.0f rollouts/s, theta_agree %s (ranks %s, golden %s)' % (n3['n_gpus'], n3['iteration_ms'], n3['rollouts_per_s'], n3['theta_agree'], n3['theta_identical_on_all_ranks'], n3['theta_equals_1rank_golden']))
+    if 'sections_ms_per_rank' in d:
+        for r in d['sections_ms_per_rank']:
+            print('   ', r)
 except Exception as e:
     print(tag, 'failed', repr(e))
