@@ -13,16 +13,21 @@ OPT_SGD, OPT_ADAM = 0, 1
 
 
 class NesContext:
-    def __init__(self, model_options=None, *, counts=None, tensors=None, flat_granule=64, seed=1234, table_len=1 << 28,
+    def __init__(self, model_options=None, *, counts=None, tensors=None, flat_granule=64, seed=1234, table_len=None,
                  n_parents=1, wave_members=256, rows=128, device=0, fill=True):
         """model_options: dict / namedtuple with the fc_caption ModelOptions fields (vocab_size,
         input_encoding_size, rnn_size, fc_feat_size, layer_n, layer_n_affine[, seq_length]); or
         counts=[...] for a generic flat parameter vector (master math only), or tensors=[(name, shape), ...] for a flat vector
-        with named tensors (the MNIST net, layout.mnist_tensors())."""
+        with named tensors (the MNIST net, layout.mnist_tensors()).
+        table_len: fp16 elements of the shared noise table; None = 2^28, or 256 padded noise rows rounded up to a power of two if
+        that is more (2^32 = 8 GB for the E = R = 512 model: 2.1 M distinct rows, so a population of 5000 draws ~6 colliding pairs
+        per iteration instead of ~100 and K7's rows do not overlap inside L2)."""
         self.lib = _lib.load()
         self.device = int(device)
         self._h = ctypes.c_void_p()
-        self.seed, self.table_len, self.n_parents = int(seed), int(table_len), int(n_parents)
+        self.seed, self.n_parents = int(seed), int(n_parents)
+        self._evolve_counter = 0           # PolicyNet.evolve() without an explicit offset: one stream per context, not per net
+        self.evolve_stream = 0             # ... offset by this (a worker / rank id) so that two processes on one seed differ
         if model_options is not None:
             mo = model_options._asdict() if hasattr(model_options, '_asdict') else dict(model_options)
             self.dims = dict(vocab_size=int(mo['vocab_size']), input_encoding_size=int(mo['input_encoding_size']),
@@ -37,6 +42,7 @@ class NesContext:
             self.tensors, self.D, self.D_pad = build_layout(
                 fc_tensors(self.dims['vocab_size'], self.dims['input_encoding_size'], self.dims['rnn_size'],
                            self.dims['fc_feat_size'], self.dims['layer_n'], self.dims['layer_n_affine']), self.G)
+            self.table_len = self._default_table_len(table_len)
             _lib.check(self.lib.nes_ctx_create_fc(ctypes.byref(self._h), self.device, ctypes.byref(d), self.seed,
                                                   self.table_len, self.n_parents, int(wave_members), int(rows)))
             self.wave_members, self.rows_cap = int(wave_members), int(rows)
@@ -47,6 +53,7 @@ class NesContext:
             named = [(n, tuple(sh)) for n, sh in tensors] if tensors is not None else [('t%d' % i, (int(c),)) for i, c in enumerate(counts)]
             counts = [int(np.prod(sh)) for _, sh in named]
             self.tensors, self.D, self.D_pad = build_layout(named, self.G)
+            self.table_len = self._default_table_len(table_len)
             arr = (ctypes.c_int64 * len(counts))(*[int(c) for c in counts])
             _lib.check(self.lib.nes_ctx_create_flat(ctypes.byref(self._h), self.device, arr, len(counts), self.G,
                                                     self.seed, self.table_len, self.n_parents))
@@ -56,6 +63,18 @@ class NesContext:
         self.use_stream(torch.cuda.current_stream(self.dev))
         if fill:
             self.fill_table()
+
+    def _default_table_len(self, table_len):
+        if table_len is not None:
+            return int(table_len)
+        return max(1 << 28, 1 << int(256 * self.D_pad - 1).bit_length())
+
+    def next_evolve_iteration(self):
+        """stream index of the next PolicyNet.evolve() that was given no offset: monotonically increasing per context (a fresh
+        PolicyNet on the same context does not replay earlier noise), disjoint between evolve_stream ids"""
+        it = (1 << 40) + (int(self.evolve_stream) << 24) + self._evolve_counter
+        self._evolve_counter += 1
+        return it
 
     # ---- plumbing
     def use_stream(self, stream):

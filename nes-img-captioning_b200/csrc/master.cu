@@ -210,10 +210,18 @@ __global__ void __launch_bounds__(256) k_opt_update(const float* __restrict__ g,
         partials[2 * blockIdx.x] = a; partials[2 * blockIdx.x + 1] = b;
     }
 }
-__global__ void k_norm_finalize(const double* __restrict__ partials, int nblocks, double* __restrict__ norms) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        double a = 0, b = 0;
-        for (int q = 0; q < nblocks; ++q) { a += partials[2 * q]; b += partials[2 * q + 1]; }
+// one block: the per-block partial sums of |step|^2 and |theta|^2 reduced in a fixed order (thread t sums partials t, t + 256, ...; then a
+// shuffle tree), so the ratio is reproducible run to run
+__global__ void __launch_bounds__(256) k_norm_finalize(const double* __restrict__ partials, int nblocks, double* __restrict__ norms) {
+    __shared__ double sh[2][8];
+    double a = 0, b = 0;
+    for (int q = threadIdx.x; q < nblocks; q += 256) { a += partials[2 * q]; b += partials[2 * q + 1]; }
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = a; sh[1][threadIdx.x >> 5] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        a = 0; b = 0;
+        for (int q = 0; q < 8; ++q) { a += sh[0][q]; b += sh[1][q]; }
         norms[0] = sqrt(a); norms[1] = sqrt(b);
     }
 }
@@ -242,7 +250,7 @@ int launch_opt_update(Ctx* c, const float* d_g, const double* d_G64, int direct,
     }
     c->launches++;
     NES_CUDA(cudaGetLastError());
-    k_norm_finalize<<<1, 32, 0, c->stream>>>(c->d_norm_partials, c->norm_blocks, c->d_norms);
+    k_norm_finalize<<<1, 256, 0, c->stream>>>(c->d_norm_partials, c->norm_blocks, c->d_norms);
     c->launches++;
     NES_CUDA(cudaGetLastError());
     c->theta_is_f32[0] = 0;

@@ -285,6 +285,8 @@ class ESPopulation:
             def serialize(self, path=''):
                 if path.startswith(pop.it.offspring_dir()):      # a parent: the half that the first survivors do NOT go to
                     slot = pop.mu + self.k
+                elif self.k >= pop.C:                            # the reference writes an elite file for every single and keeps the first
+                    return path                                  # num_elite_cands (nic_es/iteration.py:70-81): no slot for the dropped ones
                 else:
                     slot = pop.store.free.pop(0)
                 pop.store.adopt(path, slot, tag='single:%d' % self.k)
@@ -308,7 +310,7 @@ class ESPopulation:
         return [self.store.slot(p) for _, p in self.it.elites_to_evaluate()]
 
     def podium(self):
-        return [(self.store.slot(p), sc) for p, sc in self.it.best_elites()]
+        return [(self.store.slot(p), sc) for p, sc in self.it.best_elites() if p]
 
     @property
     def sigma(self):
@@ -324,7 +326,7 @@ class ESPopulation:
                 t = 'g%d:o%d' % (gen, int(order[rank]))
             return t
         return {'parents': [tag(p) for _, p in self.it.parents()], 'elites_to_evaluate': [tag(p) for _, p in self.it.elites_to_evaluate()],
-                'podium': [[tag(p), sc] for p, sc in self.it.best_elites()]}
+                'podium': [[tag(p), sc] for p, sc in self.it.best_elites() if p]}
 
     # ---- one generation
     def begin_generation(self):
@@ -361,12 +363,15 @@ class ESPopulation:
         it = self.it
         cands = it.elites_to_evaluate()
         assert len(elite_scores) == len(cands)
-        for (cid, cpath), score in zip(cands, elite_scores):
-            it.record_eval_result(EvalES(cid, cpath, float(score)))
-        best_sc, best_ind = it.process_evaluated_elites()
+        # The survivors first: an offspring IS theta[parent] + sigma * eps with the parent as it was when the offspring was evaluated (the
+        # worker wrote its file then, nic_es_worker.py:188), so they are re-derived before the podium copies below overwrite elite slots
+        # that served as parents.  They go to the idle half of the slots, which nothing else touches.
         n_keep = min(self.mu - self.E, int(fitness_all.numel()))
         base = self.block * self.mu
         order = self.ctx.es_select_evolve(fitness_all, offs, slots, n_keep, self.sigma, base)
+        for (cid, cpath), score in zip(cands, elite_scores):
+            it.record_eval_result(EvalES(cid, cpath, float(score)))
+        best_sc, best_ind = it.process_evaluated_elites()
         self._leave_fresh_mode()
         gen = it.iteration()
         paths = []

@@ -54,7 +54,6 @@ class PolicyNet:
         self.nb_learnable_params = ctx.D
         self.nb_params = ctx.D
         self._theta_dtype = torch.float32
-        self._evolve_counter = 0
 
     # -- src/algorithm/nets.py:163-168
     def set_from_vector(self, vector):
@@ -77,9 +76,8 @@ class PolicyNet:
     def evolve(self, sigma, rng_state=None, offset=None):
         """theta <- theta + sigma*eps(offset); returns the float32 noise vector (numpy, owned)."""
         if offset is None:
-            it = self._evolve_counter if rng_state is None else int(rng_state)
-            offset = int(self.ctx.sample_offsets((1 << 40) + it, 1)[0])
-            self._evolve_counter += 1
+            it = self.ctx.next_evolve_iteration() if rng_state is None else (1 << 40) + int(rng_state)
+            offset = int(self.ctx.sample_offsets(it, 1)[0])
         member, noise = self.ctx.evolve(offset, sigma, +1.0, self.parent, device=self.ctx.dev)
         self.ctx.set_theta(member, self.parent)
         self._theta_dtype = torch.float32

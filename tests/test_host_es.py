@@ -27,6 +27,7 @@ class StubContext:
         self.n_parents, self.dev, self.mutation = n_parents, torch.device('cpu'), ''
         self.tensors, self.D, _ = nes_b200.layout.build_layout(nes_b200.layout.fc_tensors(19, 64, 64, 64), 64)
         self.content = {}
+        self.lineage = {}                  # slot -> content of the parent slot at the moment the survivor was derived from it
         self.gen = -1
         self.n_fresh = 0
         self.modes = []
@@ -53,6 +54,7 @@ class StubContext:
         for r, k in enumerate(order):
             assert not (dst_base <= int(parents[k]) < dst_base + n_keep), 'a survivor would be written over its own parent'
             self.content[dst_base + r] = 'g%d:o%d' % (self.gen, k)
+            self.lineage[dst_base + r] = self.content[int(parents[k])]
         return torch.from_numpy(order.astype(np.int64))
 
 
@@ -75,7 +77,12 @@ def test_es_population_follows_the_reference_master_bookkeeping():
             assert set(slots.tolist()) == {pop.blank} and ctx.mutation == 'SCALE'      # parent is None: a fresh model per offspring
         else:
             assert ctx.mutation == '' and set(slots.tolist()) <= set(pop.parent_slots())
+        evaluated_from = {k: ctx.content[int(s)] for k, s in enumerate(slots.tolist())}      # what each offspring's parent held when it was evaluated
         info = pop.end_generation(torch.from_numpy(sc.fitnesses(gen)), offs, slots, sc.elite_scores(gen))
+        # a survivor is its parent AS EVALUATED plus noise (the worker wrote the file then, nic_es_worker.py:188): the podium update of the
+        # same generation, which overwrites elite slots that served as parents, must not leak into it
+        for r, k in enumerate(info['order'].tolist()):
+            assert ctx.lineage[pop.parent_slots()[len(pop.podium()) + r]] == evaluated_from[k], (gen, r, k)
         got = pop.tags()
         assert got['parents'] == want['parents'], (gen, got['parents'], want['parents'])
         assert got['elites_to_evaluate'] == want['elites_to_evaluate'], gen
