@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libnes_b200.so')
 SOURCES = ['noise.cu', 'master.cu', 'decode.cu', 'cider.cu', 'mnist.cu', 'capi.cu']
-HEADERS = ['common.cuh', 'tc_ptx.cuh', 'member_gemm.cuh', 'dense.cuh', 'hybrid.cuh', os.path.join('..', '..', 'include', 'nes_b200.h')]
+HEADERS = ['common.cuh', 'tc_ptx.cuh', 'member_gemm.cuh', 'dense.cuh', 'hybrid.cuh', 'lstm_pair.cuh', os.path.join('..', '..', 'include', 'nes_b200.h')]
 FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
          '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr', '-Xptxas', '-v']
 

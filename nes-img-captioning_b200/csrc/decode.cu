@@ -7,6 +7,7 @@
 //              logits = logit(h) -> argmax, log-prob    LOGIT member GEMM + k_finalize
 // Finished-mask, early break and the seq / seq_logprobs writes follow :233-243.
 #include "hybrid.cuh"
+#include "lstm_pair.cuh"
 #include <cstdlib>
 #include <map>
 #include <tuple>
@@ -565,6 +566,43 @@ static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
     return 0;
 }
 
+// LSTM step as clusters of two CTAs sharing the activation block (lstm_pair.cuh); NES_LSTM_PAIR=0 keeps the one-CTA-per-item kernel
+static int lstm_pair_clusters(Ctx* c) {
+    static int n[64] = {0};
+    if (!n[c->device]) {
+        using C = DenseCfg<DEN_LSTM>;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * 74); cfg.blockDim = dim3(C::THREADS); cfg.dynamicSmemBytes = C::SMEM_BYTES;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        int m = 0;
+        if (cudaOccupancyMaxActiveClusters(&m, k_lstm_pair, &cfg) != cudaSuccess || m < 1) { cudaGetLastError(); m = sm_count(c) / 2; }
+        n[c->device] = m;
+    }
+    return n[c->device];
+}
+static bool lstm_pair_enabled() { static int v = -1; if (v < 0) { const char* e = getenv("NES_LSTM_PAIR"); v = (e && atoi(e) == 0) ? 0 : 1; } return v == 1; }
+static int launch_lstm_pair(Ctx* c, DenseParams& p, int64_t n_members) {
+    using C = DenseCfg<DEN_LSTM>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        NES_CUDA(cudaFuncSetAttribute(k_lstm_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        attr_done = true;
+    }
+    const int64_t units = n_members * p.m_tiles;
+    NES_CHECK(units >= 1 && units * p.n_tiles < (1ll << 30), "bad unit count");
+    p.n_units = (int32_t)units;
+    const int64_t pairs = (units * p.n_tiles + 1) / 2;
+    const int ncl = lstm_pair_clusters(c);
+    const unsigned grid = 2u * (unsigned)(pairs < ncl ? pairs : ncl);
+    ProfScope prof(c, PROF_LSTM);
+    k_lstm_pair<<<grid, C::THREADS, C::SMEM_BYTES, c->stream>>>(p);
+    c->launches++;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
 // member weights of one wave, materialised once per rollout (dense.cuh)
 static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit, bool img, bool ln, bool ln_par) {
     DecodeWorkspace* ws = c->ws;
@@ -575,7 +613,8 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32; q.scale_div = c->scale_div;
         q.w_start = L.t[wt].start; q.w_pstart = L.t[wt].pstart; q.K = K; q.out_rows = out_rows; q.mode = mode; q.R = ws->R; q.src_rows = src_rows;
         q.sigma = sigma; q.hi = hi; q.lo = lo; q.n_members = nm;
-        const dim3 grid((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(nm < 32768 ? nm : 32768));
+        const int64_t groups = (nm + kMatGroup - 1) / kMatGroup;
+        const dim3 grid((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(groups < 32768 ? groups : 32768));
         if (q.scale) { if (lo) k_materialise<true, true><<<grid, 256, 0, c->stream>>>(q); else k_materialise<true, false><<<grid, 256, 0, c->stream>>>(q); }
         else         { if (lo) k_materialise<false, true><<<grid, 256, 0, c->stream>>>(q); else k_materialise<false, false><<<grid, 256, 0, c->stream>>>(q); }
         c->launches++;
@@ -786,7 +825,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 p.rows = rows; p.rows_pad = rows_pad; p.m_tiles = m_tiles; p.n_tiles = ws->ntl; p.N = R;
                 p.b_rows = ws->ntl * kLstmTileCols; p.bias = ws->wl_bias; p.bias_stride = ws->ntl * kLstmTileCols;
                 p.c_state = ws->c_state; p.out_hi = ws->h_hi[hb ^ 1]; p.out_lo = ws->h_lo[hb ^ 1]; p.h_trace = ht;
-                if (launch_dense<DEN_LSTM>(c, p, nm)) return 1;
+                if (lstm_pair_enabled() ? launch_lstm_pair(c, p, nm) : launch_dense<DEN_LSTM>(c, p, nm)) return 1;
             } else if (!c->dims.layer_n) {
                 GemmParams p = base;
                 p.nseg = 2; p.N = R; p.chunk_stride = R; p.n_tiles = R / 16;

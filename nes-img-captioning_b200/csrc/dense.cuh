@@ -411,32 +411,26 @@ __device__ __forceinline__ uint4 ld_nc_128(const void* p) {
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
-// grid = (ceil(out_rows / 64), members): one block writes 64 output rows of one member; a row is covered by K/8 threads
-// (16 bytes of eps each), so all index arithmetic is 32-bit and per row, not per element.  HBM-stream bound: a thread keeps
-// kMatBatch rows (one 16-byte table load and two 16-byte theta loads each) in flight, the operand tiles leave through streaming
-// stores (they are next read a whole rollout phase later; theta stays in L2)
+// grid = (ceil(out_rows / 64), ceil(members / kMatGroup)): one block writes 64 output rows of kMatGroup consecutive members; a row is
+// covered by K/8 threads (16 bytes of eps each), so all index arithmetic is 32-bit and per row, not per element.  The rollout hands
+// the members over grouped by parent (ESPopulation.sample sorts them; NIC-NES has one parent), so a thread keeps its kMatBatch rows of
+// the parent's float32 theta (and safe-mutation scale) in registers across the group and only the eps slices and the operand tiles
+// stream: theta would otherwise cross the L2 -> SM fabric once per member (4 of every 10 bytes this kernel moved).  All loads of a
+// batch are issued before the first store; the operand tiles leave through streaming stores (they are next read a whole rollout phase later)
+constexpr int kMatGroup = 8;
 template <bool SCALED, bool HAS_LO>
-__global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
+__global__ void __launch_bounds__(256, SCALED ? 2 : 3) k_materialise(const MatParams p) {
     const int kv = p.K / 8;
     const int tpr = kv < 256 ? kv : 256;                 // threads per row
     const int rpi = 256 / tpr;                           // rows per iteration
     const int lr = threadIdx.x / tpr, kvi = threadIdx.x - lr * tpr;
     if (lr >= rpi) return;
     const int r_end = min(p.out_rows, ((int)blockIdx.x + 1) * kMatRowsPerBlock);
-    for (int64_t member = blockIdx.y; member < p.n_members; member += gridDim.y) {
-        // W * 2^8 = fma(theta, 2^8, +-fl(2^8 sigma * eps)): scaling by a power of two commutes with every rounding, so this is
-        // 2^8 * fl(theta +- fl(sigma * eps)) -- the reference's member weight -- with one FFMA instead of FADD + FMUL
-        const float ssig = __fmul_rn(p.sign[member] > 0.f ? p.sigma : -p.sigma, kThetaScale);
-        const int64_t pbase = (int64_t)(p.parent ? p.parent[member] : 0) * p.D + p.w_start;
-        const float* __restrict__ tbase = p.theta32 + pbase;
-        const float* __restrict__ sbase = p.scale ? p.scale + pbase : nullptr;
-        const __half* __restrict__ ebase = p.table + p.off[member] + p.w_pstart;
-        const bool aligned = (reinterpret_cast<uintptr_t>(tbase) & 15) == 0;          // K is a multiple of 64, so every row start is too
+    for (int64_t g0 = (int64_t)blockIdx.y * kMatGroup; g0 < p.n_members; g0 += (int64_t)gridDim.y * kMatGroup) {
+        const int64_t g1 = g0 + kMatGroup < p.n_members ? g0 + kMatGroup : p.n_members;
         for (int k = kvi * 8; k < p.K; k += tpr * 8) {
             for (int r0 = blockIdx.x * kMatRowsPerBlock + lr; r0 < r_end; r0 += rpi * kMatBatch) {
                 int src[kMatBatch];
-                uint4 ev[kMatBatch];
-                float tv[kMatBatch][8];
 #pragma unroll
                 for (int b = 0; b < kMatBatch; ++b) {
                     const int r = r0 + b * rpi;
@@ -451,46 +445,69 @@ __global__ void __launch_bounds__(256) k_materialise(const MatParams p) {
                         } else if (r >= p.src_rows) src[b] = -1;
                     }
                 }
+                float tv[kMatBatch][8];
+                float sv[SCALED ? kMatBatch : 1][8];
+                int cur_par = -1;
+                for (int64_t member = g0; member < g1; ++member) {
+                    // W * 2^8 = fma(theta, 2^8, +-fl(2^8 sigma * eps)): scaling by a power of two commutes with every rounding, so this
+                    // is 2^8 * fl(theta +- fl(sigma * eps)) -- the reference's member weight -- with one FFMA instead of FADD + FMUL
+                    const float ssig = __fmul_rn(p.sign[member] > 0.f ? p.sigma : -p.sigma, kThetaScale);
+                    const int par = p.parent ? p.parent[member] : 0;
+                    const __half* __restrict__ ebase = p.table + p.off[member] + p.w_pstart;
+                    uint4 ev[kMatBatch];
 #pragma unroll
-                for (int b = 0; b < kMatBatch; ++b) {
-                    if (src[b] < 0) continue;
-                    const float* tw = tbase + (int64_t)src[b] * p.K + k;
-                    ev[b] = ld_nc_128(ebase + (int64_t)src[b] * p.K + k);
-                    if (aligned) {
-                        *reinterpret_cast<float4*>(&tv[b][0]) = __ldg(reinterpret_cast<const float4*>(tw));
-                        *reinterpret_cast<float4*>(&tv[b][4]) = __ldg(reinterpret_cast<const float4*>(tw) + 1);
-                    } else {
+                    for (int b = 0; b < kMatBatch; ++b)
+                        if (src[b] >= 0) ev[b] = ld_nc_128(ebase + (int64_t)src[b] * p.K + k);
+                    if (par != cur_par) {
+                        cur_par = par;
+                        const int64_t pbase = (int64_t)par * p.D + p.w_start;
+                        const float* __restrict__ tbase = p.theta32 + pbase;
+                        const bool aligned = (reinterpret_cast<uintptr_t>(tbase) & 15) == 0;      // K is a multiple of 64, so every row start is too
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) tv[b][e] = __ldg(tw + e);
-                    }
-                }
+                        for (int b = 0; b < kMatBatch; ++b) {
+                            if (src[b] < 0) continue;
+                            const float* tw = tbase + (int64_t)src[b] * p.K + k;
+                            if (aligned) {
+                                *reinterpret_cast<float4*>(&tv[b][0]) = __ldg(reinterpret_cast<const float4*>(tw));
+                                *reinterpret_cast<float4*>(&tv[b][4]) = __ldg(reinterpret_cast<const float4*>(tw) + 1);
+                            } else {
 #pragma unroll
-                for (int b = 0; b < kMatBatch; ++b) {
-                    if (src[b] == -2) continue;
-                    __align__(16) __half2 hh[4];
-                    __align__(16) __half2 hl[4];
-                    if (src[b] >= 0) {
-                        const __half2* eh = reinterpret_cast<const __half2*>(&ev[b]);
-                        const float* sc = SCALED ? sbase + (int64_t)src[b] * p.K + k : nullptr;
+                                for (int e = 0; e < 8; ++e) tv[b][e] = __ldg(tw + e);
+                            }
+                            if (SCALED) {
+                                const float* sc = p.scale + pbase + (int64_t)src[b] * p.K + k;
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float2 ef = __half22float2(eh[e]);
-                            float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
-                            if (SCALED) { n0 = apply_scale(n0, __ldg(sc + 2 * e), p.scale_div); n1 = apply_scale(n1, __ldg(sc + 2 * e + 1), p.scale_div); }
-                            const float x0 = __fmaf_rn(tv[b][2 * e], kThetaScale, n0), x1 = __fmaf_rn(tv[b][2 * e + 1], kThetaScale, n1);
-                            hh[e] = __floats2half2_rn(x0, x1);
-                            if (HAS_LO) {
-                                const float2 hf = __half22float2(hh[e]);
-                                hl[e] = __floats2half2_rn(__fsub_rn(x0, hf.x), __fsub_rn(x1, hf.y));
+                                for (int e = 0; e < 8; ++e) sv[b][e] = __ldg(sc + e);
                             }
                         }
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) { hh[e] = __floats2half2_rn(0.f, 0.f); hl[e] = hh[e]; }
                     }
-                    const int64_t o = (member * p.out_rows + (r0 + b * rpi)) * (int64_t)p.K + k;
-                    st_stream_128(p.hi + o, *reinterpret_cast<uint4*>(hh));
-                    if (HAS_LO) st_stream_128(p.lo + o, *reinterpret_cast<uint4*>(hl));
+#pragma unroll
+                    for (int b = 0; b < kMatBatch; ++b) {
+                        if (src[b] == -2) continue;
+                        __align__(16) __half2 hh[4];
+                        __align__(16) __half2 hl[4];
+                        if (src[b] >= 0) {
+                            const __half2* eh = reinterpret_cast<const __half2*>(&ev[b]);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float2 ef = __half22float2(eh[e]);
+                                float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
+                                if (SCALED) { n0 = apply_scale(n0, sv[b][2 * e], p.scale_div); n1 = apply_scale(n1, sv[b][2 * e + 1], p.scale_div); }
+                                const float x0 = __fmaf_rn(tv[b][2 * e], kThetaScale, n0), x1 = __fmaf_rn(tv[b][2 * e + 1], kThetaScale, n1);
+                                hh[e] = __floats2half2_rn(x0, x1);
+                                if (HAS_LO) {
+                                    const float2 hf = __half22float2(hh[e]);
+                                    hl[e] = __floats2half2_rn(__fsub_rn(x0, hf.x), __fsub_rn(x1, hf.y));
+                                }
+                            }
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) { hh[e] = __floats2half2_rn(0.f, 0.f); hl[e] = hh[e]; }
+                        }
+                        const int64_t o = (member * p.out_rows + (r0 + b * rpi)) * (int64_t)p.K + k;
+                        st_stream_128(p.hi + o, *reinterpret_cast<uint4*>(hh));
+                        if (HAS_LO) st_stream_128(p.lo + o, *reinterpret_cast<uint4*>(hl));
+                    }
                 }
             }
         }
