@@ -19,7 +19,7 @@ from .noise import flat_layout
 
 class Dims:
     def __init__(self, vocab_size, input_encoding_size, rnn_size, fc_feat_size,
-                 seq_length=16, layer_n=False, layer_n_affine=False, vbn=False, vbn_affine=False):
+                 seq_length=16, layer_n=False, layer_n_affine=False, vbn=False, vbn_affine=False, vbn_e=False):
         self.vocab_size = vocab_size
         self.input_encoding_size = input_encoding_size
         self.rnn_size = rnn_size
@@ -27,12 +27,13 @@ class Dims:
         self.seq_length = seq_length
         self.vbn = bool(vbn)                       # batch norm over the rows of the batch, no running statistics (captioning/nets.py:87-91)
         self.vbn_affine = bool(vbn_affine)
+        self.vbn_e = bool(vbn_e)                   # batch norm on the outputs of img_embed and embed (captioning/nets.py:156-165)
         self.layer_n = bool(layer_n) and not self.vbn
         self.layer_n_affine = bool(layer_n_affine)
 
     def layout(self):
         return flat_layout(self.vocab_size, self.input_encoding_size, self.rnn_size,
-                           self.fc_feat_size, self.layer_n, self.layer_n_affine, self.vbn, self.vbn_affine)
+                           self.fc_feat_size, self.layer_n, self.layer_n_affine, self.vbn, self.vbn_affine, self.vbn_e)
 
     def num_params(self):
         lay = self.layout()
@@ -55,7 +56,7 @@ def xavier_theta(dims, seed):
     from .noise import table_slice
     theta = np.zeros(dims.num_params(), dtype=np.float32)
     for name, shape, start, cnt in dims.layout():
-        if 'ln' in name or 'bn' in name:
+        if 'ln' in name or 'bn' in name or '1' in name:              # algorithm/nets.py:62-64 skips them: torch's default 1 / 0
             if name.endswith('weight'):
                 theta[start:start + cnt] = 1.0
         elif name.endswith('weight'):

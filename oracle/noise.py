@@ -108,13 +108,19 @@ def lcm(*xs):
 
 
 def flat_layout(vocab_size, input_encoding_size, rnn_size, fc_feat_size,
-                layer_n=False, layer_n_affine=False, vbn=False, vbn_affine=False):
+                layer_n=False, layer_n_affine=False, vbn=False, vbn_affine=False, vbn_e=False):
     """[(name, shape, start, count)] in `named_parameters()` order of the
-    reference FCModel (src/captioning/nets.py:150-153, LSTMCore :81-96)."""
+    reference FCModel (src/captioning/nets.py:150-153, LSTMCore :81-96).  vbn_e (:156-165) wraps img_embed and embed into
+    Sequential(layer, BatchNorm1d): their parameters are renamed `<layer>.0.*` and, with vbn_affine, followed by `<layer>.1.weight / bias`."""
     V1, E, R, Fd = vocab_size + 1, input_encoding_size, rnn_size, fc_feat_size
-    tensors = [
-        ('img_embed.weight', (E, Fd)), ('img_embed.bias', (E,)),
-        ('embed.weight', (V1, E)),
+    if vbn_e:
+        tensors = [('img_embed.0.weight', (E, Fd)), ('img_embed.0.bias', (E,))]
+        tensors += [('img_embed.1.weight', (E,)), ('img_embed.1.bias', (E,))] if vbn_affine else []
+        tensors += [('embed.0.weight', (V1, E))]
+        tensors += [('embed.1.weight', (E,)), ('embed.1.bias', (E,))] if vbn_affine else []
+    else:
+        tensors = [('img_embed.weight', (E, Fd)), ('img_embed.bias', (E,)), ('embed.weight', (V1, E))]
+    tensors += [
         ('logit.weight', (V1, R)), ('logit.bias', (V1,)),
         ('core.i2h.weight', (5 * R, E)), ('core.i2h.bias', (5 * R,)),
         ('core.h2h.weight', (5 * R, R)), ('core.h2h.bias', (5 * R,)),
