@@ -40,6 +40,10 @@ typedef struct nes_fc_dims {
     int32_t layer_n;               /* 1: LayerNorm on i2h / h2h / c (captioning/nets.py:93-96); 2: the reference's "virtual batch norm",
                                       BatchNorm1d over the rows of the batch without running statistics (captioning/nets.py:87-91) */
     int32_t layer_n_affine;        /* elementwise affine parameters of either (layer_n_affine / vbn_affine) */
+    int32_t vbn_e;                 /* 1: batch norm over the rows of the batch on the outputs of img_embed and embed as well
+                                      (captioning/nets.py:156-165: Sequential(layer, BatchNorm1d(track_running_stats=False, affine=vbn_affine)));
+                                      vbn_e_affine (the reference's vbn_affine) adds img_embed.1.{weight,bias} and embed.1.{weight,bias} */
+    int32_t vbn_e_affine;
 } nes_fc_dims;
 
 /* precision of the population GEMMs */
@@ -57,7 +61,8 @@ const char* nes_last_error(void);
 int  nes_version(void);
 
 /* ---- context ------------------------------------------------------------------------------- */
-/* fc_caption context: flat-theta layout = FCModel.named_parameters() order (captioning/nets.py:150-153).
+/* fc_caption context: flat-theta layout = FCModel.named_parameters() order (captioning/nets.py:150-153; with vbn_e the
+ * Sequential wrappers put img_embed.1.* right behind img_embed.0.* and embed.1.* behind embed.0.weight).
  * table_len: number of fp16 elements of the shared noise table (multiple of 4).
  * n_parents: how many theta vectors the context holds (1 for NIC-NES; mu for NIC-ES).
  * wave_members / rows: capacity of the decode workspace (members evaluated per wave, rows per rollout). */

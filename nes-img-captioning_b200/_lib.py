@@ -12,7 +12,7 @@ c_i32, c_i64, c_u64, c_f32, c_f64, c_vp = (ctypes.c_int32, ctypes.c_int64, ctype
 
 class FcDims(ctypes.Structure):
     _fields_ = [('vocab_size', c_i32), ('input_encoding_size', c_i32), ('rnn_size', c_i32), ('fc_feat_size', c_i32),
-                ('seq_length', c_i32), ('layer_n', c_i32), ('layer_n_affine', c_i32)]
+                ('seq_length', c_i32), ('layer_n', c_i32), ('layer_n_affine', c_i32), ('vbn_e', c_i32), ('vbn_e_affine', c_i32)]
 
 
 # name -> (restype, argtypes); every symbol include/nes_b200.h declares

@@ -35,13 +35,15 @@ class NesContext:
                              seq_length=int(mo.get('seq_length') or 16), layer_n=int(bool(mo.get('layer_n'))),
                              layer_n_affine=int(bool(mo.get('layer_n_affine'))))
             if mo.get('vbn'):                      # LSTMCore: `if self.vbn ... elif self.layer_n` (captioning/nets.py:87-96)
-                assert not mo.get('vbn_e'), 'vbn_e (batch norm on the embeddings) is not on the B200 path'
                 self.dims.update(layer_n=2, layer_n_affine=int(bool(mo.get('vbn_affine'))))
+            # batch norm on the embeddings as well (captioning/nets.py:156-165); its affine flag is vbn_affine whatever the cell uses
+            self.dims.update(vbn_e=int(bool(mo.get('vbn_e'))), vbn_e_affine=int(bool(mo.get('vbn_e')) and bool(mo.get('vbn_affine'))))
             d = _lib.FcDims(**self.dims)
             self.G = granule(self.dims['input_encoding_size'], self.dims['rnn_size'], self.dims['fc_feat_size'])
             self.tensors, self.D, self.D_pad = build_layout(
                 fc_tensors(self.dims['vocab_size'], self.dims['input_encoding_size'], self.dims['rnn_size'],
-                           self.dims['fc_feat_size'], self.dims['layer_n'], self.dims['layer_n_affine']), self.G)
+                           self.dims['fc_feat_size'], self.dims['layer_n'], self.dims['layer_n_affine'],
+                           self.dims['vbn_e'], self.dims['vbn_e_affine']), self.G)
             self.table_len = self._default_table_len(table_len)
             _lib.check(self.lib.nes_ctx_create_fc(ctypes.byref(self._h), self.device, ctypes.byref(d), self.seed,
                                                   self.table_len, self.n_parents, int(wave_members), int(rows)))

@@ -116,9 +116,17 @@ int nes_ctx_create_fc(nes_ctx** out, int device, const nes_fc_dims* dims, uint64
     c->is_fc = true; c->dims = *dims;
     const int64_t V1 = dims->vocab_size + 1, E = dims->input_encoding_size, R = dims->rnn_size, Fd = dims->fc_feat_size;
     int64_t counts[kMaxTensors]; int32_t rws[kMaxTensors], cls[kMaxTensors]; int n = 0;
-    auto add = [&](int64_t r, int64_t cl) { counts[n] = r * cl; rws[n] = (int32_t)r; cls[n] = (int32_t)cl; ++n; };
-    add(E, Fd); add(E, 1); add(V1, E); add(V1, R); add(V1, 1); add(5 * R, E); add(5 * R, 1); add(5 * R, R); add(5 * R, 1);
-    if (dims->layer_n && dims->layer_n_affine) { add(5 * R, 1); add(5 * R, 1); add(5 * R, 1); add(5 * R, 1); add(R, 1); add(R, 1); }
+    for (int r = 0; r < T_ROLES; ++r) c->tix[r] = -1;
+    auto add = [&](int role, int64_t r, int64_t cl) { counts[n] = r * cl; rws[n] = (int32_t)r; cls[n] = (int32_t)cl; c->tix[role] = n; ++n; };
+    const bool ebn_affine = dims->vbn_e && dims->vbn_e_affine;
+    add(T_IMG_W, E, Fd); add(T_IMG_B, E, 1);
+    if (ebn_affine) { add(T_IMG_BN_W, E, 1); add(T_IMG_BN_B, E, 1); }
+    add(T_EMB_W, V1, E);
+    if (ebn_affine) { add(T_EMB_BN_W, E, 1); add(T_EMB_BN_B, E, 1); }
+    add(T_LOGIT_W, V1, R); add(T_LOGIT_B, V1, 1); add(T_I2H_W, 5 * R, E); add(T_I2H_B, 5 * R, 1); add(T_H2H_W, 5 * R, R); add(T_H2H_B, 5 * R, 1);
+    if (dims->layer_n && dims->layer_n_affine) {
+        add(T_I2H_LN_W, 5 * R, 1); add(T_I2H_LN_B, 5 * R, 1); add(T_H2H_LN_W, 5 * R, 1); add(T_H2H_LN_B, 5 * R, 1); add(T_C_LN_W, R, 1); add(T_C_LN_B, R, 1);
+    }
     build_layout(c->lay, counts, rws, cls, n, lcm64(lcm64(Fd, E), R));
     if (ctx_common_init(c, device, seed, table_len, n_parents)) { delete c; return 1; }
     if (wave_members > 0 && decode_create(c, wave_members, rows)) { nes_ctx_destroy(reinterpret_cast<nes_ctx*>(c)); return 1; }

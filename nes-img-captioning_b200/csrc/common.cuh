@@ -22,7 +22,7 @@ void set_error(const std::string& msg);
 
 // ---------------------------------------------------------------------------------------------
 // flat / padded layout of theta and of one noise row (spec: oracle/noise.py header)
-constexpr int kMaxTensors = 16;
+constexpr int kMaxTensors = 20;
 struct TensorDesc {
     int64_t start;   // flat start (elements)
     int64_t count;   // elements
@@ -35,9 +35,10 @@ struct Layout {
     TensorDesc t[kMaxTensors];
     int64_t D, D_pad, G;
 };
-// fc_caption tensor indices (FCModel.named_parameters() order)
+// fc_caption tensors by ROLE; Ctx::tix[role] is the tensor's position in the flat (named_parameters()) order, -1 if the model has none
 enum { T_IMG_W = 0, T_IMG_B, T_EMB_W, T_LOGIT_W, T_LOGIT_B, T_I2H_W, T_I2H_B, T_H2H_W, T_H2H_B,
-       T_I2H_LN_W, T_I2H_LN_B, T_H2H_LN_W, T_H2H_LN_B, T_C_LN_W, T_C_LN_B };
+       T_I2H_LN_W, T_I2H_LN_B, T_H2H_LN_W, T_H2H_LN_B, T_C_LN_W, T_C_LN_B,
+       T_IMG_BN_W, T_IMG_BN_B, T_EMB_BN_W, T_EMB_BN_B, T_ROLES };
 
 constexpr int kAbsBlocks = 296;
 // the perturbation of one parameter: f32(sigma) * eps, times the safe-mutation scale when one is set (algorithm/nets.py:101-111)
@@ -63,6 +64,7 @@ struct Ctx {
     bool is_fc = false;
     nes_fc_dims dims{};
     Layout lay{};
+    int tix[T_ROLES];                 // role -> index into lay.t (fc_caption contexts)
     uint64_t seed = 0;
     int64_t table_len = 0;
     int n_parents = 1;

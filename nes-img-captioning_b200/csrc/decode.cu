@@ -71,6 +71,7 @@ struct DecodeWorkspace {
     __half *h_hi[2] = {nullptr, nullptr}, *h_lo[2] = {nullptr, nullptr};
     float* c_state = nullptr;
     float *pre_i = nullptr, *pre_h = nullptr;               // LayerNorm path
+    float* x32 = nullptr; float* ebn_par = nullptr;         // vbn_e: the embedding before its batch norm [W * rows_pad, E]; member BN parameters [W][4E]
     LogitPartial* partials = nullptr;
     CandHead* heads = nullptr; CandEntry* entries = nullptr;                                       // HYBRID candidate lists
     // materialised member weights of the wave (dense.cuh): LSTM split fp16 per segment, vocabulary projection single fp16
@@ -139,6 +140,7 @@ struct FinalizeParams {
     int64_t* seq; float* lp;                     // wave-local [n_members, rows, T]
     const int64_t* forced;                       // nullable
     __half *x_hi, *x_lo;
+    float* x32;                                  // vbn_e: the gathered embedding as float32 instead (k_embed_bn normalises it)
     int gather;                                  // write x for the next step
 };
 // one warp per (member, row): merge the per-tile (max, argmax, sum-exp) partials, apply the
@@ -229,8 +231,47 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
             const float2 hf = __half22float2(hh[u]);
             hl[u] = __floats2half2_rn(__fsub_rn(x0, hf.x), __fsub_rn(x1, hf.y));
         }
+        if (p.x32) {                                 // x = (x * 2^5) / 2^5, exact
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                float n0 = __fmul_rn(ssig, __half22float2(eh[u]).x), n1 = __fmul_rn(ssig, __half22float2(eh[u]).y);
+                if (se) { n0 = apply_scale(n0, se[e + 2 * u], p.scale_div); n1 = apply_scale(n1, se[e + 2 * u + 1], p.scale_div); }
+                p.x32[grow * p.E + e + 2 * u] = __fmaf_rn(tv[2 * u], kActScale, n0) * (1.0f / kActScale);
+                p.x32[grow * p.E + e + 2 * u + 1] = __fmaf_rn(tv[2 * u + 1], kActScale, n1) * (1.0f / kActScale);
+            }
+            continue;
+        }
         *reinterpret_cast<uint4*>(p.x_hi + grow * p.E + e) = *reinterpret_cast<uint4*>(hh);
         *reinterpret_cast<uint4*>(p.x_lo + grow * p.E + e) = *reinterpret_cast<uint4*>(hl);
+    }
+}
+
+// vbn_e (captioning/nets.py:156-165): nn.BatchNorm1d(E, track_running_stats=False) on the output of img_embed / embed -- every feature
+// normalised by its mean and biased variance over the ROWS of the member's batch (eval mode too), then the member's affine pair.
+// grid (ceil(E / 32), members), 256 threads: lane = feature, warp = row subset; float32 in, split-fp16 GEMM operand out.
+struct EmbedBnParams { const float* x32; __half *x_hi, *x_lo; const float* par; int site; int rows, rows_pad, E; };
+__global__ void __launch_bounds__(256) k_embed_bn(const EmbedBnParams p) {
+    __shared__ float s_red[8][32];
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    const int64_t member = blockIdx.y;
+    const int j = blockIdx.x * 32 + lane;
+    const bool live = j < p.E;
+    const float* x = p.x32 + member * (int64_t)p.rows_pad * p.E;
+    const float inv_n = 1.0f / (float)p.rows;
+    auto reduce = [&](float v) { __syncthreads(); s_red[wq][lane] = v; __syncthreads(); float a = 0.f; for (int w = 0; w < 8; ++w) a += s_red[w][lane]; return a; };
+    float acc = 0.f;
+    if (live) for (int r = wq; r < p.rows; r += 8) acc += x[(int64_t)r * p.E + j];
+    const float mean = reduce(acc) * inv_n;
+    acc = 0.f;
+    if (live) for (int r = wq; r < p.rows; r += 8) { const float d = x[(int64_t)r * p.E + j] - mean; acc = fmaf(d, d, acc); }
+    const float rstd = 1.0f / sqrtf(reduce(acc) * inv_n + 1e-5f);
+    const float w = (p.par && live) ? p.par[member * 4 * p.E + (2 * p.site) * p.E + j] : 1.f;
+    const float b = (p.par && live) ? p.par[member * 4 * p.E + (2 * p.site + 1) * p.E + j] : 0.f;
+    if (live) for (int r = wq; r < p.rows; r += 8) {
+        const float y = (x[(int64_t)r * p.E + j] - mean) * rstd * w + b;
+        __half hi, lo; split_half_dev(y, kActScale, hi, lo);
+        const int64_t o = (member * p.rows_pad + r) * (int64_t)p.E + j;
+        p.x_hi[o] = hi; p.x_lo[o] = lo;
     }
 }
 
@@ -490,6 +531,7 @@ int decode_create(Ctx* c, int wave_members, int rows) {
     NES_CUDA(cudaMemsetAsync(ws->stats, 0, 32, c->stream));
     if (dmalloc(&ws->unfinished, WR) || dmalloc(&ws->unf_count, (int64_t)(ws->T + 2) * ws->W)) return 1;
     if (d.layer_n) { if (dmalloc(&ws->pre_i, WR * 5 * ws->R) || dmalloc(&ws->pre_h, WR * 5 * ws->R)) return 1; }
+    if (d.vbn_e) { if (dmalloc(&ws->x32, WR * ws->E) || (d.vbn_e_affine && dmalloc(&ws->ebn_par, (int64_t)ws->W * 4 * ws->E))) return 1; }
     // zero everything once: padding rows of the operand buffers must stay finite forever
     NES_CUDA(cudaMemsetAsync(ws->x_hi, 0, sizeof(__half) * WR * ws->E, c->stream));
     NES_CUDA(cudaMemsetAsync(ws->x_lo, 0, sizeof(__half) * WR * ws->E, c->stream));
@@ -505,7 +547,7 @@ void decode_destroy(Ctx* c) {
     DecodeWorkspace* ws = c->ws;
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
-                    ws->pre_i, ws->pre_h, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
+                    ws->pre_i, ws->pre_h, ws->x32, ws->ebn_par, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
                     ws->d_lp, ws->d_forced, ws->d_uniforms, ws->samp_logits};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
@@ -604,14 +646,14 @@ static int launch_lstm_pair(Ctx* c, DenseParams& p, int64_t n_members) {
 }
 
 // member weights of one wave, materialised once per rollout (dense.cuh)
-static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit, bool img, bool ln, bool ln_par) {
+static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit, bool img, bool ln, bool ln_par, bool ebn_par) {
     DecodeWorkspace* ws = c->ws;
     const Layout& L = c->lay;
     ProfScope prof(c, PROF_MATERIALISE);
     auto mat = [&](int wt, int K, int out_rows, int mode, int src_rows, __half* hi, __half* lo) {
         MatParams q{};
         q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32; q.scale_div = c->scale_div;
-        q.w_start = L.t[wt].start; q.w_pstart = L.t[wt].pstart; q.K = K; q.out_rows = out_rows; q.mode = mode; q.R = ws->R; q.src_rows = src_rows;
+        q.w_start = L.t[c->tix[wt]].start; q.w_pstart = L.t[c->tix[wt]].pstart; q.K = K; q.out_rows = out_rows; q.mode = mode; q.R = ws->R; q.src_rows = src_rows;
         q.sigma = sigma; q.hi = hi; q.lo = lo; q.n_members = nm;
         const int64_t groups = (nm + kMatGroup - 1) / kMatGroup;
         const dim3 grid((unsigned)((out_rows + kMatRowsPerBlock - 1) / kMatRowsPerBlock), (unsigned)(groups < 32768 ? groups : 32768));
@@ -623,8 +665,8 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         MatBiasParams q{};
         q.out_stride = out_stride; q.out_off = out_off;
         q.off = off; q.sign = sign; q.parent = parent; q.theta32 = c->theta32; q.table = c->table; q.D = L.D; q.scale = c->scale32; q.scale_div = c->scale_div;
-        q.b_start[0] = L.t[b0].start; q.b_pstart[0] = L.t[b0].pstart; q.nb = 1;
-        if (b1 >= 0) { q.b_start[1] = L.t[b1].start; q.b_pstart[1] = L.t[b1].pstart; q.nb = 2; }
+        q.b_start[0] = L.t[c->tix[b0]].start; q.b_pstart[0] = L.t[c->tix[b0]].pstart; q.nb = 1;
+        if (b1 >= 0) { q.b_start[1] = L.t[c->tix[b1]].start; q.b_pstart[1] = L.t[c->tix[b1]].pstart; q.nb = 2; }
         q.out_cols = out_cols; q.mode = mode; q.R = ws->R; q.src_n = src_n; q.sigma = sigma; q.out = out; q.n_members = nm;
         k_materialise_bias<<<148 * 4, 256, 0, c->stream>>>(q);
         c->launches++;
@@ -647,6 +689,10 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         const int64_t st = 22ll * ws->R;
         for (int i = 0; i < 4; ++i) matb(T_I2H_LN_W + i, -1, N5, 0, N5, ws->ln_par, st, (int64_t)i * N5);
         for (int i = 0; i < 2; ++i) matb(T_C_LN_W + i, -1, ws->R, 0, ws->R, ws->ln_par, st, 4ll * N5 + (int64_t)i * ws->R);
+    }
+    if (ebn_par) {       // member affine pairs of the two embedding batch norms (vbn_e): img_embed.1.{weight,bias}, embed.1.{weight,bias}
+        const int roles[4] = {T_IMG_BN_W, T_IMG_BN_B, T_EMB_BN_W, T_EMB_BN_B};
+        for (int i = 0; i < 4; ++i) matb(roles[i], -1, ws->E, 0, ws->E, ws->ebn_par, 4ll * ws->E, (int64_t)i * ws->E);
     }
     if (img) {
         mat(T_IMG_W, ws->Fd, ws->E, 0, ws->E, ws->wi_hi, ws->wi_lo);
@@ -671,9 +717,9 @@ static int fill_seg(Ctx* c, GemmParams& p, int s, const __half* a_hi, const __ha
     if (get_map(ws, &p.maps[s].w_hi, c->theta_hi, th_rows, K, box_rows, bk, n_chunks, chunk_stride) ||
         get_map(ws, &p.maps[s].w_lo, c->theta_lo, th_rows, K, box_rows, bk, n_chunks, chunk_stride)) return 1;
     if (get_map(ws, &p.maps[s].eps, c->table, c->table_len / K, K, box_rows, bk, n_chunks, chunk_stride)) return 1;
-    p.seg[s].K = K; p.seg[s].a_shared = a_shared; p.seg[s].w_pstart = L.t[wt].pstart;
-    p.seg[s].b_start = bt >= 0 ? L.t[bt].start : -1;
-    p.seg[s].b_pstart = bt >= 0 ? L.t[bt].pstart : -1;
+    p.seg[s].K = K; p.seg[s].a_shared = a_shared; p.seg[s].w_pstart = L.t[c->tix[wt]].pstart;
+    p.seg[s].b_start = bt >= 0 ? L.t[c->tix[bt]].start : -1;
+    p.seg[s].b_pstart = bt >= 0 ? L.t[c->tix[bt]].pstart : -1;
     return 0;
 }
 
@@ -779,7 +825,18 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
         NES_CUDA(cudaMemsetAsync(ws->h_lo[0], 0, sizeof(__half) * WR * R, c->stream));
         NES_CUDA(cudaMemsetAsync(ws->unf_count, 0, sizeof(int32_t) * (T + 2) * ws->W, c->stream));
         const bool ln_par = c->dims.layer_n && c->dims.layer_n_affine;
-        if ((dense_lstm || hybrid || dense_ln || ln_par) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid, scaled, dense_ln, ln_par)) return 1;
+        const bool vbn_e = c->dims.vbn_e != 0, ebn_par = vbn_e && c->dims.vbn_e_affine;
+        if ((dense_lstm || hybrid || dense_ln || ln_par || ebn_par) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid, scaled, dense_ln, ln_par, ebn_par)) return 1;
+        auto embed_bn = [&](int site) -> int {          // batch norm of the embedding the wave just produced (vbn_e)
+            EmbedBnParams q{};
+            q.x32 = ws->x32; q.x_hi = ws->x_hi; q.x_lo = ws->x_lo; q.par = ebn_par ? ws->ebn_par : nullptr; q.site = site;
+            q.rows = rows; q.rows_pad = rows_pad; q.E = E;
+            ProfScope prof(c, PROF_FINALIZE);
+            k_embed_bn<<<dim3((unsigned)((E + 31) / 32), (unsigned)nm), 256, 0, c->stream>>>(q);
+            c->launches++;
+            NES_CUDA(cudaGetLastError());
+            return 0;
+        };
 
         GemmParams base{};
         base.rows = rows; base.rows_pad = rows_pad; base.m_tiles = m_tiles;
@@ -800,15 +857,16 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             p.K[0] = Fd; p.K[1] = 0; p.nseg = 1; p.a_shared = shared_batch ? 1 : 0;
             p.rows = rows; p.rows_pad = rows_pad; p.m_tiles = m_tiles; p.n_tiles = (E + 255) / 256; p.N = E;
             p.b_rows = E; p.bias = ws->wi_bias; p.bias_stride = E;
-            p.out_hi = ws->x_hi; p.out_lo = ws->x_lo;
+            if (vbn_e) { p.out_f32 = ws->x32; p.ld_out = E; } else { p.out_hi = ws->x_hi; p.out_lo = ws->x_lo; }
             if (launch_dense<DEN_PLAIN>(c, p, nm)) return 1;
         } else {
             GemmParams p = base;
             p.nseg = 1; p.N = E; p.chunk_stride = 0; p.n_tiles = (E + 127) / 128;
             if (fill_seg(c, p, 0, ws->fc_hi, ws->fc_lo, ws->fc_members * ws->rows_pad, Fd, shared_batch ? 1 : 0, T_IMG_W, T_IMG_B, 128, precision)) return 1;
-            p.out_hi = ws->x_hi; p.out_lo = ws->x_lo;
+            if (vbn_e) { p.out_f32 = ws->x32; p.ld_out = E; } else { p.out_hi = ws->x_hi; p.out_lo = ws->x_lo; }
             if (launch_gemm_prec<EPI_PLAIN>(c, p, nm, precision)) return 1;
         }
+        if (vbn_e && embed_bn(0)) return 1;
         int hb = 0;   // h buffer holding the current state
         for (int t = 0; t <= T; ++t) {
             // ---- (h, c) = core(x_t, (h, c))
@@ -900,7 +958,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     rf.heads = ws->heads; rf.entries = ws->entries; rf.margin = ws->margin; rf.h_hi = ws->h_hi[hb]; rf.h_lo = ws->h_lo[hb]; rf.R = R; rf.V1 = V1;
                     rf.rows = rows; rf.rows_pad = rows_pad; rf.m_tiles = m_tiles; rf.n_members = nm;
                     rf.off = base.off; rf.sign = base.sign; rf.parent = base.parent; rf.theta32 = c->theta32; rf.table = c->table; rf.D = L.D; rf.scale = c->scale32; rf.scale_div = c->scale_div;
-                    rf.w_start = L.t[T_LOGIT_W].start; rf.w_pstart = L.t[T_LOGIT_W].pstart; rf.b_start = L.t[T_LOGIT_B].start; rf.b_pstart = L.t[T_LOGIT_B].pstart;
+                    rf.w_start = L.t[c->tix[T_LOGIT_W]].start; rf.w_pstart = L.t[c->tix[T_LOGIT_W]].pstart; rf.b_start = L.t[c->tix[T_LOGIT_B]].start; rf.b_pstart = L.t[c->tix[T_LOGIT_B]].pstart;
                     rf.sigma = sigma; rf.tok = ws->pre_tok; rf.lp = ws->pre_lp; rf.unit_flag = ws->unit_flag; rf.stats = c->profiling ? ws->stats : nullptr;
                     rf.force_overflow = (env_debug() & 64) ? 1 : 0;
                     { ProfScope prof(c, PROF_FINALIZE);
@@ -934,17 +992,18 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 FinalizeParams f{};
                 f.partials = ws->partials; f.n_tiles = 2; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
                 f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table; f.scale = c->scale32; f.scale_div = c->scale_div;
-                f.D = L.D; f.emb_start = L.t[T_EMB_W].start; f.emb_pstart = L.t[T_EMB_W].pstart; f.sigma = sigma;
+                f.D = L.D; f.emb_start = L.t[c->tix[T_EMB_W]].start; f.emb_pstart = L.t[c->tix[T_EMB_W]].pstart; f.sigma = sigma;
                 f.unfinished = ws->unfinished; f.unf_count = ws->unf_count; f.W = ws->W;
                 f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;
                 f.forced = forced ? ws->d_forced + m0 * rows * T : nullptr;
-                f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0;
+                f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0; f.x32 = vbn_e ? ws->x32 : nullptr;
                 if (sampling && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = 1; }
                 if (hybrid && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = scaled ? 1 : 0; }
                 ProfScope prof(c, PROF_FINALIZE);
                 k_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(f);
                 c->launches++;
                 NES_CUDA(cudaGetLastError());
+                if (vbn_e && f.gather && embed_bn(1)) return 1;
             }
         }
     }
@@ -959,7 +1018,7 @@ int launch_bound_norms(Ctx* c, int parent) {
     const int R = c->dims.rnn_size, V1 = c->dims.vocab_size + 1;
     if (parent >= 0) {
         NES_CUDA(cudaMemsetAsync(c->d_theta_rowmax + parent, 0, sizeof(float), c->stream));
-        k_rowmax_theta<<<148, 256, 0, c->stream>>>(c->theta32 + (int64_t)parent * c->lay.D + c->lay.t[T_LOGIT_W].start, V1, R, c->d_theta_rowmax + parent);
+        k_rowmax_theta<<<148, 256, 0, c->stream>>>(c->theta32 + (int64_t)parent * c->lay.D + c->lay.t[c->tix[T_LOGIT_W]].start, V1, R, c->d_theta_rowmax + parent);
     } else {
         NES_CUDA(cudaMemsetAsync(c->d_eps_rowmax, 0, sizeof(float), c->stream));
         k_rowmax_eps<<<148 * 8, 256, 0, c->stream>>>(c->table, c->table_len / R, R, c->d_eps_rowmax);
@@ -976,7 +1035,7 @@ int launch_bound_norms_batch(Ctx* c, const int32_t* parents, int n) {
     const int R = c->dims.rnn_size, V1 = c->dims.vocab_size + 1;
     (void)parents;
     k_zero_slots<<<(n + 255) / 256, 256, 0, c->stream>>>(c->d_ranks, n, c->d_theta_rowmax);
-    k_rowmax_theta_batch<<<dim3(37, n), 256, 0, c->stream>>>(c->theta32, c->lay.D, c->lay.t[T_LOGIT_W].start, V1, R, c->d_ranks, c->d_theta_rowmax);
+    k_rowmax_theta_batch<<<dim3(37, n), 256, 0, c->stream>>>(c->theta32, c->lay.D, c->lay.t[c->tix[T_LOGIT_W]].start, V1, R, c->d_ranks, c->d_theta_rowmax);
     c->launches++;
     NES_CUDA(cudaGetLastError());
     return 0;

@@ -11,13 +11,21 @@ import numpy as np
 TensorSpec = namedtuple('TensorSpec', ['name', 'shape', 'start', 'count', 'pstart'])
 
 
-def fc_tensors(vocab_size, input_encoding_size, rnn_size, fc_feat_size, layer_n=False, layer_n_affine=False):
-    """layer_n: 0 none, 1 LayerNorm (core.*_ln), 2 batch norm over the rows = the reference's vbn (core.*_bn)"""
+def fc_tensors(vocab_size, input_encoding_size, rnn_size, fc_feat_size, layer_n=False, layer_n_affine=False, vbn_e=False, vbn_e_affine=False):
+    """layer_n: 0 none, 1 LayerNorm (core.*_ln), 2 batch norm over the rows = the reference's vbn (core.*_bn).  vbn_e: img_embed and
+    embed are Sequential(layer, BatchNorm1d) in the reference (captioning/nets.py:156-165), which renames their parameters to
+    `<layer>.0.*` and, with vbn_affine, puts `<layer>.1.weight / bias` right behind them"""
     V1, E, R, Fd = vocab_size + 1, input_encoding_size, rnn_size, fc_feat_size
-    t = [('img_embed.weight', (E, Fd)), ('img_embed.bias', (E,)), ('embed.weight', (V1, E)),
-         ('logit.weight', (V1, R)), ('logit.bias', (V1,)),
-         ('core.i2h.weight', (5 * R, E)), ('core.i2h.bias', (5 * R,)),
-         ('core.h2h.weight', (5 * R, R)), ('core.h2h.bias', (5 * R,))]
+    if vbn_e:
+        t = [('img_embed.0.weight', (E, Fd)), ('img_embed.0.bias', (E,))]
+        t += [('img_embed.1.weight', (E,)), ('img_embed.1.bias', (E,))] if vbn_e_affine else []
+        t += [('embed.0.weight', (V1, E))]
+        t += [('embed.1.weight', (E,)), ('embed.1.bias', (E,))] if vbn_e_affine else []
+    else:
+        t = [('img_embed.weight', (E, Fd)), ('img_embed.bias', (E,)), ('embed.weight', (V1, E))]
+    t += [('logit.weight', (V1, R)), ('logit.bias', (V1,)),
+          ('core.i2h.weight', (5 * R, E)), ('core.i2h.bias', (5 * R,)),
+          ('core.h2h.weight', (5 * R, R)), ('core.h2h.bias', (5 * R,))]
     if layer_n and layer_n_affine:
         k = 'bn' if int(layer_n) == 2 else 'ln'
         t += [('core.i2h_%s.weight' % k, (5 * R,)), ('core.i2h_%s.bias' % k, (5 * R,)),
@@ -60,7 +68,7 @@ def fresh_model_vectors(tensors):
     blank, std = np.zeros(D, dtype=np.float32), np.zeros(D, dtype=np.float32)
     for t in tensors:
         sl = slice(t.start, t.start + t.count)
-        if 'bn' in t.name or 'ln' in t.name:
+        if 'bn' in t.name or 'ln' in t.name or t.name.startswith(('img_embed.1.', 'embed.1.')):
             if t.name.endswith('weight'):
                 blank[sl] = 1.0
         elif '1' in t.name:

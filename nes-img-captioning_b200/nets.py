@@ -149,7 +149,7 @@ class FCModel(PolicyNet):
         gen.manual_seed(int(rng_state) if rng_state is not None else torch.seed() % (1 << 31))
         flat = torch.zeros(self.ctx.D, dtype=torch.float32)
         for t in self.ctx.tensors:
-            if 'ln' in t.name or 'bn' in t.name:
+            if 'ln' in t.name or 'bn' in t.name or '1' in t.name:      # algorithm/nets.py:62-64: skipped, torch's default 1 / 0
                 if t.name.endswith('weight'):
                     flat[t.start:t.start + t.count] = 1.0
             elif t.name.endswith('weight'):

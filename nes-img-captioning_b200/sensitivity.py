@@ -66,11 +66,16 @@ def forward_for_sensitivity(theta, tensors, dims, fc_feats, orig_bs=0, i=-1, spl
     B, R = fc.size(0), dims['rnn_size']
     h = fc.new_zeros(B, R)
     c = fc.new_zeros(B, R)
-    h, c = _core(p, dims, F.linear(fc, p['img_embed.weight'], p['img_embed.bias']), h, c)
+    vbn_e = bool(dims.get('vbn_e'))                   # Sequential(layer, BatchNorm1d) on both embeddings (captioning/nets.py:156-165)
+    n0 = '.0' if vbn_e else ''
+
+    def bn(x, layer):
+        return F.batch_norm(x, None, None, p.get(layer + '.1.weight'), p.get(layer + '.1.bias'), True, 0.1, 1e-5) if vbn_e else x
+    h, c = _core(p, dims, bn(F.linear(fc, p['img_embed%s.weight' % n0], p['img_embed%s.bias' % n0]), 'img_embed'), h, c)
     it = torch.zeros(B, dtype=torch.long, device=fc.device)
     logprobs = None
     for _ in range(length):
-        h, c = _core(p, dims, F.embedding(it, p['embed.weight']), h, c)
+        h, c = _core(p, dims, bn(F.embedding(it, p['embed%s.weight' % n0]), 'embed'), h, c)
         logprobs = F.log_softmax(F.linear(h, p['logit.weight'], p['logit.bias']), dim=1)
         it = torch.max(logprobs.detach(), 1)[1].view(-1).long()
     cat_size = split - (logprobs.size(1) % split)

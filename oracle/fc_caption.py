@@ -75,6 +75,20 @@ def _bn(x, w, b):
     return F.batch_norm(x, None, None, w, b, True, 0.1, 1e-5)
 
 
+def img_embed(dims, p, fc):
+    """src/captioning/nets.py:150,156-165,195: Linear, followed by batch norm over the rows when vbn_e"""
+    if dims.vbn_e:
+        return _bn(F.linear(fc, p['img_embed.0.weight'], p['img_embed.0.bias']), p.get('img_embed.1.weight'), p.get('img_embed.1.bias'))
+    return F.linear(fc, p['img_embed.weight'], p['img_embed.bias'])
+
+
+def embed(dims, p, it):
+    """src/captioning/nets.py:151,156-165,199: Embedding, followed by batch norm over the rows when vbn_e"""
+    if dims.vbn_e:
+        return _bn(F.embedding(it, p['embed.0.weight']), p.get('embed.1.weight'), p.get('embed.1.bias'))
+    return F.embedding(it, p['embed.weight'])
+
+
 def lstm_core(dims, p, xt, h, c):
     """src/captioning/nets.py:98-134."""
     R = dims.rnn_size
@@ -119,11 +133,11 @@ def decode_greedy(dims, theta, fc_feats, trace=False):
         it = None
         for t in range(T + 1):
             if t == 0:
-                xt = F.linear(fc, p['img_embed.weight'], p['img_embed.bias'])
+                xt = img_embed(dims, p, fc)
             else:
                 if t == 1:
                     it = torch.zeros(B, dtype=torch.long)   # <bos>
-                xt = F.embedding(it, p['embed.weight'])
+                xt = embed(dims, p, it)
             h, c = lstm_core(dims, p, xt, h, c)
             if trace:
                 tr['x'].append(xt.numpy().copy()); tr['h'].append(h.numpy().copy()); tr['c'].append(c.numpy().copy())
@@ -178,11 +192,11 @@ def decode_sample(dims, theta, fc_feats, uniforms, forced=None):
         it = None
         for t in range(T + 1):
             if t == 0:
-                xt = F.linear(fc, p['img_embed.weight'], p['img_embed.bias'])
+                xt = img_embed(dims, p, fc)
             else:
                 if t == 1:
                     it = torch.zeros(B, dtype=torch.long)
-                xt = F.embedding(it, p['embed.weight'])
+                xt = embed(dims, p, it)
             h, c = lstm_core(dims, p, xt, h, c)
             if t == 0:
                 continue

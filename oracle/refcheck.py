@@ -11,16 +11,16 @@ import torch
 from . import _refimport, fc_caption, nes_math, noise
 
 
-def check_decode(ref, V, E, R, Fd, B, ln=False, affine=False, seed=0, vbn=False):
+def check_decode(ref, V, E, R, Fd, B, ln=False, affine=False, seed=0, vbn=False, vbn_e=False):
     opt = ref.ModelOptions(vocab_size=V, input_encoding_size=E, rnn_size=R, fc_feat_size=Fd,
-                           layer_n=ln, layer_n_affine=affine, vbn=vbn, vbn_e=False, vbn_affine=affine and vbn)
+                           layer_n=ln, layer_n_affine=affine and ln, vbn=vbn, vbn_e=vbn_e, vbn_affine=affine and (vbn or vbn_e))
     torch.manual_seed(seed)
     model = ref.FCModel(options=opt, vbn=vbn)
-    if vbn and affine:                       # the reference leaves BN at 1 / 0: give the affine parameters something to do
+    if (vbn or vbn_e) and affine:            # the reference leaves BN at 1 / 0: give the affine parameters something to do
         for n, p_ in model.named_parameters():
-            if 'bn' in n:
+            if 'bn' in n or '.1.' in n:
                 p_.data.add_(torch.randn(p_.shape) * 0.1)
-    dims = fc_caption.Dims(V, E, R, Fd, layer_n=ln, layer_n_affine=affine, vbn=vbn, vbn_affine=affine and vbn)
+    dims = fc_caption.Dims(V, E, R, Fd, layer_n=ln, layer_n_affine=affine and ln, vbn=vbn, vbn_affine=affine and (vbn or vbn_e), vbn_e=vbn_e)
     # layout: names, shapes and order must match named_parameters()
     got = [(n, tuple(p.shape)) for n, p in model.named_parameters()]
     want = [(n, tuple(s)) for n, s, _, _ in dims.layout()]
@@ -196,10 +196,13 @@ def check_grad_sensitivity(ref):
     pkg_sm = importlib.import_module('nes-img-captioning_b200.sensitivity')
     lay = importlib.import_module('nes-img-captioning_b200.layout')
     for cfg in [dict(V=199, E=64, R=64, Fd=128, ln=0, aff=0, vbn=0, uf=1e-4), dict(V=299, E=32, R=64, Fd=128, ln=1, aff=1, vbn=0, uf=0.01),
-                dict(V=230, E=32, R=32, Fd=64, ln=0, aff=1, vbn=1, uf=0.01), dict(V=230, E=32, R=32, Fd=64, ln=1, aff=0, vbn=0, uf=0.01)]:
+                dict(V=230, E=32, R=32, Fd=64, ln=0, aff=1, vbn=1, uf=0.01), dict(V=230, E=32, R=32, Fd=64, ln=1, aff=0, vbn=0, uf=0.01),
+                dict(V=230, E=32, R=32, Fd=64, ln=0, aff=0, vbn=0, uf=0.01, vbn_e=1, vaff=1), dict(V=230, E=32, R=32, Fd=64, ln=0, aff=1, vbn=1, uf=0.01, vbn_e=1, vaff=1)]:
+        vbn_e, vaff = bool(cfg.get('vbn_e')), bool(cfg.get('vaff'))
         opt = ref.ModelOptions(vocab_size=cfg['V'], input_encoding_size=cfg['E'], rnn_size=cfg['R'], fc_feat_size=cfg['Fd'],
                                safe_mutations='SM-G-SUM', safe_mutation_underflow=cfg['uf'], layer_n=bool(cfg['ln']),
-                               layer_n_affine=bool(cfg['aff'] and cfg['ln']), vbn=bool(cfg['vbn']), vbn_affine=bool(cfg['aff'] and cfg['vbn']))
+                               layer_n_affine=bool(cfg['aff'] and cfg['ln']), vbn=bool(cfg['vbn']), vbn_e=vbn_e,
+                               vbn_affine=bool(cfg['aff'] and cfg['vbn']) or vaff)
         torch.manual_seed(3)
         model = ref.FCModel(options=opt, vbn=bool(cfg['vbn']))
         theta = model.parameter_vector().detach().clone()
@@ -209,8 +212,8 @@ def check_grad_sensitivity(ref):
             want = model.get_sensitivity_vector().numpy().copy()
         torch.set_grad_enabled(False)                    # the reference leaves it off (safe_mutations.py:67)
         layer_n = 2 if cfg['vbn'] else cfg['ln']
-        dims = dict(vocab_size=cfg['V'], input_encoding_size=cfg['E'], rnn_size=cfg['R'], fc_feat_size=cfg['Fd'], layer_n=layer_n, layer_n_affine=cfg['aff'])
-        tensors, D, _ = lay.build_layout(lay.fc_tensors(cfg['V'], cfg['E'], cfg['R'], cfg['Fd'], layer_n, cfg['aff']), 64)
+        dims = dict(vocab_size=cfg['V'], input_encoding_size=cfg['E'], rnn_size=cfg['R'], fc_feat_size=cfg['Fd'], layer_n=layer_n, layer_n_affine=cfg['aff'], vbn_e=vbn_e)
+        tensors, D, _ = lay.build_layout(lay.fc_tensors(cfg['V'], cfg['E'], cfg['R'], cfg['Fd'], layer_n, cfg['aff'], vbn_e, vbn_e and vaff), 64)
         assert D == theta.numel()
         got = pkg_sm.sum_sensitivity(theta, tensors, dims, fc, 4)
         got[got < cfg['uf']] = cfg['uf']
@@ -255,6 +258,8 @@ def main():
                 dict(V=300, E=128, R=128, Fd=512, B=12, ln=True),
                 dict(V=300, E=128, R=128, Fd=512, B=12, ln=True, affine=True),
                 dict(V=300, E=128, R=128, Fd=512, B=12, vbn=True), dict(V=300, E=128, R=128, Fd=512, B=12, vbn=True, affine=True),
+                dict(V=300, E=128, R=128, Fd=512, B=12, vbn_e=True, affine=True), dict(V=300, E=64, R=64, Fd=128, B=9, vbn_e=True),
+                dict(V=300, E=128, R=128, Fd=512, B=12, vbn=True, vbn_e=True, affine=True), dict(V=300, E=64, R=64, Fd=128, B=9, ln=True, vbn_e=True, affine=True),
                 dict(V=9487, E=128, R=128, Fd=2048, B=4)]:
         check_decode(ref, **cfg); n += 1
     # the parameter-count checksum the reference states (src/algorithm/tools/utils.py:180)

@@ -64,6 +64,11 @@ def test_host_layout_equals_oracle_layout():
         assert (D, D_pad) == (D2, D_pad2)
         assert [(t.name, t.shape, t.start, t.count, t.pstart) for t in specs] == [tuple(x) for x in play]
     assert nes_b200.layout.build_layout(nes_b200.layout.fc_tensors(9487, 128, 128, 2048), 2048)[1] == 2865808   # tools/utils.py:180
+    # vbn_e: the Sequential wrappers rename and reorder the embedding tensors (captioning/nets.py:156-165)
+    for ln, aff, vbn, vaff in [(0, 0, False, True), (2, 1, True, True), (0, 0, False, False), (1, 1, False, True)]:
+        specs, D, D_pad = nes_b200.layout.build_layout(nes_b200.layout.fc_tensors(300, 64, 64, 128, ln, aff, True, vaff), 128)
+        play, D2, D_pad2 = noise.padded_layout(noise.flat_layout(300, 64, 64, 128, ln == 1, bool(aff) and ln == 1, vbn, vaff, True), 128)
+        assert (D, D_pad) == (D2, D_pad2) and [(t.name, t.start, t.pstart) for t in specs] == [(x[0], x[2], x[4]) for x in play]
 
 
 def test_shard_bounds_cover_the_population():

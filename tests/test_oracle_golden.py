@@ -126,3 +126,23 @@ def test_oracle_matches_reference_at_the_timed_shapes(name, members):
         s, lp = fc_caption.decode_greedy(dims, th, fc)
         assert np.array_equal(s, gold[name + '_seq'][i].astype(np.int64))
         assert np.allclose(lp, gold[name + '_logprobs'][i], rtol=2e-6, atol=2e-6)     # MKL's summation order follows the thread count
+
+
+@pytest.mark.parametrize('name', ['e1', 'e2', 'e3', 'e4'])
+def test_oracle_vbn_e_matches_reference_golden(name):
+    """batch norm on the embeddings (src/captioning/nets.py:156-165), with every cell variant, against the real reference's goldens"""
+    import os
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, 'golden'))
+    import make_golden_vbne as me
+    from oracle import fc_caption, noise
+    gold = np.load(os.path.join(here, 'golden', 'golden_vbne_v1.npz'))
+    c = me.CASES[name]
+    dims, G, play, D, D_pad, L, theta, fc, offs = me.case_inputs(c)
+    eps = noise.noise_row(me.TABLE_SEED, offs[0], play, D)
+    for j, sign in enumerate((+1, -1)):
+        th, _ = noise.member_theta(theta, eps, c['sigma'], sign)
+        s, lp = fc_caption.decode_greedy(dims, th, fc)
+        assert np.array_equal(s, gold[name + '_seq'][j].astype(np.int64))
+        assert np.allclose(lp, gold[name + '_logprobs'][j], rtol=2e-6, atol=2e-6)
