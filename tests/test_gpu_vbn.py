@@ -78,7 +78,7 @@ def test_vbn_hidden_states_teacher_forced(name):
 
 
 def test_vbn_through_the_policy_interface():
-    """policy_options.vbn (src/algorithm/policies.py:62-64) reaches the context; vbn_e is refused"""
+    """policy_options.vbn (src/algorithm/policies.py:62-64) and model_options.vbn_e reach the context"""
     import nes_b200
     exp = dict(policy_options=dict(net='fc_caption', fitness='greedy', vbn=True,
                                    model_options=dict(vocab_size=99, input_encoding_size=64, rnn_size=64, fc_feat_size=64, vbn_affine=True)))
@@ -90,8 +90,15 @@ def test_vbn_through_the_policy_interface():
     s, l = fc_caption.decode_greedy(dims, pol.parameter_vector().numpy(), fc)
     assert np.array_equal(seq.numpy(), s) and np.allclose(lp.numpy(), l, atol=1e-4)
     pol.ctx.close()
-    with pytest.raises(AssertionError):
-        nes_b200.NesContext(dict(vocab_size=99, input_encoding_size=64, rnn_size=64, fc_feat_size=64, vbn=True, vbn_e=True), table_len=1 << 20)
+    exp['policy_options']['model_options'].update(vbn_e=True)
+    pol = nes_b200.PolicyFactory.create(nes_b200.SuppDataset.MSCOCO, exp, seed=2, table_len=1 << 20, wave_members=2, rows=8)
+    assert pol.ctx.dims['vbn_e'] == 1 and [t.name for t in pol.ctx.tensors][:7] == [
+        'img_embed.0.weight', 'img_embed.0.bias', 'img_embed.1.weight', 'img_embed.1.bias', 'embed.0.weight', 'embed.1.weight', 'embed.1.bias']
+    seq, lp = pol.policy_net(torch.from_numpy(fc), greedy=True)
+    dims = fc_caption.Dims(99, 64, 64, 64, vbn=True, vbn_affine=True, vbn_e=True)
+    s, l = fc_caption.decode_greedy(dims, pol.parameter_vector().numpy(), fc)
+    assert np.array_equal(seq.numpy(), s) and np.allclose(lp.numpy(), l, atol=1e-4)
+    pol.ctx.close()
 
 
 @pytest.mark.parametrize('name', ['e1', 'e2', 'e3', 'e4'])
