@@ -337,7 +337,6 @@ int nes_rollout_sample(nes_ctx* ctx, int64_t n_members, const int64_t* offsets, 
     NES_CHECK(n_members >= 0, "negative member count");
     if (n_members == 0) return 0;
     NES_CHECK(offsets && signs && fc && uniforms, "null argument");
-    NES_CHECK(c->scale32 == nullptr, "sampled decode with a safe-mutation scale is not built");
     if (decode_rollout(c, n_members, offsets, signs, parents, fc, rows, shared_batch, sigma, NES_PREC_EXACT, nullptr, seq, logprobs, nullptr, nullptr, uniforms)) return 1;
     if (finish_output(c, seq) || finish_output(c, logprobs)) return 1;
     return 0;

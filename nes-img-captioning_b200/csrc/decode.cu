@@ -90,7 +90,8 @@ struct DecodeWorkspace {
     int64_t* d_seq = nullptr; float* d_lp = nullptr; int64_t out_cap = 0;
     int64_t* d_forced = nullptr; int64_t forced_cap = 0;
     double* d_uniforms = nullptr; int64_t uniforms_cap = 0;      // sampled decode: the caller's draws [n_members, rows, T]
-    float* samp_logits = nullptr;                                // sampled decode: all logits of one step of one wave [W * rows_cap, V1]
+    float* samp_logits = nullptr;                                // sampled decode: all logits of one step of one wave [W * rows_pad, round_up(V1, 4)]
+    __half* wv_lo = nullptr;                                     // sampled decode: low halves of the materialised logit.weight (split fp16)
     std::map<std::tuple<const void*, int64_t, int64_t, int, int, int, int64_t>, CUtensorMap> maps;
     bool attrs_set = false;
 };
@@ -277,7 +278,8 @@ __global__ void __launch_bounds__(256) k_embed_bn(const EmbedBnParams p) {
 
 struct SampleParams {
     const float* logits;                         // [n_members * rows, V1] of this step
-    const LogitPartial* partials; int n_tiles;
+    const LogitPartial* partials; int n_tiles;   // nullable: the row's max / sum-exp are then taken from the logits themselves
+    int64_t ld; int row_stride;                  // logits of (member, row) start at (member * row_stride + row) * ld
     const double* u;                             // [n_members, rows, T]
     int rows, rows_pad, T, t, V1; int64_t n_members;
     int32_t* tok; float* lp;                     // [n_members * rows_pad]
@@ -294,11 +296,27 @@ __global__ void __launch_bounds__(256) k_sample(const SampleParams p) {
     const int64_t member = blockIdx.x / p.rows;
     const int r = (int)(blockIdx.x % p.rows);
     const int64_t grow = member * p.rows_pad + r;
-    const float* lg = p.logits + (member * p.rows + r) * (int64_t)p.V1;
-    float mx = -INFINITY;
-    for (int j = 0; j < p.n_tiles; ++j) mx = fmaxf(mx, p.partials[grow * p.n_tiles + j].mx);
-    float se = 0.f;
-    for (int j = 0; j < p.n_tiles; ++j) { const LogitPartial q = p.partials[grow * p.n_tiles + j]; se += q.sum * expf(q.mx - mx); }
+    const float* lg = p.logits + (member * p.row_stride + r) * p.ld;
+    float mx = -INFINITY, se = 0.f;
+    if (p.partials) {
+        for (int j = 0; j < p.n_tiles; ++j) mx = fmaxf(mx, p.partials[grow * p.n_tiles + j].mx);
+        for (int j = 0; j < p.n_tiles; ++j) { const LogitPartial q = p.partials[grow * p.n_tiles + j]; se += q.sum * expf(q.mx - mx); }
+    } else {                                     // log_softmax(x) = (x - max) - log(sum exp(x - max)) (captioning/nets.py:202)
+        for (int j = tid; j < p.V1; j += 256) mx = fmaxf(mx, lg[j]);
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if (lane == 0) s_f[wq] = mx;
+        __syncthreads();
+        mx = s_f[0];
+        for (int w = 1; w < 8; ++w) mx = fmaxf(mx, s_f[w]);
+        __syncthreads();
+        for (int j = tid; j < p.V1; j += 256) se += expf(lg[j] - mx);
+        for (int o = 16; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+        if (lane == 0) s_f[wq] = se;
+        __syncthreads();
+        se = 0.f;
+        for (int w = 0; w < 8; ++w) se += s_f[w];
+        __syncthreads();
+    }
     const float lse = logf(se);
     float acc = 0.f;
     for (int j = tid; j < p.V1; j += 256) { const float e = expf(__fsub_rn(__fsub_rn(lg[j], mx), lse)); s_p[j] = e; acc += e; }
@@ -548,7 +566,7 @@ void decode_destroy(Ctx* c) {
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
                     ws->pre_i, ws->pre_h, ws->x32, ws->ebn_par, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
-                    ws->d_lp, ws->d_forced, ws->d_uniforms, ws->samp_logits};
+                    ws->d_lp, ws->d_forced, ws->d_uniforms, ws->samp_logits, ws->wv_lo};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
     c->ws = nullptr;
@@ -646,7 +664,7 @@ static int launch_lstm_pair(Ctx* c, DenseParams& p, int64_t n_members) {
 }
 
 // member weights of one wave, materialised once per rollout (dense.cuh)
-static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit, bool img, bool ln, bool ln_par, bool ebn_par) {
+static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float* sign, const int32_t* parent, float sigma, bool lstm, bool logit, bool img, bool ln, bool ln_par, bool ebn_par, bool logit_split = false) {
     DecodeWorkspace* ws = c->ws;
     const Layout& L = c->lay;
     ProfScope prof(c, PROF_MATERIALISE);
@@ -699,7 +717,7 @@ static int materialise_wave(Ctx* c, int64_t nm, const int64_t* off, const float*
         matb(T_IMG_B, -1, ws->E, 0, ws->E, ws->wi_bias);
     }
     if (logit) {
-        mat(T_LOGIT_W, ws->R, ws->V1, 0, ws->V1, ws->wv16, nullptr);
+        mat(T_LOGIT_W, ws->R, ws->V1, 0, ws->V1, ws->wv16, logit_split ? ws->wv_lo : nullptr);
         matb(T_LOGIT_B, -1, ws->V1, 0, ws->V1, ws->wv_bias);
     }
     NES_CUDA(cudaGetLastError());
@@ -762,8 +780,10 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
     const bool dense_lstm = ws->dense_lstm && precision == NES_PREC_EXACT;     // split-fp16 LSTM on materialised member weights
     const bool dense_ln = ws->dense_ln && precision == NES_PREC_EXACT;         // LayerNorm cell on dense pre-activation GEMMs
     const bool scaled = c->scale32 != nullptr;                                 // safe-mutation scale: every member weight is materialised
+    // sampled decode needs every accurate logit: split-fp16 projection on the materialised logit.weight (hi + lo), float32 logits out
+    const bool samp_dense = sampling && ws->dense_logit && (dense_lstm || dense_ln);
     if (scaled) {
-        NES_CHECK(hybrid && (dense_lstm || dense_ln), "a safe-mutation scale needs HYBRID precision on the dense kernels (no logit trace, R <= 512)");
+        NES_CHECK((hybrid || samp_dense) && (dense_lstm || dense_ln), "a safe-mutation scale needs HYBRID precision on the dense kernels (no logit trace, R <= 512)");
         if (!ws->wi_hi) {
             if (dmalloc(&ws->wi_hi, (int64_t)ws->W * ws->E * ws->Fd) || dmalloc(&ws->wi_lo, (int64_t)ws->W * ws->E * ws->Fd) || dmalloc(&ws->wi_bias, (int64_t)ws->W * ws->E)) return 1;
         }
@@ -789,7 +809,8 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             ws->uniforms_cap = un;
         }
         NES_CUDA(cudaMemcpyAsync(ws->d_uniforms, uniforms, sizeof(double) * un, cudaMemcpyDefault, c->stream));
-        if (!ws->samp_logits && dmalloc(&ws->samp_logits, (int64_t)ws->W * ws->rows_cap * V1)) return 1;
+        if (!ws->samp_logits && dmalloc(&ws->samp_logits, (int64_t)ws->W * ws->rows_pad * ((V1 + 3) / 4 * 4))) return 1;
+        if (samp_dense && !ws->wv_lo && dmalloc(&ws->wv_lo, (int64_t)ws->W * V1 * ws->R)) return 1;
     }
     NES_CUDA(cudaMemsetAsync(ws->d_seq, 0, sizeof(int64_t) * n_members * rows * T, c->stream));
     NES_CUDA(cudaMemsetAsync(ws->d_lp, 0, sizeof(float) * n_members * rows * T, c->stream));
@@ -826,7 +847,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
         NES_CUDA(cudaMemsetAsync(ws->unf_count, 0, sizeof(int32_t) * (T + 2) * ws->W, c->stream));
         const bool ln_par = c->dims.layer_n && c->dims.layer_n_affine;
         const bool vbn_e = c->dims.vbn_e != 0, ebn_par = vbn_e && c->dims.vbn_e_affine;
-        if ((dense_lstm || hybrid || dense_ln || ln_par || ebn_par) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid, scaled, dense_ln, ln_par, ebn_par)) return 1;
+        if ((dense_lstm || hybrid || samp_dense || dense_ln || ln_par || ebn_par) && materialise_wave(c, nm, ws->d_off + m0, ws->d_sign + m0, ws->d_parent + m0, sigma, dense_lstm, hybrid || samp_dense, scaled, dense_ln, ln_par, ebn_par, samp_dense)) return 1;
         auto embed_bn = [&](int site) -> int {          // batch norm of the embedding the wave just produced (vbn_e)
             EmbedBnParams q{};
             q.x32 = ws->x32; q.x_hi = ws->x_hi; q.x_lo = ws->x_lo; q.par = ebn_par ? ws->ebn_par : nullptr; q.site = site;
@@ -971,7 +992,20 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                         NES_CUDA(cudaGetLastError());
                     }
                 }
-                if (!(hybrid && scaled)) {
+                const int64_t samp_ld = (V1 + 3) / 4 * 4;
+                if (samp_dense) {
+                    DenseParams pd{};
+                    const int bk = DenseCfg<DEN_PLAIN>::BK;
+                    if (get_map(ws, &pd.a_hi[0], ws->h_hi[hb], a_rows_w, R, 128, bk) || get_map(ws, &pd.a_lo[0], ws->h_lo[hb], a_rows_w, R, 128, bk) ||
+                        get_map(ws, &pd.b_hi[0], ws->wv16, (int64_t)ws->W * V1, R, 256, bk) || get_map(ws, &pd.b_lo[0], ws->wv_lo, (int64_t)ws->W * V1, R, 256, bk)) return 1;
+                    pd.a_hi[1] = pd.a_hi[0]; pd.a_lo[1] = pd.a_lo[0]; pd.b_hi[1] = pd.b_hi[0]; pd.b_lo[1] = pd.b_lo[0];
+                    pd.K[0] = R; pd.K[1] = 0; pd.nseg = 1; pd.a_shared = 0;
+                    pd.rows = rows; pd.rows_pad = rows_pad; pd.m_tiles = m_tiles; pd.n_tiles = (V1 + 255) / 256; pd.N = V1;
+                    pd.b_rows = V1; pd.bias = ws->wv_bias; pd.bias_stride = V1;
+                    pd.out_f32 = ws->samp_logits; pd.ld_out = (int32_t)samp_ld;
+                    if (launch_dense<DEN_PLAIN>(c, pd, nm)) return 1;
+                }
+                if (!(hybrid && scaled) && !samp_dense) {
                 if (fill_seg(c, p, 0, ws->h_hi[hb], ws->h_lo[hb], a_rows_w, R, 0, T_LOGIT_W, T_LOGIT_B, 128, precision)) return 1;
                 p.logit_trace = logit_trace ? logit_trace + (int64_t)(t - 1) * n_members * rows * V1 : nullptr; p.ld_trace = V1;
                 if (sampling) p.logit_trace = ws->samp_logits;
@@ -979,7 +1013,8 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 }
                 if (sampling) {
                     SampleParams sp{};
-                    sp.logits = ws->samp_logits; sp.partials = ws->partials; sp.n_tiles = 2; sp.u = ws->d_uniforms + m0 * rows * T;
+                    sp.logits = ws->samp_logits; sp.partials = samp_dense ? nullptr : ws->partials; sp.n_tiles = 2; sp.u = ws->d_uniforms + m0 * rows * T;
+                    sp.ld = samp_dense ? samp_ld : V1; sp.row_stride = samp_dense ? rows_pad : rows;
                     sp.rows = rows; sp.rows_pad = rows_pad; sp.T = T; sp.t = t; sp.V1 = V1; sp.n_members = nm; sp.tok = ws->pre_tok; sp.lp = ws->pre_lp;
                     const size_t smem = sizeof(float) * V1;
                     if (smem > 48 * 1024) { static size_t set_to = 0; if (set_to < smem) { NES_CUDA(cudaFuncSetAttribute(k_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set_to = smem; } }

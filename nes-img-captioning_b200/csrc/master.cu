@@ -2,6 +2,7 @@
 // K8 (fused L2 + SGD/Adam update).  Reference: algorithm/nic_nes/nic_nes_master.py:123-136,170-221
 // and algorithm/nic_nes/optimizers.py:15-22,44-47,78-83.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace nes {
 
@@ -59,7 +60,8 @@ int launch_rank_weights(Ctx* c, const double* d_fit, int64_t F, double* d_center
 // ---- K7 -----------------------------------------------------------------------------------------
 // g[p] = f32(sigma) * (sum_i w_i * eps_i[p]) / (2F), eps_i = table[off_i + pstart_k + (p - start_k)].
 // HBM-bound: reads F * D * 2 bytes (fp16 table) once, writes 4*D.  One thread owns 8 consecutive
-// elements (one 128-bit load per row); the row loop is unrolled so 8 independent loads are in flight.
+// elements (one 128-bit load per row); the row loop is unrolled so 16 independent loads are in flight per thread (measured on B200,
+// tools/k7_sweep.py: 8 -> 16 loads +7 %, 32 no further gain; the block size does not matter).
 struct GradPlan { int n; int64_t vec_prefix[kMaxTensors + 1]; };
 
 __device__ __forceinline__ uint4 ld_stream_128(const void* p) {
@@ -79,7 +81,7 @@ __device__ __forceinline__ void fma8(float (&acc)[8], const uint4& v, float w) {
 
 constexpr int kGradChunk = 512;
 template <int UNROLL>
-__global__ void __launch_bounds__(256) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
+__global__ void __launch_bounds__(512) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
                                                   const float* __restrict__ w, int64_t F, GradPlan plan,
                                                   const Layout* __restrict__ lay, float sigma, float* __restrict__ g, int64_t v_lo, int64_t v_hi) {
     __shared__ int64_t s_off[kGradChunk];
@@ -133,12 +135,18 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
     // multi-GPU: the parameter axis is cut into n_shards runs of whole CTAs; every element is summed over all F rows by one rank in the
     // single-GPU order, the other ranks hold zeros, so the all-reduce that follows reproduces the single-GPU vector bit for bit
     NES_CHECK(n_shards >= 1 && shard >= 0 && shard < n_shards, "bad gradient shard");
-    const int64_t blocks = (total + 255) / 256, per = (blocks + n_shards - 1) / n_shards;
-    const int64_t v_lo = std::min(total, (int64_t)shard * per * 256), v_hi = std::min(total, v_lo + per * 256);
+    static int kb = 0, ku = 0;                 // experiment switches: block size / rows in flight per thread
+    if (!kb) { const char* e = getenv("NES_K7_BLOCK"); kb = e ? atoi(e) : 256; if (kb != 128 && kb != 256 && kb != 512) kb = 256;
+               const char* u = getenv("NES_K7_UNROLL"); ku = u ? atoi(u) : 16; }
+    const int64_t blocks = (total + kb - 1) / kb, per = (blocks + n_shards - 1) / n_shards;
+    const int64_t v_lo = std::min(total, (int64_t)shard * per * kb), v_hi = std::min(total, v_lo + per * kb);
     if (n_shards > 1) NES_CUDA(cudaMemsetAsync(d_g, 0, sizeof(float) * c->lay.D, c->stream));
-    unsigned grid = (unsigned)((v_hi - v_lo + 255) / 256);
+    unsigned grid = (unsigned)((v_hi - v_lo + kb - 1) / kb);
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_a, c->stream));
-    if (grid) k_gradient<8><<<grid, 256, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
+    if (grid && ku == 32) k_gradient<32><<<grid, kb, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
+    else if (grid && ku == 16) k_gradient<16><<<grid, kb, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
+    else if (grid && ku == 4) k_gradient<4><<<grid, kb, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
+    else if (grid) k_gradient<8><<<grid, kb, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
     if (c->scale32) { k_scale_vec<<<148 * 8, 256, 0, c->stream>>>(d_g, c->scale32, c->lay.D, c->scale_div); c->launches++; }
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_b, c->stream));
     c->launches++;
