@@ -521,7 +521,9 @@ def rooflines(prof, a, wave, rows, ms_total, peaks):
     ks = {}
     for name, key, flop, bytes_8d, bytes_design, dense, kern in (
             ('lstm', 'lstm', 2.0 * rows * (E + R) * 5 * R * wave, wave * 5.0 * R * (E + R) * 2, wave * (5.0 * R * (E + R) * 4 + rows * (E + R) * 4 + rows * R * 8), dense_lstm,
-             'k_member_dense<LSTM> (split-fp16 LSTM step on materialised member weights, fused maxout cell)' if dense_lstm else 'k_member_gemm<LSTM> (factored theta*x + sigma*eps*x, fused maxout cell)'),
+             ('k_lstm_pair (split-fp16 LSTM step on materialised member weights, clusters of 2 CTAs sharing the activation block by TMA multicast, fused maxout cell)'
+              if os.environ.get('NES_LSTM_PAIR', '1') != '0' else 'k_member_dense<LSTM> (split-fp16 LSTM step on materialised member weights, fused maxout cell)')
+             if dense_lstm else 'k_member_gemm<LSTM> (factored theta*x + sigma*eps*x, fused maxout cell)'),
             ('logit', 'logit', 2.0 * rows * R * (V + 1) * wave, wave * (V + 1.0) * R * 2, wave * ((V + 1.0) * R * 2 + rows * R * 2), dense_logit,
              'k_member_dense<LOGITC> (fp16 vocabulary projection, smem-resident x block, fused max / sum-exp / candidate lists)' if dense_logit else 'k_member_gemm<LOGIT> (factored vocabulary projection + fused argmax/log-prob)')):
         k = prof[key]

@@ -71,6 +71,7 @@ struct DecodeWorkspace {
     __half *h_hi[2] = {nullptr, nullptr}, *h_lo[2] = {nullptr, nullptr};
     float* c_state = nullptr;
     float *pre_i = nullptr, *pre_h = nullptr;               // LayerNorm path
+    float* y0 = nullptr; int64_t* pp_off = nullptr; float* pp_sign = nullptr; int32_t* pp_par = nullptr;   // img_embed theta term per parent slot (shared batch)
     float* x32 = nullptr; float* ebn_par = nullptr;         // vbn_e: the embedding before its batch norm [W * rows_pad, E]; member BN parameters [W][4E]
     LogitPartial* partials = nullptr;
     CandHead* heads = nullptr; CandEntry* entries = nullptr;                                       // HYBRID candidate lists
@@ -565,7 +566,7 @@ void decode_destroy(Ctx* c) {
     DecodeWorkspace* ws = c->ws;
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
-                    ws->pre_i, ws->pre_h, ws->x32, ws->ebn_par, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
+                    ws->pre_i, ws->pre_h, ws->x32, ws->ebn_par, ws->y0, ws->pp_off, ws->pp_sign, ws->pp_par, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
                     ws->d_lp, ws->d_forced, ws->d_uniforms, ws->samp_logits, ws->wv_lo};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
@@ -884,6 +885,27 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             GemmParams p = base;
             p.nseg = 1; p.N = E; p.chunk_stride = 0; p.n_tiles = (E + 127) / 128;
             if (fill_seg(c, p, 0, ws->fc_hi, ws->fc_lo, ws->fc_members * ws->rows_pad, Fd, shared_batch ? 1 : 0, T_IMG_W, T_IMG_B, 128, precision)) return 1;
+            if (shared_batch && precision == NES_PREC_EXACT) {
+                // every member sees the same features: x theta_p^T + theta_b once per parent slot (sigma = 0 pseudo members), then the
+                // members only add their sigma * x eps^T (2 of the 5 split-fp16 passes, no theta tiles through shared memory)
+                const int np = c->n_parents;
+                if (!ws->y0) {
+                    if (dmalloc(&ws->y0, (int64_t)np * ws->rows_pad * E) || dmalloc(&ws->pp_off, np) || dmalloc(&ws->pp_sign, np) || dmalloc(&ws->pp_par, np)) return 1;
+                    std::vector<float> ones(np, 1.0f); std::vector<int32_t> iota(np);
+                    for (int i = 0; i < np; ++i) iota[i] = i;
+                    NES_CUDA(cudaMemsetAsync(ws->pp_off, 0, sizeof(int64_t) * np, c->stream));
+                    NES_CUDA(cudaMemcpyAsync(ws->pp_sign, ones.data(), sizeof(float) * np, cudaMemcpyHostToDevice, c->stream));
+                    NES_CUDA(cudaMemcpyAsync(ws->pp_par, iota.data(), sizeof(int32_t) * np, cudaMemcpyHostToDevice, c->stream));
+                    NES_CUDA(cudaStreamSynchronize(c->stream));
+                }
+                if (m0 == 0) {
+                    GemmParams pt = p;
+                    pt.off = ws->pp_off; pt.sign = ws->pp_sign; pt.parent = ws->pp_par; pt.sigma = 0.f;
+                    pt.out_f32 = ws->y0; pt.ld_out = E; pt.out_hi = nullptr; pt.out_lo = nullptr; pt.y0 = nullptr;
+                    if (launch_gemm_prec<EPI_PLAIN>(c, pt, np, precision)) return 1;
+                }
+                p.y0 = ws->y0;
+            }
             if (vbn_e) { p.out_f32 = ws->x32; p.ld_out = E; } else { p.out_hi = ws->x_hi; p.out_lo = ws->x_lo; }
             if (launch_gemm_prec<EPI_PLAIN>(c, p, nm, precision)) return 1;
         }

@@ -81,7 +81,7 @@ __device__ __forceinline__ void fma8(float (&acc)[8], const uint4& v, float w) {
 
 constexpr int kGradChunk = 512;
 template <int UNROLL>
-__global__ void __launch_bounds__(512) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
+__global__ void __launch_bounds__(256) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
                                                   const float* __restrict__ w, int64_t F, GradPlan plan,
                                                   const Layout* __restrict__ lay, float sigma, float* __restrict__ g, int64_t v_lo, int64_t v_hi) {
     __shared__ int64_t s_off[kGradChunk];
@@ -135,9 +135,12 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
     // multi-GPU: the parameter axis is cut into n_shards runs of whole CTAs; every element is summed over all F rows by one rank in the
     // single-GPU order, the other ranks hold zeros, so the all-reduce that follows reproduces the single-GPU vector bit for bit
     NES_CHECK(n_shards >= 1 && shard >= 0 && shard < n_shards, "bad gradient shard");
-    static int kb = 0, ku = 0;                 // experiment switches: block size / rows in flight per thread
-    if (!kb) { const char* e = getenv("NES_K7_BLOCK"); kb = e ? atoi(e) : 256; if (kb != 128 && kb != 256 && kb != 512) kb = 256;
-               const char* u = getenv("NES_K7_UNROLL"); ku = u ? atoi(u) : 16; }
+    // rows in flight per thread (NES_K7_UNROLL, experiment switch).  Measured on B200 (tools/k7_sweep.py, F = 5000, D = 13.4 M, 2^32-element
+    // table): 8 -> 16 rows +7 %, 32 no further gain; 128 / 256 / 512 threads per block alike; giving a block a 2x / 4x longer contiguous run
+    // of every row (several vectors per thread) alike or worse.  ncu: 134.7 GB from DRAM for 134.1 GB algorithmic at 7.0 TB/s
+    static int ku = 0;
+    if (!ku) { const char* u = getenv("NES_K7_UNROLL"); ku = u ? atoi(u) : 16; }
+    constexpr int kb = 256;
     const int64_t blocks = (total + kb - 1) / kb, per = (blocks + n_shards - 1) / n_shards;
     const int64_t v_lo = std::min(total, (int64_t)shard * per * kb), v_hi = std::min(total, v_lo + per * kb);
     if (n_shards > 1) NES_CUDA(cudaMemsetAsync(d_g, 0, sizeof(float) * c->lay.D, c->stream));

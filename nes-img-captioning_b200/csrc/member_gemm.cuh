@@ -64,6 +64,10 @@ struct GemmParams {
     float* logit_trace; int64_t ld_trace;    // nullable, [member*rows + row, ld_trace]
     float tie_delta;                         // one float32 ulp of log(V+1)
     const uint8_t* unit_mask;                // nullable: only units with a non-zero flag are computed (HYBRID fallback)
+    // PLAIN with a batch that all members share: x theta_p^T + theta_b is the same for every member of parent p, so it is computed once
+    // per parent slot (a launch of this kernel with one pseudo member per slot and sigma = 0, float32 out) and handed in as y0
+    // [slot * rows_pad + row, N]; this launch then streams and multiplies the eps tiles only (2 of the 5 split-fp16 passes)
+    const float* y0;
 };
 
 template <int EPI, int PREC> struct GemmCfg {
@@ -152,7 +156,8 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                             if (((q++) & 1) != pid) { if (++stage == C::STAGES) { stage = 0; phase ^= 1; } continue; }
                             tc::mbar_wait(&empty_bar[stage], phase ^ 1);
                             uint8_t* st = smem + stage * C::STAGE_BYTES;
-                            tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                            const bool eps_only = EPI == EPI_PLAIN && PREC == NES_PREC_EXACT && p.y0 != nullptr;
+                            tc::mbar_expect_tx(&full_bar[stage], eps_only ? C::NA * C::A_BYTES + C::B_BYTES : C::STAGE_BYTES);
                             tc::tma_load_2d(st, &mp.a_hi, &full_bar[stage], kb * C::BK, a_row);
                             if (PREC == NES_PREC_EXACT) tc::tma_load_2d(st + C::A_BYTES, &mp.a_lo, &full_bar[stage], kb * C::BK, a_row);
                             uint8_t* sb = st + C::NA * C::A_BYTES;      // [theta_hi | eps | theta_lo]
@@ -160,6 +165,8 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                                 tc::tma_load_3d(sb, &mp.w_hi, &full_bar[stage], kb * C::BK, w_row0, 0);
                                 tc::tma_load_3d(sb + C::B_BYTES, &mp.eps, &full_bar[stage], kb * C::BK, e_row0, 0);
                                 if (PREC == NES_PREC_EXACT) tc::tma_load_3d(sb + 2 * C::B_BYTES, &mp.w_lo, &full_bar[stage], kb * C::BK, w_row0, 0);
+                            } else if (eps_only) {
+                                tc::tma_load_2d(sb + C::B_BYTES, &mp.eps, &full_bar[stage], kb * C::BK, e_row0);
                             } else {
                                 tc::tma_load_2d(sb, &mp.w_hi, &full_bar[stage], kb * C::BK, w_row0);
                                 tc::tma_load_2d(sb + C::B_BYTES, &mp.eps, &full_bar[stage], kb * C::BK, e_row0);
@@ -196,6 +203,13 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
 #pragma unroll
                             for (int k = 0; k < C::BK / 16; ++k) {
                                 const uint64_t a_hi = tc::make_smem_desc<C::SWZ>(sa + k * 32);
+                                if (EPI == EPI_PLAIN && PREC == NES_PREC_EXACT && p.y0 != nullptr) {
+                                    // (x_hi + x_lo) * eps -> eps-acc; the theta term comes in through y0
+                                    const uint64_t b_eps = tc::make_smem_desc<C::SWZ>(sb + C::B_BYTES + k * 32);
+                                    tc::umma_f16(d_tmem + C::BN, a_hi, b_eps, idesc1, (first && k == 0) ? 0u : 1u);
+                                    tc::umma_f16(d_tmem + C::BN, tc::make_smem_desc<C::SWZ>(sa + C::A_BYTES + k * 32), b_eps, idesc1, 1u);
+                                    continue;
+                                }
                                 // x_hi * [theta_hi | eps] -> [theta-acc | eps-acc]
                                 tc::umma_f16(d_tmem, a_hi, tc::make_smem_desc<C::SWZ>(sb + k * 32), idesc2, (first && k == 0) ? 0u : 1u);
                                 if (PREC == NES_PREC_EXACT) {
@@ -237,7 +251,7 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
             float b = 0.f;
             for (int s = 0; s < p.nseg; ++s) {
                 if (p.seg[s].b_start >= 0) {
-                    const float tb = p.theta32[(int64_t)par * p.D + p.seg[s].b_start + n];
+                    const float tb = (EPI == EPI_PLAIN && p.y0) ? 0.f : p.theta32[(int64_t)par * p.D + p.seg[s].b_start + n];
                     const float nz = __fmul_rn(p.sigma, __half2float(p.table[off + p.seg[s].b_pstart + n]));
                     b += (sgn > 0.f) ? __fadd_rn(tb, nz) : __fsub_rn(tb, nz);
                 }
@@ -317,7 +331,15 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
 #pragma unroll 1
                     for (int c0 = hf * 64; c0 < hf * 64 + 64; c0 += 32) {
                         float y[32];
-                        {
+                        if (EPI == EPI_PLAIN && PREC == NES_PREC_EXACT && p.y0 != nullptr) {
+                            float ve[32];
+                            tc::tmem_ld32(trow + COL_EPS + c0, ve);
+                            tc::tmem_ld_wait();
+                            const int par = p.parent ? p.parent[member] : 0;
+                            const float* y0 = p.y0 + ((int64_t)par * p.rows_pad + m_local) * p.N + n_base + c0;
+#pragma unroll
+                            for (int uu = 0; uu < 32; ++uu) y[uu] = ve[uu] * sE + bias[c0 + uu] + ((row_ok && n_base + c0 + uu < p.N) ? y0[uu] : 0.f);
+                        } else {
                             float vh[32], ve[32];
                             tc::tmem_ld32(trow + c0, vh);
                             tc::tmem_ld32(trow + COL_EPS + c0, ve);
