@@ -337,8 +337,16 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                             tc::tmem_ld_wait();
                             const int par = p.parent ? p.parent[member] : 0;
                             const float* y0 = p.y0 + ((int64_t)par * p.rows_pad + m_local) * p.N + n_base + c0;
+                            float yp[32];
+                            if (row_ok && n_base + c0 + 32 <= p.N && (p.N & 3) == 0) {
 #pragma unroll
-                            for (int uu = 0; uu < 32; ++uu) y[uu] = ve[uu] * sE + bias[c0 + uu] + ((row_ok && n_base + c0 + uu < p.N) ? y0[uu] : 0.f);
+                                for (int v4 = 0; v4 < 8; ++v4) *reinterpret_cast<float4*>(&yp[v4 * 4]) = __ldg(reinterpret_cast<const float4*>(y0) + v4);
+                            } else {
+#pragma unroll
+                                for (int uu = 0; uu < 32; ++uu) yp[uu] = (row_ok && n_base + c0 + uu < p.N) ? y0[uu] : 0.f;
+                            }
+#pragma unroll
+                            for (int uu = 0; uu < 32; ++uu) y[uu] = ve[uu] * sE + bias[c0 + uu] + yp[uu];
                         } else {
                             float vh[32], ve[32];
                             tc::tmem_ld32(trow + c0, vh);
@@ -348,7 +356,31 @@ __global__ void __launch_bounds__(352, 1) k_member_gemm(const __grid_constant__ 
                             for (int uu = 0; uu < 32; ++uu) y[uu] = vh[uu] * sW + ve[uu] * sE + bias[c0 + uu];
                         }
                         if (EPI == EPI_PLAIN) {
-                            if (row_ok) {
+                            // a thread owns 32 consecutive columns of its row: 16-byte stores when the whole chunk is inside N and the
+                            // rows are 16-byte aligned (element-wise 2-byte stores from 32 lanes in 32 different rows made this epilogue,
+                            // not the MMAs, the bound of img_embed: 65 us per tile whatever the population)
+                            const bool vec_ok = n_base + c0 + 32 <= p.N && (p.N & 7) == 0 && (!p.out_f32 || (p.ld_out & 3) == 0);
+                            if (row_ok && vec_ok) {
+                                if (p.out_f32) {
+                                    float4* o = reinterpret_cast<float4*>(p.out_f32 + grow * p.ld_out + n_base + c0);
+#pragma unroll
+                                    for (int v4 = 0; v4 < 8; ++v4) o[v4] = *reinterpret_cast<float4*>(&y[v4 * 4]);
+                                }
+                                if (p.out_hi) {
+                                    __align__(16) __half hh[32];
+                                    __align__(16) __half hl[32];
+#pragma unroll
+                                    for (int uu = 0; uu < 32; ++uu) split_half_dev(y[uu], kActScale, hh[uu], hl[uu]);
+                                    uint4* oh = reinterpret_cast<uint4*>(p.out_hi + grow * p.N + n_base + c0);
+#pragma unroll
+                                    for (int v8 = 0; v8 < 4; ++v8) oh[v8] = *reinterpret_cast<uint4*>(&hh[v8 * 8]);
+                                    if (p.out_lo) {
+                                        uint4* ol = reinterpret_cast<uint4*>(p.out_lo + grow * p.N + n_base + c0);
+#pragma unroll
+                                        for (int v8 = 0; v8 < 4; ++v8) ol[v8] = *reinterpret_cast<uint4*>(&hl[v8 * 8]);
+                                    }
+                                }
+                            } else if (row_ok) {
 #pragma unroll
                                 for (int uu = 0; uu < 32; ++uu) {
                                     const int n = n_base + c0 + uu;
