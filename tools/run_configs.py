@@ -53,6 +53,10 @@ def nes_config(a, E, R, rows, ln, pairs, sigma, label):
         nes_b200.nes_iteration(ctx, opt, it[0], pairs, fc, sigma, 1e-7, fitness_fn, world_size=world, rank=rank,
                                precision=nes_b200.PREC_HYBRID, group=group)
     ms = time_ms(step, a.steps)
+    ctx.profile(True)                      # one more iteration with an event pair around every launch: where the time goes
+    step()
+    prof = {k: round(v['ms'], 2) for k, v in ctx.profile_read().items() if v['count']}
+    ctx.profile(False)
     if world > 1:
         import torch.distributed as dist
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -60,7 +64,7 @@ def nes_config(a, E, R, rows, ln, pairs, sigma, label):
         ms = t.item()
     if rank == 0:
         print(json.dumps({'config': label, 'n_gpus': world, 'pairs': pairs, 'rollouts': 2 * pairs, 'rows': rows, 'E': E, 'R': R, 'layer_n': ln,
-                          'D': ctx.D, 'iteration_ms': ms, 'rollouts_per_s': 2 * pairs / (ms * 1e-3), 'precision': 'hybrid'}))
+                          'D': ctx.D, 'iteration_ms': ms, 'rollouts_per_s': 2 * pairs / (ms * 1e-3), 'precision': 'hybrid', 'kernel_ms_rank0': prof}))
     ctx.close()
     if world > 1:
         import torch.distributed as dist
