@@ -412,6 +412,71 @@ __global__ void __launch_bounds__(128) k_ln_gates(const LnParams p) {
     }
 }
 
+// The same cell with the row held in registers (R <= 256, i.e. config 4's R = 128): a lane owns NV = 5R / 32 pre-activation values of each
+// addend, so each is read from global memory ONCE (the kernel above re-reads them for the mean, the variance and the normalisation and
+// was bound by instruction issue: 5.5 ms per step of 2500 members x 512 rows); the gate inputs of unit j = the lane's values at
+// j, j + R, ... live in the lane that owns column j mod 32, so the cell needs no shared memory either.
+template <int RV>                                          // RV = R / 32 hidden units per lane
+__global__ void __launch_bounds__(128) k_ln_gates_reg(const LnParams p) {
+    constexpr int NV = 5 * RV;
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + wq;
+    if (wid >= p.n_members * p.rows) return;
+    const int64_t member = wid / p.rows;
+    const int r = (int)(wid % p.rows);
+    const int64_t grow = member * p.rows_pad + r;
+    constexpr int R = 32 * RV, N = 5 * R;
+    const float* par = p.ln_par ? p.ln_par + member * (int64_t)(4 * N + 2 * R) : nullptr;
+    float sum[NV];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+        const float* src = (a == 0 ? p.pre_i : p.pre_h) + grow * N;
+        float v[NV];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) { v[i] = src[i * 32 + lane]; s += v[i]; }        // column i * 32 + lane: coalesced
+        const float mean = warp_sum_f(s) / (float)N;
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) { const float d = v[i] - mean; q += d * d; }
+        const float rstd = 1.0f / sqrtf(warp_sum_f(q) / (float)N + 1e-5f);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int j = i * 32 + lane;
+            const float w = par ? par[(2 * a) * N + j] : 1.f, b = par ? par[(2 * a + 1) * N + j] : 0.f;
+            const float y = (v[i] - mean) * rstd * w + b;
+            sum[i] = a == 0 ? y : sum[i] + y;
+        }
+    }
+    // unit j = u * 32 + lane (u < RV): gate g of unit j is column g * R + j = (g * RV + u) * 32 + lane -> sum[g * RV + u]
+    float* cs = p.c_state + grow * R;
+    float cn[RV];
+    float cs_sum = 0.f;
+#pragma unroll
+    for (int u = 0; u < RV; ++u) {
+        const float ig = sigmoid_f(sum[u]), fg = sigmoid_f(sum[RV + u]);
+        const float cand = fmaxf(sum[3 * RV + u], sum[4 * RV + u]);
+        cn[u] = __fadd_rn(__fmul_rn(fg, cs[u * 32 + lane]), __fmul_rn(ig, cand));
+        cs[u * 32 + lane] = cn[u];
+        cs_sum += cn[u];
+    }
+    const float mean = warp_sum_f(cs_sum) / (float)R;
+    float q = 0.f;
+#pragma unroll
+    for (int u = 0; u < RV; ++u) { const float d = cn[u] - mean; q += d * d; }
+    const float rstd = 1.0f / sqrtf(warp_sum_f(q) / (float)R + 1e-5f);
+#pragma unroll
+    for (int u = 0; u < RV; ++u) {
+        const int j = u * 32 + lane;
+        const float w = par ? par[4 * N + j] : 1.f, b = par ? par[4 * N + R + j] : 0.f;
+        const float og = sigmoid_f(sum[2 * RV + u]);
+        const float hn = og * tanhf((cn[u] - mean) * rstd * w + b);
+        __half hi, lo; split_half_dev(hn, kActScale, hi, lo);
+        p.h_hi[grow * R + j] = hi; p.h_lo[grow * R + j] = lo;
+        if (p.h_trace) p.h_trace[(member * p.rows + r) * (int64_t)R + j] = hn;
+    }
+}
+
 // Batch-norm variant of the cell -- the reference's "virtual batch norm" (captioning/nets.py:87-91,99-101,124-125):
 // nn.BatchNorm1d(track_running_stats=False), i.e. every feature is normalised with the mean / biased variance over the ROWS of the
 // batch at hand, in eval mode too.  grid (ceil(R/32), members): a block owns 32 units of one member (lane = unit, warp = row subset),
@@ -543,7 +608,7 @@ int decode_create(Ctx* c, int wave_members, int rows) {
         if (d.layer_n && d.layer_n_affine && dmalloc(&ws->ln_par, (int64_t)ws->W * 22 * ws->R)) return 1;
         if (ws->dense_logit) {
             if (dmalloc(&ws->wv16, (int64_t)ws->W * ws->V1 * ws->R) || dmalloc(&ws->wv_bias, (int64_t)ws->W * ws->V1) ||
-                dmalloc(&ws->heads, 2 * WR) || dmalloc(&ws->entries, 2 * WR * kCandCap)) return 1;
+                dmalloc(&ws->heads, kCandLists * WR) || dmalloc(&ws->entries, (int64_t)kCandLists * WR * kCandCap)) return 1;
         }
     }
     if (dmalloc(&ws->margin, WR) || dmalloc(&ws->pre_tok, WR) || dmalloc(&ws->pre_lp, WR) || dmalloc(&ws->unit_flag, WR / 128) || dmalloc(&ws->stats, 4)) return 1;
@@ -965,6 +1030,9 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 if (ln_smem > 48 * 1024) { static size_t set_to = 0; if (set_to < ln_smem) { NES_CUDA(cudaFuncSetAttribute(k_ln_gates, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ln_smem)); set_to = ln_smem; } }
                 ProfScope prof(c, PROF_FINALIZE);
                 if (c->dims.layer_n == 2) k_bn_gates<<<dim3((unsigned)((R + 31) / 32), (unsigned)nm), 256, 0, c->stream>>>(q);
+                else if (R == 128) k_ln_gates_reg<4><<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(q);
+                else if (R == 64) k_ln_gates_reg<2><<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(q);
+                else if (R == 256) k_ln_gates_reg<8><<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(q);
                 else k_ln_gates<<<(unsigned)((nm * rows + 3) / 4), 128, ln_smem, c->stream>>>(q);
                 c->launches++;
                 NES_CUDA(cudaGetLastError());

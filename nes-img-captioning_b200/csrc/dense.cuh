@@ -29,7 +29,11 @@ constexpr int kLstmHalfUnits = kLstmTileUnits / 2;    // per epilogue warp of a 
 constexpr int kLstmSubBatches = kLstmHalfUnits / 8;
 static_assert(kLstmTileUnits % 16 == 0 && 5 * kLstmTileUnits <= 256, "LSTM tile shape");
 constexpr int kLstmTileCols = 5 * kLstmTileUnits;
-constexpr int kCandCap = 64;                // candidate entries per half row (append-only; overflow -> split-fp16 fallback)
+constexpr int kCandCap = 64;                // candidate entries per list (append-only; overflow -> split-fp16 fallback)
+#ifndef NES_LOGITC_WARPS
+#define NES_LOGITC_WARPS 16                 // epilogue warps of the LOGITC kernel: 8 or 16 (A/B builds)
+#endif
+constexpr int kCandLists = NES_LOGITC_WARPS / 4;               // lists per row: one per LOGITC epilogue warp of the row's TMEM lane quarter (64 of a tile's 256 columns each)
 
 struct alignas(16) CandHead { float mx; float sum; int32_t n; int32_t pad; };
 struct alignas(8) CandEntry { float v; int32_t idx; };
@@ -69,7 +73,10 @@ template <int EPI> struct DenseCfg {
     static constexpr int ACC_STRIDE = 256;
     static constexpr int TMEM_COLS = 512;
     static constexpr int SMEM_BYTES = ARES_BYTES + STAGES * STAGE_BYTES + 1024 + CTRL_BYTES;
-    static constexpr int THREADS = 352;
+    // warps 0 and 10 TMA producers, warp 1 MMA issuer, the rest epilogue: 8 warps (2 per TMEM lane quarter), or 16 for LOGITC, whose
+    // epilogue (scale + bias, running max, one exp per logit) is the bound once K is small (config 4: K = 128, 512 rows)
+    static constexpr int EPI_WARPS = EPI == DEN_LOGITC ? NES_LOGITC_WARPS : 8;
+    static constexpr int THREADS = (3 + EPI_WARPS) * 32;
     static_assert(STAGES >= 3, "pipeline too shallow");
     static_assert(BN <= ACC_STRIDE && BN % 16 == 0, "accumulator shape");
     static_assert(STAGE_BYTES % 1024 == 0 && A_BYTES % 1024 == 0 && B_BYTES % 1024 == 0, "swizzle atoms need 1024-byte alignment");
@@ -77,7 +84,7 @@ template <int EPI> struct DenseCfg {
 };
 
 template <int EPI>
-__global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__ DenseParams p) {
+__global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(const __grid_constant__ DenseParams p) {
     using C = DenseCfg<EPI>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -96,7 +103,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
-        for (int b = 0; b < 2; ++b) { tc::mbar_init(&tfull_bar[b], 1); tc::mbar_init(&tempty_bar[b], 8); }
+        for (int b = 0; b < 2; ++b) { tc::mbar_init(&tfull_bar[b], 1); tc::mbar_init(&tempty_bar[b], C::EPI_WARPS); }
         for (int k = 0; k < 8; ++k) { tc::mbar_init(&afull_bar[k], 1); tc::mbar_init(&aempty_bar[k], 1); }
         tc::fence_barrier_init();
     }
@@ -204,10 +211,12 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
             }
         }
     } else {
-        // ======= epilogue: warps 2..9.  TMEM lane quarter = warp & 3 (rows), column half = (warp - 2) >> 2 =======
+        // ======= epilogue: warps 2..9 (and 11..18 for LOGITC).  TMEM lane quarter = warp & 3 (rows); hf = which of the warps of that
+        // quarter this is = which column half (quarter for LOGITC) of every tile it owns =======
         const int q = warp & 3;
-        const int hf = (warp - 2) >> 2;
-        const int et = (warp - 2) * 32 + lane;               // 0..255 among epilogue threads
+        const int ew = warp < 10 ? warp - 2 : warp - 3;      // 0 .. EPI_WARPS-1 among epilogue warps
+        const int hf = warp < 10 ? (warp - 2) >> 2 : 2 + ((warp - 11) >> 2);
+        const int et = ew * 32 + lane;                       // index among epilogue threads
         const int row = q * 32 + lane;
         const float sW = 1.0f / (kThetaScale * kActScale);
         constexpr float kLog2e = 1.4426950408889634f;
@@ -230,13 +239,13 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
             const int64_t grow = member * p.rows_pad + m_local;
             float run_max = -INFINITY, run_sum = 0.f; int n_cand = 0;
             const float margin = (EPI == DEN_LOGITC && row_ok) ? p.margin[grow] : 0.f;
-            CandEntry* ent = EPI != DEN_LOGITC ? nullptr : p.entries + (grow * 2 + hf) * (int64_t)kCandCap;
+            CandEntry* ent = EPI != DEN_LOGITC ? nullptr : p.entries + (grow * kCandLists + hf) * (int64_t)kCandCap;
 
             for (int nt = nt0; nt < nt1; ++nt, ++it) {
                 const uint32_t buf = it & 1;
-                asm volatile("bar.sync 1, 256;" ::: "memory");           // everyone is done with the previous tile's bias
+                asm volatile("bar.sync 1, %0;" ::"n"(C::EPI_WARPS * 32) : "memory");           // everyone is done with the previous tile's bias
                 if (et < C::BN) s_bias[et] = b_cur;
-                asm volatile("bar.sync 1, 256;" ::: "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(C::EPI_WARPS * 32) : "memory");
                 {
                     const int nx = item + (int)gridDim.x;                  // first tile of this CTA's next work item
                     b_cur = (nt + 1 < nt1) ? bias_val(u, nt + 1)
@@ -327,10 +336,11 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
                         }
                     }
                 } else {
-                    // LOGITC: this warp owns 128 of the tile's 256 vocabulary columns, 32 at a time
+                    // LOGITC: this warp owns 64 (128 with 8 epilogue warps) of the tile's 256 vocabulary columns, 32 at a time
                     const int n_base = nt * C::BN;
+                    constexpr int kCols = 256 / kCandLists;
 #pragma unroll 1
-                    for (int c0 = hf * 128; c0 < hf * 128 + 128; c0 += 32) {
+                    for (int c0 = hf * kCols; c0 < hf * kCols + kCols; c0 += 32) {
                         float y[32];
                         tc::tmem_ld32(trow + c0, y);
                         tc::tmem_ld_wait();
@@ -377,7 +387,7 @@ __global__ void __launch_bounds__(352, 1) k_member_dense(const __grid_constant__
             }
             if (EPI == DEN_LOGITC && row_ok) {
                 CandHead hd; hd.mx = run_max; hd.sum = run_sum; hd.n = n_cand; hd.pad = 0;
-                *reinterpret_cast<float4*>(&p.heads[grow * 2 + hf]) = *reinterpret_cast<float4*>(&hd);
+                *reinterpret_cast<float4*>(&p.heads[grow * kCandLists + hf]) = *reinterpret_cast<float4*>(&hd);
             }
         }
         tc::tc_fence_before();

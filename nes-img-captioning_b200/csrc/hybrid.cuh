@@ -124,15 +124,22 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
     const int64_t member = wid / p.rows;
     const int r = (int)(wid % p.rows);
     const int64_t grow = member * p.rows_pad + r;
-    const CandHead h0 = p.heads[grow * 2], h1 = p.heads[grow * 2 + 1];
-    const float M = fmaxf(h0.mx, h1.mx);
+    CandHead hd[kCandLists];
+    float M = -INFINITY;
+    bool overflow = p.force_overflow != 0;
+#pragma unroll
+    for (int hf = 0; hf < kCandLists; ++hf) {
+        hd[hf] = p.heads[grow * kCandLists + hf];
+        M = fmaxf(M, hd[hf].mx);
+        overflow = overflow || hd[hf].n > kCandCap;
+    }
     const float thr = M - p.margin[grow];
     int count = 0;
-    bool overflow = h0.n > kCandCap || h1.n > kCandCap || p.force_overflow;
     if (!overflow) {
-        for (int hf = 0; hf < 2; ++hf) {
-            const int n = hf ? h1.n : h0.n;
-            const CandEntry* ent = p.entries + (grow * 2 + hf) * (int64_t)kCandCap;
+#pragma unroll
+        for (int hf = 0; hf < kCandLists; ++hf) {
+            const int n = hd[hf].n;
+            const CandEntry* ent = p.entries + (grow * kCandLists + hf) * (int64_t)kCandCap;
             for (int e0 = 0; e0 < n; e0 += 32) {
                 const int e = e0 + lane;
                 CandEntry ce; ce.v = -INFINITY; ce.idx = 0;
@@ -151,7 +158,9 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
         return;
     }
     __syncwarp();
-    const float S = h0.sum * expf(h0.mx - M) + h1.sum * expf(h1.mx - M);
+    float S = 0.f;
+#pragma unroll
+    for (int hf = 0; hf < kCandLists; ++hf) S += hd[hf].sum * expf(hd[hf].mx - M);
     const int my_idx = lane < count ? s_idx[wq][lane] : -1;
     const float ssig = p.sign[member] > 0.f ? p.sigma : -p.sigma;      // theta - fl(sigma eps) == theta + fl(-sigma eps), bit for bit
     const int64_t off = p.off[member];

@@ -4,7 +4,6 @@ d=nes-img-captioning_b200
 cp $d/libnes_b200.so /tmp/libA.so
 for leg in A B A B; do
   if [ $leg = A ]; then cp /tmp/libA.so $d/libnes_b200.so; else cp $d/libnes_b200_$1.so $d/libnes_b200.so; fi
-  echo "== $leg"; python bench.py --steps 10 --warmup 3 --no-extras --nes-pairs 0 2>/dev/null | python tools/show_bench.py - hybrid
+  python bench.py --steps 10 --warmup 3 --no-extras --nes-pairs 0 2>/dev/null > gpurun_out/ablib_$leg.json; python tools/show_bench.py gpurun_out/ablib_$leg.json $leg
 done
 cp /tmp/libA.so $d/libnes_b200.so
-cp $d/libnes_b200_$1.so $d/libnes_b200.so; timeout 600 python -m pytest tests/test_gpu_decode.py -m gpu -q -x --timeout 300 2>&1 | tail -2; cp /tmp/libA.so $d/libnes_b200.so
