@@ -82,7 +82,8 @@ struct DecodeWorkspace {
     __half *wi_hi = nullptr, *wi_lo = nullptr; float* wi_bias = nullptr;      // img_embed, only with a safe-mutation scale (lazy)
     bool dense_ln = false;                                                    // LayerNorm cell: dense PLAIN pre-activation GEMMs
     __half *wn_hi[2] = {nullptr, nullptr}, *wn_lo[2] = {nullptr, nullptr}; float* wn_bias[2] = {nullptr, nullptr}; float* ln_par = nullptr;
-    float* margin = nullptr; int32_t* pre_tok = nullptr; float* pre_lp = nullptr; uint8_t* unit_flag = nullptr;   // HYBRID
+    float* hsq = nullptr; int hsq_n = 0;                     // |h|^2 pieces per row from the cell kernels (HYBRID margin without a pass over h)
+    float* margin = nullptr; int32_t* pre_tok = nullptr; float* pre_lp = nullptr; uint8_t* unit_flag = nullptr; uint8_t* row_flag = nullptr;   // HYBRID
     unsigned long long* stats = nullptr;
     uint8_t* unfinished = nullptr; int32_t* unf_count = nullptr;
     // per call
@@ -144,47 +145,14 @@ struct FinalizeParams {
     __half *x_hi, *x_lo;
     float* x32;                                  // vbn_e: the gathered embedding as float32 instead (k_embed_bn normalises it)
     int gather;                                  // write x for the next step
+    const uint8_t* row_flag;                     // nullable: k_finalize handles only the rows flagged here
 };
-// one warp per (member, row): merge the per-tile (max, argmax, sum-exp) partials, apply the
-// finished-mask bookkeeping of captioning/nets.py:233-243, gather the next input embedding.
-__global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
-    const int lane = threadIdx.x & 31;
-    const int64_t wid = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (wid >= p.n_members * p.rows) return;
-    const int64_t member = wid / p.rows;
-    const int r = (int)(wid % p.rows);
-    const int64_t grow = member * p.rows_pad + r;
+// what happens to a row once its arg-max token and log-prob are known: the finished-mask bookkeeping of captioning/nets.py:233-243, the
+// seq / log-prob writes, and the gather of the next input embedding theta_emb[it] +- sigma eps_emb[it] (t = 0: the <bos> gather only)
+__device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t member, int r, int64_t grow, int lane, int idx, float best) {
     const float sgn = p.sign[member];
     int64_t tok = 0;
     if (p.t >= 1) {
-        float best = -INFINITY; int idx = 0x7fffffff;
-        if (p.pre_tok && (p.pre_always || !p.unit_flag[member * p.m_tiles + r / 128])) { idx = p.pre_tok[grow]; best = p.pre_lp[grow]; }
-        else {
-        // global max and sum-exp over the vocabulary tiles
-        float mx = -INFINITY;
-        for (int j = lane; j < p.n_tiles; j += 32) mx = fmaxf(mx, p.partials[grow * p.n_tiles + j].mx);
-        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        float s = 0.f;
-        for (int j = lane; j < p.n_tiles; j += 32) {
-            const LogitPartial q = p.partials[grow * p.n_tiles + j];
-            s += q.sum * expf(q.mx - mx);
-        }
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        const float lse = logf(s);
-        // the reference's argmax runs over float32 log-probs, log_softmax(x) = (x - max) - log(sum) (captioning/nets.py:202-208):
-        // logits closer than the float32 quantum of log(sum) tie there and torch.max returns the LOWEST index.
-        for (int j = lane; j < p.n_tiles; j += 32) {
-            const LogitPartial q = p.partials[grow * p.n_tiles + j];
-            const float l1 = __fsub_rn(__fsub_rn(q.mx, mx), lse), l2 = __fsub_rn(__fsub_rn(q.lo_val, mx), lse);
-            if (l1 > best || (l1 == best && q.idx < idx)) { best = l1; idx = q.idx; }
-            if (l2 > best || (l2 == best && q.lo_idx < idx)) { best = l2; idx = q.lo_idx; }
-        }
-        for (int o = 16; o > 0; o >>= 1) {
-            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
-            if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
-        }
-        }
         const float logp = best;                                  // = max log-prob
         const bool done = p.t > 1 && p.unf_count[(p.t - 1) * p.W + member] == 0;   // the reference broke out of the loop
         int64_t it = 0;
@@ -246,6 +214,67 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
         *reinterpret_cast<uint4*>(p.x_hi + grow * p.E + e) = *reinterpret_cast<uint4*>(hh);
         *reinterpret_cast<uint4*>(p.x_lo + grow * p.E + e) = *reinterpret_cast<uint4*>(hl);
     }
+}
+
+
+// one warp per (member, row): merge the per-tile (max, argmax, sum-exp) partials (or take the refined arg-max), then finalize_row.
+// row_flag given: only the rows flagged there (the ones k_refine_finalize left to the fallback) are handled.
+__global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (wid >= p.n_members * p.rows) return;
+    const int64_t member = wid / p.rows;
+    const int r = (int)(wid % p.rows);
+    const int64_t grow = member * p.rows_pad + r;
+    if (p.row_flag && !p.row_flag[grow]) return;
+    float best = -INFINITY; int idx = 0x7fffffff;
+    if (p.t >= 1) {
+        if (p.pre_tok && (p.pre_always || !p.unit_flag[member * p.m_tiles + r / 128])) { idx = p.pre_tok[grow]; best = p.pre_lp[grow]; }
+        else {
+        // global max and sum-exp over the vocabulary tiles
+        float mx = -INFINITY;
+        for (int j = lane; j < p.n_tiles; j += 32) mx = fmaxf(mx, p.partials[grow * p.n_tiles + j].mx);
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        float s = 0.f;
+        for (int j = lane; j < p.n_tiles; j += 32) {
+            const LogitPartial q = p.partials[grow * p.n_tiles + j];
+            s += q.sum * expf(q.mx - mx);
+        }
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float lse = logf(s);
+        // the reference's argmax runs over float32 log-probs, log_softmax(x) = (x - max) - log(sum) (captioning/nets.py:202-208):
+        // logits closer than the float32 quantum of log(sum) tie there and torch.max returns the LOWEST index.
+        for (int j = lane; j < p.n_tiles; j += 32) {
+            const LogitPartial q = p.partials[grow * p.n_tiles + j];
+            const float l1 = __fsub_rn(__fsub_rn(q.mx, mx), lse), l2 = __fsub_rn(__fsub_rn(q.lo_val, mx), lse);
+            if (l1 > best || (l1 == best && q.idx < idx)) { best = l1; idx = q.idx; }
+            if (l2 > best || (l2 == best && q.lo_idx < idx)) { best = l2; idx = q.lo_idx; }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+            if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+        }
+        }
+    }
+    finalize_row(p, member, r, grow, lane, idx, best);
+}
+
+// HYBRID: the fp32 re-evaluation of a row's arg-max candidates (refine_row, hybrid.cuh) and everything that follows from the token
+// (finalize_row) in one pass, one warp per (member, row).  A row whose candidate lists overflowed is flagged instead (row_flag, and its
+// unit for the fallback projection); k_finalize with row_flag set picks those up after the fallback.
+__global__ void __launch_bounds__(128) k_refine_finalize(const RefineParams rp, const FinalizeParams fp, uint8_t* __restrict__ row_flag) {
+    __shared__ int s_idx[4][32];
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + wq;
+    if (wid >= rp.n_members * rp.rows) return;
+    const int64_t member = wid / rp.rows;
+    const int r = (int)(wid % rp.rows);
+    const int64_t grow = member * rp.rows_pad + r;
+    int idx = 0; float best = 0.f;
+    const bool ok = refine_row(rp, member, r, grow, lane, wq, s_idx, idx, best);
+    if (lane == 0) row_flag[grow] = ok ? 0 : 1;
+    if (ok) finalize_row(fp, member, r, grow, lane, idx, best);
 }
 
 // vbn_e (captioning/nets.py:156-165): nn.BatchNorm1d(E, track_running_stats=False) on the output of img_embed / embed -- every feature
@@ -357,6 +386,7 @@ __global__ void __launch_bounds__(256) k_sample(const SampleParams p) {
 struct LnParams {
     const float *pre_i, *pre_h; float* c_state; __half *h_hi, *h_lo; float* h_trace;
     int rows, rows_pad, R; int64_t n_members;
+    float* hsq; int hsq_n;     // nullable: the row's |h|^2 (in hsq_n pieces; the batch-norm cell writes one per block of 32 units) for the HYBRID margin
     const float* ln_par;       // nullable (no affine): member LayerNorm parameters [n_members][4*5R + 2R]:
                                // i2h_ln.w, i2h_ln.b, h2h_ln.w, h2h_ln.b [5R each], c_ln.w, c_ln.b [R each] (k_materialise_bias)
 };
@@ -402,14 +432,18 @@ __global__ void __launch_bounds__(128) k_ln_gates(const LnParams p) {
     float v = 0.f;
     for (int j = lane; j < R; j += 32) { const float d = s_c[j] - mean; v += d * d; }
     const float rstd = 1.0f / sqrtf(warp_sum_f(v) / (float)R + 1e-5f);
+    float hs = 0.f;
     for (int j = lane; j < R; j += 32) {
         const float w = par ? par[4 * N + j] : 1.f, b = par ? par[4 * N + R + j] : 0.f;
         const float og = sigmoid_f(s_sum[2 * R + j]);
         const float hn = og * tanhf((s_c[j] - mean) * rstd * w + b);
+        hs = fmaf(hn, hn, hs);
         __half a, l; split_half_dev(hn, kActScale, a, l);
         p.h_hi[grow * R + j] = a; p.h_lo[grow * R + j] = l;
         if (p.h_trace) p.h_trace[(member * p.rows + r) * (int64_t)R + j] = hn;
     }
+    hs = warp_sum_f(hs);
+    if (p.hsq && lane == 0) p.hsq[grow * p.hsq_n] = hs;
 }
 
 // The same cell with the row held in registers (R <= 256, i.e. config 4's R = 128): a lane owns NV = 5R / 32 pre-activation values of each
@@ -465,16 +499,20 @@ __global__ void __launch_bounds__(128) k_ln_gates_reg(const LnParams p) {
 #pragma unroll
     for (int u = 0; u < RV; ++u) { const float d = cn[u] - mean; q += d * d; }
     const float rstd = 1.0f / sqrtf(warp_sum_f(q) / (float)R + 1e-5f);
+    float hs = 0.f;
 #pragma unroll
     for (int u = 0; u < RV; ++u) {
         const int j = u * 32 + lane;
         const float w = par ? par[4 * N + j] : 1.f, b = par ? par[4 * N + R + j] : 0.f;
         const float og = sigmoid_f(sum[2 * RV + u]);
         const float hn = og * tanhf((cn[u] - mean) * rstd * w + b);
+        hs = fmaf(hn, hn, hs);
         __half hi, lo; split_half_dev(hn, kActScale, hi, lo);
         p.h_hi[grow * R + j] = hi; p.h_lo[grow * R + j] = lo;
         if (p.h_trace) p.h_trace[(member * p.rows + r) * (int64_t)R + j] = hn;
     }
+    hs = warp_sum_f(hs);
+    if (p.hsq && lane == 0) p.hsq[grow * p.hsq_n] = hs;
 }
 
 // Batch-norm variant of the cell -- the reference's "virtual batch norm" (captioning/nets.py:87-91,99-101,124-125):
@@ -543,13 +581,18 @@ __global__ void __launch_bounds__(256) k_bn_gates(const LnParams p) {
     }
     const float cw = (par && live) ? par[4 * N + j] : 1.f, cb = (par && live) ? par[4 * N + R + j] : 0.f;
     // ---- h = o tanh(bn(c'))
-    if (live) for (int r = wq; r < p.rows; r += 8) {
-        const float og = sigmoid_f(gate(r, 2));
-        const float hn = og * tanhf((cs[(int64_t)r * R + j] - mean[10]) * rstd[10] * cw + cb);
+    for (int r = wq; r < p.rows; r += 8) {
         const int64_t grow = member * p.rows_pad + r;
-        __half a, l; split_half_dev(hn, kActScale, a, l);
-        p.h_hi[grow * R + j] = a; p.h_lo[grow * R + j] = l;
-        if (p.h_trace) p.h_trace[(member * p.rows + r) * (int64_t)R + j] = hn;
+        float hn = 0.f;
+        if (live) {
+            const float og = sigmoid_f(gate(r, 2));
+            hn = og * tanhf((cs[(int64_t)r * R + j] - mean[10]) * rstd[10] * cw + cb);
+            __half a, l; split_half_dev(hn, kActScale, a, l);
+            p.h_hi[grow * R + j] = a; p.h_lo[grow * R + j] = l;
+            if (p.h_trace) p.h_trace[(member * p.rows + r) * (int64_t)R + j] = hn;
+        }
+        const float hs = warp_sum_f(hn * hn);                 // this block's 32 units of the row
+        if (p.hsq && lane == 0) p.hsq[grow * p.hsq_n + blockIdx.x] = hs;
     }
 }
 
@@ -611,7 +654,9 @@ int decode_create(Ctx* c, int wave_members, int rows) {
                 dmalloc(&ws->heads, kCandLists * WR) || dmalloc(&ws->entries, (int64_t)kCandLists * WR * kCandCap)) return 1;
         }
     }
-    if (dmalloc(&ws->margin, WR) || dmalloc(&ws->pre_tok, WR) || dmalloc(&ws->pre_lp, WR) || dmalloc(&ws->unit_flag, WR / 128) || dmalloc(&ws->stats, 4)) return 1;
+    ws->hsq_n = ws->dense_lstm ? 2 * ws->ntl : (d.layer_n == 2 ? (ws->R + 31) / 32 : 1);
+    if (dmalloc(&ws->hsq, WR * ws->hsq_n)) return 1;
+    if (dmalloc(&ws->margin, WR) || dmalloc(&ws->pre_tok, WR) || dmalloc(&ws->pre_lp, WR) || dmalloc(&ws->unit_flag, WR / 128) || dmalloc(&ws->row_flag, WR) || dmalloc(&ws->stats, 4)) return 1;
     NES_CUDA(cudaMemsetAsync(ws->stats, 0, 32, c->stream));
     if (dmalloc(&ws->unfinished, WR) || dmalloc(&ws->unf_count, (int64_t)(ws->T + 2) * ws->W)) return 1;
     if (d.layer_n) { if (dmalloc(&ws->pre_i, WR * 5 * ws->R) || dmalloc(&ws->pre_h, WR * 5 * ws->R)) return 1; }
@@ -631,7 +676,7 @@ void decode_destroy(Ctx* c) {
     DecodeWorkspace* ws = c->ws;
     if (!ws) return;
     void* ptrs[] = {ws->fc32, ws->fc_hi, ws->fc_lo, ws->x_hi, ws->x_lo, ws->h_hi[0], ws->h_hi[1], ws->h_lo[0], ws->h_lo[1], ws->c_state,
-                    ws->pre_i, ws->pre_h, ws->x32, ws->ebn_par, ws->y0, ws->pp_off, ws->pp_sign, ws->pp_par, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
+                    ws->pre_i, ws->pre_h, ws->x32, ws->ebn_par, ws->y0, ws->pp_off, ws->pp_sign, ws->pp_par, ws->partials, ws->heads, ws->entries, ws->wl_hi[0], ws->wl_hi[1], ws->wl_lo[0], ws->wl_lo[1], ws->wl_bias, ws->wv16, ws->wv_bias, ws->wi_hi, ws->wi_lo, ws->wi_bias, ws->wn_hi[0], ws->wn_hi[1], ws->wn_lo[0], ws->wn_lo[1], ws->wn_bias[0], ws->wn_bias[1], ws->ln_par, ws->hsq, ws->margin, ws->pre_tok, ws->pre_lp, ws->unit_flag, ws->row_flag, ws->stats, ws->unfinished, ws->unf_count, ws->d_off, ws->d_sign, ws->d_parent, ws->d_seq,
                     ws->d_lp, ws->d_forced, ws->d_uniforms, ws->samp_logits, ws->wv_lo};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete ws;
@@ -975,6 +1020,19 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             if (launch_gemm_prec<EPI_PLAIN>(c, p, nm, precision)) return 1;
         }
         if (vbn_e && embed_bn(0)) return 1;
+        auto make_fin = [&](int t) {
+            FinalizeParams f{};
+            f.partials = ws->partials; f.n_tiles = 2; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
+            f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table; f.scale = c->scale32; f.scale_div = c->scale_div;
+            f.D = L.D; f.emb_start = L.t[c->tix[T_EMB_W]].start; f.emb_pstart = L.t[c->tix[T_EMB_W]].pstart; f.sigma = sigma;
+            f.unfinished = ws->unfinished; f.unf_count = ws->unf_count; f.W = ws->W;
+            f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;
+            f.forced = forced ? ws->d_forced + m0 * rows * T : nullptr;
+            f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0; f.x32 = vbn_e ? ws->x32 : nullptr;
+            if (sampling && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = 1; }
+            if (hybrid && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = scaled ? 1 : 0; }
+            return f;
+        };
         int hb = 0;   // h buffer holding the current state
         for (int t = 0; t <= T; ++t) {
             // ---- (h, c) = core(x_t, (h, c))
@@ -991,6 +1049,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 p.rows = rows; p.rows_pad = rows_pad; p.m_tiles = m_tiles; p.n_tiles = ws->ntl; p.N = R;
                 p.b_rows = ws->ntl * kLstmTileCols; p.bias = ws->wl_bias; p.bias_stride = ws->ntl * kLstmTileCols;
                 p.c_state = ws->c_state; p.out_hi = ws->h_hi[hb ^ 1]; p.out_lo = ws->h_lo[hb ^ 1]; p.h_trace = ht;
+                p.hsq = hybrid ? ws->hsq : nullptr; p.hsq_n = ws->hsq_n;
                 if (lstm_pair_enabled() ? launch_lstm_pair(c, p, nm) : launch_dense<DEN_LSTM>(c, p, nm)) return 1;
             } else if (!c->dims.layer_n) {
                 GemmParams p = base;
@@ -1026,6 +1085,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 q.pre_i = ws->pre_i; q.pre_h = ws->pre_h; q.c_state = ws->c_state; q.h_hi = ws->h_hi[hb ^ 1]; q.h_lo = ws->h_lo[hb ^ 1];
                 q.h_trace = ht; q.rows = rows; q.rows_pad = rows_pad; q.R = R; q.n_members = nm;
                 q.ln_par = c->dims.layer_n_affine ? ws->ln_par : nullptr;
+                q.hsq = hybrid ? ws->hsq : nullptr; q.hsq_n = ws->hsq_n;
                 const size_t ln_smem = sizeof(float) * 4 * 6 * R;
                 if (ln_smem > 48 * 1024) { static size_t set_to = 0; if (set_to < ln_smem) { NES_CUDA(cudaFuncSetAttribute(k_ln_gates, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ln_smem)); set_to = ln_smem; } }
                 ProfScope prof(c, PROF_FINALIZE);
@@ -1049,8 +1109,13 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     MarginParams mg{};
                     mg.h_hi = ws->h_hi[hb]; mg.h_lo = ws->h_lo[hb]; mg.R = R; mg.rows = rows; mg.rows_pad = rows_pad; mg.n_members = nm;
                     mg.parent = base.parent; mg.theta_rowmax = c->d_theta_rowmax; mg.eps_rowmax = c->d_eps_rowmax; mg.scale_max = c->d_scale_max; mg.sigma = sigma; mg.margin = ws->margin;
-                    { ProfScope prof(c, PROF_FINALIZE);
-                      k_row_margin<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(mg); c->launches++; }
+                    // the cell kernel that produced h left the pieces of |h|^2 behind: LOGITC forms the margin itself; only the factored
+                    // LSTM kernel (NES_FACTORED) needs the separate pass over h
+                    const bool hsq_ok = dense_lstm || c->dims.layer_n != 0;
+                    if (!hsq_ok) {
+                        ProfScope prof(c, PROF_FINALIZE);
+                        k_row_margin<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(mg); c->launches++;
+                    }
                     NES_CUDA(cudaGetLastError());
                     {
                         DenseParams pc{};
@@ -1062,6 +1127,10 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                         pc.rows = rows; pc.rows_pad = rows_pad; pc.m_tiles = m_tiles; pc.n_tiles = ws->ntv; pc.N = V1;
                         pc.b_rows = V1; pc.bias = ws->wv_bias; pc.bias_stride = V1;
                         pc.heads = ws->heads; pc.entries = ws->entries; pc.margin = ws->margin;
+                        if (hsq_ok) {
+                            pc.hsq = ws->hsq; pc.hsq_n = ws->hsq_n; pc.mg_parent = base.parent; pc.mg_theta_rowmax = c->d_theta_rowmax;
+                            pc.mg_eps_rowmax = c->d_eps_rowmax; pc.mg_scale_max = c->d_scale_max; pc.mg_sigma = sigma; pc.margin_out = ws->margin;
+                        }
                         if (launch_dense<DEN_LOGITC>(c, pc, nm)) return 1;
                     }
                     NES_CUDA(cudaMemsetAsync(ws->unit_flag, 0, (size_t)nm * m_tiles, c->stream));
@@ -1072,8 +1141,8 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     rf.w_start = L.t[c->tix[T_LOGIT_W]].start; rf.w_pstart = L.t[c->tix[T_LOGIT_W]].pstart; rf.b_start = L.t[c->tix[T_LOGIT_B]].start; rf.b_pstart = L.t[c->tix[T_LOGIT_B]].pstart;
                     rf.sigma = sigma; rf.tok = ws->pre_tok; rf.lp = ws->pre_lp; rf.unit_flag = ws->unit_flag; rf.stats = c->profiling ? ws->stats : nullptr;
                     rf.force_overflow = (env_debug() & 64) ? 1 : 0;
-                    { ProfScope prof(c, PROF_FINALIZE);
-                      k_refine<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(rf); c->launches++; }
+                    { ProfScope prof(c, PROF_FINALIZE);       // (3) + the rows' bookkeeping and next-input gather, for every row that did not overflow
+                      k_refine_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(rf, make_fin(t), ws->row_flag); c->launches++; }
                     NES_CUDA(cudaGetLastError());
                     p.unit_mask = ws->unit_flag;      // (4) units whose candidate list overflowed: the split-fp16 kernel, everything else skips
                     if (scaled) {                     //     ... or, with scaled noise, every logit of those rows in fp32 (k_exact_rows)
@@ -1114,16 +1183,8 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                 }
             }
             if (t < T || t >= 1) {
-                FinalizeParams f{};
-                f.partials = ws->partials; f.n_tiles = 2; f.rows = rows; f.rows_pad = rows_pad; f.T = T; f.E = E; f.t = t;
-                f.n_members = nm; f.off = base.off; f.sign = base.sign; f.parent = base.parent; f.theta32 = c->theta32; f.table = c->table; f.scale = c->scale32; f.scale_div = c->scale_div;
-                f.D = L.D; f.emb_start = L.t[c->tix[T_EMB_W]].start; f.emb_pstart = L.t[c->tix[T_EMB_W]].pstart; f.sigma = sigma;
-                f.unfinished = ws->unfinished; f.unf_count = ws->unf_count; f.W = ws->W;
-                f.seq = ws->d_seq + m0 * rows * T; f.lp = ws->d_lp + m0 * rows * T;
-                f.forced = forced ? ws->d_forced + m0 * rows * T : nullptr;
-                f.x_hi = ws->x_hi; f.x_lo = ws->x_lo; f.gather = t < T ? 1 : 0; f.x32 = vbn_e ? ws->x32 : nullptr;
-                if (sampling && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = 1; }
-                if (hybrid && t >= 1) { f.pre_tok = ws->pre_tok; f.pre_lp = ws->pre_lp; f.unit_flag = ws->unit_flag; f.m_tiles = m_tiles; f.pre_always = scaled ? 1 : 0; }
+                FinalizeParams f = make_fin(t);
+                if (hybrid && t >= 1) f.row_flag = ws->row_flag;       // the rows k_refine_finalize left to the fallback (normally none)
                 ProfScope prof(c, PROF_FINALIZE);
                 k_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(f);
                 c->launches++;

@@ -50,6 +50,10 @@ struct alignas(64) DenseParams {
     float* c_state; __half* out_hi; __half* out_lo; float* h_trace;       // LSTM (PLAIN: out_hi / out_lo and / or out_f32)
     float* out_f32; int32_t ld_out;                                       // PLAIN: [member*rows_pad + row, ld_out] float32 (nullable)
     CandHead* heads; CandEntry* entries; const float* margin;            // LOGITC
+    // the row's |h|^2 in pieces, written by the cell kernel that produced h (LSTM: one piece per (tile, column half)) and summed by the
+    // LOGITC epilogue into the HYBRID error margin (hybrid.cuh: k_row_margin's formula) -- saves a pass over h per decode step
+    float* hsq; int32_t hsq_n;                                            // [row * hsq_n + piece]; LSTM writes, LOGITC reads (nullable)
+    const int32_t* mg_parent; const float* mg_theta_rowmax; const float* mg_eps_rowmax; const float* mg_scale_max; float mg_sigma; float* margin_out;
 };
 
 template <int EPI> struct DenseCfg {
@@ -238,7 +242,18 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
             const bool row_ok = m_local < p.rows;
             const int64_t grow = member * p.rows_pad + m_local;
             float run_max = -INFINITY, run_sum = 0.f; int n_cand = 0;
-            const float margin = (EPI == DEN_LOGITC && row_ok) ? p.margin[grow] : 0.f;
+            float margin = 0.f;
+            if (EPI == DEN_LOGITC && row_ok) {
+                if (p.hsq) {                                              // k_row_margin's bound from the pieces of |h|^2 (hybrid.cuh)
+                    float ss = 0.f;
+                    for (int i = 0; i < p.hsq_n; ++i) ss += p.hsq[grow * p.hsq_n + i];
+                    const int par = p.mg_parent ? p.mg_parent[member] : 0;
+                    const float smax = p.mg_scale_max ? p.mg_scale_max[par] : 1.f;
+                    const float wsum = 2.f * (p.mg_theta_rowmax[par] + fabsf(p.mg_sigma) * p.mg_eps_rowmax[0] * smax);
+                    margin = 2.f * 1.1f * 4.8828125e-4f * sqrtf(ss) * 1.0001f * (wsum + 1e-4f) + 1e-7f;
+                    if (hf == 0) p.margin_out[grow] = margin;             // k_refine_finalize filters the lists with the same number
+                } else margin = p.margin[grow];
+            }
             CandEntry* ent = EPI != DEN_LOGITC ? nullptr : p.entries + (grow * kCandLists + hf) * (int64_t)kCandCap;
 
             for (int nt = nt0; nt < nt1; ++nt, ++it) {
@@ -271,6 +286,7 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
                 const uint32_t trow = tmem_base + buf * C::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
                 {
                 if (C::LSTM) {
+                    float hs = 0.f;
 #pragma unroll
                     for (int sb = 0; sb < kLstmSubBatches; ++sb) {
                         const int cu = hf * kLstmHalfUnits + sb * 8;                 // first unit of this sub-batch inside the tile
@@ -296,7 +312,7 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
                             *reinterpret_cast<float4*>(cp + 4) = *reinterpret_cast<float4*>(&cn[4]);
                             __half hh[8], hl[8];
 #pragma unroll
-                            for (int uu = 0; uu < 8; ++uu) split_half_dev(hn[uu], kActScale, hh[uu], hl[uu]);
+                            for (int uu = 0; uu < 8; ++uu) { split_half_dev(hn[uu], kActScale, hh[uu], hl[uu]); hs = fmaf(hn[uu], hn[uu], hs); }
                             *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + j0) = *reinterpret_cast<uint4*>(hh);
                             *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + j0) = *reinterpret_cast<uint4*>(hl);
                             if (p.h_trace) {
@@ -306,6 +322,7 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
                             }
                         }
                     }
+                    if (p.hsq && row_ok) p.hsq[grow * p.hsq_n + nt * 2 + hf] = hs;
                 } else if (EPI == DEN_PLAIN) {
                     // PLAIN: y = acc * 2^-13 + bias, written as the next split-fp16 A operand; this warp owns 128 of the 256 columns
                     const int n_base = nt * C::BN;

@@ -116,14 +116,9 @@ struct RefineParams {
 // one warp per (member, row): filter the two half-row candidate lists by the final threshold, re-evaluate every survivor
 // in fp32 with the member weight theta +- f32(sigma)*eps (algorithm/nets.py:113), pick the reference's argmax of float32
 // log-probs (lowest index among equal rounded log-probs, captioning/nets.py:202-208)
-__global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
-    __shared__ int s_idx[4][32];
-    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
-    const int64_t wid = (int64_t)blockIdx.x * 4 + wq;
-    if (wid >= p.n_members * p.rows) return;
-    const int64_t member = wid / p.rows;
-    const int r = (int)(wid % p.rows);
-    const int64_t grow = member * p.rows_pad + r;
+// -> false if the row's lists overflowed (its unit is flagged for the fallback), else idx / best = arg-max column and its log-prob
+__device__ __forceinline__ bool refine_row(const RefineParams& p, int64_t member, int r, int64_t grow, int lane, int wq, int (*s_idx)[32],
+                                           int& idx_out, float& best_out) {
     CandHead hd[kCandLists];
     float M = -INFINITY;
     bool overflow = p.force_overflow != 0;
@@ -155,7 +150,7 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
     }
     if (overflow) {                                            // more candidates than the lists / one warp hold
         if (lane == 0) { p.unit_flag[member * p.m_tiles + r / 128] = 1; if (p.stats) atomicAdd(&p.stats[2], 1ull); }
-        return;
+        return false;
     }
     __syncwarp();
     float S = 0.f;
@@ -231,8 +226,20 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
         const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
         if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
     }
-    if (lane == 0) { p.tok[grow] = idx; p.lp[grow] = best; }
     if (p.stats && lane == 0) { atomicAdd(&p.stats[0], 1ull); atomicAdd(&p.stats[1], (unsigned long long)count); }
+    idx_out = idx; best_out = best;
+    return true;
+}
+__global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
+    __shared__ int s_idx[4][32];
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    const int64_t wid = (int64_t)blockIdx.x * 4 + wq;
+    if (wid >= p.n_members * p.rows) return;
+    const int64_t member = wid / p.rows;
+    const int r = (int)(wid % p.rows);
+    const int64_t grow = member * p.rows_pad + r;
+    int idx; float best;
+    if (refine_row(p, member, r, grow, lane, wq, s_idx, idx, best) && lane == 0) { p.tok[grow] = idx; p.lp[grow] = best; }
 }
 
 // Fallback of the HYBRID projection when member weights carry a safe-mutation scale (the factored split-fp16 kernel cannot

@@ -208,6 +208,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(352, 1) k_lstm_pair(
             tc::mbar_wait(&tfull_bar[buf], (it >> 1) & 1);
             tc::tc_fence_after();
             const uint32_t trow = tmem_base + buf * C::ACC_STRIDE + ((uint32_t)(q * 32) << 16);
+            float hs = 0.f;
 #pragma unroll
             for (int sb = 0; sb < kLstmSubBatches; ++sb) {
                 const int cu = hf * kLstmHalfUnits + sb * 8;                 // first unit of this sub-batch inside the tile
@@ -233,7 +234,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(352, 1) k_lstm_pair(
                     *reinterpret_cast<float4*>(cp + 4) = *reinterpret_cast<float4*>(&cn[4]);
                     __half hh[8], hl[8];
 #pragma unroll
-                    for (int uu = 0; uu < 8; ++uu) split_half_dev(hn[uu], kActScale, hh[uu], hl[uu]);
+                    for (int uu = 0; uu < 8; ++uu) { split_half_dev(hn[uu], kActScale, hh[uu], hl[uu]); hs = fmaf(hn[uu], hn[uu], hs); }
                     *reinterpret_cast<uint4*>(p.out_hi + grow * p.N + j0) = *reinterpret_cast<uint4*>(hh);
                     *reinterpret_cast<uint4*>(p.out_lo + grow * p.N + j0) = *reinterpret_cast<uint4*>(hl);
                     if (p.h_trace) {
@@ -243,6 +244,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(352, 1) k_lstm_pair(
                     }
                 }
             }
+            if (p.hsq && row_ok) p.hsq[grow * p.hsq_n + nt * 2 + hf] = hs;      // this (tile, half)'s piece of the row's |h|^2 (HYBRID margin)
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&tempty_bar[buf]);
