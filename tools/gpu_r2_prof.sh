@@ -10,7 +10,7 @@ python tools/ncu_agg.py gpurun_out/${tag}_launches.csv > gpurun_out/${tag}_launc
 # generation 0 of the bench is the fresh-model one (scaled kernels) and every generation first scores its 2 elite candidates with tiny
 # launches: the skip counts (-s) land on the full-size launches of generation 1 (indices read off the launch list)
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_lstm_pair|k_member_dense" -s 104 -c 4 -o gpurun_out/${tag}_full_dense -f $CMD > gpurun_out/${tag}_ncu_full_dense.log 2>&1; echo "ncu full dense rc=$?"
-timeout 900 ncu --set full --clock-control none -k regex:"k_materialise|k_refine|k_finalize|k_row_margin|k_member_gemm|k_es_select|k_evolve_batch" -s 180 -c 24 -o gpurun_out/${tag}_full_aux -f $CMD > gpurun_out/${tag}_ncu_full_aux.log 2>&1; echo "ncu full aux rc=$?"
+timeout 900 ncu --set full --clock-control none -k regex:"k_materialise|k_refine_finalize|k_finalize|k_member_gemm|k_es_select|k_evolve_batch" -s 168 -c 14 -o gpurun_out/${tag}_full_aux -f $CMD > gpurun_out/${tag}_ncu_full_aux.log 2>&1; echo "ncu full aux rc=$?"
 timeout 600 ncu --set full --clock-control none -k regex:"k_gradient" -s 3 -c 2 -o gpurun_out/${tag}_full_master -f python bench.py --steps 1 --warmup 1 --population 148 --cpu-seconds 1 --nes-pairs 0 > gpurun_out/${tag}_ncu_full_master.log 2>&1; echo "ncu full master rc=$?"
 for k in dense aux master; do
   python tools/ncu_full.py gpurun_out/${tag}_full_$k.ncu-rep > gpurun_out/${tag}_full_${k}_summary.txt 2>&1
