@@ -291,6 +291,7 @@ def main():
             offs = offs[:1].expand(Pg).contiguous()
         mark()
         elite = elite_scores_device()
+        mark()
         ctx.rollout(offs[lo:lo + P], ones, fc_dev, pop.sigma, parents=slots[lo:lo + P], precision=prec, out_device=dev)
         mark()
         fit = gather(ctx.logprob_fitness(P, rows, device=dev))
@@ -357,14 +358,14 @@ def main():
     prof = ctx.profile_read()
     per_rank = None
     if a.sections:
-        n = 5
+        n = 6
         tail = sections[-n * a.steps:]
-        names = ['sample', 'elites+rollout', 'fitness+gather', 'podium+select+evolve']
-        acc = [0.0] * 4
+        names = ['sample', 'elite_candidates', 'rollout', 'fitness+gather', 'podium+select+evolve']
+        acc = [0.0] * (n - 1)
         for k in range(a.steps):
-            for j in range(4):
+            for j in range(n - 1):
                 acc[j] += tail[k * n + j].elapsed_time(tail[k * n + j + 1])
-        between = sum(tail[k * n + 4].elapsed_time(tail[(k + 1) * n]) for k in range(a.steps - 1)) / max(1, a.steps - 1)
+        between = sum(tail[k * n + n - 1].elapsed_time(tail[(k + 1) * n]) for k in range(a.steps - 1)) / max(1, a.steps - 1)
         mine = {nm: round(v / a.steps, 3) for nm, v in zip(names, acc)}
         mine.update(between_steps=round(between, 3), own_ms_per_step=round(ms_own / a.steps, 3), rank=rank)
         try:

@@ -149,15 +149,22 @@ struct FinalizeParams {
 };
 // what happens to a row once its arg-max token and log-prob are known: the finished-mask bookkeeping of captioning/nets.py:233-243, the
 // seq / log-prob writes, and the gather of the next input embedding theta_emb[it] +- sigma eps_emb[it] (t = 0: the <bos> gather only)
-__device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t member, int r, int64_t grow, int lane, int idx, float best) {
+// the two loads of finalize_row that do not depend on the token: issued before the candidate re-evaluation, not after it
+struct FinalizePre { int unf_prev; int prev; };
+__device__ __forceinline__ FinalizePre finalize_prefetch(const FinalizeParams& p, int64_t member, int64_t grow) {
+    FinalizePre q; q.unf_prev = 1; q.prev = 1;
+    if (p.t > 1) { q.unf_prev = p.unf_count[(p.t - 1) * p.W + member]; q.prev = p.unfinished[grow]; }
+    return q;
+}
+__device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t member, int r, int64_t grow, int lane, int idx, float best, const FinalizePre pre) {
     const float sgn = p.sign[member];
     int64_t tok = 0;
     if (p.t >= 1) {
         const float logp = best;                                  // = max log-prob
-        const bool done = p.t > 1 && p.unf_count[(p.t - 1) * p.W + member] == 0;   // the reference broke out of the loop
+        const bool done = p.t > 1 && pre.unf_prev == 0;           // the reference broke out of the loop
         int64_t it = 0;
         if (!done) {
-            const bool prev = p.t == 1 ? true : (p.unfinished[grow] != 0);
+            const bool prev = p.t == 1 ? true : (pre.prev != 0);
             const bool unf = prev && idx > 0;
             it = unf ? idx : 0;
             if (lane == 0) {
@@ -257,13 +264,13 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
         }
         }
     }
-    finalize_row(p, member, r, grow, lane, idx, best);
+    finalize_row(p, member, r, grow, lane, idx, best, finalize_prefetch(p, member, grow));
 }
 
 // HYBRID: the fp32 re-evaluation of a row's arg-max candidates (refine_row, hybrid.cuh) and everything that follows from the token
 // (finalize_row) in one pass, one warp per (member, row).  A row whose candidate lists overflowed is flagged instead (row_flag, and its
 // unit for the fallback projection); k_finalize with row_flag set picks those up after the fallback.
-__global__ void __launch_bounds__(128) k_refine_finalize(const RefineParams rp, const FinalizeParams fp, uint8_t* __restrict__ row_flag) {
+__global__ void __launch_bounds__(128, 6) k_refine_finalize(const RefineParams rp, const FinalizeParams fp, uint8_t* __restrict__ row_flag) {
     __shared__ int s_idx[4][32];
     const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
     const int64_t wid = (int64_t)blockIdx.x * 4 + wq;
@@ -272,9 +279,10 @@ __global__ void __launch_bounds__(128) k_refine_finalize(const RefineParams rp, 
     const int r = (int)(wid % rp.rows);
     const int64_t grow = member * rp.rows_pad + r;
     int idx = 0; float best = 0.f;
+    const FinalizePre pre = finalize_prefetch(fp, member, grow);
     const bool ok = refine_row(rp, member, r, grow, lane, wq, s_idx, idx, best);
     if (lane == 0) row_flag[grow] = ok ? 0 : 1;
-    if (ok) finalize_row(fp, member, r, grow, lane, idx, best);
+    if (ok) finalize_row(fp, member, r, grow, lane, idx, best, pre);
 }
 
 // vbn_e (captioning/nets.py:156-165): nn.BatchNorm1d(E, track_running_stats=False) on the output of img_embed / embed -- every feature
@@ -378,6 +386,99 @@ __global__ void __launch_bounds__(256) k_sample(const SampleParams p) {
         int idx = 0x7fffffff;
         for (int w = 0; w < 8; ++w) idx = min(idx, s_i[w]);
         if (idx >= p.V1) idx = p.V1 - 1;         // u within rounding of 1: the last entry, as searchsorted would clamp through choice's own check
+        p.tok[grow] = idx;
+        p.lp[grow] = __fsub_rn(__fsub_rn(lg[idx], mx), lse);
+    }
+}
+
+// The same sampler for 16-byte aligned logit rows of at most 1024 * NV entries (the dense projection pads ld to a multiple of 4): the row is
+// read from global memory ONCE, 128 bits at a time with every load in flight together, and lives in registers through the max / sum-exp /
+// probability passes (k_sample walks the row three times with a few loads in flight: 4 ms per step of 1000 members at V = 9487).
+template <int NV>
+__global__ void __launch_bounds__(256) k_sample_reg(const SampleParams p) {
+    extern __shared__ float s_p[];               // V1 probabilities, padded to a multiple of 4
+    __shared__ float s_f[8];
+    __shared__ double s_d[8];
+    __shared__ int s_i[8];
+    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
+    const int64_t member = blockIdx.x / p.rows;
+    const int r = (int)(blockIdx.x % p.rows);
+    const int64_t grow = member * p.rows_pad + r;
+    const float* lg = p.logits + (member * p.row_stride + r) * p.ld;
+    const float4* lg4 = reinterpret_cast<const float4*>(lg);
+    const int n4 = (p.V1 + 3) / 4;
+    float v[NV][4];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int q = tid + 256 * i;
+        float4 x = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        if (q < n4) x = lg4[q];
+        v[i][0] = x.x; v[i][1] = x.y; v[i][2] = x.z; v[i][3] = x.w;
+    }
+    {   // the padding columns of the last 128-bit word hold nothing meaningful
+        const int q = (n4 - 1) & 255, i_last = (n4 - 1) >> 8;
+        if (tid == q) {
+#pragma unroll
+            for (int i = 0; i < NV; ++i) if (i == i_last) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (4 * (n4 - 1) + e >= p.V1) v[i][e] = -INFINITY;
+            }
+        }
+    }
+    auto block_sum = [&](float x) { for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o); __syncthreads(); if (lane == 0) s_f[wq] = x; __syncthreads();
+                                    float a = 0.f; for (int w = 0; w < 8; ++w) a += s_f[w]; return a; };
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) mx = fmaxf(fmaxf(fmaxf(v[i][0], v[i][1]), fmaxf(v[i][2], v[i][3])), mx);
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) s_f[wq] = mx;
+    __syncthreads();
+    mx = s_f[0];
+    for (int w = 1; w < 8; ++w) mx = fmaxf(mx, s_f[w]);
+    float se = 0.f;                              // log_softmax(x) = (x - max) - log(sum exp(x - max)) (captioning/nets.py:202)
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) se += expf(v[i][e] - mx);
+    }
+    se = block_sum(se);
+    const float lse = logf(se);
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int q = tid + 256 * i;
+        float4 pr;
+        pr.x = expf(__fsub_rn(__fsub_rn(v[i][0], mx), lse)); pr.y = expf(__fsub_rn(__fsub_rn(v[i][1], mx), lse));
+        pr.z = expf(__fsub_rn(__fsub_rn(v[i][2], mx), lse)); pr.w = expf(__fsub_rn(__fsub_rn(v[i][3], mx), lse));
+        acc += (pr.x + pr.y) + (pr.z + pr.w);
+        if (q < n4) reinterpret_cast<float4*>(s_p)[q] = pr;
+    }
+    const float norm1 = block_sum(acc);          // its second barrier also publishes s_p
+    // float64 cdf over contiguous chunks
+    const int C = (p.V1 + 255) / 256, j0 = tid * C, j1 = min(p.V1, j0 + C);
+    double loc = 0.0;
+    for (int j = j0; j < j1; ++j) { const float nj = __fdiv_rn(s_p[j], norm1); s_p[j] = nj; loc += (double)nj; }
+    double inc = loc;                            // inclusive scan over the 256 chunk sums
+    for (int o = 1; o < 32; o <<= 1) { const double x = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += x; }
+    if (lane == 31) s_d[wq] = inc;
+    __syncthreads();
+    double base = 0.0, total = 0.0;
+    for (int w = 0; w < 8; ++w) { if (w < wq) base += s_d[w]; total += s_d[w]; }
+    const double u = p.u[(member * p.rows + r) * p.T + (p.t - 1)];
+    double run = base + (inc - loc);
+    int first = 0x7fffffff;
+    const double pre = u * total * (1.0 - 1e-15);
+    // the crossing lies in the first chunk whose end reaches the threshold: chunks that end below it are skipped, and so are chunks that
+    // START well above it (one of their predecessors holds it) -- one or two threads of the block walk their 38 entries
+    if (base + inc >= pre && run <= u * total * (1.0 + 1e-12))
+        for (int j = j0; j < j1; ++j) { run += (double)s_p[j]; if (first == 0x7fffffff && run >= pre && run / total > u) first = j; }
+    for (int o = 16; o > 0; o >>= 1) first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+    if (lane == 0) s_i[wq] = first;
+    __syncthreads();
+    if (tid == 0) {
+        int idx = 0x7fffffff;
+        for (int w = 0; w < 8; ++w) idx = min(idx, s_i[w]);
+        if (idx >= p.V1) idx = p.V1 - 1;
         p.tok[grow] = idx;
         p.lp[grow] = __fsub_rn(__fsub_rn(lg[idx], mx), lse);
     }
@@ -727,7 +828,8 @@ static int launch_dense(Ctx* c, DenseParams& p, int64_t n_members) {
     NES_CHECK(units >= 1 && units < (1ll << 31), "bad unit count");
     p.n_units = (int32_t)units;
     const int sms = sm_count(c);
-    const int64_t items = EPI != DEN_LOGITC ? units * p.n_tiles : units;   // see k_member_dense: LSTM / PLAIN work items are (unit, tile) pairs
+    if (p.n_split < 1) { p.n_split = 1; p.tiles_per_split = p.n_tiles; }
+    const int64_t items = EPI != DEN_LOGITC ? units * p.n_tiles : units * p.n_split;   // see k_member_dense: LSTM / PLAIN work items are (unit, tile) pairs
     NES_CHECK(items < (1ll << 31), "too many work items");
     const unsigned grid = (unsigned)(items < sms ? items : sms);
     ProfScope prof(c, EPI == DEN_LSTM ? PROF_LSTM : (EPI == DEN_PLAIN ? PROF_PLAIN : PROF_LOGIT));
@@ -995,7 +1097,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
             GemmParams p = base;
             p.nseg = 1; p.N = E; p.chunk_stride = 0; p.n_tiles = (E + 127) / 128;
             if (fill_seg(c, p, 0, ws->fc_hi, ws->fc_lo, ws->fc_members * ws->rows_pad, Fd, shared_batch ? 1 : 0, T_IMG_W, T_IMG_B, 128, precision)) return 1;
-            if (shared_batch && precision == NES_PREC_EXACT) {
+            if (shared_batch && precision == NES_PREC_EXACT && n_members >= 2 * (int64_t)c->n_parents) {     // it pays when members outnumber the slots
                 // every member sees the same features: x theta_p^T + theta_b once per parent slot (sigma = 0 pseudo members), then the
                 // members only add their sigma * x eps^T (2 of the 5 split-fp16 passes, no theta tiles through shared memory)
                 const int np = c->n_parents;
@@ -1117,6 +1219,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                         k_row_margin<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(mg); c->launches++;
                     }
                     NES_CUDA(cudaGetLastError());
+                    int n_split = 1;
                     {
                         DenseParams pc{};
                         const int bk = DenseCfg<DEN_LOGITC>::BK;
@@ -1131,6 +1234,16 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                             pc.hsq = ws->hsq; pc.hsq_n = ws->hsq_n; pc.mg_parent = base.parent; pc.mg_theta_rowmax = c->d_theta_rowmax;
                             pc.mg_eps_rowmax = c->d_eps_rowmax; pc.mg_scale_max = c->d_scale_max; pc.mg_sigma = sigma; pc.margin_out = ws->margin;
                         }
+                        // a handful of units (the elite candidates of a NIC-ES generation): cut every unit's vocabulary sweep into ranges so
+                        // that the launch spreads over the SMs (0.15 ms -> 0.02 ms per step for 2 members); the lists of a row multiply
+                        const int64_t units = nm * m_tiles;
+                        const int64_t cap = ((int64_t)ws->W * ws->rows_pad) / (nm * rows_pad);
+                        int64_t sp = std::min<int64_t>(std::min<int64_t>(sm_count(c) / units, cap), ws->ntv);
+                        const char* se = getenv("NES_LOGITC_SPLIT");                  // tests: 0 keeps few-member calls on whole-unit work items
+                        if (se && atoi(se) == 0) sp = 1;
+                        pc.n_split = 1; pc.tiles_per_split = ws->ntv;
+                        if (sp >= 2) { pc.tiles_per_split = (int32_t)((ws->ntv + sp - 1) / sp); pc.n_split = (ws->ntv + pc.tiles_per_split - 1) / pc.tiles_per_split; }
+                        n_split = pc.n_split;
                         if (launch_dense<DEN_LOGITC>(c, pc, nm)) return 1;
                     }
                     NES_CUDA(cudaMemsetAsync(ws->unit_flag, 0, (size_t)nm * m_tiles, c->stream));
@@ -1140,7 +1253,7 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     rf.off = base.off; rf.sign = base.sign; rf.parent = base.parent; rf.theta32 = c->theta32; rf.table = c->table; rf.D = L.D; rf.scale = c->scale32; rf.scale_div = c->scale_div;
                     rf.w_start = L.t[c->tix[T_LOGIT_W]].start; rf.w_pstart = L.t[c->tix[T_LOGIT_W]].pstart; rf.b_start = L.t[c->tix[T_LOGIT_B]].start; rf.b_pstart = L.t[c->tix[T_LOGIT_B]].pstart;
                     rf.sigma = sigma; rf.tok = ws->pre_tok; rf.lp = ws->pre_lp; rf.unit_flag = ws->unit_flag; rf.stats = c->profiling ? ws->stats : nullptr;
-                    rf.force_overflow = (env_debug() & 64) ? 1 : 0;
+                    rf.force_overflow = (env_debug() & 64) ? 1 : 0; rf.n_split = n_split;
                     { ProfScope prof(c, PROF_FINALIZE);       // (3) + the rows' bookkeeping and next-input gather, for every row that did not overflow
                       k_refine_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(rf, make_fin(t), ws->row_flag); c->launches++; }
                     NES_CUDA(cudaGetLastError());
@@ -1175,10 +1288,21 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     sp.logits = ws->samp_logits; sp.partials = samp_dense ? nullptr : ws->partials; sp.n_tiles = 2; sp.u = ws->d_uniforms + m0 * rows * T;
                     sp.ld = samp_dense ? samp_ld : V1; sp.row_stride = samp_dense ? rows_pad : rows;
                     sp.rows = rows; sp.rows_pad = rows_pad; sp.T = T; sp.t = t; sp.V1 = V1; sp.n_members = nm; sp.tok = ws->pre_tok; sp.lp = ws->pre_lp;
-                    const size_t smem = sizeof(float) * V1;
-                    if (smem > 48 * 1024) { static size_t set_to = 0; if (set_to < smem) { NES_CUDA(cudaFuncSetAttribute(k_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set_to = smem; } }
+                    const size_t smem = sizeof(float) * ((V1 + 3) / 4 * 4);
+                    const int n4 = (V1 + 3) / 4;
+                    const bool vec = sp.ld % 4 == 0 && (reinterpret_cast<uintptr_t>(sp.logits) & 15) == 0 && n4 <= 256 * 10;
                     ProfScope prof(c, PROF_FINALIZE);
-                    k_sample<<<(unsigned)(nm * rows), 256, smem, c->stream>>>(sp); c->launches++;
+                    if (vec && n4 <= 256 * 2) {
+                        k_sample_reg<2><<<(unsigned)(nm * rows), 256, smem, c->stream>>>(sp);
+                    } else if (vec) {
+                        static bool attr_set = false;
+                        if (!attr_set) { NES_CUDA(cudaFuncSetAttribute(k_sample_reg<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 256 * 10 * 4)); attr_set = true; }
+                        k_sample_reg<10><<<(unsigned)(nm * rows), 256, smem, c->stream>>>(sp);
+                    } else {
+                        if (smem > 48 * 1024) { static size_t set_to = 0; if (set_to < smem) { NES_CUDA(cudaFuncSetAttribute(k_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set_to = smem; } }
+                        k_sample<<<(unsigned)(nm * rows), 256, smem, c->stream>>>(sp);
+                    }
+                    c->launches++;
                     NES_CUDA(cudaGetLastError());
                 }
             }

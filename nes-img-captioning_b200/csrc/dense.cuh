@@ -37,6 +37,7 @@ constexpr int kCandLists = NES_LOGITC_WARPS / 4;               // lists per row:
 
 struct alignas(16) CandHead { float mx; float sum; int32_t n; int32_t pad; };
 struct alignas(8) CandEntry { float v; int32_t idx; };
+static_assert(kCandCap >= 32, "refine_row reads the first 32 entries of every list unconditionally");
 
 struct alignas(64) DenseParams {
     CUtensorMap a_hi[2], a_lo[2];           // activations of segment s: [rows_total, K_s] fp16, box BK x 128
@@ -50,6 +51,9 @@ struct alignas(64) DenseParams {
     float* c_state; __half* out_hi; __half* out_lo; float* h_trace;       // LSTM (PLAIN: out_hi / out_lo and / or out_f32)
     float* out_f32; int32_t ld_out;                                       // PLAIN: [member*rows_pad + row, ld_out] float32 (nullable)
     CandHead* heads; CandEntry* entries; const float* margin;            // LOGITC
+    // LOGITC with few units (the elite candidates of a NIC-ES generation): the vocabulary sweep of a unit is cut into n_split ranges of
+    // tiles_per_split tiles, one work item each, so that 2 units keep more than 2 SMs busy; row `grow` then owns n_split * kCandLists lists
+    int32_t n_split, tiles_per_split;
     // the row's |h|^2 in pieces, written by the cell kernel that produced h (LSTM: one piece per (tile, column half)) and summed by the
     // LOGITC epilogue into the HYBRID error margin (hybrid.cuh: k_row_margin's formula) -- saves a pass over h per decode step
     float* hsq; int32_t hsq_n;                                            // [row * hsq_n + piece]; LSTM writes, LOGITC reads (nullable)
@@ -119,7 +123,7 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
     // work items: LSTM = (unit, weight tile) pairs in tile-minor order, so the CTAs that run concurrently share a unit's
     // activation block through L2 (it is fetched from HBM once, not once per tile); LOGITC = whole units, because the
     // running arg-max / sum-exp of a row lives in one thread's registers across all vocabulary tiles
-    const int n_items = C::SPLIT ? p.n_units * p.n_tiles : p.n_units;
+    const int n_items = C::SPLIT ? p.n_units * p.n_tiles : p.n_units * p.n_split;
 
     if (warp == 0 || warp == 10) {
         // =========================== TMA producers (two warps fill alternate stages) ===========================
@@ -131,8 +135,9 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
             }
             int stage = 0; uint32_t phase = 0; uint32_t q = 0; uint32_t uc = 0;
             for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++uc) {
-                const int u = C::SPLIT ? item / p.n_tiles : item;
-                const int nt0 = C::SPLIT ? item - u * p.n_tiles : 0, nt1 = C::SPLIT ? nt0 + 1 : p.n_tiles;
+                const int u = C::SPLIT ? item / p.n_tiles : item / p.n_split;
+                const int nt0 = C::SPLIT ? item - u * p.n_tiles : (item - u * p.n_split) * p.tiles_per_split;
+                const int nt1 = C::SPLIT ? nt0 + 1 : min(p.n_tiles, nt0 + p.tiles_per_split);
                 const int64_t member = u / p.m_tiles;
                 const int mt = u % p.m_tiles;
                 const int32_t a_row = (int32_t)((p.a_shared ? 0 : member * p.rows_pad) + mt * C::BM);
@@ -175,7 +180,8 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
             int stage = 0; uint32_t phase = 0; uint32_t it = 0; uint32_t uc = 0;
             constexpr uint32_t idesc = tc::make_idesc_f16(128, C::BN);
             for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++uc) {
-                const int nt0 = C::SPLIT ? item % p.n_tiles : 0, nt1 = C::SPLIT ? nt0 + 1 : p.n_tiles;
+                const int nt0 = C::SPLIT ? item % p.n_tiles : (item % p.n_split) * p.tiles_per_split;
+                const int nt1 = C::SPLIT ? nt0 + 1 : min(p.n_tiles, nt0 + p.tiles_per_split);
                 for (int nt = nt0; nt < nt1; ++nt, ++it) {
                     const uint32_t buf = it & 1;
                     tc::mbar_wait(&tempty_bar[buf], ((it >> 1) & 1) ^ 1);
@@ -185,7 +191,7 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
                     for (int s = 0; s < p.nseg; ++s) {
                         const int nkb = p.K[s] / C::BK;
                         for (int kb = 0; kb < nkb; ++kb) {
-                            if (!C::SPLIT && nt == 0) tc::mbar_wait(&afull_bar[kb], uc & 1);
+                            if (!C::SPLIT && nt == nt0) tc::mbar_wait(&afull_bar[kb], uc & 1);
                             tc::mbar_wait(&full_bar[stage], phase);
                             tc::tc_fence_after();
                             const uint32_t st = tc::smem_u32(ring + stage * C::STAGE_BYTES);
@@ -206,7 +212,7 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
                             }
                             first = false;
                             tc::umma_commit(&empty_bar[stage]);
-                            if (!C::SPLIT && nt == p.n_tiles - 1) tc::umma_commit(&aempty_bar[kb]);
+                            if (!C::SPLIT && nt == nt1 - 1) tc::umma_commit(&aempty_bar[kb]);
                             if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                         }
                     }
@@ -231,11 +237,14 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
             const int col = nt * C::BN + et;
             return col < p.bias_stride ? p.bias[member * p.bias_stride + col] : 0.f;
         };
-        float b_cur = C::SPLIT ? bias_val(blockIdx.x / p.n_tiles, blockIdx.x % p.n_tiles) : bias_val(blockIdx.x, 0);
+        float b_cur = C::SPLIT ? bias_val(blockIdx.x / p.n_tiles, blockIdx.x % p.n_tiles)
+                               : bias_val(blockIdx.x / p.n_split, (blockIdx.x % p.n_split) * p.tiles_per_split);
         uint32_t it = 0;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int u = C::SPLIT ? item / p.n_tiles : item;
-            const int nt0 = C::SPLIT ? item - u * p.n_tiles : 0, nt1 = C::SPLIT ? nt0 + 1 : p.n_tiles;
+            const int u = C::SPLIT ? item / p.n_tiles : item / p.n_split;
+            const int sp = C::SPLIT ? 0 : item - u * p.n_split;
+            const int nt0 = C::SPLIT ? item - u * p.n_tiles : sp * p.tiles_per_split;
+            const int nt1 = C::SPLIT ? nt0 + 1 : min(p.n_tiles, nt0 + p.tiles_per_split);
             const int64_t member = u / p.m_tiles;
             const int mt = u % p.m_tiles;
             const int m_local = mt * C::BM + row;
@@ -254,7 +263,8 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
                     if (hf == 0) p.margin_out[grow] = margin;             // k_refine_finalize filters the lists with the same number
                 } else margin = p.margin[grow];
             }
-            CandEntry* ent = EPI != DEN_LOGITC ? nullptr : p.entries + (grow * kCandLists + hf) * (int64_t)kCandCap;
+            const int64_t list = EPI != DEN_LOGITC ? 0 : (grow * p.n_split + sp) * kCandLists + hf;
+            CandEntry* ent = EPI != DEN_LOGITC ? nullptr : p.entries + list * (int64_t)kCandCap;
 
             for (int nt = nt0; nt < nt1; ++nt, ++it) {
                 const uint32_t buf = it & 1;
@@ -264,7 +274,7 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
                 {
                     const int nx = item + (int)gridDim.x;                  // first tile of this CTA's next work item
                     b_cur = (nt + 1 < nt1) ? bias_val(u, nt + 1)
-                          : (C::SPLIT ? bias_val(nx / p.n_tiles, nx % p.n_tiles) : bias_val(nx, 0));
+                          : (C::SPLIT ? bias_val(nx / p.n_tiles, nx % p.n_tiles) : bias_val(nx / p.n_split, (nx % p.n_split) * p.tiles_per_split));
                 }
                 float cprev[kLstmHalfUnits];
                 if (C::LSTM) {
@@ -404,7 +414,7 @@ __global__ void __launch_bounds__(DenseCfg<EPI>::THREADS, 1) k_member_dense(cons
             }
             if (EPI == DEN_LOGITC && row_ok) {
                 CandHead hd; hd.mx = run_max; hd.sum = run_sum; hd.n = n_cand; hd.pad = 0;
-                *reinterpret_cast<float4*>(&p.heads[grow * kCandLists + hf]) = *reinterpret_cast<float4*>(&hd);
+                *reinterpret_cast<float4*>(&p.heads[list]) = *reinterpret_cast<float4*>(&hd);
             }
         }
         tc::tc_fence_before();

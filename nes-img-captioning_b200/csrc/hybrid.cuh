@@ -112,6 +112,7 @@ struct RefineParams {
     uint8_t* unit_flag;                               // [n_members*m_tiles]: 1 -> recompute this unit with the split-fp16 kernel
     unsigned long long* stats;                        // nullable: [0] rows refined, [1] candidates evaluated, [2] rows overflowed
     int force_overflow;                               // NES_DEBUG bit 6 (64): every row takes the fallback (tests)
+    int n_split;                                      // lists of a row: n_split * kCandLists (DenseParams::n_split; 1 for full-size launches)
 };
 // one warp per (member, row): filter the two half-row candidate lists by the final threshold, re-evaluate every survivor
 // in fp32 with the member weight theta +- f32(sigma)*eps (algorithm/nets.py:113), pick the reference's argmax of float32
@@ -119,44 +120,6 @@ struct RefineParams {
 // -> false if the row's lists overflowed (its unit is flagged for the fallback), else idx / best = arg-max column and its log-prob
 __device__ __forceinline__ bool refine_row(const RefineParams& p, int64_t member, int r, int64_t grow, int lane, int wq, int (*s_idx)[32],
                                            int& idx_out, float& best_out) {
-    CandHead hd[kCandLists];
-    float M = -INFINITY;
-    bool overflow = p.force_overflow != 0;
-#pragma unroll
-    for (int hf = 0; hf < kCandLists; ++hf) {
-        hd[hf] = p.heads[grow * kCandLists + hf];
-        M = fmaxf(M, hd[hf].mx);
-        overflow = overflow || hd[hf].n > kCandCap;
-    }
-    const float thr = M - p.margin[grow];
-    int count = 0;
-    if (!overflow) {
-#pragma unroll
-        for (int hf = 0; hf < kCandLists; ++hf) {
-            const int n = hd[hf].n;
-            const CandEntry* ent = p.entries + (grow * kCandLists + hf) * (int64_t)kCandCap;
-            for (int e0 = 0; e0 < n; e0 += 32) {
-                const int e = e0 + lane;
-                CandEntry ce; ce.v = -INFINITY; ce.idx = 0;
-                if (e < n) ce = ent[e];
-                const bool ok = e < n && ce.v >= thr;
-                const unsigned bal = __ballot_sync(0xffffffffu, ok);
-                const int pos = count + __popc(bal & ((1u << lane) - 1u));
-                if (ok && pos < 32) s_idx[wq][pos] = ce.idx;
-                count += __popc(bal);
-            }
-        }
-        overflow = count > 32;
-    }
-    if (overflow) {                                            // more candidates than the lists / one warp hold
-        if (lane == 0) { p.unit_flag[member * p.m_tiles + r / 128] = 1; if (p.stats) atomicAdd(&p.stats[2], 1ull); }
-        return false;
-    }
-    __syncwarp();
-    float S = 0.f;
-#pragma unroll
-    for (int hf = 0; hf < kCandLists; ++hf) S += hd[hf].sum * expf(hd[hf].mx - M);
-    const int my_idx = lane < count ? s_idx[wq][lane] : -1;
     const float ssig = p.sign[member] > 0.f ? p.sigma : -p.sigma;      // theta - fl(sigma eps) == theta + fl(-sigma eps), bit for bit
     const int64_t off = p.off[member];
     const int par = p.parent ? p.parent[member] : 0;
@@ -177,6 +140,79 @@ __device__ __forceinline__ bool refine_row(const RefineParams& p, int64_t member
             }
         }
     }
+    const float mg = p.margin[grow];
+    float M = -INFINITY, S = 0.f;
+    bool overflow = p.force_overflow != 0;
+    int count = 0;
+    if (p.n_split == 1) {
+        // every load whose address does not depend on another load goes out first (heads, the first 32 entries of each list whether or
+        // not they are all in use -- kCandCap >= 32 --, the margin and the hidden state above): one DRAM round trip, not six dependent ones
+        CandHead hd[kCandLists];
+        CandEntry pre[kCandLists];
+#pragma unroll
+        for (int hf = 0; hf < kCandLists; ++hf) {
+            hd[hf] = p.heads[grow * kCandLists + hf];
+            pre[hf] = p.entries[(grow * kCandLists + hf) * (int64_t)kCandCap + lane];
+        }
+#pragma unroll
+        for (int hf = 0; hf < kCandLists; ++hf) {
+            M = fmaxf(M, hd[hf].mx);
+            overflow = overflow || hd[hf].n > kCandCap;
+        }
+        const float thr = M - mg;
+        if (!overflow) {
+#pragma unroll
+            for (int hf = 0; hf < kCandLists; ++hf) {
+                const int n = hd[hf].n;
+                const CandEntry* ent = p.entries + (grow * kCandLists + hf) * (int64_t)kCandCap;
+                for (int e0 = 0; e0 < n; e0 += 32) {
+                    const int e = e0 + lane;
+                    CandEntry ce = pre[hf];
+                    if (e0 > 0) { ce.v = -INFINITY; ce.idx = 0; if (e < n) ce = ent[e]; }
+                    const bool ok = e < n && ce.v >= thr;
+                    const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                    const int pos = count + __popc(bal & ((1u << lane) - 1u));
+                    if (ok && pos < 32) s_idx[wq][pos] = ce.idx;
+                    count += __popc(bal);
+                }
+            }
+        }
+#pragma unroll
+        for (int hf = 0; hf < kCandLists; ++hf) S += hd[hf].sum * expf(hd[hf].mx - M);
+    } else {
+        // few-unit launches: the row's vocabulary sweep was cut into n_split ranges with kCandLists lists each (dense.cuh)
+        const int n_lists = p.n_split * kCandLists;
+        const CandHead* hd = p.heads + grow * n_lists;
+        for (int l = lane; l < n_lists; l += 32) { const CandHead h = hd[l]; M = fmaxf(M, h.mx); overflow = overflow || h.n > kCandCap; }
+        M = warp_max(M);
+        overflow = __any_sync(0xffffffffu, overflow);
+        for (int l = lane; l < n_lists; l += 32) { const CandHead h = hd[l]; if (h.mx > -INFINITY) S += h.sum * expf(h.mx - M); }
+        S = warp_sum(S);
+        const float thr = M - mg;
+        if (!overflow) {
+            for (int l = 0; l < n_lists; ++l) {
+                const int n = hd[l].n;
+                const CandEntry* ent = p.entries + (grow * n_lists + l) * (int64_t)kCandCap;
+                for (int e0 = 0; e0 < n; e0 += 32) {
+                    const int e = e0 + lane;
+                    CandEntry ce; ce.v = -INFINITY; ce.idx = 0;
+                    if (e < n) ce = ent[e];
+                    const bool ok = e < n && ce.v >= thr;
+                    const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                    const int pos = count + __popc(bal & ((1u << lane) - 1u));
+                    if (ok && pos < 32) s_idx[wq][pos] = ce.idx;
+                    count += __popc(bal);
+                }
+            }
+        }
+    }
+    overflow = overflow || count > 32;
+    if (overflow) {                                            // more candidates than the lists / one warp hold
+        if (lane == 0) { p.unit_flag[member * p.m_tiles + r / 128] = 1; if (p.stats) atomicAdd(&p.stats[2], 1ull); }
+        return false;
+    }
+    __syncwarp();
+    const int my_idx = lane < count ? s_idx[wq][lane] : -1;
     const float* wbase = p.theta32 + (int64_t)par * p.D + p.w_start;
     const bool aligned = (reinterpret_cast<uintptr_t>(wbase) & 15) == 0;     // R is a multiple of 64: every row start shares it
     float my_val = -INFINITY;

@@ -21,12 +21,15 @@ def _members(offs):
     return offs2, signs
 
 
-@pytest.mark.parametrize('prec', [1, 2], ids=['exact', 'hybrid'])
+@pytest.mark.parametrize('prec,split', [(1, '1'), (2, '1'), (2, '0')], ids=['exact', 'hybrid', 'hybrid-whole-units'])
 @pytest.mark.parametrize('name', ['g1', 'g2', 'g3', 'g4', 'g5', 'g6'])
-def test_tokens_and_logprobs_match_reference_golden_exact_mode(name, prec, golden, golden_mod):
+def test_tokens_and_logprobs_match_reference_golden_exact_mode(name, prec, split, golden, golden_mod, monkeypatch):
     """token ids bit-exact, log-probs to float32 round-off, against what the REAL reference produced; in both the
-    split-fp16 mode and the HYBRID mode bench.py headlines (fp16-operand logits + exact re-evaluation of the candidates)"""
+    split-fp16 mode and the HYBRID mode bench.py headlines (fp16-operand logits + exact re-evaluation of the candidates).
+    A call of a few members cuts every unit's vocabulary sweep into ranges (decode.cu, NES_LOGITC_SPLIT); 'whole-units' keeps these
+    small cases on the work items a full-size population runs with."""
     import nes_b200
+    monkeypatch.setenv('NES_LOGITC_SPLIT', split)
     c = golden_mod.CASES[name]
     dims, G, play, D, D_pad, L, theta, fc, offs = golden_mod.case_inputs(c)
     ctx = _ctx_for(c, golden_mod, L)

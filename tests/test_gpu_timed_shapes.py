@@ -18,7 +18,7 @@ import make_golden_timed as mt  # noqa: E402
 GOLD = np.load(os.path.join(HERE, 'golden', 'golden_timed_v1.npz'))
 
 
-def _run(name, prec, wave):
+def _run(name, prec, wave, one_wave=False):
     import nes_b200
     c = mt.CASES[name]
     dims, G, play, D, D_pad, L, thetas, fc, offs = mt.case_inputs(c)
@@ -29,7 +29,7 @@ def _run(name, prec, wave):
     for p in range(c['n_parents']):
         ctx.set_theta(thetas[p], p)
     P = len(c['parents'])
-    assert P > wave or name != 't2'                                      # t2 must take more than one wave
+    assert P > wave or name != 't2' or one_wave                          # t2 must take more than one wave
     seq, lp = ctx.rollout(offs, np.asarray(c['signs'], dtype=np.float32), fc, c['sigma'], parents=np.asarray(c['parents'], dtype=np.int32), precision=prec)
     want_seq, want_lp = GOLD[name + '_seq'].astype(np.int64), GOLD[name + '_logprobs']
     bad = (seq.numpy() != want_seq)
@@ -42,6 +42,12 @@ def _run(name, prec, wave):
 @pytest.mark.parametrize('prec', [2, 1], ids=['hybrid', 'exact'])
 def test_config2_shape_16_members_4_parents_two_waves(prec):
     _run('t2', prec, wave=8)
+
+
+def test_config2_shape_few_units_split_the_vocabulary_sweep():
+    """16 units in a workspace of 64: every unit's vocabulary sweep is cut into 4 ranges with their own candidate lists (decode.cu,
+    the launch shape of the elite-candidate rollout of a NIC-ES generation)"""
+    _run('t2', 2, wave=64, one_wave=True)
 
 
 @pytest.mark.parametrize('prec', [2, 1], ids=['hybrid', 'exact'])
