@@ -182,6 +182,18 @@ int nes_logprob_fitness(nes_ctx* ctx, int64_t n_members, int rows, double* out);
 /* K6: NESMaster.compute_centered_ranks + weights (nic_nes_master.py:178-179,184-205); stable tie rule.
  * fitness float64 [F,2]; centered float64 [F,2] (nullable); weights float32 [F] (nullable; kept in ctx). */
 int nes_rank_weights(nes_ctx* ctx, const double* fitness, int64_t F, double* centered, float* weights);
+/* nes_rank_weights for callers that cannot allocate (code under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.  Same arithmetic and kernels as nes_rank_weights,
+ * with the int64 rank scratch in a fixed device array of the library (2 * NES_STATIC_RANK_MAX_F entries = 512 KB, held by every GPU
+ * that loads the library until exit) instead of the context's growable buffer.  The call allocates and frees nothing, copies
+ * nothing and does not synchronise: it enqueues two kernels on the context stream (nes_set_stream) and returns.
+ *   fitness  float64 [F,2], DEVICE pointer;  centered float64 [F,2] / weights float32 [F]: DEVICE pointers, either may be NULL.
+ *   F > NES_STATIC_RANK_MAX_F (or a host pointer) is refused with an error; the context's resident weights (the ones
+ *   nes_gradient(weights = NULL) uses) are NOT updated -- pass `weights` on.
+ *   All calls share the one scratch array per GPU: calls that may overlap on the GPU (different streams, two contexts on one device)
+ *   race on it; calls in stream order are safe (every entry that is read was written by the same call). */
+#define NES_STATIC_RANK_MAX_F 32768
+int nes_rank_weights_static(nes_ctx* ctx, const double* fitness, int64_t F, double* centered, float* weights);
 /* ranks of a flat float64 vector (compute_ranks, nic_nes_master.py:196-205) -> int64 [n] */
 int nes_compute_ranks(nes_ctx* ctx, const double* x, int64_t n, int64_t* ranks);
 /* K7: NESMaster.gradient_estimate / batched_weighted_sum (nic_nes_master.py:170-182,207-221):

@@ -51,6 +51,7 @@ SIGNATURES = {
     'nes_rollout_trace': (c_i32, [c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_f32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
     'nes_logprob_fitness': (c_i32, [c_vp, c_i64, c_i32, c_vp]),
     'nes_rank_weights': (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp]),
+    'nes_rank_weights_static': (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     'nes_compute_ranks': (c_i32, [c_vp, c_vp, c_i64, c_vp]),
     'nes_gradient': (c_i32, [c_vp, c_vp, c_vp, c_i64, c_f32, c_vp]),
     'nes_gradient_shard': (c_i32, [c_vp, c_vp, c_vp, c_i64, c_f32, c_i32, c_i32, c_vp]),

@@ -314,6 +314,19 @@ class NesContext:
         _lib.check(self.lib.nes_rank_weights(self._h, _lib.ptr(fit), F, _lib.ptr(cen), _lib.ptr(w)))
         return cen, w
 
+    STATIC_RANK_MAX_F = 32768
+
+    def rank_weights_static(self, fitness, centered=None, weights=None):
+        """nes_rank_weights_static: K6 for callers that cannot allocate.  fitness float64 [F, 2], centered float64 [F, 2] and weights
+        float32 [F] are tensors ON THE CONTEXT'S DEVICE that the caller made beforehand (either output may be None); nothing is
+        allocated, copied or synchronised here, the two kernels are enqueued on the context stream.  F <= STATIC_RANK_MAX_F."""
+        assert torch.is_tensor(fitness) and fitness.dtype == torch.float64 and fitness.is_contiguous()
+        F = fitness.shape[0]
+        assert fitness.numel() == 2 * F
+        assert centered is None or (centered.dtype == torch.float64 and centered.is_contiguous() and centered.numel() == 2 * F)
+        assert weights is None or (weights.dtype == torch.float32 and weights.is_contiguous() and weights.numel() == F)
+        _lib.check(self.lib.nes_rank_weights_static(self._h, _lib.ptr(fitness), F, _lib.ptr(centered), _lib.ptr(weights)))
+
     def gradient(self, offsets, weights, sigma, out_device='cpu', want=True, shard=(0, 1)):
         """K7.  weights None = the weights the last rank_weights call left on the device.  shard (r, n): only slice r of n of the
         parameter axis is summed, the rest of the vector is zero (all-reduce over the n ranks gives the whole)."""

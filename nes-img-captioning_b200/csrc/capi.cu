@@ -458,6 +458,19 @@ int nes_rank_weights(nes_ctx* ctx, const double* fitness, int64_t F, double* cen
     return 0;
 }
 
+// No counterpart in the reference: added for callers that cannot allocate (include/nes_b200.h).
+// Enqueues two kernels on the context stream and returns; no cudaMalloc / cudaFree / copy, the context's own buffers are not touched.
+int nes_rank_weights_static(nes_ctx* ctx, const double* fitness, int64_t F, double* centered, float* weights) {
+    NEED_CTX(ctx); Ctx* c = CTX(ctx);
+    NES_CHECK(F >= 0, "negative F");
+    NES_CHECK(F <= NES_STATIC_RANK_MAX_F, "nes_rank_weights_static: F exceeds NES_STATIC_RANK_MAX_F (32768 antithetic pairs); use nes_rank_weights");
+    if (F == 0) return 0;
+    NES_CHECK(fitness && (centered || weights), "nes_rank_weights_static: null fitness, or neither output given");
+    NES_CHECK(is_device_ptr(fitness) && (!centered || is_device_ptr(centered)) && (!weights || is_device_ptr(weights)),
+              "nes_rank_weights_static takes device pointers only (it stages nothing)");
+    return launch_rank_weights_static(c, fitness, F, centered, weights);
+}
+
 int nes_gradient(nes_ctx* ctx, const int64_t* offsets, const float* weights, int64_t F, float sigma, float* g_out) {
     return nes_gradient_shard(ctx, offsets, weights, F, sigma, 0, 1, g_out);
 }

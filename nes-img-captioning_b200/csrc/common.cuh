@@ -157,6 +157,8 @@ int launch_bound_norms_batch(Ctx* c, const int32_t* parents, int n);   // theta_
 // master.cu
 int launch_ranks(Ctx* c, const double* d_x, int64_t n, int64_t* d_ranks);
 int launch_rank_weights(Ctx* c, const double* d_fit, int64_t F, double* d_centered, float* d_w);
+constexpr int64_t kStaticRankCap = 2 * NES_STATIC_RANK_MAX_F;      // entries of the static rank scratch (include/nes_b200.h)
+int launch_rank_weights_static(Ctx* c, const double* d_fit, int64_t F, double* d_centered, float* d_w);
 int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g, int shard = 0, int n_shards = 1);
 int launch_opt_update(Ctx* c, const float* d_g, const double* d_G64, int direct, double l2, double* ratio_host_or_null);
 

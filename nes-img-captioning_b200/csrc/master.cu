@@ -57,6 +57,44 @@ int launch_rank_weights(Ctx* c, const double* d_fit, int64_t F, double* d_center
     return 0;
 }
 
+// ---- K6 without any allocation ------------------------------------------------------------------
+// nes_rank_weights_static (capi.cu): the same two launches as launch_rank_weights with the int64 rank scratch in a file-scope device
+// array instead of the context's growable buffer, for callers that cannot reach cudaMalloc (CUDA graph capture, serving loops).  Every
+// GPU that loads the library holds the array (kStaticRankCap * 8 B = 512 KB) until exit.  Every call shares it: k_ranks overwrites
+// entries [0, 2F) before k_rank_weights reads them, nothing in it has to start at zero, and two calls that overlap on the GPU (different
+// streams, or two contexts on one device) race on it.
+static __device__ __align__(256) long long g_static_ranks[kStaticRankCap];
+
+// host side: `g_static_ranks` here is a host stand-in for the symbol, not a device address -- the address comes from
+// cudaGetSymbolAddress, once per device, with that device current
+static int static_ranks_ptr(int device, int64_t** out) {
+    static int64_t* ptr[64] = {nullptr};
+    NES_CHECK(device >= 0 && device < 64, "device index out of range");
+    if (!ptr[device]) {
+        int cur = -1;
+        NES_CUDA(cudaGetDevice(&cur));
+        if (cur != device) NES_CUDA(cudaSetDevice(device));
+        void* a = nullptr;
+        NES_CUDA(cudaGetSymbolAddress(&a, g_static_ranks));
+        NES_CHECK(a != nullptr, "no device address for the static rank scratch");
+        ptr[device] = reinterpret_cast<int64_t*>(a);
+        if (cur != device) NES_CUDA(cudaSetDevice(cur));
+    }
+    *out = ptr[device];
+    return 0;
+}
+int launch_rank_weights_static(Ctx* c, const double* d_fit, int64_t F, double* d_centered, float* d_w) {
+    NES_CHECK(2 * F <= kStaticRankCap, "nes_rank_weights_static: F exceeds NES_STATIC_RANK_MAX_F (32768 antithetic pairs)");
+    if (F == 0) return 0;
+    int64_t* d_ranks = nullptr;
+    if (static_ranks_ptr(c->device, &d_ranks)) return 1;
+    k_ranks<<<(unsigned)((2 * F + 255) / 256), 256, 0, c->stream>>>(d_fit, 2 * F, d_ranks);
+    k_rank_weights<<<(unsigned)((F + 255) / 256), 256, 0, c->stream>>>(d_ranks, F, d_centered, d_w);
+    c->launches += 2;
+    NES_CUDA(cudaGetLastError());
+    return 0;
+}
+
 // ---- K7 -----------------------------------------------------------------------------------------
 // g[p] = f32(sigma) * (sum_i w_i * eps_i[p]) / (2F), eps_i = table[off_i + pstart_k + (p - start_k)].
 // HBM-bound: reads F * D * 2 bytes (fp16 table) once, writes 4*D.  One thread owns 8 consecutive
