@@ -36,7 +36,7 @@ static void build_layout(Layout& L, const int64_t* counts, const int32_t* rows, 
 
 int ensure_small(Ctx* c, int64_t n) {
     if (n <= c->small_cap) return 0;
-    void* olds[] = {c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks};
+    void* olds[] = {c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks, c->d_off_sorted, c->d_w_sorted};
     for (void* o : olds) if (o) cudaFree(o);
     int64_t cap = n < 1024 ? 1024 : n;
     NES_CUDA(cudaMalloc((void**)&c->d_offsets, sizeof(int64_t) * cap));
@@ -44,6 +44,8 @@ int ensure_small(Ctx* c, int64_t n) {
     NES_CUDA(cudaMalloc((void**)&c->d_fitness, sizeof(double) * 2 * cap));
     NES_CUDA(cudaMalloc((void**)&c->d_centered, sizeof(double) * 2 * cap));
     NES_CUDA(cudaMalloc((void**)&c->d_ranks, sizeof(int64_t) * 2 * cap));
+    NES_CUDA(cudaMalloc((void**)&c->d_off_sorted, sizeof(int64_t) * cap));
+    NES_CUDA(cudaMalloc((void**)&c->d_w_sorted, sizeof(float) * cap));
     c->small_cap = cap;
     return 0;
 }
@@ -155,7 +157,7 @@ int nes_ctx_destroy(nes_ctx* ctx) {
     decode_destroy(c);
     cider_destroy(c);
     void* ptrs[] = {c->table, c->theta64, c->theta32, c->theta_hi, c->theta_lo, c->grad, c->opt_m, c->opt_v, c->d_lay, c->d_norm_partials,
-                    c->d_norms, c->d_G64, c->d_theta_rowmax, c->d_eps_rowmax, c->scale32, c->d_scale_max, c->d_abs_partials, c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks};
+                    c->d_norms, c->d_G64, c->d_theta_rowmax, c->d_eps_rowmax, c->scale32, c->d_scale_max, c->d_abs_partials, c->d_offsets, c->d_weights, c->d_fitness, c->d_centered, c->d_ranks, c->d_off_sorted, c->d_w_sorted};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->ev_a) cudaEventDestroy(c->ev_a);
     if (c->ev_b) cudaEventDestroy(c->ev_b);

@@ -105,6 +105,7 @@ struct Ctx {
     // scratch for per-iteration small arrays
     int64_t* d_offsets = nullptr; float* d_weights = nullptr; double* d_fitness = nullptr;
     double* d_centered = nullptr; int64_t* d_ranks = nullptr; int64_t small_cap = 0;
+    int64_t* d_off_sorted = nullptr; float* d_w_sorted = nullptr;          // K7: the rows in table order (launch_gradient)
 
     cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr;
     bool grad_timed = false, rollout_timed = false;

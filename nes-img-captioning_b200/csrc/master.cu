@@ -3,6 +3,7 @@
 // and algorithm/nic_nes/optimizers.py:15-22,44-47,78-83.
 #include "common.cuh"
 #include <cstdlib>
+#include <cstring>
 
 namespace nes {
 
@@ -118,45 +119,95 @@ __device__ __forceinline__ void fma8(float (&acc)[8], const uint4& v, float w) {
 }
 
 constexpr int kGradChunk = 512;
-template <int UNROLL>
-__global__ void __launch_bounds__(256) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
+// Rows in table order.  A noise row is D_pad elements long and the F offsets lie L / F apart on average: at F = 5000 on the 2^32-element
+// table every table element belongs to ~16 rows (F * D_pad / L).  Summed in the order they were sampled, those 16 reads are hours apart
+// and every one comes from HBM.  Sorted by offset, the rows that share a table line are neighbours in the loop: thread column p at row i
+// reads table[off_i + p], and column p - (off_{i+1} - off_i) reads the same line one row later -- an L2 hit as long as both columns
+// are resident at the same time.  k_sort_rows puts (offset, weight) in ascending offset order (ties: by index, so the order is a
+// function of the offsets alone and identical on every rank); O(F^2) compares like k_ranks.
+__global__ void __launch_bounds__(256) k_sort_rows(const int64_t* __restrict__ off, const float* __restrict__ w, int64_t F,
+                                                   int64_t* __restrict__ off_sorted, float* __restrict__ w_sorted) {
+    __shared__ int64_t tile[1024];
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t oi = i < F ? off[i] : 0;
+    int64_t cnt = 0;
+    for (int64_t base = 0; base < F; base += 1024) {
+        const int m = (int)((F - base) < 1024 ? (F - base) : 1024);
+        __syncthreads();
+        for (int t = threadIdx.x; t < m; t += blockDim.x) tile[t] = off[base + t];
+        __syncthreads();
+        if (i < F) {
+#pragma unroll 8
+            for (int t = 0; t < m; ++t) {
+                const int64_t oj = tile[t];
+                cnt += (oj < oi) || (oj == oi && (base + t) < i);
+            }
+        }
+    }
+    if (i < F) { off_sorted[cnt] = oi; w_sorted[cnt] = w[i]; }
+}
+
+// One thread owns NC vectors of 8 consecutive elements, 256 vectors apart (a CTA covers NC * 2048 consecutive elements of every row), and
+// keeps U rows of all of them in flight.  NC > 1 widens the band of columns that is resident on the chip at one time (148 SMs x resident
+// threads x NC x 8 elements), which is what turns the overlap of neighbouring sorted rows into L2 hits.
+template <int NC, int U>
+__global__ void __launch_bounds__(256, (NC * U >= 16 || NC * (U + 2) > 24) ? 1 : 2) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
                                                   const float* __restrict__ w, int64_t F, GradPlan plan,
                                                   const Layout* __restrict__ lay, float sigma, float* __restrict__ g, int64_t v_lo, int64_t v_hi) {
     __shared__ int64_t s_off[kGradChunk];
     __shared__ float s_w[kGradChunk];
-    const int64_t v = v_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // [v_lo, v_hi): this rank's slice of the parameter axis
-    const bool active = v < v_hi;
-    int k = 0;
-    if (active) { while (v >= plan.vec_prefix[k + 1]) ++k; }
-    const TensorDesc t = lay->t[k];
-    const int64_t j0 = active ? (v - plan.vec_prefix[k]) * 8 : 0;
-    const __half* base = table + t.pstart + j0;
-    float acc[8];
+    const int64_t v0 = v_lo + (int64_t)blockIdx.x * (256 * NC) + threadIdx.x;     // [v_lo, v_hi): this rank's slice of the parameter axis
+    const __half* base[NC]; bool act[NC];      // only the row pointers stay live through the loop; the tensor lookup is redone at the end
+    float acc[NC][8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-
+    for (int c = 0; c < NC; ++c) {
+        const int64_t v = v0 + c * 256;
+        act[c] = v < v_hi;
+        int k = 0;
+        if (act[c]) { while (v >= plan.vec_prefix[k + 1]) ++k; }
+        base[c] = table + lay->t[k].pstart + (act[c] ? (v - plan.vec_prefix[k]) * 8 : 0);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[c][e] = 0.f;
+    }
     for (int64_t c0 = 0; c0 < F; c0 += kGradChunk) {
         const int m = (int)((F - c0) < kGradChunk ? (F - c0) : kGradChunk);
         __syncthreads();
         for (int i = threadIdx.x; i < m; i += blockDim.x) { s_off[i] = off[c0 + i]; s_w[i] = w[c0 + i]; }
         __syncthreads();
-        if (active) {
-            int i = 0;
-            for (; i + UNROLL <= m; i += UNROLL) {
-                uint4 buf[UNROLL];
+        int i = 0;
+        for (; i + U <= m; i += U) {
+            uint4 buf[U][NC];
 #pragma unroll
-                for (int u = 0; u < UNROLL; ++u) buf[u] = ld_stream_128(base + s_off[i + u]);
+            for (int u = 0; u < U; ++u) {
+                const int64_t o = s_off[i + u];
 #pragma unroll
-                for (int u = 0; u < UNROLL; ++u) fma8(acc, buf[u], s_w[i + u]);
+                for (int c = 0; c < NC; ++c) if (act[c]) buf[u][c] = ld_stream_128(base[c] + o);
             }
-            for (; i < m; ++i) { uint4 b = ld_stream_128(base + s_off[i]); fma8(acc, b, s_w[i]); }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const float wi = s_w[i + u];
+#pragma unroll
+                for (int c = 0; c < NC; ++c) if (act[c]) fma8(acc[c], buf[u][c], wi);
+            }
+        }
+        for (; i < m; ++i) {
+            const int64_t o = s_off[i]; const float wi = s_w[i];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) if (act[c]) { const uint4 b = ld_stream_128(base[c] + o); fma8(acc[c], b, wi); }
         }
     }
-    if (active) {
-        const float denom = (float)(2 * F);
+    const float denom = (float)(2 * F);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+        if (!act[c]) continue;
+        const int64_t v = v0 + c * 256;
+        int k = 0;
+        while (v >= plan.vec_prefix[k + 1]) ++k;
+        const TensorDesc t = lay->t[k];
+        const int64_t j0 = (v - plan.vec_prefix[k]) * 8;
 #pragma unroll
         for (int e = 0; e < 8; ++e)
-            if (j0 + e < t.count) g[t.start + j0 + e] = __fdiv_rn(__fmul_rn(sigma, acc[e]), denom);
+            if (j0 + e < t.count) g[t.start + j0 + e] = __fdiv_rn(__fmul_rn(sigma, acc[c][e]), denom);
     }
 }
 
@@ -164,6 +215,12 @@ __global__ void __launch_bounds__(256) k_gradient(const __half* __restrict__ tab
 // once to the sum (agrees to float32 round-off, within the 1e-5 the update is held to)
 __global__ void __launch_bounds__(256) k_scale_vec(float* __restrict__ g, const float* __restrict__ s, int64_t D, int div) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < D; i += (int64_t)gridDim.x * blockDim.x) g[i] = apply_scale(g[i], s[i], div);
+}
+static int sm_count_of(Ctx* c) {
+    static int n[64] = {0};
+    if (c->device < 0 || c->device >= 64) return 148;
+    if (!n[c->device]) { int v = 0; if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, c->device) != cudaSuccess || v < 1) { cudaGetLastError(); v = 148; } n[c->device] = v; }
+    return n[c->device];
 }
 int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, float sigma, float* d_g, int shard, int n_shards) {
     GradPlan plan; plan.n = c->lay.n; plan.vec_prefix[0] = 0;
@@ -173,21 +230,53 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
     // multi-GPU: the parameter axis is cut into n_shards runs of whole CTAs; every element is summed over all F rows by one rank in the
     // single-GPU order, the other ranks hold zeros, so the all-reduce that follows reproduces the single-GPU vector bit for bit
     NES_CHECK(n_shards >= 1 && shard >= 0 && shard < n_shards, "bad gradient shard");
-    // rows in flight per thread (NES_K7_UNROLL, experiment switch).  Measured on B200 (tools/k7_sweep.py, F = 5000, D = 13.4 M, 2^32-element
-    // table): 8 -> 16 rows +7 %, 32 no further gain; 128 / 256 / 512 threads per block alike; giving a block a 2x / 4x longer contiguous run
-    // of every row (several vectors per thread) alike or worse.  ncu: 134.7 GB from DRAM for 134.1 GB algorithmic at 7.0 TB/s
-    static int ku = 0;
-    if (!ku) { const char* u = getenv("NES_K7_UNROLL"); ku = u ? atoi(u) : 16; }
-    constexpr int kb = 256;
-    const int64_t blocks = (total + kb - 1) / kb, per = (blocks + n_shards - 1) / n_shards;
-    const int64_t v_lo = std::min(total, (int64_t)shard * per * kb), v_hi = std::min(total, v_lo + per * kb);
+    // NES_K7 = "<vectors per thread>x<rows in flight>" and NES_K7_SORT=0 are experiment switches (tools/k7_sweep.py).  Measured on B200
+    // (F = 5000, D = 13.4 M, 2^32-element table, one box): rows in the order they were sampled 18.4 ms = 7.3 TB/s whatever the shape (ncu:
+    // 134.7 GB from DRAM for 134.1 GB algorithmic); rows sorted by offset: 1x16 17.9, 2x4 15.1, 4x2 13.0, 8x1 12.4 ms = 10.8 TB/s on the
+    // algorithmic bytes (1.35 of the 8 TB/s nominal HBM rate: most reads are L2 hits; the same kernel with all rows packed into 256 MB,
+    // i.e. its L2 -> SM ceiling, takes 11.7 ms).  More rows in flight per thread at the same width cost registers, hence residency: 4x4 /
+    // 8x2 fall back to 19 ms.  Holding the rows in flight in shared memory instead (cp.async into a private ring per thread, 8 vectors x
+    // 3 - 6 rows, 128 - 192 KB in flight per SM) was tried and lost: 14.3 - 16.6 ms, same 11.5 ms ceiling.  The widest shape that still fills
+    // the GPU twice over is used.
+    static int env_nc = -1, env_u = 0, ksort = 1;
+    if (env_nc < 0) {
+        const char* u = getenv("NES_K7");
+        env_nc = 0;
+        if (u && strlen(u) >= 3 && u[1] == 'x') { env_nc = u[0] - '0'; env_u = atoi(u + 2); }
+        const char* so = getenv("NES_K7_SORT");
+        if (so && atoi(so) == 0) ksort = 0;
+    }
+    int knc = env_nc, ku = env_u;
+    if (!knc) {
+        const int64_t share = (total + n_shards - 1) / n_shards, want = 2 * (int64_t)sm_count_of(c);
+        knc = 8;
+        while (knc > 1 && (share + 256 * knc - 1) / (256 * knc) < want) knc >>= 1;
+        ku = knc == 8 ? 1 : (knc == 4 ? 2 : (knc == 2 ? 4 : 16));
+    }
+    const int64_t per_cta = 256 * (int64_t)knc;
+    const int64_t blocks = (total + per_cta - 1) / per_cta, per = (blocks + n_shards - 1) / n_shards;
+    const int64_t v_lo = std::min(total, (int64_t)shard * per * per_cta), v_hi = std::min(total, v_lo + per * per_cta);
     if (n_shards > 1) NES_CUDA(cudaMemsetAsync(d_g, 0, sizeof(float) * c->lay.D, c->stream));
-    unsigned grid = (unsigned)((v_hi - v_lo + kb - 1) / kb);
+    unsigned grid = (unsigned)((v_hi - v_lo + per_cta - 1) / per_cta);
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_a, c->stream));
-    if (grid && ku == 32) k_gradient<32><<<grid, kb, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
-    else if (grid && ku == 16) k_gradient<16><<<grid, kb, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
-    else if (grid && ku == 4) k_gradient<4><<<grid, kb, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
-    else if (grid) k_gradient<8><<<grid, kb, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi);
+    if (ksort) {
+        k_sort_rows<<<(unsigned)((F + 255) / 256), 256, 0, c->stream>>>(d_off, d_w, F, c->d_off_sorted, c->d_w_sorted);
+        c->launches++;
+        d_off = c->d_off_sorted; d_w = c->d_w_sorted;
+    }
+#define NES_K7_LAUNCH(NC, U) k_gradient<NC, U><<<grid, 256, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi)
+    if (grid) {
+        if (knc == 1 && ku == 16) NES_K7_LAUNCH(1, 16);
+        else if (knc == 1 && ku == 8) NES_K7_LAUNCH(1, 8);
+        else if (knc == 2 && ku == 8) NES_K7_LAUNCH(2, 8);
+        else if (knc == 2 && ku == 4) NES_K7_LAUNCH(2, 4);
+        else if (knc == 4 && ku == 2) NES_K7_LAUNCH(4, 2);
+        else if (knc == 4 && ku == 4) NES_K7_LAUNCH(4, 4);
+        else if (knc == 8 && ku == 2) NES_K7_LAUNCH(8, 2);
+        else if (knc == 8 && ku == 1) NES_K7_LAUNCH(8, 1);
+        else { NES_CHECK(false, "NES_K7: unsupported shape (1x16 1x8 2x8 2x4 4x4 4x2 8x2 8x1)"); }
+    }
+#undef NES_K7_LAUNCH
     if (c->scale32) { k_scale_vec<<<148 * 8, 256, 0, c->stream>>>(d_g, c->scale32, c->lay.D, c->scale_div); c->launches++; }
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_b, c->stream));
     c->launches++;
