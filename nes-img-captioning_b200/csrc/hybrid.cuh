@@ -190,11 +190,15 @@ __device__ __forceinline__ bool refine_row(const RefineParams& p, int64_t member
         S = warp_sum(S);
         const float thr = M - mg;
         if (!overflow) {
-            for (int l = 0; l < n_lists; ++l) {
-                const int n = hd[l].n;
-                const CandEntry* ent = p.entries + (grow * n_lists + l) * (int64_t)kCandCap;
-                for (int e0 = 0; e0 < n; e0 += 32) {
-                    const int e = e0 + lane;
+            // one lane per list (32 lists at a time), entry e of all of them in one step: the lists are short (1 - 3 entries), so this is
+            // a handful of dependent loads instead of one per list.  A list whose own maximum is below the threshold holds nothing.
+            for (int l0 = 0; l0 < n_lists; l0 += 32) {
+                const int l = l0 + lane;
+                int n = 0;
+                if (l < n_lists) { const CandHead h = hd[l]; n = h.mx >= thr ? h.n : 0; }
+                const CandEntry* ent = p.entries + (grow * n_lists + (l < n_lists ? l : 0)) * (int64_t)kCandCap;
+                const int nmax = __reduce_max_sync(0xffffffffu, n);
+                for (int e = 0; e < nmax; ++e) {
                     CandEntry ce; ce.v = -INFINITY; ce.idx = 0;
                     if (e < n) ce = ent[e];
                     const bool ok = e < n && ce.v >= thr;
