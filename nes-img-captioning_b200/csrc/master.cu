@@ -151,21 +151,23 @@ __global__ void __launch_bounds__(256) k_sort_rows(const int64_t* __restrict__ o
 // keeps U rows of all of them in flight.  NC > 1 widens the band of columns that is resident on the chip at one time (148 SMs x resident
 // threads x NC x 8 elements), which is what turns the overlap of neighbouring sorted rows into L2 hits.
 template <int NC, int U>
-__global__ void __launch_bounds__(256, (NC * U >= 16 || NC * (U + 2) > 24) ? 1 : 2) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
+__global__ void __launch_bounds__(256, (NC * U >= 16 && NC > 1) ? 1 : 2) k_gradient(const __half* __restrict__ table, const int64_t* __restrict__ off,
                                                   const float* __restrict__ w, int64_t F, GradPlan plan,
-                                                  const Layout* __restrict__ lay, float sigma, float* __restrict__ g, int64_t v_lo, int64_t v_hi) {
+                                                  const Layout* __restrict__ lay, float sigma, float* __restrict__ g, int64_t v_lo, int64_t v_hi, int span) {
     __shared__ int64_t s_off[kGradChunk];
     __shared__ float s_w[kGradChunk];
-    const int64_t v0 = v_lo + (int64_t)blockIdx.x * (256 * NC) + threadIdx.x;     // [v_lo, v_hi): this rank's slice of the parameter axis
-    const __half* base[NC]; bool act[NC];      // only the row pointers stay live through the loop; the tensor lookup is redone at the end
+    // CTA b owns vectors [v_lo + b * span, v_lo + (b + 1) * span) below v_hi, span <= 256 * NC (the host balances span so that every
+    // launch is one full wave of co-resident CTAs, see launch_gradient)
+    const int64_t v0 = v_lo + (int64_t)blockIdx.x * span + threadIdx.x;
+    uint32_t pos[NC]; bool act[NC];            // only the row positions (< D_pad) stay live through the loop; the tensor lookup is redone at the end
     float acc[NC][8];
 #pragma unroll
     for (int c = 0; c < NC; ++c) {
         const int64_t v = v0 + c * 256;
-        act[c] = v < v_hi;
+        act[c] = (c * 256 + (int)threadIdx.x) < span && v < v_hi;
         int k = 0;
         if (act[c]) { while (v >= plan.vec_prefix[k + 1]) ++k; }
-        base[c] = table + lay->t[k].pstart + (act[c] ? (v - plan.vec_prefix[k]) * 8 : 0);
+        pos[c] = (uint32_t)(lay->t[k].pstart + (act[c] ? (v - plan.vec_prefix[k]) * 8 : 0));
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[c][e] = 0.f;
     }
@@ -181,7 +183,7 @@ __global__ void __launch_bounds__(256, (NC * U >= 16 || NC * (U + 2) > 24) ? 1 :
             for (int u = 0; u < U; ++u) {
                 const int64_t o = s_off[i + u];
 #pragma unroll
-                for (int c = 0; c < NC; ++c) if (act[c]) buf[u][c] = ld_stream_128(base[c] + o);
+                for (int c = 0; c < NC; ++c) if (act[c]) buf[u][c] = ld_stream_128(table + (o + pos[c]));
             }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
@@ -193,7 +195,7 @@ __global__ void __launch_bounds__(256, (NC * U >= 16 || NC * (U + 2) > 24) ? 1 :
         for (; i < m; ++i) {
             const int64_t o = s_off[i]; const float wi = s_w[i];
 #pragma unroll
-            for (int c = 0; c < NC; ++c) if (act[c]) { const uint4 b = ld_stream_128(base[c] + o); fma8(acc[c], b, wi); }
+            for (int c = 0; c < NC; ++c) if (act[c]) { const uint4 b = ld_stream_128(table + (o + pos[c])); fma8(acc[c], b, wi); }
         }
     }
     const float denom = (float)(2 * F);
@@ -227,8 +229,9 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
     for (int k = 0; k < c->lay.n; ++k) plan.vec_prefix[k + 1] = plan.vec_prefix[k] + (c->lay.t[k].count + 7) / 8;
     const int64_t total = plan.vec_prefix[plan.n];
     if (F == 0) { NES_CUDA(cudaMemsetAsync(d_g, 0, sizeof(float) * c->lay.D, c->stream)); return 0; }
-    // multi-GPU: the parameter axis is cut into n_shards runs of whole CTAs; every element is summed over all F rows by one rank in the
-    // single-GPU order, the other ranks hold zeros, so the all-reduce that follows reproduces the single-GPU vector bit for bit
+    // multi-GPU: the parameter axis is cut into n_shards runs of vectors; every element is summed over all F rows by one rank in the
+    // single-GPU order (table order, whatever the launch shape), the other ranks hold zeros, so the all-reduce that follows reproduces the
+    // single-GPU vector bit for bit
     NES_CHECK(n_shards >= 1 && shard >= 0 && shard < n_shards, "bad gradient shard");
     // NES_K7 = "<vectors per thread>x<rows in flight>" and NES_K7_SORT=0 are experiment switches (tools/k7_sweep.py).  Measured on B200
     // (F = 5000, D = 13.4 M, 2^32-element table, one box): rows in the order they were sampled 18.4 ms = 7.3 TB/s whatever the shape (ncu:
@@ -236,8 +239,8 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
     // algorithmic bytes (1.35 of the 8 TB/s nominal HBM rate: most reads are L2 hits; the same kernel with all rows packed into 256 MB,
     // i.e. its L2 -> SM ceiling, takes 11.7 ms).  More rows in flight per thread at the same width cost registers, hence residency: 4x4 /
     // 8x2 fall back to 19 ms.  Holding the rows in flight in shared memory instead (cp.async into a private ring per thread, 8 vectors x
-    // 3 - 6 rows, 128 - 192 KB in flight per SM) was tried and lost: 14.3 - 16.6 ms, same 11.5 ms ceiling.  The widest shape that still fills
-    // the GPU twice over is used.
+    // 3 - 6 rows, 128 - 192 KB in flight per SM) was tried and lost: 14.3 - 16.6 ms, same 11.5 ms ceiling.  The shape follows
+    // from the band width below (8x1 whenever a band of 2 CTAs per SM needs more than 1024 vectors per CTA).
     static int env_nc = -1, env_u = 0, ksort = 1;
     if (env_nc < 0) {
         const char* u = getenv("NES_K7");
@@ -246,26 +249,36 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
         const char* so = getenv("NES_K7_SORT");
         if (so && atoi(so) == 0) ksort = 0;
     }
-    int knc = env_nc, ku = env_u;
-    if (!knc) {
-        const int64_t share = (total + n_shards - 1) / n_shards, want = 2 * (int64_t)sm_count_of(c);
-        knc = 8;
-        while (knc > 1 && (share + 256 * knc - 1) / (256 * knc) < want) knc >>= 1;
-        ku = knc == 8 ? 1 : (knc == 4 ? 2 : (knc == 2 ? 4 : 16));
-    }
-    const int64_t per_cta = 256 * (int64_t)knc;
-    const int64_t blocks = (total + per_cta - 1) / per_cta, per = (blocks + n_shards - 1) / n_shards;
-    const int64_t v_lo = std::min(total, (int64_t)shard * per * per_cta), v_hi = std::min(total, v_lo + per * per_cta);
+    // this rank's slice of the parameter axis, in vectors of 8 elements
+    const int64_t per = (total + n_shards - 1) / n_shards;
+    const int64_t s_lo = std::min(total, (int64_t)shard * per), s_hi = std::min(total, s_lo + per);
     if (n_shards > 1) NES_CUDA(cudaMemsetAsync(d_g, 0, sizeof(float) * c->lay.D, c->stream));
-    unsigned grid = (unsigned)((v_hi - v_lo + per_cta - 1) / per_cta);
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_a, c->stream));
-    if (ksort) {
+    if (ksort && s_hi > s_lo) {
         k_sort_rows<<<(unsigned)((F + 255) / 256), 256, 0, c->stream>>>(d_off, d_w, F, c->d_off_sorted, c->d_w_sorted);
         c->launches++;
         d_off = c->d_off_sorted; d_w = c->d_w_sorted;
     }
-#define NES_K7_LAUNCH(NC, U) k_gradient<NC, U><<<grid, 256, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, v_hi)
-    if (grid) {
+    // One launch per BAND of columns, every band exactly one wave of co-resident CTAs (2 per SM) with the vectors spread evenly over
+    // them.  A single launch of ceil(vectors / 2048) CTAs leaves a ragged last wave (D = 5 M: 305 CTAs on 296 slots took two full
+    // waves) and, over many waves, CTAs that start whenever a slot frees up: the resident CTAs then sit at unrelated rows and stop
+    // sharing table lines (D = 50 M: 6.5 TB/s).  Bands keep every resident CTA on the same rows.
+    const int slots = 2 * sm_count_of(c);
+    const int64_t n_vec = s_hi - s_lo;
+    const int64_t waves = std::max<int64_t>(1, (n_vec + (int64_t)slots * 2048 - 1) / ((int64_t)slots * 2048));
+    int span = (int)((n_vec + waves * slots - 1) / (waves * slots));                 // vectors per CTA, <= 2048
+    if (span < 1) span = 1;
+    int knc = env_nc, ku = env_u;
+    if (!knc) {                             // as many vectors per thread as the band needs, and rows in flight so that a thread keeps 8 - 16 loads going
+        static const int u_of[9] = {0, 16, 4, 4, 2, 2, 2, 1, 1};
+        knc = (span + 255) / 256;
+        ku = u_of[knc];
+    }
+    if (span > 256 * knc) span = 256 * knc;                                           // a narrower shape was forced: more bands
+#define NES_K7_LAUNCH(NC, U) k_gradient<NC, U><<<grid, 256, 0, c->stream>>>(c->table, d_off, d_w, F, plan, c->d_lay, sigma, d_g, v_lo, s_hi, span)
+    for (int64_t v_lo = s_lo; v_lo < s_hi; v_lo += (int64_t)slots * span) {
+        const int64_t left = s_hi - v_lo;
+        const unsigned grid = (unsigned)std::min<int64_t>(slots, (left + span - 1) / span);
         if (knc == 1 && ku == 16) NES_K7_LAUNCH(1, 16);
         else if (knc == 1 && ku == 8) NES_K7_LAUNCH(1, 8);
         else if (knc == 2 && ku == 8) NES_K7_LAUNCH(2, 8);
@@ -274,12 +287,16 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
         else if (knc == 4 && ku == 4) NES_K7_LAUNCH(4, 4);
         else if (knc == 8 && ku == 2) NES_K7_LAUNCH(8, 2);
         else if (knc == 8 && ku == 1) NES_K7_LAUNCH(8, 1);
-        else { NES_CHECK(false, "NES_K7: unsupported shape (1x16 1x8 2x8 2x4 4x4 4x2 8x2 8x1)"); }
+        else if (knc == 3 && ku == 4) NES_K7_LAUNCH(3, 4);
+        else if (knc == 5 && ku == 2) NES_K7_LAUNCH(5, 2);
+        else if (knc == 6 && ku == 2) NES_K7_LAUNCH(6, 2);
+        else if (knc == 7 && ku == 1) NES_K7_LAUNCH(7, 1);
+        else { NES_CHECK(false, "NES_K7: unsupported shape (1x16 1x8 2x8 2x4 3x4 4x4 4x2 5x2 6x2 7x1 8x2 8x1)"); }
+        c->launches++;
     }
 #undef NES_K7_LAUNCH
     if (c->scale32) { k_scale_vec<<<148 * 8, 256, 0, c->stream>>>(d_g, c->scale32, c->lay.D, c->scale_div); c->launches++; }
     if (c->grad_timed) NES_CUDA(cudaEventRecord(c->ev_b, c->stream));
-    c->launches++;
     NES_CUDA(cudaGetLastError());
     return 0;
 }
