@@ -241,10 +241,9 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
     // 8x2 fall back to 19 ms.  Holding the rows in flight in shared memory instead (cp.async into a private ring per thread, 8 vectors x
     // 3 - 6 rows, 128 - 192 KB in flight per SM) was tried and lost: 14.3 - 16.6 ms, same 11.5 ms ceiling.  The shape follows
     // from the band width below (8x1 whenever a band of 2 CTAs per SM needs more than 1024 vectors per CTA).
-    static int env_nc = -1, env_u = 0, ksort = 1;
-    if (env_nc < 0) {
+    int env_nc = 0, env_u = 0, ksort = 1;            // read on every call: the tests walk through the shapes in one process
+    {
         const char* u = getenv("NES_K7");
-        env_nc = 0;
         if (u && strlen(u) >= 3 && u[1] == 'x') { env_nc = u[0] - '0'; env_u = atoi(u + 2); }
         const char* so = getenv("NES_K7_SORT");
         if (so && atoi(so) == 0) ksort = 0;

@@ -104,3 +104,31 @@ def test_k7_full_size_properties():
         got = g1[t.start + j: t.start + j + 64].cpu().numpy()
         assert np.allclose(got, want, rtol=2e-5, atol=1e-5 * np.abs(want).max()), (t.name, np.abs(got - want).max())
     ctx.close()
+
+
+@pytest.mark.parametrize('D', [350000, 2865808])
+def test_k7_every_launch_shape_gives_the_same_bits(D, monkeypatch):
+    """the sum over the rows runs in table order per element whatever the launch shape (vectors per thread x rows in flight, bands):
+    every shape the library can pick (NES_K7 forces one) must reproduce the default's bits, and the rows as sampled (NES_K7_SORT=0,
+    another sum order) must agree to float32 round-off"""
+    import nes_b200
+    ctx = nes_b200.NesContext(counts=[D - 1000, 1000], seed=9, table_len=1 << 26)
+    F = 700
+    g = torch.Generator().manual_seed(D)
+    offs = torch.unique(ctx.sample_offsets(2, F))
+    offs = offs[torch.randperm(offs.numel(), generator=g)]
+    w = torch.randn(offs.numel(), generator=g)
+    monkeypatch.delenv('NES_K7', raising=False)
+    monkeypatch.delenv('NES_K7_SORT', raising=False)
+    want = ctx.gradient(offs, w, 0.02, out_device=ctx.dev)
+    assert float(want.abs().max()) > 0
+    for shape in ('1x16', '1x8', '2x8', '2x4', '3x4', '4x4', '4x2', '5x2', '6x2', '7x1', '8x2', '8x1'):
+        monkeypatch.setenv('NES_K7', shape)
+        assert torch.equal(ctx.gradient(offs, w, 0.02, out_device=ctx.dev), want), shape
+        parts = sum(ctx.gradient(offs, w, 0.02, out_device=ctx.dev, shard=(r, 3)) for r in range(3))
+        assert torch.equal(parts, want), shape
+    monkeypatch.delenv('NES_K7')
+    monkeypatch.setenv('NES_K7_SORT', '0')
+    got = ctx.gradient(offs, w, 0.02, out_device=ctx.dev)
+    assert float((got - want).abs().max()) <= 1e-5 * float(want.abs().max())
+    ctx.close()
