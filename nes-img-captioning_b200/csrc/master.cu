@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include <cstdlib>
 #include <cstring>
+#include <cmath>
 
 namespace nes {
 
@@ -262,9 +263,15 @@ int launch_gradient(Ctx* c, const int64_t* d_off, const float* d_w, int64_t F, f
     // them.  A single launch of ceil(vectors / 2048) CTAs leaves a ragged last wave (D = 5 M: 305 CTAs on 296 slots took two full
     // waves) and, over many waves, CTAs that start whenever a slot frees up: the resident CTAs then sit at unrelated rows and stop
     // sharing table lines (D = 50 M: 6.5 TB/s).  Bands keep every resident CTA on the same rows.
+    // Band width: a table line is first touched by the band's highest column and last by its lowest, (band width / offset spacing) rows
+    // later; everything the band reads in between (that many rows x the band's bytes) has to stay in L2, so the width that still shares
+    // grows with the square root of the spacing.  Measured at D = 13.4 M on the 2^32 table: F = 5000 (spacing 0.86 M elements) 4.85 M
+    // columns = 8 vectors per thread is best (12.3 ms; 2.4 M columns 13.0); F = 20000 (spacing 0.21 M) 2.4 M columns (41 ms; 4.85 M: 60 ms).
     const int slots = 2 * sm_count_of(c);
     const int64_t n_vec = s_hi - s_lo;
-    const int64_t waves = std::max<int64_t>(1, (n_vec + (int64_t)slots * 2048 - 1) / ((int64_t)slots * 2048));
+    const double spacing = (double)std::max<int64_t>(1, c->table_len - c->lay.D_pad) / (double)F;
+    const int64_t span_max = std::min<int64_t>(2048, std::max<int64_t>(256, (int64_t)(5200.0 * sqrt(spacing) / (8.0 * slots))));
+    const int64_t waves = std::max<int64_t>(1, (n_vec + (int64_t)slots * span_max - 1) / ((int64_t)slots * span_max));
     int span = (int)((n_vec + waves * slots - 1) / (waves * slots));                 // vectors per CTA, <= 2048
     if (span < 1) span = 1;
     int knc = env_nc, ku = env_u;

@@ -7,7 +7,7 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import nes_b200
-D, F = 13400848, 5000
+D, F = int(os.environ.get('K7_D', '13400848')), int(os.environ.get('K7_F', '5000'))
 ctx = nes_b200.NesContext(counts=[D], flat_granule=int(os.environ.get('K7_GRANULE', '2048')), seed=1234, table_len=1 << 32, device=0)
 dev = torch.device('cuda', 0)
 offs = ctx.sample_offsets(1, F, device=True)
