@@ -156,6 +156,7 @@ __device__ __forceinline__ FinalizePre finalize_prefetch(const FinalizeParams& p
     if (p.t > 1) { q.unf_prev = p.unf_count[(p.t - 1) * p.W + member]; q.prev = p.unfinished[grow]; }
     return q;
 }
+template <bool SCALED>
 __device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t member, int r, int64_t grow, int lane, int idx, float best, const FinalizePre pre) {
     const float sgn = p.sign[member];
     int64_t tok = 0;
@@ -181,7 +182,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t me
     const int par = p.parent ? p.parent[member] : 0;
     const float* te = p.theta32 + (int64_t)par * p.D + p.emb_start + tok * p.E;
     const __half* ee = p.table + p.off[member] + p.emb_pstart + tok * p.E;
-    const float* se = p.scale ? p.scale + (int64_t)par * p.D + p.emb_start + tok * p.E : nullptr;
+    const float* se = SCALED ? p.scale + (int64_t)par * p.D + p.emb_start + tok * p.E : nullptr;
     // x * 2^5 = fma(theta, 2^5, +-fl(2^5 sigma eps)) = 2^5 fl(theta +- fl(sigma eps)): powers of two commute with the roundings
     const float ssig = __fmul_rn(sgn > 0.f ? p.sigma : -p.sigma, kActScale);
     const bool aligned = (reinterpret_cast<uintptr_t>(te) & 15) == 0;
@@ -202,7 +203,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t me
         for (int u = 0; u < 4; ++u) {
             const float2 ef = __half22float2(eh[u]);
             float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
-            if (se) { n0 = apply_scale(n0, se[e + 2 * u], p.scale_div); n1 = apply_scale(n1, se[e + 2 * u + 1], p.scale_div); }
+            if (SCALED) { n0 = apply_scale(n0, se[e + 2 * u], p.scale_div); n1 = apply_scale(n1, se[e + 2 * u + 1], p.scale_div); }
             const float x0 = __fmaf_rn(tv[2 * u], kActScale, n0), x1 = __fmaf_rn(tv[2 * u + 1], kActScale, n1);
             hh[u] = __floats2half2_rn(x0, x1);
             const float2 hf = __half22float2(hh[u]);
@@ -212,7 +213,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t me
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 float n0 = __fmul_rn(ssig, __half22float2(eh[u]).x), n1 = __fmul_rn(ssig, __half22float2(eh[u]).y);
-                if (se) { n0 = apply_scale(n0, se[e + 2 * u], p.scale_div); n1 = apply_scale(n1, se[e + 2 * u + 1], p.scale_div); }
+                if (SCALED) { n0 = apply_scale(n0, se[e + 2 * u], p.scale_div); n1 = apply_scale(n1, se[e + 2 * u + 1], p.scale_div); }
                 p.x32[grow * p.E + e + 2 * u] = __fmaf_rn(tv[2 * u], kActScale, n0) * (1.0f / kActScale);
                 p.x32[grow * p.E + e + 2 * u + 1] = __fmaf_rn(tv[2 * u + 1], kActScale, n1) * (1.0f / kActScale);
             }
@@ -264,25 +265,27 @@ __global__ void __launch_bounds__(128) k_finalize(const FinalizeParams p) {
         }
         }
     }
-    finalize_row(p, member, r, grow, lane, idx, best, finalize_prefetch(p, member, grow));
+    if (p.scale) finalize_row<true>(p, member, r, grow, lane, idx, best, finalize_prefetch(p, member, grow));
+    else finalize_row<false>(p, member, r, grow, lane, idx, best, finalize_prefetch(p, member, grow));
 }
 
 // HYBRID: the fp32 re-evaluation of a row's arg-max candidates (refine_row, hybrid.cuh) and everything that follows from the token
 // (finalize_row) in one pass, one warp per (member, row).  A row whose candidate lists overflowed is flagged instead (row_flag, and its
 // unit for the fallback projection); k_finalize with row_flag set picks those up after the fallback.
+template <bool SCALED>
 __global__ void __launch_bounds__(128, 6) k_refine_finalize(const RefineParams rp, const FinalizeParams fp, uint8_t* __restrict__ row_flag) {
     __shared__ int s_idx[4][32];
     const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
-    const int64_t wid = (int64_t)blockIdx.x * 4 + wq;
-    if (wid >= rp.n_members * rp.rows) return;
+    const int wid = (int)blockIdx.x * 4 + wq;                         // members * rows of a wave fit 31 bits (checked at launch)
+    if (wid >= (int)rp.n_members * rp.rows) return;
     const int64_t member = wid / rp.rows;
-    const int r = (int)(wid % rp.rows);
+    const int r = wid % rp.rows;
     const int64_t grow = member * rp.rows_pad + r;
     int idx = 0; float best = 0.f;
     const FinalizePre pre = finalize_prefetch(fp, member, grow);
-    const bool ok = refine_row(rp, member, r, grow, lane, wq, s_idx, idx, best);
+    const bool ok = refine_row<SCALED>(rp, member, r, grow, lane, wq, s_idx, idx, best);
     if (lane == 0) row_flag[grow] = ok ? 0 : 1;
-    if (ok) finalize_row(fp, member, r, grow, lane, idx, best, pre);
+    if (ok) finalize_row<SCALED>(fp, member, r, grow, lane, idx, best, pre);
 }
 
 // vbn_e (captioning/nets.py:156-165): nn.BatchNorm1d(E, track_running_stats=False) on the output of img_embed / embed -- every feature
@@ -1255,7 +1258,10 @@ int decode_rollout(Ctx* c, int64_t n_members, const int64_t* offsets, const floa
                     rf.sigma = sigma; rf.tok = ws->pre_tok; rf.lp = ws->pre_lp; rf.unit_flag = ws->unit_flag; rf.stats = c->profiling ? ws->stats : nullptr;
                     rf.force_overflow = (env_debug() & 64) ? 1 : 0; rf.n_split = n_split;
                     { ProfScope prof(c, PROF_FINALIZE);       // (3) + the rows' bookkeeping and next-input gather, for every row that did not overflow
-                      k_refine_finalize<<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(rf, make_fin(t), ws->row_flag); c->launches++; }
+                      NES_CHECK(nm * rows < (1ll << 30), "too many rows in a wave");
+                      if (c->scale32) k_refine_finalize<true><<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(rf, make_fin(t), ws->row_flag);
+                      else k_refine_finalize<false><<<(unsigned)((nm * rows + 3) / 4), 128, 0, c->stream>>>(rf, make_fin(t), ws->row_flag);
+                      c->launches++; }
                     NES_CUDA(cudaGetLastError());
                     p.unit_mask = ws->unit_flag;      // (4) units whose candidate list overflowed: the split-fp16 kernel, everything else skips
                     if (scaled) {                     //     ... or, with scaled noise, every logit of those rows in fp32 (k_exact_rows)

@@ -118,6 +118,8 @@ struct RefineParams {
 // in fp32 with the member weight theta +- f32(sigma)*eps (algorithm/nets.py:113), pick the reference's argmax of float32
 // log-probs (lowest index among equal rounded log-probs, captioning/nets.py:202-208)
 // -> false if the row's lists overflowed (its unit is flagged for the fallback), else idx / best = arg-max column and its log-prob
+// SCALED = p.scale is set (safe-mutation scale): a template flag, so that the plain kernels carry none of the per-element scale code
+template <bool SCALED>
 __device__ __forceinline__ bool refine_row(const RefineParams& p, int64_t member, int r, int64_t grow, int lane, int wq, int (*s_idx)[32],
                                            int& idx_out, float& best_out) {
     const float ssig = p.sign[member] > 0.f ? p.sigma : -p.sigma;      // theta - fl(sigma eps) == theta + fl(-sigma eps), bit for bit
@@ -224,7 +226,7 @@ __device__ __forceinline__ bool refine_row(const RefineParams& p, int64_t member
         const int j = __shfl_sync(0xffffffffu, my_idx, c);
         const float* tw = wbase + (int64_t)j * p.R;
         const __half* ew = p.table + off + p.w_pstart + (int64_t)j * p.R;
-        const float* sw = p.scale ? p.scale + (int64_t)par * p.D + p.w_start + (int64_t)j * p.R : nullptr;
+        const float* sw = SCALED ? p.scale + (int64_t)par * p.D + p.w_start + (int64_t)j * p.R : nullptr;
         float acc = 0.f;
 #pragma unroll
         for (int c2 = 0; c2 < 2; ++c2) {
@@ -244,7 +246,7 @@ __device__ __forceinline__ bool refine_row(const RefineParams& p, int64_t member
                 for (int e = 0; e < 4; ++e) {
                     const float2 ef = __half22float2(he[e]);
                     float n0 = __fmul_rn(ssig, ef.x), n1 = __fmul_rn(ssig, ef.y);
-                    if (sw) { n0 = apply_scale(n0, sw[k + 2 * e], p.scale_div); n1 = apply_scale(n1, sw[k + 2 * e + 1], p.scale_div); }
+                    if (SCALED) { n0 = apply_scale(n0, sw[k + 2 * e], p.scale_div); n1 = apply_scale(n1, sw[k + 2 * e + 1], p.scale_div); }
                     acc = fmaf(xs[c2][2 * e], __fadd_rn(tv[2 * e], n0), acc);
                     acc = fmaf(xs[c2][2 * e + 1], __fadd_rn(tv[2 * e + 1], n1), acc);
                 }
@@ -252,7 +254,7 @@ __device__ __forceinline__ bool refine_row(const RefineParams& p, int64_t member
         }
         acc = warp_sum(acc);
         const float tb = p.theta32[(int64_t)par * p.D + p.b_start + j];
-        const float nzb = mut_noise(ssig, __half2float(p.table[off + p.b_pstart + j]), p.scale, (int64_t)par * p.D + p.b_start + j, p.scale_div);
+        const float nzb = mut_noise(ssig, __half2float(p.table[off + p.b_pstart + j]), SCALED ? p.scale : nullptr, (int64_t)par * p.D + p.b_start + j, p.scale_div);
         const float v = acc + __fadd_rn(tb, nzb);
         if (lane == c) my_val = v;
     }
@@ -279,7 +281,8 @@ __global__ void __launch_bounds__(128) k_refine(const RefineParams p) {
     const int r = (int)(wid % p.rows);
     const int64_t grow = member * p.rows_pad + r;
     int idx; float best;
-    if (refine_row(p, member, r, grow, lane, wq, s_idx, idx, best) && lane == 0) { p.tok[grow] = idx; p.lp[grow] = best; }
+    const bool ok = p.scale ? refine_row<true>(p, member, r, grow, lane, wq, s_idx, idx, best) : refine_row<false>(p, member, r, grow, lane, wq, s_idx, idx, best);
+    if (ok && lane == 0) { p.tok[grow] = idx; p.lp[grow] = best; }
 }
 
 // Fallback of the HYBRID projection when member weights carry a safe-mutation scale (the factored split-fp16 kernel cannot
