@@ -150,15 +150,19 @@ struct FinalizeParams {
 // what happens to a row once its arg-max token and log-prob are known: the finished-mask bookkeeping of captioning/nets.py:233-243, the
 // seq / log-prob writes, and the gather of the next input embedding theta_emb[it] +- sigma eps_emb[it] (t = 0: the <bos> gather only)
 // the two loads of finalize_row that do not depend on the token: issued before the candidate re-evaluation, not after it
-struct FinalizePre { int unf_prev; int prev; };
+struct FinalizePre { int unf_prev; int prev; float sgn; int64_t off; int par; };
 __device__ __forceinline__ FinalizePre finalize_prefetch(const FinalizeParams& p, int64_t member, int64_t grow) {
     FinalizePre q; q.unf_prev = 1; q.prev = 1;
-    if (p.t > 1) { q.unf_prev = p.unf_count[(p.t - 1) * p.W + member]; q.prev = p.unfinished[grow]; }
+    if (p.t > 1) { q.unf_prev = (int)ldp_32(p.unf_count + (p.t - 1) * p.W + member); q.prev = p.unfinished[grow]; }
+    q.sgn = __uint_as_float(ldp_32(p.sign + member));
+    const uint2 o = ldp_64(p.off + member);
+    q.off = (int64_t)(((uint64_t)o.y << 32) | o.x);
+    q.par = p.parent ? (int)ldp_32(p.parent + member) : 0;
     return q;
 }
 template <bool SCALED>
 __device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t member, int r, int64_t grow, int lane, int idx, float best, const FinalizePre pre) {
-    const float sgn = p.sign[member];
+    const float sgn = pre.sgn;
     int64_t tok = 0;
     if (p.t >= 1) {
         const float logp = best;                                  // = max log-prob
@@ -179,24 +183,36 @@ __device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t me
         if (p.forced) tok = p.forced[(member * p.rows + r) * p.T + (p.t - 1)];
     }
     if (!p.gather) return;
-    const int par = p.parent ? p.parent[member] : 0;
+    const int par = pre.par;
     const float* te = p.theta32 + (int64_t)par * p.D + p.emb_start + tok * p.E;
-    const __half* ee = p.table + p.off[member] + p.emb_pstart + tok * p.E;
+    const __half* ee = p.table + pre.off + p.emb_pstart + tok * p.E;
     const float* se = SCALED ? p.scale + (int64_t)par * p.D + p.emb_start + tok * p.E : nullptr;
     // x * 2^5 = fma(theta, 2^5, +-fl(2^5 sigma eps)) = 2^5 fl(theta +- fl(sigma eps)): powers of two commute with the roundings
     const float ssig = __fmul_rn(sgn > 0.f ? p.sigma : -p.sigma, kActScale);
     const bool aligned = (reinterpret_cast<uintptr_t>(te) & 15) == 0;
-    for (int e = lane * 8; e < p.E; e += 256) {
-        const uint4 ev = *reinterpret_cast<const uint4*>(ee + e);
-        const __half2* eh = reinterpret_cast<const __half2*>(&ev);
-        float tv[8];
-        if (aligned) {
-            *reinterpret_cast<float4*>(&tv[0]) = __ldg(reinterpret_cast<const float4*>(te + e));
-            *reinterpret_cast<float4*>(&tv[4]) = __ldg(reinterpret_cast<const float4*>(te + e) + 1);
-        } else {
+    // ---- phase 3: the embedding row of the token, two chunks at a time with all their loads pinned ahead of the arithmetic
+    for (int e0 = lane * 8; e0 < p.E; e0 += 512) {
+      uint4 evs[2]; float tvs[2][8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) tv[u] = te[e + u];
-        }
+      for (int c2 = 0; c2 < 2; ++c2) {
+          const int e = e0 + c2 * 256;
+          const int es = e < p.E ? e : 0;
+          evs[c2] = ldp_128(ee + es);
+          if (aligned) {
+              const uint4 t0 = ldp_128(te + es), t1 = ldp_128(te + es + 4);
+              tvs[c2][0] = __uint_as_float(t0.x); tvs[c2][1] = __uint_as_float(t0.y); tvs[c2][2] = __uint_as_float(t0.z); tvs[c2][3] = __uint_as_float(t0.w);
+              tvs[c2][4] = __uint_as_float(t1.x); tvs[c2][5] = __uint_as_float(t1.y); tvs[c2][6] = __uint_as_float(t1.z); tvs[c2][7] = __uint_as_float(t1.w);
+          } else {
+#pragma unroll
+              for (int u = 0; u < 8; ++u) tvs[c2][u] = __uint_as_float(ldp_32(te + es + u));
+          }
+      }
+#pragma unroll
+      for (int c2 = 0; c2 < 2; ++c2) {
+        const int e = e0 + c2 * 256;
+        if (e >= p.E) break;
+        const __half2* eh = reinterpret_cast<const __half2*>(&evs[c2]);
+        const float* tv = tvs[c2];
         __align__(16) __half2 hh[4];
         __align__(16) __half2 hl[4];
 #pragma unroll
@@ -221,6 +237,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeParams& p, int64_t me
         }
         *reinterpret_cast<uint4*>(p.x_hi + grow * p.E + e) = *reinterpret_cast<uint4*>(hh);
         *reinterpret_cast<uint4*>(p.x_lo + grow * p.E + e) = *reinterpret_cast<uint4*>(hl);
+      }
     }
 }
 
